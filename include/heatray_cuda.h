@@ -1,0 +1,243 @@
+/*
+ * heatray_cuda.h — C-ABI of the B200-native path-tracing backend (libheatray_cuda.so).
+ *
+ * This is the drop-in boundary: the entry points below are what Heatray's
+ * RLWrapper layer (reference the headers in Source/RLWrapper/, a header-only C++ veneer over the
+ * closed OpenRL C API, 3rdParty/OpenRL/rl.h:383-528) would bind instead of rl*().
+ * RLSL compilation has no CUDA meaning, so the shader/program string API collapses
+ * into enums + POD parameter blocks; everything else maps 1:1.
+ *
+ * Conventions (mirroring OpenRL as the reference uses it):
+ *  - plain C, plain pointers and sizes, no C++/torch types;
+ *  - every call returns HRC_OK (0) or an HRC_ERR_* code; hrcGetLastError() gives text
+ *    (reference: RLFunc()/rlGetError(), RLWrapper/Error.h:18-41);
+ *  - a context is thread-affine: one owner thread at a time, like an OpenRL context
+ *    (PassGenerator.h:229-231);
+ *  - host memory passed in is copied at call time; the caller keeps ownership;
+ *  - matrices are column-major float[16] (glm layout);
+ *  - the frame buffer holds SUMS of clamped radiance in RGB and the sample count in A,
+ *    row 0 = bottom row (PassGenerator.cpp:176-188, displayGL.frag:77-78).
+ *
+ * The same declarations with the prefix `orc` are exported by the CPU oracle
+ * (oracle/liboracle.so) — test infrastructure only, never linked by this library.
+ */
+#ifndef HEATRAY_CUDA_H
+#define HEATRAY_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef HRC_API
+#define HRC_API __attribute__((visibility("default")))
+#endif
+
+/* ---- error codes ---------------------------------------------------------------- */
+enum {
+    HRC_OK = 0,
+    HRC_ERR_INVALID_VALUE = 1,   /* ↔ RL_INVALID_VALUE */
+    HRC_ERR_INVALID_OPERATION = 2, /* ↔ RL_INVALID_OPERATION (e.g. double map, render without commit) */
+    HRC_ERR_OUT_OF_MEMORY = 3,   /* ↔ RL_OUT_OF_MEMORY */
+    HRC_ERR_CUDA = 4,            /* a CUDA runtime call failed; text has the CUDA error string */
+    HRC_ERR_UNSUPPORTED = 5,     /* feature of the reference not built yet; never a silent fallback */
+    HRC_ERR_NO_DEVICE = 6        /* no CUDA device: the product has no CPU path */
+};
+
+typedef struct HrcContext_t* HrcContext;
+typedef int32_t HrcMesh;      /* ↔ RLprimitive (one per submesh, Mesh.cpp:69) */
+typedef int32_t HrcMaterial;  /* ↔ RLprogram + "Material" uniform block */
+typedef int32_t HrcTexture;   /* ↔ RLtexture */
+#define HRC_NULL_TEXTURE (-1)
+
+#define HRC_MAX_LIGHTS_PER_TYPE 5   /* ShaderLightingDefines.h:18-20 */
+#define HRC_NUM_RANDOM_SEQUENCES 16 /* PassGenerator.h:193 (informative; any count is accepted) */
+
+/* ---- context (↔ OpenRLCreateContext / OpenRLDestroyContext, PassGenerator.cpp:164,432) */
+typedef struct HrcContextDesc {
+    int32_t device;          /* CUDA ordinal */
+    int32_t collectStats;    /* 1: traversal counters (nodes visited / triangles tested) are kept */
+} HrcContextDesc;
+
+HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out);
+HRC_API int hrcDestroyContext(HrcContext ctx);
+/* ctx may be NULL for errors raised before a context exists. */
+HRC_API const char* hrcGetLastError(HrcContext ctx);
+
+/* ---- framebuffer + readback (↔ Framebuffer/Texture RGBA32F + PixelPackBuffer) ------- */
+/* ↔ runInitJob FBO part + runResizeJob (PassGenerator.cpp:172-197, 301-323); clears. */
+HRC_API int hrcResize(HrcContext ctx, int32_t width, int32_t height);
+/* ↔ rlClear(RL_COLOR_BUFFER_BIT) (PassGenerator.cpp:439) */
+HRC_API int hrcClear(HrcContext ctx);
+/* ↔ PixelPackBuffer::setPixelData + mapPixelData (PixelPackBuffer.h:39-60): copies the
+ * accumulation buffer into pinned host memory and returns the pointer (valid until release).
+ * A second read without release is HRC_ERR_INVALID_OPERATION (the reference asserts). */
+HRC_API int hrcReadPixels(HrcContext ctx, const float** rgba);
+HRC_API int hrcReleasePixels(HrcContext ctx);   /* ↔ unmapPixelData (PixelPackBuffer.h:64-70) */
+/* Add `rgba` (w*h*4 floats, host) into the accumulation buffer: the multi-GPU reduce path
+ * writes the summed buffer back through this (no reference equivalent). */
+HRC_API int hrcAddPixels(HrcContext ctx, const float* rgba);
+/* Device pointer of the accumulation buffer (w*h float4), for NCCL reduce without staging. */
+HRC_API int hrcGetDevicePixels(HrcContext ctx, void** devPtr);
+
+/* ---- textures (↔ openrl::Texture::create, Texture.h:59-91) ------------------------- */
+enum { HRC_TEX_R32F = 0, HRC_TEX_RGB32F = 1, HRC_TEX_RGBA32F = 2, HRC_TEX_RGBA8 = 3 };
+enum { HRC_WRAP_CLAMP = 0, HRC_WRAP_REPEAT = 1 };
+typedef struct HrcTextureDesc {
+    int32_t width, height;
+    int32_t format;          /* HRC_TEX_* */
+    int32_t wrapS, wrapT;    /* HRC_WRAP_* */
+} HrcTextureDesc;
+/* Row 0 of `pixels` is the row addressed by t = 0 (bottom row, GL convention).
+ * Filtering is level-0 bilinear in fp32 (policy A-12 in SURVEY.md). */
+HRC_API int hrcCreateTexture2D(HrcContext ctx, const HrcTextureDesc* desc, const void* pixels, HrcTexture* out);
+HRC_API int hrcDestroyTexture(HrcContext ctx, HrcTexture tex);
+
+/* ---- materials (↔ Material::build/modify + the "Material" uniform block) ---------- */
+enum { HRC_MATERIAL_PBR = 0, HRC_MATERIAL_GLASS = 1 };
+/* feature flags ↔ the #defines injected by PhysicallyBasedMaterial.cpp:49-113 / GlassMaterial.cpp:40-74 */
+enum {
+    HRC_MAT_DOUBLE_SIDED                = 1 << 0,
+    HRC_MAT_ALPHA_MASK                  = 1 << 1,
+    HRC_MAT_HAS_BASE_COLOR_TEXTURE      = 1 << 2,
+    HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE = 1 << 3,
+    HRC_MAT_HAS_EMISSIVE_TEXTURE        = 1 << 4,
+    HRC_MAT_HAS_NORMALMAP               = 1 << 5,
+    HRC_MAT_HAS_CLEARCOAT_TEXTURE       = 1 << 6,
+    HRC_MAT_HAS_CLEARCOAT_ROUGHNESS_TEXTURE = 1 << 7,
+    HRC_MAT_HAS_CLEARCOAT_NORMALMAP     = 1 << 8,
+    HRC_MAT_VERTEX_COLORS               = 1 << 9
+};
+/* ↔ ShaderParams, PhysicallyBasedMaterial.cpp:16-36 / uniformblock Material, physicallyBased.rlsl:29-48.
+ * Values are the ALREADY CLAMPED shader-side values (modify(), PhysicallyBasedMaterial.cpp:127-145). */
+typedef struct HrcPbrParams {
+    HrcTexture baseColorTexture, metallicRoughnessTexture, emissiveTexture, normalmap;
+    HrcTexture clearCoatTexture, clearCoatRoughnessTexture, clearCoatNormalmap, multiscatterLUT;
+    float baseColor[3];
+    float emissiveColor[3];
+    float metallic, roughness, specularF0, roughnessAlpha;
+    float clearCoat, clearCoatRoughness, clearCoatRoughnessAlpha;
+} HrcPbrParams;
+/* ↔ ShaderParams, GlassMaterial.cpp:15-28 / uniformblock Material, glass.rlsl:30-40 */
+typedef struct HrcGlassParams {
+    HrcTexture baseColorTexture, normalmap, metallicRoughnessTexture;
+    float baseColor[3];
+    float roughness, roughnessAlpha, ior, density, specularF0;
+} HrcGlassParams;
+HRC_API int hrcCreateMaterial(HrcContext ctx, int32_t type, uint32_t featureFlags,
+                              const void* params, size_t paramBytes, HrcMaterial* out);
+/* ↔ Material::modify → Buffer::modify (PhysicallyBasedMaterial.cpp:190) */
+HRC_API int hrcUpdateMaterial(HrcContext ctx, HrcMaterial mat, const void* params, size_t paramBytes);
+
+/* ---- geometry (↔ Buffer + Primitive + rlDrawElements, Mesh.cpp:28-155) -------------- */
+enum { HRC_DRAW_TRIANGLES = 0, HRC_DRAW_TRIANGLE_STRIP = 1 };   /* MeshProvider.h DrawMode */
+typedef struct HrcMeshDesc {
+    const float* positions;  int32_t positionStride;   /* bytes; 3 floats per vertex; required */
+    const float* normals;    int32_t normalStride;     /* required */
+    const float* texCoords;  int32_t texCoordStride;   /* optional (NULL) */
+    const float* tangents;   int32_t tangentStride;    /* optional */
+    const float* bitangents; int32_t bitangentStride;  /* optional */
+    const float* colors;     int32_t colorStride;      /* optional */
+    uint32_t vertexCount;
+    const uint32_t* indices; /* already offset to the submesh's first element */
+    uint32_t elementCount;   /* number of indices (Submesh::elementCount) */
+    int32_t drawMode;        /* HRC_DRAW_* */
+    float worldFromEntity[16]; /* submesh.localTransform * transform (Mesh.cpp:85) */
+    int32_t frontFaceCW;     /* det(worldFromEntity) < 0 (Mesh.cpp:86-91) */
+    int32_t isOccluder;      /* 0 for PBR + alphaMask (Mesh.cpp:95-100) */
+    HrcMaterial material;
+} HrcMeshDesc;
+HRC_API int hrcCreateMesh(HrcContext ctx, const HrcMeshDesc* desc, HrcMesh* out);
+HRC_API int hrcDestroyMesh(HrcContext ctx, HrcMesh mesh);
+HRC_API int hrcClearScene(HrcContext ctx);  /* ↔ Scene::clearMeshesAndMaterials (PassGenerator.cpp:408) */
+/* Flattens all meshes to world space (vertex.rlsl:25-43), builds the SAH BVH on the host,
+ * collapses it to 8-wide compressed nodes and uploads. Explicit where OpenRL is implicit. */
+HRC_API int hrcCommitScene(HrcContext ctx);
+
+/* ---- lights (↔ the four light uniform blocks, ShaderLightingDefines.h:33-64) ------- */
+typedef struct HrcEnvLight {
+    int32_t enabled;             /* ↔ EnvironmentLight.lightPrimitive != rl_NullPrimitive */
+    HrcTexture texture;          /* lat-long map or 1x1 solid colour */
+    float exposureCompensation;  /* already 2^EV (EnvironmentLight.cpp:95) */
+    float thetaRotation;         /* radians */
+} HrcEnvLight;
+typedef struct HrcDirLight   { float direction[3]; float color[3]; } HrcDirLight;   /* direction TO the light */
+typedef struct HrcPointLight { float position[3];  float color[3]; } HrcPointLight;
+typedef struct HrcSpotLight  { float position[3];  float direction[3]; float color[3]; float angles[2]; } HrcSpotLight; /* direction FROM the light; angles = cos(inner), cos(outer) */
+HRC_API int hrcSetEnvironment(HrcContext ctx, const HrcEnvLight* env);
+HRC_API int hrcSetDirectionalLights(HrcContext ctx, int32_t n, const HrcDirLight* lights);
+HRC_API int hrcSetPointLights(HrcContext ctx, int32_t n, const HrcPointLight* lights);
+HRC_API int hrcSetSpotLights(HrcContext ctx, int32_t n, const HrcSpotLight* lights);
+
+/* ---- QMC tables + globals ---------------------------------------------------------- */
+/* ↔ RandomSequences / RandomSequenceMetadata / ApertureSamples blocks (PassGenerator.cpp:603-684):
+ * xy and apertureXY are vec2[numSequences*sequenceLength], sequence-major. */
+HRC_API int hrcSetSequences(HrcContext ctx, int32_t numSequences, int32_t sequenceLength,
+                            const float* xy, const float* apertureXY);
+/* ↔ SequenceOffsets block (PassGenerator.cpp:150-159; only .x is read, perspective.rlsl:64) and the
+ * per-pixel sequenceID = floor(random(FrameCoord/FrameSize)*numSequences) (perspective.rlsl:62),
+ * which the host evaluates once (quirk B-Q2). offsetCount must cover the reference's index formula
+ * int(FrameCoord.y*FrameSize.y + FrameCoord.x) for every pixel (quirk B-Q1). */
+HRC_API int hrcSetPixelTables(HrcContext ctx, const float* seqOffsetX, size_t offsetCount,
+                              const uint8_t* sequenceId /* w*h */);
+/* ↔ PassGenerator::GlobalData (PassGenerator.h:269-294) / uniformblock Globals (globalData.rlsl:9-34): 84 bytes */
+typedef struct HrcGlobals {
+    int32_t maxRayDepth;
+    int32_t sampleIndex;       /* overwritten per pass by HrcFrameParams.sampleIndex */
+    float   maxChannelValue;
+    int32_t enableDebugVisualizer;
+    int32_t showGeometricNormals, showUVs, showTangents, showBitangents, showNormalmap;
+    int32_t showFinalNormals, showBaseColor, showRoughness, showMetallic, showEmissive;
+    int32_t showClearcoat, showClearcoatRoughness, showClearcoatNormalmap, showShader;
+    int32_t enableAccumulatorVisualizer, showNANs, showInf;
+} HrcGlobals;
+HRC_API int hrcSetGlobals(HrcContext ctx, const HrcGlobals* globals);
+
+/* ---- the pass (↔ frame uniforms + rlRenderFrame, PassGenerator.cpp:349-386) -------- */
+typedef struct HrcFrameParams {
+    float fovTan, aspectRatio, focusDistance, apertureRadius;   /* perspective.rlsl:15-18 */
+    float viewMatrix[16];        /* camera-to-world (quirk B-Q19) */
+    int32_t sampleIndex;         /* Globals.sampleIndex for this pass */
+    float maxSampleIndex;        /* float(maxRenderPasses) (PassGenerator.cpp:368) */
+    int32_t interactiveMode;     /* must be 0 for now (HRC_ERR_UNSUPPORTED otherwise) */
+    int32_t blockSize[2], currentBlockPixelSample[2];
+    /* screen-band sharding: this context renders rows y with (y / bandHeight) % bandCount == bandIndex.
+     * bandCount <= 1 renders the whole frame. */
+    int32_t bandHeight, bandIndex, bandCount;
+} HrcFrameParams;
+typedef struct HrcPassStats {
+    float    gpuMs;                 /* CUDA-event time of the pass on the context's stream */
+    uint64_t raysPrimary, raysExtension, raysOcclusion;   /* segments submitted to traversal */
+    uint64_t nodesVisited, trianglesTested;               /* only when collectStats */
+    uint64_t closestLaunches, anyLaunches, shadeLaunches; /* kernels launched by this pass */
+    float    msClosest, msAny, msShade, msRaygen;         /* only when collectStats (per-kernel events) */
+} HrcPassStats;
+/* Enqueues and completes one pass; stats may be NULL. */
+HRC_API int hrcRenderPass(HrcContext ctx, const HrcFrameParams* frame, HrcPassStats* stats);
+/* Asynchronous variant: enqueue only (no host sync, no stats read-back). hrcSynchronize() waits.
+ * hrcGetStats() returns the totals accumulated since the last hrcResetStats(). */
+HRC_API int hrcEnqueuePass(HrcContext ctx, const HrcFrameParams* frame);
+HRC_API int hrcSynchronize(HrcContext ctx);
+HRC_API int hrcResetStats(HrcContext ctx);
+HRC_API int hrcGetStats(HrcContext ctx, HrcPassStats* stats);
+
+/* ---- parity hooks (no reference equivalent; the fixed-ray-set test) ---- */
+typedef struct HrcRay { float origin[3]; float tmin; float direction[3]; float tmax; } HrcRay; /* 32 B */
+typedef struct HrcHit { float t, u, v; int32_t primId; /* -1 = miss; bit 30 set = back face */ } HrcHit; /* 16 B */
+#define HRC_HIT_BACKFACE 0x40000000
+/* Closest hit (anyHit = 0) or occlusion test (anyHit = 1: primId = 0 if occluded else -1) for n host rays. */
+HRC_API int hrcTraceRays(HrcContext ctx, int32_t n, const HrcRay* rays, int32_t anyHit, HrcHit* hits);
+/* Scene facts after commit. */
+typedef struct HrcSceneInfo {
+    uint64_t triangleCount, nodeCount;
+    uint64_t nodeBytes, triangleBytes, shadingBytes;
+    float    buildSeconds;
+} HrcSceneInfo;
+HRC_API int hrcGetSceneInfo(HrcContext ctx, HrcSceneInfo* info);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HEATRAY_CUDA_H */

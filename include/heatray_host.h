@@ -1,0 +1,103 @@
+/*
+ * heatray_host.h — flat C view of the host layer that sits ABOVE the backend C-ABI
+ * (heatray_cuda.h): the parts of the reference that run on the CPU before/around a pass and
+ * that the reference keeps in PassGenerator / Materials / Lights / Scene / Utility.
+ *
+ * In a real integration these stay reference code (they are unchanged by swapping OpenRL for
+ * the CUDA backend); they are rebuilt here because the reference host cannot be linked without
+ * OpenRL + OpenGL, and they are what the headless bench and the tests drive. The C++ classes
+ * behind these functions live in heatray_b200/csrc/host_*.{h,cpp} (namespace hr) and mirror the
+ * reference's names: hr::PassGenerator, hr::RenderOptions, hr::PhysicallyBasedMaterial, ...
+ */
+#ifndef HEATRAY_HOST_H
+#define HEATRAY_HOST_H
+
+#include "heatray_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- QMC (reference Source/Utility/Random.h, BlueNoise.h; PassGenerator.cpp:150-159,603-684) ---- */
+enum { HRH_SAMPLE_RANDOM = 0, HRH_SAMPLE_HALTON = 1, HRH_SAMPLE_HAMMERSLEY = 2, HRH_SAMPLE_BLUE_NOISE = 3, HRH_SAMPLE_SOBOL = 4 }; /* RenderOptions::SampleMode, PassGenerator.h:99-105 */
+enum { HRH_BOKEH_CIRCULAR = 0, HRH_BOKEH_PENTAGON = 1, HRH_BOKEH_HEXAGON = 2, HRH_BOKEH_OCTAGON = 3 };                           /* RenderOptions::BokehShape, PassGenerator.h:111-116 */
+HRC_API void hrhSobol(float* xy, uint32_t count, uint32_t sequenceIndex);           /* util::sobol, Random.h:221-264 */
+HRC_API void hrhHalton(float* xy, uint32_t count, uint32_t sequenceIndex);          /* util::halton, Random.h:169-217 */
+HRC_API void hrhHammersley(float* xy, uint32_t count, uint32_t sequenceIndex);      /* util::hammersley, Random.h:134-154 */
+HRC_API void hrhBlueNoise(float* xy, uint32_t count, int32_t sequenceIndex);        /* util::blueNoise, Random.h:158-165 */
+HRC_API void hrhUniformRandom(float* xy, uint32_t count, uint32_t seed, float lo, float hi); /* util::uniformRandomFloats<vec2>, Random.h:113-130 */
+HRC_API void hrhRadialSobol(float* xy, uint32_t count, uint32_t sequenceIndex);     /* util::radialSobol, Random.h:268-289 */
+HRC_API void hrhRandomPolygonal(float* xy, uint32_t numEdges, uint32_t count, uint32_t seed); /* util::randomPolygonal, Random.h:293-355 */
+/* generateRandomSequences (PassGenerator.cpp:603-684): xy and aperture are vec2[numSequences*sampleCount]. */
+HRC_API void hrhGenerateRandomSequences(int32_t sampleMode, int32_t bokehShape, uint32_t numSequences, uint32_t sampleCount, float* xy, float* aperture);
+/* generateSequenceOffsets (PassGenerator.cpp:150-159), extended to the entries the shader's index formula reaches (quirk B-Q1). */
+HRC_API size_t hrhSequenceOffsetCount(int32_t w, int32_t h);
+HRC_API void hrhGenerateSequenceOffsets(int32_t w, int32_t h, float* outX, size_t count);
+/* sequenceID = floor(random(FrameCoord/FrameSize) * numSequences) per pixel (perspective.rlsl:62, quirk B-Q2). */
+HRC_API void hrhGenerateSequenceIds(int32_t w, int32_t h, int32_t numSequences, uint8_t* out);
+
+/* ---- materials (PhysicallyBasedMaterial::Parameters → ShaderParams; GlassMaterial likewise) ---- */
+typedef struct HrhPbrMaterial {       /* PhysicallyBasedMaterial.h Parameters (user-facing, unclamped) */
+    float baseColor[3]; float emissiveColor[3];
+    float metallic, roughness, specularF0, clearCoat, clearCoatRoughness;
+    int32_t doubleSided, alphaMask;
+} HrhPbrMaterial;
+typedef struct HrhGlassMaterial {     /* GlassMaterial.h Parameters */
+    float baseColor[3]; float roughness, ior, density;
+} HrhGlassMaterial;
+/* modify(): clamps and derived values (PhysicallyBasedMaterial.cpp:127-145, quirk B-Q16); returns the feature flags. */
+HRC_API uint32_t hrhPackPbrMaterial(const HrhPbrMaterial* in, HrcTexture multiscatterLUT, HrcPbrParams* out);
+HRC_API uint32_t hrhPackGlassMaterial(const HrhGlassMaterial* in, HrcGlassParams* out);   /* GlassMaterial.cpp:88-126 */
+/* generateMultiScatterTexture (MultiScatterUtil.cpp:49-139): dim x dim floats, row = roughness bin, col = NdotV bin. */
+HRC_API void hrhGenerateMultiscatterLUT(float* out, int32_t dim, int32_t sampleCount, int32_t threads);
+
+/* ---- lights (photometric → radiometric packing, quirks B-Q17/B-Q18) ---- */
+HRC_API void hrhPackDirectionalLight(const float color[3], float illuminance, float theta, float phi, HrcDirLight* out);   /* DirectionalLight.cpp:42-78 */
+HRC_API void hrhPackPointLight(const float color[3], float luminousIntensity, const float position[3], HrcPointLight* out); /* PointLight.cpp:41-50 */
+HRC_API void hrhPackSpotLight(const float color[3], float luminousIntensity, const float position[3], float theta, float phi,
+                              float innerAngle, float outerAngle, HrcSpotLight* out);                                        /* SpotLight.cpp:44-91 */
+HRC_API float hrhEnvironmentExposure(float exposureCompensationEV);                                                         /* EnvironmentLight.cpp:95 */
+
+/* ---- camera ---- */
+HRC_API void hrhOrbitCameraViewMatrix(float distance, float phi, float theta, const float target[3], float out[16]);       /* OrbitCamera.h:32-45 */
+HRC_API float hrhFovTan(float focalLengthMm);                          /* PassGenerator.cpp:341-343,357 */
+HRC_API float hrhApertureRadius(float focalLengthMm, float fstop);    /* RenderOptions::Camera::setApertureRadius, PassGenerator.h:92-94 */
+
+/* ---- procedural mesh providers (Scene/PlaneMeshProvider.h, Scene/SphereMeshProvider.h) ---- */
+/* Plane: 4 vertices, strip indices {0,1,3,2}. Buffers: positions[12], normals[12], uvs[8], indices[4]. */
+HRC_API void hrhPlaneMesh(float width, float length, float* positions, float* normals, float* uvs, uint32_t* indices);
+/* Sphere: (u+1)*(v+2) vertices, 2*u*v triangles. Pass NULL buffers to query counts only. */
+HRC_API void hrhSphereMesh(int32_t uSlices, int32_t vSlices, float radius, float* positions, float* normals, float* uvs,
+                           uint32_t* indices, uint32_t* vertexCount, uint32_t* indexCount);
+
+/* ---- the pass interface: hr::PassGenerator (reference PassGenerator.h:35-193) ---- */
+typedef struct HrhPassGenerator_t* HrhPassGenerator;
+typedef struct HrhRenderOptions {      /* PassGenerator::RenderOptions, PassGenerator.h:49-150 (strings → handled by callers) */
+    int32_t enableInteractiveMode, enableOfflineMode, resetInternalState;
+    uint32_t maxRenderPasses, maxRayDepth;
+    float maxChannelValue;
+    /* environment */
+    int32_t envEnabled; int32_t envUseSolidColor; float envSolidColor[3]; HrcTexture envTexture;
+    float envExposureCompensation, envThetaRotation;
+    /* camera */
+    float aspectRatio, focusDistance, focalLength, apertureRadius, fstop; float viewMatrix[16];
+    int32_t sampleMode, bokehShape, debugVisMode, debugPassRendering, debugPassIndex;
+} HrhRenderOptions;
+/* PassCompleteCallback (PassGenerator.h:161): invoked on the worker thread. `pixels` stays mapped until the next pass. */
+typedef void (*HrhPassCompleteCallback)(void* user, int32_t frameDataAvailable, const float* pixels, int32_t width, int32_t height,
+                                        float passTimeSeconds, uint64_t passIndex);
+HRC_API void hrhDefaultRenderOptions(HrhRenderOptions* out);
+HRC_API int  hrhPassGeneratorCreate(int32_t device, int32_t width, int32_t height, HrhPassGenerator* out);  /* init(), PassGenerator.cpp:30-42,161-299 */
+HRC_API int  hrhPassGeneratorDestroy(HrhPassGenerator pg);                                                    /* destroy(), :100-106 */
+HRC_API int  hrhPassGeneratorResize(HrhPassGenerator pg, int32_t width, int32_t height);                      /* resize(), :108-113 */
+HRC_API int  hrhPassGeneratorRenderPass(HrhPassGenerator pg, const HrhRenderOptions* opts, HrhPassCompleteCallback cb, void* user); /* renderPass(), :115-122 (asynchronous enqueue) */
+/* loadScene / changeLighting / modifyScene / runOpenRLTask (PassGenerator.cpp:124-148): the task runs on the worker thread and gets the backend context. */
+typedef void (*HrhContextTask)(void* user, HrcContext ctx);
+HRC_API int  hrhPassGeneratorRunTask(HrhPassGenerator pg, HrhContextTask task, void* user);
+HRC_API int  hrhPassGeneratorWaitIdle(HrhPassGenerator pg);       /* drains the job queue (test/bench helper) */
+HRC_API const char* hrhPassGeneratorLastError(HrhPassGenerator pg);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HEATRAY_HOST_H */
