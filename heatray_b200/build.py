@@ -1,0 +1,97 @@
+"""In-tree build of libheatray_cuda.so (sm_100a only) and of the CPU oracle used by the tests.
+
+    python -m heatray_b200.build            # build everything that is out of date
+    python -m heatray_b200.build --force
+
+nvcc cross-compiles without a GPU; the built .so is git-ignored but travels to the GPU box.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+ROOT = PKG.parent
+CSRC = PKG / "csrc"
+OBJ = PKG / "_build"
+LIB = PKG / "libheatray_cuda.so"
+
+NVCC = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden,-ffp-contract=off,-pthread"]
+CU_FLAGS = ["--expt-relaxed-constexpr", "-Xptxas", "-v"]
+
+
+def _sources():
+    return sorted(CSRC.glob("*.cu")) + sorted(CSRC.glob("*.cpp"))
+
+
+def _headers():
+    return sorted(CSRC.glob("*.h")) + sorted((ROOT / "include").glob("*.h"))
+
+
+def _stale(target: Path, deps) -> bool:
+    if not target.exists():
+        return True
+    t = target.stat().st_mtime
+    return any(Path(d).stat().st_mtime > t for d in deps)
+
+
+def build_cuda(force: bool = False, verbose: bool = False) -> Path:
+    OBJ.mkdir(exist_ok=True)
+    objs = []
+    hdrs = _headers()
+    for src in _sources():
+        obj = OBJ / (src.name + ".o")
+        objs.append(obj)
+        if force or _stale(obj, [src] + hdrs):
+            cmd = [NVCC, *ARCH, *COMMON, "-c", str(src), "-o", str(obj)]
+            if src.suffix == ".cu":
+                cmd += CU_FLAGS
+            else:
+                cmd += ["-x", "cu"] if False else []
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            if verbose or res.returncode != 0:
+                sys.stderr.write(res.stdout + res.stderr)
+            if res.returncode != 0:
+                raise RuntimeError(f"nvcc failed on {src.name}")
+            (OBJ / (src.name + ".log")).write_text(res.stdout + res.stderr)
+    if force or _stale(LIB, objs):
+        cmd = [NVCC, *ARCH, "-shared", "-cudart", "static", "-o", str(LIB), *map(str, objs), "-Xcompiler", "-pthread"]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            sys.stderr.write(res.stdout + res.stderr)
+            raise RuntimeError("link failed")
+    return LIB
+
+
+def build_oracle(force: bool = False) -> None:
+    odir = ROOT / "oracle"
+    args = ["make", "-C", str(odir)]
+    if force:
+        args.append("-B")
+    res = subprocess.run(args, capture_output=True, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("oracle build failed")
+    ref = odir / "ref_probe" / "build_ref.sh"
+    if Path("/root/reference/Source").is_dir() and ref.exists():
+        have = all((odir / "_ref" / n).exists() for n in ("libref_qmc.so", "libref_lut.so", "libref_rlsl.so"))
+        if force or not have:
+            res = subprocess.run(["sh", str(ref)], capture_output=True, text=True)
+            if res.returncode != 0:
+                sys.stderr.write(res.stdout + res.stderr)
+                raise RuntimeError("oracle/_ref build failed")
+
+
+def build_all(force: bool = False, verbose: bool = False) -> None:
+    build_cuda(force, verbose)
+    build_oracle(force)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    print(LIB)

@@ -1,0 +1,357 @@
+"""ctypes mirror of include/heatray_cuda.h and include/heatray_host.h.
+
+`load_library()` returns the in-tree CUDA backend and FAILS LOUDLY when it is missing — the product has
+no CPU path. `Backend` is a thin object wrapper over a library that exports the C-ABI with a given
+prefix; the tests build the same wrapper around the CPU oracle (see oracle/loader.py).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libheatray_cuda.so"
+
+HRC_OK = 0
+ERR_NAMES = {1: "INVALID_VALUE", 2: "INVALID_OPERATION", 3: "OUT_OF_MEMORY", 4: "CUDA", 5: "UNSUPPORTED", 6: "NO_DEVICE"}
+MATERIAL_PBR, MATERIAL_GLASS = 0, 1
+MAT_DOUBLE_SIDED = 1
+TEX_R32F, TEX_RGB32F, TEX_RGBA32F, TEX_RGBA8 = 0, 1, 2, 3
+WRAP_CLAMP, WRAP_REPEAT = 0, 1
+DRAW_TRIANGLES, DRAW_TRIANGLE_STRIP = 0, 1
+HIT_BACKFACE = 0x40000000
+SAMPLE_RANDOM, SAMPLE_HALTON, SAMPLE_HAMMERSLEY, SAMPLE_BLUE_NOISE, SAMPLE_SOBOL = range(5)
+BOKEH_CIRCULAR, BOKEH_PENTAGON, BOKEH_HEXAGON, BOKEH_OCTAGON = range(4)
+
+f32, i32, u32, u64 = C.c_float, C.c_int32, C.c_uint32, C.c_uint64
+fp = C.POINTER(C.c_float)
+
+
+class HrcError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"HRC_ERR_{ERR_NAMES.get(code, code)}: {text}")
+        self.code = code
+
+
+class ContextDesc(C.Structure):
+    _fields_ = [("device", i32), ("collectStats", i32)]
+
+
+class TextureDesc(C.Structure):
+    _fields_ = [("width", i32), ("height", i32), ("format", i32), ("wrapS", i32), ("wrapT", i32)]
+
+
+class PbrParams(C.Structure):
+    _fields_ = [("baseColorTexture", i32), ("metallicRoughnessTexture", i32), ("emissiveTexture", i32), ("normalmap", i32),
+                ("clearCoatTexture", i32), ("clearCoatRoughnessTexture", i32), ("clearCoatNormalmap", i32), ("multiscatterLUT", i32),
+                ("baseColor", f32 * 3), ("emissiveColor", f32 * 3),
+                ("metallic", f32), ("roughness", f32), ("specularF0", f32), ("roughnessAlpha", f32),
+                ("clearCoat", f32), ("clearCoatRoughness", f32), ("clearCoatRoughnessAlpha", f32)]
+
+
+class GlassParams(C.Structure):
+    _fields_ = [("baseColorTexture", i32), ("normalmap", i32), ("metallicRoughnessTexture", i32),
+                ("baseColor", f32 * 3), ("roughness", f32), ("roughnessAlpha", f32), ("ior", f32), ("density", f32), ("specularF0", f32)]
+
+
+class MeshDesc(C.Structure):
+    _fields_ = [("positions", C.c_void_p), ("positionStride", i32), ("normals", C.c_void_p), ("normalStride", i32),
+                ("texCoords", C.c_void_p), ("texCoordStride", i32), ("tangents", C.c_void_p), ("tangentStride", i32),
+                ("bitangents", C.c_void_p), ("bitangentStride", i32), ("colors", C.c_void_p), ("colorStride", i32),
+                ("vertexCount", u32), ("indices", C.c_void_p), ("elementCount", u32), ("drawMode", i32),
+                ("worldFromEntity", f32 * 16), ("frontFaceCW", i32), ("isOccluder", i32), ("material", i32)]
+
+
+class EnvLight(C.Structure):
+    _fields_ = [("enabled", i32), ("texture", i32), ("exposureCompensation", f32), ("thetaRotation", f32)]
+
+
+class DirLight(C.Structure):
+    _fields_ = [("direction", f32 * 3), ("color", f32 * 3)]
+
+
+class PointLight(C.Structure):
+    _fields_ = [("position", f32 * 3), ("color", f32 * 3)]
+
+
+class SpotLight(C.Structure):
+    _fields_ = [("position", f32 * 3), ("direction", f32 * 3), ("color", f32 * 3), ("angles", f32 * 2)]
+
+
+class Globals(C.Structure):
+    _fields_ = [("maxRayDepth", i32), ("sampleIndex", i32), ("maxChannelValue", f32), ("enableDebugVisualizer", i32),
+                ("showGeometricNormals", i32), ("showUVs", i32), ("showTangents", i32), ("showBitangents", i32), ("showNormalmap", i32),
+                ("showFinalNormals", i32), ("showBaseColor", i32), ("showRoughness", i32), ("showMetallic", i32), ("showEmissive", i32),
+                ("showClearcoat", i32), ("showClearcoatRoughness", i32), ("showClearcoatNormalmap", i32), ("showShader", i32),
+                ("enableAccumulatorVisualizer", i32), ("showNANs", i32), ("showInf", i32)]
+
+
+class FrameParams(C.Structure):
+    _fields_ = [("fovTan", f32), ("aspectRatio", f32), ("focusDistance", f32), ("apertureRadius", f32), ("viewMatrix", f32 * 16),
+                ("sampleIndex", i32), ("maxSampleIndex", f32), ("interactiveMode", i32), ("blockSize", i32 * 2),
+                ("currentBlockPixelSample", i32 * 2), ("bandHeight", i32), ("bandIndex", i32), ("bandCount", i32)]
+
+
+class PassStats(C.Structure):
+    _fields_ = [("gpuMs", f32), ("raysPrimary", u64), ("raysExtension", u64), ("raysOcclusion", u64), ("nodesVisited", u64),
+                ("trianglesTested", u64), ("closestLaunches", u64), ("anyLaunches", u64), ("shadeLaunches", u64),
+                ("msClosest", f32), ("msAny", f32), ("msShade", f32), ("msRaygen", f32)]
+
+    @property
+    def rays(self):
+        return self.raysPrimary + self.raysExtension + self.raysOcclusion
+
+
+class SceneInfo(C.Structure):
+    _fields_ = [("triangleCount", u64), ("nodeCount", u64), ("nodeBytes", u64), ("triangleBytes", u64), ("shadingBytes", u64), ("buildSeconds", f32)]
+
+
+RAY_DTYPE = np.dtype([("origin", np.float32, 3), ("tmin", np.float32), ("direction", np.float32, 3), ("tmax", np.float32)])
+HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("primId", np.int32)])
+
+
+class HrhPbrMaterial(C.Structure):
+    _fields_ = [("baseColor", f32 * 3), ("emissiveColor", f32 * 3), ("metallic", f32), ("roughness", f32), ("specularF0", f32),
+                ("clearCoat", f32), ("clearCoatRoughness", f32), ("doubleSided", i32), ("alphaMask", i32)]
+
+
+class HrhGlassMaterial(C.Structure):
+    _fields_ = [("baseColor", f32 * 3), ("roughness", f32), ("ior", f32), ("density", f32)]
+
+
+# names of every exported symbol of the backend C-ABI (checked by tests/test_abi.py against the header)
+BACKEND_SYMBOLS = [
+    "CreateContext", "DestroyContext", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels",
+    "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "ClearScene", "CommitScene",
+    "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetGlobals",
+    "RenderPass", "EnqueuePass", "Synchronize", "ResetStats", "GetStats", "TraceRays", "GetSceneInfo",
+]
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """The in-tree CUDA backend. Raises if it has not been built: there is no fallback."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is missing: run `python -m heatray_b200.build` (nvcc, sm_100a). There is no CPU fallback.")
+        _lib = C.CDLL(str(LIB_PATH))
+        _declare_host(_lib)
+    return _lib
+
+
+def _declare_host(lib):
+    lib.hrhSequenceOffsetCount.restype = C.c_size_t
+    lib.hrhSequenceOffsetCount.argtypes = [i32, i32]
+    lib.hrhGenerateSequenceOffsets.argtypes = [i32, i32, C.c_void_p, C.c_size_t]
+    lib.hrhGenerateSequenceIds.argtypes = [i32, i32, i32, C.c_void_p]
+    lib.hrhGenerateRandomSequences.argtypes = [i32, i32, u32, u32, C.c_void_p, C.c_void_p]
+    for n in ("hrhSobol", "hrhHalton", "hrhHammersley", "hrhRadialSobol"):
+        getattr(lib, n).argtypes = [C.c_void_p, u32, u32]
+    lib.hrhBlueNoise.argtypes = [C.c_void_p, u32, i32]
+    lib.hrhUniformRandom.argtypes = [C.c_void_p, u32, u32, f32, f32]
+    lib.hrhRandomPolygonal.argtypes = [C.c_void_p, u32, u32, u32]
+    lib.hrhPackPbrMaterial.restype = u32
+    lib.hrhPackPbrMaterial.argtypes = [C.POINTER(HrhPbrMaterial), i32, C.POINTER(PbrParams)]
+    lib.hrhPackGlassMaterial.restype = u32
+    lib.hrhPackGlassMaterial.argtypes = [C.POINTER(HrhGlassMaterial), C.POINTER(GlassParams)]
+    lib.hrhGenerateMultiscatterLUT.argtypes = [C.c_void_p, i32, i32, i32]
+    lib.hrhPackDirectionalLight.argtypes = [fp, f32, f32, f32, C.POINTER(DirLight)]
+    lib.hrhPackPointLight.argtypes = [fp, f32, fp, C.POINTER(PointLight)]
+    lib.hrhPackSpotLight.argtypes = [fp, f32, fp, f32, f32, f32, f32, C.POINTER(SpotLight)]
+    lib.hrhEnvironmentExposure.restype = f32
+    lib.hrhEnvironmentExposure.argtypes = [f32]
+    lib.hrhOrbitCameraViewMatrix.argtypes = [f32, f32, f32, fp, fp]
+    lib.hrhFovTan.restype = f32
+    lib.hrhFovTan.argtypes = [f32]
+    lib.hrhApertureRadius.restype = f32
+    lib.hrhApertureRadius.argtypes = [f32, f32]
+    lib.hrhPlaneMesh.argtypes = [f32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.hrhSphereMesh.argtypes = [i32, i32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(u32), C.POINTER(u32)]
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Backend:
+    """Object view of one backend context: the calls a reference-side RLWrapper shim would make."""
+
+    def __init__(self, lib: C.CDLL, prefix: str = "hrc", device: int = 0, collect_stats: bool = False):
+        self.lib, self.prefix = lib, prefix
+        self._fn = {}
+        for name in BACKEND_SYMBOLS:
+            try:
+                self._fn[name] = getattr(lib, prefix + name)
+            except AttributeError:
+                if prefix == "hrc":
+                    raise
+        self._fn["GetLastError"].restype = C.c_char_p
+        self._fn["GetLastError"].argtypes = [C.c_void_p]
+        self.ctx = C.c_void_p()
+        desc = ContextDesc(device, int(collect_stats))
+        rc = self._fn["CreateContext"](C.byref(desc), C.byref(self.ctx))
+        if rc != HRC_OK:
+            raise HrcError(rc, (self._fn["GetLastError"](None) or b"").decode())
+        self.width = self.height = 0
+        self._keep = []
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _call(self, name, *args):
+        rc = self._fn[name](self.ctx, *args)
+        if rc != HRC_OK:
+            raise HrcError(rc, (self._fn["GetLastError"](self.ctx) or b"").decode())
+
+    def close(self):
+        if self.ctx:
+            self._fn["DestroyContext"](self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- framebuffer ------------------------------------------------------------------------
+    def resize(self, w, h):
+        self._call("Resize", i32(w), i32(h))
+        self.width, self.height = w, h
+
+    def clear(self):
+        self._call("Clear")
+
+    def read_pixels(self) -> np.ndarray:
+        p = fp()
+        self._call("ReadPixels", C.byref(p))
+        out = np.ctypeslib.as_array(p, shape=(self.height, self.width, 4)).copy()
+        self._call("ReleasePixels")
+        return out
+
+    def map_pixels(self):
+        p = fp()
+        self._call("ReadPixels", C.byref(p))
+        return np.ctypeslib.as_array(p, shape=(self.height, self.width, 4))
+
+    def unmap_pixels(self):
+        self._call("ReleasePixels")
+
+    def add_pixels(self, rgba: np.ndarray):
+        a = np.ascontiguousarray(rgba, np.float32)
+        self._call("AddPixels", _ptr(a))
+
+    def device_pixels(self) -> int:
+        p = C.c_void_p()
+        self._call("GetDevicePixels", C.byref(p))
+        return p.value
+
+    # -- resources --------------------------------------------------------------------------
+    def create_texture(self, pixels: np.ndarray, fmt: int, wrap_s=WRAP_CLAMP, wrap_t=WRAP_CLAMP) -> int:
+        a = np.ascontiguousarray(pixels)
+        d = TextureDesc(a.shape[1], a.shape[0], fmt, wrap_s, wrap_t)
+        t = i32()
+        self._call("CreateTexture2D", C.byref(d), _ptr(a), C.byref(t))
+        return t.value
+
+    def destroy_texture(self, t):
+        self._call("DestroyTexture", i32(t))
+
+    def create_material(self, mtype: int, flags: int, params) -> int:
+        m = i32()
+        self._call("CreateMaterial", i32(mtype), u32(flags), C.byref(params), C.c_size_t(C.sizeof(params)), C.byref(m))
+        return m.value
+
+    def update_material(self, mat: int, params):
+        self._call("UpdateMaterial", i32(mat), C.byref(params), C.c_size_t(C.sizeof(params)))
+
+    def create_mesh(self, positions, normals, indices, material, transform=None, draw_mode=DRAW_TRIANGLES,
+                    front_face_cw=None, is_occluder=True) -> int:
+        pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+        nrm = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        idx = np.ascontiguousarray(indices, np.uint32).reshape(-1)
+        M = np.eye(4, dtype=np.float32) if transform is None else np.asarray(transform, np.float32).reshape(4, 4)
+        d = MeshDesc()
+        d.positions, d.positionStride = _ptr(pos), 12
+        d.normals, d.normalStride = _ptr(nrm), 12
+        d.vertexCount, d.indices, d.elementCount, d.drawMode = pos.shape[0], _ptr(idx), idx.shape[0], draw_mode
+        # `transform` is given as a mathematical 4x4 (row-major numpy); the ABI wants glm column-major
+        d.worldFromEntity = (f32 * 16)(*M.T.reshape(-1))
+        if front_face_cw is None:
+            front_face_cw = bool(np.linalg.det(M.astype(np.float64)) < 0.0)     # Mesh.cpp:86-91
+        d.frontFaceCW, d.isOccluder, d.material = int(front_face_cw), int(is_occluder), material
+        m = i32()
+        self._call("CreateMesh", C.byref(d), C.byref(m))
+        return m.value
+
+    def destroy_mesh(self, mesh):
+        self._call("DestroyMesh", i32(mesh))
+
+    def clear_scene(self):
+        self._call("ClearScene")
+
+    def commit(self):
+        self._call("CommitScene")
+
+    def scene_info(self) -> SceneInfo:
+        s = SceneInfo()
+        self._call("GetSceneInfo", C.byref(s))
+        return s
+
+    # -- lights / tables / globals ----------------------------------------------------------
+    def set_environment(self, enabled, texture=-1, exposure=1.0, theta=0.0):
+        e = EnvLight(int(enabled), texture, exposure, theta)
+        self._call("SetEnvironment", C.byref(e))
+
+    def set_directional_lights(self, lights):
+        arr = (DirLight * max(1, len(lights)))(*lights)
+        self._call("SetDirectionalLights", i32(len(lights)), arr)
+
+    def set_point_lights(self, lights):
+        arr = (PointLight * max(1, len(lights)))(*lights)
+        self._call("SetPointLights", i32(len(lights)), arr)
+
+    def set_spot_lights(self, lights):
+        arr = (SpotLight * max(1, len(lights)))(*lights)
+        self._call("SetSpotLights", i32(len(lights)), arr)
+
+    def set_sequences(self, xy: np.ndarray, aperture: np.ndarray):
+        xy = np.ascontiguousarray(xy, np.float32)
+        ap = np.ascontiguousarray(aperture, np.float32)
+        self._call("SetSequences", i32(xy.shape[0]), i32(xy.shape[1]), _ptr(xy), _ptr(ap))
+
+    def set_pixel_tables(self, seq_offset_x: np.ndarray, sequence_id: np.ndarray):
+        a = np.ascontiguousarray(seq_offset_x, np.float32)
+        b = np.ascontiguousarray(sequence_id, np.uint8)
+        self._call("SetPixelTables", _ptr(a), C.c_size_t(a.size), _ptr(b))
+
+    def set_globals(self, g: Globals):
+        self._call("SetGlobals", C.byref(g))
+
+    # -- passes -----------------------------------------------------------------------------
+    def render_pass(self, frame: FrameParams, want_stats=True):
+        st = PassStats()
+        self._call("RenderPass", C.byref(frame), C.byref(st) if want_stats else None)
+        return st
+
+    def enqueue_pass(self, frame: FrameParams):
+        self._call("EnqueuePass", C.byref(frame))
+
+    def synchronize(self):
+        self._call("Synchronize")
+
+    def reset_stats(self):
+        self._call("ResetStats")
+
+    def get_stats(self) -> PassStats:
+        st = PassStats()
+        self._call("GetStats", C.byref(st))
+        return st
+
+    def trace_rays(self, rays: np.ndarray, any_hit=False) -> np.ndarray:
+        r = np.ascontiguousarray(rays, RAY_DTYPE)
+        hits = np.zeros(r.shape[0], HIT_DTYPE)
+        self._call("TraceRays", i32(r.shape[0]), _ptr(r), i32(int(any_hit)), _ptr(hits))
+        return hits

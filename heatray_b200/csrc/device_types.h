@@ -1,0 +1,104 @@
+// device_types.h — data layout shared by the host side of the backend (hrc_api.cu) and the kernels.
+// Everything here lives in HBM unless noted; see DESIGN.md "Data layout".
+#pragma once
+#include "../../include/heatray_cuda.h"
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace hr {
+
+constexpr int kMaxIterations = 64;        // wavefront iterations per pass: maxRayDepth + 1 (+16 pass-through cap, policy A-14)
+constexpr int kTraceStack = 32;           // per-thread traversal stack entries (uint2)
+
+// miss-shader selector carried by a ray (policy A-6)
+enum : uint32_t { kMissNone = 0, kMissEnv = 1, kMissDir = 2, kMissPoint = 3, kMissSpot = 4 };
+
+struct alignas(16) DMaterial {            // 80 B, one per HrcMaterial
+    float baseColor[3]; uint32_t typeFlags;       // bits 0..3 type, bits 4.. feature flags
+    float emissive[3];  float metallic;
+    float roughness, specularF0, roughnessAlpha, clearCoat;
+    float clearCoatRoughness, clearCoatRoughnessAlpha, ior, density;
+    int32_t lutTex; int32_t pad[3];
+};
+
+struct DTexture {                          // all textures are expanded to RGBA32F
+    const float4* texels; int32_t w, h, wrapS, wrapT;
+};
+
+struct DLights {
+    int32_t nDir, nPoint, nSpot, envEnabled;
+    float dirDirection[HRC_MAX_LIGHTS_PER_TYPE][3], dirColor[HRC_MAX_LIGHTS_PER_TYPE][3];
+    float pointPosition[HRC_MAX_LIGHTS_PER_TYPE][3], pointColor[HRC_MAX_LIGHTS_PER_TYPE][3];
+    float spotPosition[HRC_MAX_LIGHTS_PER_TYPE][3], spotDirection[HRC_MAX_LIGHTS_PER_TYPE][3], spotColor[HRC_MAX_LIGHTS_PER_TYPE][3];
+    float spotAngles[HRC_MAX_LIGHTS_PER_TYPE][2];
+    int32_t envTex; float envExposure, envTheta; int32_t pad;
+};
+
+// Per-pass constants, passed to kernels BY VALUE (constant bank).
+struct DFrame {
+    HrcGlobals g;
+    float fovTan, aspectRatio, focusDistance, apertureRadius;
+    float view[16];
+    float maxSampleIndex;
+    int32_t w, h;
+    int32_t bandHeight, bandIndex, bandCount, localRows;   // screen-band sharding
+    int32_t numSequences, sequenceLength;
+    uint32_t offsetCount;
+    DLights lights;
+};
+
+// Wavefront queues (structure of arrays; one slot per in-flight ray).
+struct RayQueue {
+    float4* o;     // origin.xyz, tmax
+    float4* d;     // direction.xyz, extraT
+    float4* w;     // weight.xyz, pixel index (int bits)
+    uint2*  m;     // x: depth | missKind<<8 | missIndex<<12 | sequenceID<<16 ; y: sequenceIndexOffset
+};
+struct ShadowQueue {
+    float4* o;     // origin.xyz, tmax
+    float4* d;     // direction.xyz, extraT
+    float4* w;     // weight.xyz, pixel (24 bits) | missKind<<24 | missIndex<<27
+};
+
+// Per-iteration control words, zeroed at the start of every pass.
+struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; };
+
+struct DeviceStats {                       // accumulated by k_finish_pass
+    unsigned long long raysPrimary, raysExtension, raysOcclusion, nodesVisited, trianglesTested, stackOverflows;
+};
+
+struct DScene {
+    const float4* nodes;      // 5 x float4 per wide node
+    const float4* tris;       // 3 x float4 per triangle, leaf order: (v0, primId) (e1, 0) (e2, 0)
+    const float4* shade;      // 4 x float4 per triangle, primId order: (n0, material) (n1, frontFaceCW) (n2, 0) (Ng, 0)
+    const DMaterial* materials;
+    const DTexture* textures;
+    const float2* seq;        // RandomSequences
+    const float2* aperture;   // ApertureSamples
+    const float* seqOffsetX;  // SequenceOffsets.x
+    const uint8_t* sequenceId;
+};
+
+// Launch wrappers implemented in kernels.cu
+struct PassBuffers {
+    RayQueue ext[2];
+    ShadowQueue shadow;
+    float4* hits;
+    IterCtrl* ctrl;           // kMaxIterations entries
+    DeviceStats* stats;
+    float4* accum;
+    uint32_t capacity;        // rays per queue
+};
+
+struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; };
+
+void launchClearCtrl(const PassBuffers& pb, cudaStream_t s);
+void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s);
+void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s);
+void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig& lc, cudaStream_t s);
+void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s);
+
+} // namespace hr

@@ -18,3 +18,10 @@ size_t sequenceOffsetCount(int w, int h);
 void generateSequenceOffsets(int w, int h, float* outX, size_t count);
 void generateSequenceIds(int w, int h, int numSequences, uint8_t* out);
 } // namespace hr
+
+namespace hr {
+// host_scene.cpp
+uint32_t packPbrMaterial(const HrhPbrMaterial& in, HrcTexture lut, HrcPbrParams& out);
+uint32_t packGlassMaterial(const HrhGlassMaterial& in, HrcGlassParams& out);
+void generateMultiscatterLUT(float* out, int dim, int sampleCount, int threads);
+} // namespace hr

@@ -1,0 +1,610 @@
+// hrc_api.cu — implementation of the backend C-ABI (include/heatray_cuda.h) over CUDA device memory.
+// Reference-side counterparts are cited in the header next to each entry point.
+#include "device_types.h"
+#include "bvh_builder.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace hr;
+
+namespace {
+
+struct TextureRec { float4* dev = nullptr; int w = 0, h = 0, wrapS = 0, wrapT = 0; bool alive = false; };
+struct MaterialRec { DMaterial d; int type; uint32_t flags; };
+struct MeshRec {
+    bool alive = false;
+    std::vector<float> pos, nrm;       // entity space, tightly packed xyz
+    std::vector<uint32_t> idx;
+    int drawMode = 0; float M[16]; int frontFaceCW = 0, isOccluder = 1, material = 0;
+};
+
+thread_local std::string g_err;
+
+} // namespace
+
+struct HrcContext_t {
+    int device = 0;
+    bool collectStats = false;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    std::vector<cudaEvent_t> evPool;
+    std::string err;
+    int smCount = 148;
+
+    int w = 0, h = 0;
+    float4* accum = nullptr;
+    float* pinned = nullptr; size_t pinnedBytes = 0; bool mapped = false;
+    float4* staging = nullptr;        // device staging for hrcAddPixels
+
+    std::vector<TextureRec> textures;
+    std::vector<MaterialRec> materials;
+    std::vector<MeshRec> meshes;
+    bool committed = false, materialsDirty = true, texturesDirty = true;
+    bool anySingleSided = false;
+
+    float4 *dNodes = nullptr, *dTris = nullptr, *dShade = nullptr;
+    DMaterial* dMaterials = nullptr; size_t dMaterialsCap = 0;
+    DTexture* dTextures = nullptr; size_t dTexturesCap = 0;
+    float2 *dSeq = nullptr, *dAperture = nullptr; float* dSeqOffsetX = nullptr; uint8_t* dSequenceId = nullptr;
+    int numSequences = 0, sequenceLength = 0; size_t offsetCount = 0; bool pixelTables = false;
+
+    PassBuffers pb{};
+    DLights lights{};
+    HrcGlobals globals{};
+    HrcSceneInfo info{};
+    DeviceStats lastStats{};
+};
+
+namespace {
+
+int fail(HrcContext c, int code, const std::string& msg) { if (c) c->err = msg; else g_err = msg; return code; }
+int failCuda(HrcContext c, cudaError_t e, const char* what) {
+    return fail(c, e == cudaErrorMemoryAllocation ? HRC_ERR_OUT_OF_MEMORY : HRC_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(c, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return failCuda(c, e_, #call); } while (0)
+
+template <class T> void freeDev(T*& p) { if (p) { cudaFree(p); p = nullptr; } }
+
+void freeQueues(HrcContext c) {
+    for (int k = 0; k < 2; ++k) { freeDev(c->pb.ext[k].o); freeDev(c->pb.ext[k].d); freeDev(c->pb.ext[k].w); freeDev(c->pb.ext[k].m); }
+    freeDev(c->pb.shadow.o); freeDev(c->pb.shadow.d); freeDev(c->pb.shadow.w); freeDev(c->pb.hits);
+    c->pb.capacity = 0;
+}
+
+DScene sceneOf(HrcContext c) {
+    DScene s; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.materials = c->dMaterials; s.textures = c->dTextures;
+    s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId;
+    return s;
+}
+LaunchConfig configOf(HrcContext c) { LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->collectStats; return lc; }
+
+int uploadMaterials(HrcContext c) {
+    if (!c->materialsDirty) return HRC_OK;
+    size_t n = std::max<size_t>(1, c->materials.size());
+    if (n > c->dMaterialsCap) { freeDev(c->dMaterials); CU(c, cudaMalloc(&c->dMaterials, n * sizeof(DMaterial))); c->dMaterialsCap = n; }
+    std::vector<DMaterial> host(n);
+    c->anySingleSided = false;
+    for (size_t i = 0; i < c->materials.size(); ++i) {
+        host[i] = c->materials[i].d;
+        if (c->materials[i].type == HRC_MATERIAL_PBR && !(c->materials[i].flags & HRC_MAT_DOUBLE_SIDED)) c->anySingleSided = true;
+    }
+    CU(c, cudaMemcpyAsync(c->dMaterials, host.data(), n * sizeof(DMaterial), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->materialsDirty = false;
+    return HRC_OK;
+}
+int uploadTextures(HrcContext c) {
+    if (!c->texturesDirty) return HRC_OK;
+    size_t n = std::max<size_t>(1, c->textures.size());
+    if (n > c->dTexturesCap) { freeDev(c->dTextures); CU(c, cudaMalloc(&c->dTextures, n * sizeof(DTexture))); c->dTexturesCap = n; }
+    std::vector<DTexture> host(n);
+    for (size_t i = 0; i < c->textures.size(); ++i) { const TextureRec& t = c->textures[i]; host[i] = DTexture{t.dev, t.w, t.h, t.wrapS, t.wrapT}; }
+    CU(c, cudaMemcpyAsync(c->dTextures, host.data(), n * sizeof(DTexture), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->texturesDirty = false;
+    return HRC_OK;
+}
+
+int packMaterial(HrcContext c, MaterialRec& m, int type, const void* params, size_t bytes) {
+    DMaterial d; std::memset(&d, 0, sizeof(d));
+    if (type == HRC_MATERIAL_PBR) {
+        if (bytes != sizeof(HrcPbrParams)) return fail(c, HRC_ERR_INVALID_VALUE, "PBR parameter block has the wrong size");
+        const HrcPbrParams* p = (const HrcPbrParams*)params;
+        for (int k = 0; k < 3; ++k) { d.baseColor[k] = p->baseColor[k]; d.emissive[k] = p->emissiveColor[k]; }
+        d.metallic = p->metallic; d.roughness = p->roughness; d.specularF0 = p->specularF0; d.roughnessAlpha = p->roughnessAlpha;
+        d.clearCoat = p->clearCoat; d.clearCoatRoughness = p->clearCoatRoughness; d.clearCoatRoughnessAlpha = p->clearCoatRoughnessAlpha;
+        d.lutTex = p->multiscatterLUT;
+    } else if (type == HRC_MATERIAL_GLASS) {
+        if (bytes != sizeof(HrcGlassParams)) return fail(c, HRC_ERR_INVALID_VALUE, "glass parameter block has the wrong size");
+        const HrcGlassParams* p = (const HrcGlassParams*)params;
+        for (int k = 0; k < 3; ++k) d.baseColor[k] = p->baseColor[k];
+        d.roughness = p->roughness; d.roughnessAlpha = p->roughnessAlpha; d.ior = p->ior; d.density = p->density; d.specularF0 = p->specularF0;
+        d.lutTex = -1;
+    } else return fail(c, HRC_ERR_INVALID_VALUE, "unknown material type");
+    if (d.lutTex >= (int)c->textures.size() || (d.lutTex >= 0 && !c->textures[d.lutTex].alive)) return fail(c, HRC_ERR_INVALID_VALUE, "bad multiscatter LUT texture handle");
+    d.typeFlags = (uint32_t)type | (m.flags << 4);
+    m.d = d; m.type = type;
+    return HRC_OK;
+}
+
+// vertex.rlsl:25-43 on the host; glm evaluates mat4*vec4 as (m0*x + m1*y) + (m2*z + m3*w)
+inline void xformPoint(const float* M, const float* p, float* o) {
+    o[0] = (M[0] * p[0] + M[4] * p[1]) + (M[8] * p[2] + M[12] * 1.0f);
+    o[1] = (M[1] * p[0] + M[5] * p[1]) + (M[9] * p[2] + M[13] * 1.0f);
+    o[2] = (M[2] * p[0] + M[6] * p[1]) + (M[10] * p[2] + M[14] * 1.0f);
+}
+inline void xformNormal(const float* M, const float* n, float* o) {   // mat3(worldFromEntity) * n (quirk B-Q7)
+    o[0] = (M[0] * n[0] + M[4] * n[1]) + M[8] * n[2];
+    o[1] = (M[1] * n[0] + M[5] * n[1]) + M[9] * n[2];
+    o[2] = (M[2] * n[0] + M[6] * n[1]) + M[10] * n[2];
+}
+
+} // namespace
+
+extern "C" {
+
+HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
+    if (!out) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null out pointer");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, HRC_ERR_NO_DEVICE, std::string("no CUDA device available (this backend has no CPU path): ") + cudaGetErrorString(e));
+    int dev = desc ? desc->device : 0;
+    if (dev < 0 || dev >= count) return fail(nullptr, HRC_ERR_INVALID_VALUE, "bad CUDA device ordinal");
+    HrcContext c = new HrcContext_t();
+    c->device = dev; c->collectStats = desc && desc->collectStats;
+    if ((e = cudaSetDevice(dev)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaSetDevice"); delete c; return r; }
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaGetDeviceProperties"); delete c; return r; }
+    c->smCount = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaStreamCreate"); delete c; return r; }
+    cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop);
+    cudaMalloc(&c->pb.ctrl, sizeof(IterCtrl) * kMaxIterations);
+    cudaMalloc(&c->pb.stats, sizeof(DeviceStats));
+    cudaMemsetAsync(c->pb.stats, 0, sizeof(DeviceStats), c->stream);
+    cudaMemsetAsync(c->pb.ctrl, 0, sizeof(IterCtrl) * kMaxIterations, c->stream);
+    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) { int r = failCuda(nullptr, e, "context setup"); delete c; return r; }
+    std::memset(&c->globals, 0, sizeof(c->globals));
+    c->globals.maxRayDepth = 5; c->globals.maxChannelValue = 3.14159265358979f;   // GlobalData defaults, PassGenerator.h:270-272
+    c->lights.envTex = -1;
+    *out = c;
+    return HRC_OK;
+}
+
+HRC_API int hrcDestroyContext(HrcContext c) {
+    if (!c) return HRC_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    freeQueues(c);
+    freeDev(c->accum); freeDev(c->staging); if (c->pinned) cudaFreeHost(c->pinned);
+    for (auto& t : c->textures) freeDev(t.dev);
+    freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade); freeDev(c->dMaterials); freeDev(c->dTextures);
+    freeDev(c->dSeq); freeDev(c->dAperture); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
+    freeDev(c->pb.ctrl); freeDev(c->pb.stats);
+    for (auto ev : c->evPool) cudaEventDestroy(ev);
+    cudaEventDestroy(c->evStart); cudaEventDestroy(c->evStop);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return HRC_OK;
+}
+
+HRC_API const char* hrcGetLastError(HrcContext c) { return c ? c->err.c_str() : g_err.c_str(); }
+
+HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (w <= 0 || h <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "non-positive framebuffer size");
+    if ((uint64_t)w * (uint64_t)h > (1u << 24)) return fail(c, HRC_ERR_UNSUPPORTED, "framebuffers above 2^24 pixels are not supported (pixel index is packed in 24 bits)");
+    if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "resize while pixels are mapped");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    freeQueues(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
+    if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
+    c->pixelTables = false; c->offsetCount = 0;
+    const size_t n = (size_t)w * h;
+    CU(c, cudaMalloc(&c->accum, n * sizeof(float4)));
+    CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));
+    CU(c, cudaMallocHost(&c->pinned, n * sizeof(float4))); c->pinnedBytes = n * sizeof(float4);
+    for (int k = 0; k < 2; ++k) {
+        CU(c, cudaMalloc(&c->pb.ext[k].o, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.ext[k].d, n * sizeof(float4)));
+        CU(c, cudaMalloc(&c->pb.ext[k].w, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.ext[k].m, n * sizeof(uint2)));
+    }
+    CU(c, cudaMalloc(&c->pb.shadow.o, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.shadow.d, n * sizeof(float4)));
+    CU(c, cudaMalloc(&c->pb.shadow.w, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.hits, n * sizeof(float4)));
+    c->pb.capacity = (uint32_t)n; c->pb.accum = c->accum;
+    c->w = w; c->h = h;
+    CU(c, cudaStreamSynchronize(c->stream));
+    return HRC_OK;
+}
+
+HRC_API int hrcClear(HrcContext c) {
+    if (!c || !c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
+    cudaSetDevice(c->device);
+    CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->w * c->h * sizeof(float4), c->stream));
+    return HRC_OK;
+}
+
+HRC_API int hrcReadPixels(HrcContext c, const float** rgba) {
+    if (!c || !rgba) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
+    if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "pixels already mapped");
+    cudaSetDevice(c->device);
+    CU(c, cudaMemcpyAsync(c->pinned, c->accum, (size_t)c->w * c->h * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->mapped = true; *rgba = c->pinned;
+    return HRC_OK;
+}
+HRC_API int hrcReleasePixels(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (!c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "pixels are not mapped");
+    c->mapped = false; return HRC_OK;
+}
+HRC_API int hrcAddPixels(HrcContext c, const float* rgba) {
+    if (!c || !rgba) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
+    cudaSetDevice(c->device);
+    const size_t n = (size_t)c->w * c->h;
+    if (!c->staging) CU(c, cudaMalloc(&c->staging, n * sizeof(float4)));
+    CU(c, cudaMemcpyAsync(c->staging, rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    launchAddPixels(c->accum, c->staging, n, c->stream);
+    CU(c, cudaStreamSynchronize(c->stream));
+    return HRC_OK;
+}
+HRC_API int hrcGetDevicePixels(HrcContext c, void** devPtr) {
+    if (!c || !devPtr) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    *devPtr = c->accum; return HRC_OK;
+}
+
+HRC_API int hrcCreateTexture2D(HrcContext c, const HrcTextureDesc* d, const void* pixels, HrcTexture* out) {
+    if (!c || !d || !pixels || !out || d->width <= 0 || d->height <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad texture descriptor");
+    cudaSetDevice(c->device);
+    const size_t n = (size_t)d->width * d->height;
+    std::vector<float4> host(n);
+    const float* f = (const float*)pixels; const uint8_t* b = (const uint8_t*)pixels;
+    for (size_t i = 0; i < n; ++i) {
+        switch (d->format) {
+        case HRC_TEX_R32F: host[i] = make_float4(f[i], 0.f, 0.f, 1.f); break;
+        case HRC_TEX_RGB32F: host[i] = make_float4(f[3 * i], f[3 * i + 1], f[3 * i + 2], 1.f); break;
+        case HRC_TEX_RGBA32F: host[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]); break;
+        case HRC_TEX_RGBA8: host[i] = make_float4((float)b[4 * i] / 255.0f, (float)b[4 * i + 1] / 255.0f, (float)b[4 * i + 2] / 255.0f, (float)b[4 * i + 3] / 255.0f); break;
+        default: return fail(c, HRC_ERR_INVALID_VALUE, "unknown texture format");
+        }
+    }
+    TextureRec t; t.w = d->width; t.h = d->height; t.wrapS = d->wrapS; t.wrapT = d->wrapT; t.alive = true;
+    CU(c, cudaMalloc(&t.dev, n * sizeof(float4)));
+    CU(c, cudaMemcpyAsync(t.dev, host.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->textures.push_back(t); c->texturesDirty = true;
+    *out = (HrcTexture)c->textures.size() - 1;
+    return HRC_OK;
+}
+HRC_API int hrcDestroyTexture(HrcContext c, HrcTexture tex) {
+    if (!c || tex < 0 || tex >= (int)c->textures.size() || !c->textures[tex].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad texture handle");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    freeDev(c->textures[tex].dev); c->textures[tex].alive = false; c->texturesDirty = true;
+    return HRC_OK;
+}
+
+HRC_API int hrcCreateMaterial(HrcContext c, int32_t type, uint32_t flags, const void* params, size_t bytes, HrcMaterial* out) {
+    if (!c || !params || !out) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    const uint32_t unsupported = ~(uint32_t)(HRC_MAT_DOUBLE_SIDED);
+    if (flags & unsupported) return fail(c, HRC_ERR_UNSUPPORTED, "material textures / alpha mask / vertex colours are not built yet");
+    MaterialRec m; m.flags = flags;
+    int r = packMaterial(c, m, type, params, bytes); if (r) return r;
+    c->materials.push_back(m); c->materialsDirty = true;
+    *out = (HrcMaterial)c->materials.size() - 1;
+    return HRC_OK;
+}
+HRC_API int hrcUpdateMaterial(HrcContext c, HrcMaterial mat, const void* params, size_t bytes) {
+    if (!c || mat < 0 || mat >= (int)c->materials.size() || !params) return fail(c, HRC_ERR_INVALID_VALUE, "bad material handle");
+    int r = packMaterial(c, c->materials[mat], c->materials[mat].type, params, bytes); if (r) return r;
+    c->materialsDirty = true; return HRC_OK;
+}
+
+HRC_API int hrcCreateMesh(HrcContext c, const HrcMeshDesc* d, HrcMesh* out) {
+    if (!c || !d || !out || !d->positions || !d->normals || !d->indices) return fail(c, HRC_ERR_INVALID_VALUE, "mesh needs positions, normals and indices");
+    if (d->material < 0 || d->material >= (int)c->materials.size()) return fail(c, HRC_ERR_INVALID_VALUE, "bad material handle");
+    if (d->drawMode != HRC_DRAW_TRIANGLES && d->drawMode != HRC_DRAW_TRIANGLE_STRIP) return fail(c, HRC_ERR_INVALID_VALUE, "bad draw mode");
+    if (!d->isOccluder) return fail(c, HRC_ERR_UNSUPPORTED, "non-occluder (alpha-masked) primitives are not built yet");
+    MeshRec m; m.alive = true;
+    m.pos.resize((size_t)3 * d->vertexCount); m.nrm.resize((size_t)3 * d->vertexCount);
+    const int ps = d->positionStride ? d->positionStride : 12, ns = d->normalStride ? d->normalStride : 12;
+    for (uint32_t i = 0; i < d->vertexCount; ++i) {
+        std::memcpy(&m.pos[3 * (size_t)i], (const char*)d->positions + (size_t)i * ps, 12);
+        std::memcpy(&m.nrm[3 * (size_t)i], (const char*)d->normals + (size_t)i * ns, 12);
+    }
+    m.idx.assign(d->indices, d->indices + d->elementCount);
+    for (uint32_t i : m.idx) if (i >= d->vertexCount) return fail(c, HRC_ERR_INVALID_VALUE, "index out of range");
+    m.drawMode = d->drawMode; std::memcpy(m.M, d->worldFromEntity, sizeof(m.M));
+    m.frontFaceCW = d->frontFaceCW; m.isOccluder = d->isOccluder; m.material = d->material;
+    c->meshes.push_back(std::move(m)); c->committed = false;
+    *out = (HrcMesh)c->meshes.size() - 1;
+    return HRC_OK;
+}
+HRC_API int hrcDestroyMesh(HrcContext c, HrcMesh mesh) {
+    if (!c || mesh < 0 || mesh >= (int)c->meshes.size() || !c->meshes[mesh].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad mesh handle");
+    c->meshes[mesh] = MeshRec(); c->committed = false; return HRC_OK;
+}
+HRC_API int hrcClearScene(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    c->meshes.clear(); c->materials.clear(); c->committed = false; c->materialsDirty = true;
+    return HRC_OK;
+}
+
+HRC_API int hrcCommitScene(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    // 1. flatten to world space; primitive id = running triangle index in (mesh, element) order (policy A-9)
+    std::vector<BuildTriangle> bt;
+    std::vector<float4> shade;      // 4 per triangle
+    size_t triTotal = 0;
+    for (const MeshRec& m : c->meshes) if (m.alive) triTotal += m.drawMode == HRC_DRAW_TRIANGLES ? m.idx.size() / 3 : (m.idx.size() >= 3 ? m.idx.size() - 2 : 0);
+    if (triTotal >= (1u << 30)) return fail(c, HRC_ERR_UNSUPPORTED, "more than 2^30 triangles");
+    bt.reserve(triTotal); shade.reserve(triTotal * 4);
+    for (const MeshRec& m : c->meshes) {
+        if (!m.alive) continue;
+        const size_t nv = m.pos.size() / 3;
+        std::vector<float> wp(3 * nv), wn(3 * nv);
+        for (size_t i = 0; i < nv; ++i) { xformPoint(m.M, &m.pos[3 * i], &wp[3 * i]); xformNormal(m.M, &m.nrm[3 * i], &wn[3 * i]); }
+        auto emit = [&](uint32_t a, uint32_t b, uint32_t cc) {
+            BuildTriangle t;
+            for (int k = 0; k < 3; ++k) { t.v0[k] = wp[3 * a + k]; t.v1[k] = wp[3 * b + k]; t.v2[k] = wp[3 * cc + k]; }
+            bt.push_back(t);
+            // geometric normal = normalize(cross(e1, e2)) with the same fp32 operation order as the shaders' restatement
+            float e1[3], e2[3];
+            for (int k = 0; k < 3; ++k) { e1[k] = t.v1[k] - t.v0[k]; e2[k] = t.v2[k] - t.v0[k]; }
+            float nx = e1[1] * e2[2] - e1[2] * e2[1], ny = e1[2] * e2[0] - e1[0] * e2[2], nz = e1[0] * e2[1] - e1[1] * e2[0];
+            float inv = 1.0f / std::sqrt((nx * nx + ny * ny) + nz * nz);
+            shade.push_back(make_float4(wn[3 * a], wn[3 * a + 1], wn[3 * a + 2], __builtin_bit_cast(float, (int32_t)m.material)));
+            shade.push_back(make_float4(wn[3 * b], wn[3 * b + 1], wn[3 * b + 2], __builtin_bit_cast(float, (int32_t)m.frontFaceCW)));
+            shade.push_back(make_float4(wn[3 * cc], wn[3 * cc + 1], wn[3 * cc + 2], 0.0f));
+            shade.push_back(make_float4(nx * inv, ny * inv, nz * inv, 0.0f));
+        };
+        if (m.drawMode == HRC_DRAW_TRIANGLES) {
+            for (size_t k = 0; k + 2 < m.idx.size(); k += 3) emit(m.idx[k], m.idx[k + 1], m.idx[k + 2]);
+        } else {
+            for (size_t k = 0; k + 2 < m.idx.size(); ++k) {
+                if (k & 1) emit(m.idx[k + 1], m.idx[k], m.idx[k + 2]);
+                else       emit(m.idx[k], m.idx[k + 1], m.idx[k + 2]);
+            }
+        }
+    }
+    // 2. build
+    WideBVH bvh;
+    buildWideBVH(bt.data(), bt.size(), 0, bvh);
+    if (bvh.maxDepth >= (uint32_t)kTraceStack) return fail(c, HRC_ERR_UNSUPPORTED, "BVH deeper than the traversal stack");
+    // 3. leaf-ordered triangle records (v0 | primId, e1, e2)
+    std::vector<float4> tris(std::max<size_t>(1, bvh.triOrder.size()) * 3);
+    for (size_t s = 0; s < bvh.triOrder.size(); ++s) {
+        const uint32_t prim = bvh.triOrder[s];
+        const BuildTriangle& t = bt[prim];
+        tris[3 * s + 0] = make_float4(t.v0[0], t.v0[1], t.v0[2], __builtin_bit_cast(float, (int32_t)prim));
+        tris[3 * s + 1] = make_float4(t.v1[0] - t.v0[0], t.v1[1] - t.v0[1], t.v1[2] - t.v0[2], 0.0f);
+        tris[3 * s + 2] = make_float4(t.v2[0] - t.v0[0], t.v2[1] - t.v0[1], t.v2[2] - t.v0[2], 0.0f);
+    }
+    if (shade.empty()) shade.resize(4, make_float4(0, 0, 0, 0));
+    // 4. upload
+    freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade);
+    CU(c, cudaMalloc(&c->dNodes, bvh.nodes.size() * sizeof(WideNode)));
+    CU(c, cudaMalloc(&c->dTris, tris.size() * sizeof(float4)));
+    CU(c, cudaMalloc(&c->dShade, shade.size() * sizeof(float4)));
+    CU(c, cudaMemcpyAsync(c->dNodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(WideNode), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaMemcpyAsync(c->dTris, tris.data(), tris.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaMemcpyAsync(c->dShade, shade.data(), shade.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->info.triangleCount = bt.size(); c->info.nodeCount = bvh.nodes.size();
+    c->info.nodeBytes = bvh.nodes.size() * sizeof(WideNode); c->info.triangleBytes = bt.size() * 48; c->info.shadingBytes = bt.size() * 64;
+    c->info.buildSeconds = (float)bvh.buildSeconds;
+    c->committed = true;
+    return HRC_OK;
+}
+
+HRC_API int hrcSetEnvironment(HrcContext c, const HrcEnvLight* env) {
+    if (!c || !env) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    if (env->enabled && env->texture >= 0 && (env->texture >= (int)c->textures.size() || !c->textures[env->texture].alive))
+        return fail(c, HRC_ERR_INVALID_VALUE, "bad environment texture handle");
+    c->lights.envEnabled = env->enabled ? 1 : 0; c->lights.envTex = env->texture; c->lights.envExposure = env->exposureCompensation; c->lights.envTheta = env->thetaRotation;
+    return HRC_OK;
+}
+HRC_API int hrcSetDirectionalLights(HrcContext c, int32_t n, const HrcDirLight* l) {
+    if (!c || n < 0 || n > HRC_MAX_LIGHTS_PER_TYPE || (n && !l)) return fail(c, HRC_ERR_INVALID_VALUE, "0..5 directional lights");
+    c->lights.nDir = n;
+    for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) { c->lights.dirDirection[i][k] = l[i].direction[k]; c->lights.dirColor[i][k] = l[i].color[k]; }
+    return HRC_OK;
+}
+HRC_API int hrcSetPointLights(HrcContext c, int32_t n, const HrcPointLight* l) {
+    if (!c || n < 0 || n > HRC_MAX_LIGHTS_PER_TYPE || (n && !l)) return fail(c, HRC_ERR_INVALID_VALUE, "0..5 point lights");
+    c->lights.nPoint = n;
+    for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) { c->lights.pointPosition[i][k] = l[i].position[k]; c->lights.pointColor[i][k] = l[i].color[k]; }
+    return HRC_OK;
+}
+HRC_API int hrcSetSpotLights(HrcContext c, int32_t n, const HrcSpotLight* l) {
+    if (!c || n < 0 || n > HRC_MAX_LIGHTS_PER_TYPE || (n && !l)) return fail(c, HRC_ERR_INVALID_VALUE, "0..5 spot lights");
+    c->lights.nSpot = n;
+    for (int i = 0; i < n; ++i) {
+        for (int k = 0; k < 3; ++k) { c->lights.spotPosition[i][k] = l[i].position[k]; c->lights.spotDirection[i][k] = l[i].direction[k]; c->lights.spotColor[i][k] = l[i].color[k]; }
+        c->lights.spotAngles[i][0] = l[i].angles[0]; c->lights.spotAngles[i][1] = l[i].angles[1];
+    }
+    return HRC_OK;
+}
+
+HRC_API int hrcSetSequences(HrcContext c, int32_t ns, int32_t len, const float* xy, const float* ap) {
+    if (!c || ns <= 0 || len <= 0 || !xy || !ap) return fail(c, HRC_ERR_INVALID_VALUE, "bad sequence tables");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    freeDev(c->dSeq); freeDev(c->dAperture);
+    const size_t bytes = (size_t)ns * len * sizeof(float2);
+    CU(c, cudaMalloc(&c->dSeq, bytes)); CU(c, cudaMalloc(&c->dAperture, bytes));
+    CU(c, cudaMemcpy(c->dSeq, xy, bytes, cudaMemcpyHostToDevice));
+    CU(c, cudaMemcpy(c->dAperture, ap, bytes, cudaMemcpyHostToDevice));
+    c->numSequences = ns; c->sequenceLength = len;
+    return HRC_OK;
+}
+HRC_API int hrcSetPixelTables(HrcContext c, const float* off, size_t count, const uint8_t* sid) {
+    if (!c || !off || !sid || count == 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad pixel tables");
+    if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "pixel tables need a framebuffer size first");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
+    CU(c, cudaMalloc(&c->dSeqOffsetX, count * sizeof(float)));
+    CU(c, cudaMalloc(&c->dSequenceId, (size_t)c->w * c->h));
+    CU(c, cudaMemcpy(c->dSeqOffsetX, off, count * sizeof(float), cudaMemcpyHostToDevice));
+    CU(c, cudaMemcpy(c->dSequenceId, sid, (size_t)c->w * c->h, cudaMemcpyHostToDevice));
+    c->offsetCount = count; c->pixelTables = true;
+    return HRC_OK;
+}
+HRC_API int hrcSetGlobals(HrcContext c, const HrcGlobals* g) {
+    if (!c || !g) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    c->globals = *g; return HRC_OK;
+}
+
+static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels, float* kernelMs /*[4]: raygen, closest, shade, any*/, int* launches /*[3]*/) {
+    if (!c || !fp) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    if (!c->committed) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a committed scene");
+    if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
+    if (!c->dSeq || !c->pixelTables) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without QMC / pixel tables");
+    if (fp->interactiveMode) return fail(c, HRC_ERR_UNSUPPORTED, "interactive block mode is not built");
+    if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass while pixels are mapped");
+    const size_t maxIdx = (size_t)(int)(((float)(c->h - 1) + 0.5f) * (float)c->h + ((float)(c->w - 1) + 0.5f));
+    if (maxIdx >= c->offsetCount) return fail(c, HRC_ERR_INVALID_VALUE, "sequence-offset table too short for the reference index formula");
+    cudaSetDevice(c->device);
+    int r = uploadMaterials(c); if (r) return r;
+    r = uploadTextures(c); if (r) return r;
+
+    DFrame fr; std::memset(&fr, 0, sizeof(fr));
+    fr.g = c->globals; fr.g.sampleIndex = fp->sampleIndex;
+    fr.fovTan = fp->fovTan; fr.aspectRatio = fp->aspectRatio; fr.focusDistance = fp->focusDistance; fr.apertureRadius = fp->apertureRadius;
+    std::memcpy(fr.view, fp->viewMatrix, sizeof(fr.view));
+    fr.maxSampleIndex = fp->maxSampleIndex; fr.w = c->w; fr.h = c->h;
+    fr.bandCount = fp->bandCount > 1 ? fp->bandCount : 1; fr.bandHeight = fp->bandHeight > 0 ? fp->bandHeight : 1; fr.bandIndex = fp->bandIndex;
+    if (fr.bandCount > 1) {
+        if (fr.bandIndex < 0 || fr.bandIndex >= fr.bandCount) return fail(c, HRC_ERR_INVALID_VALUE, "band index out of range");
+        int rows = 0; for (int y = 0; y < c->h; ++y) if ((y / fr.bandHeight) % fr.bandCount == fr.bandIndex) rows++;
+        fr.localRows = rows;
+    } else fr.localRows = c->h;
+    fr.numSequences = c->numSequences; fr.sequenceLength = c->sequenceLength; fr.offsetCount = (uint32_t)c->offsetCount;
+    fr.lights = c->lights;
+    if (fr.lights.envEnabled && fr.lights.envTex >= 0 && !c->textures[fr.lights.envTex].alive) return fail(c, HRC_ERR_INVALID_OPERATION, "environment texture was destroyed");
+
+    int iterations = std::max(0, fr.g.maxRayDepth) + 1 + (c->anySingleSided ? 16 : 0);
+    iterations = std::min(iterations, kMaxIterations);
+    const DScene sc = sceneOf(c);
+    const LaunchConfig lc = configOf(c);
+    cudaStream_t s = c->stream;
+
+    size_t evNeeded = timeKernels ? (size_t)(3 * iterations + 2) : 0;
+    while (c->evPool.size() < evNeeded) { cudaEvent_t ev; CU(c, cudaEventCreate(&ev)); c->evPool.push_back(ev); }
+    size_t ev = 0;
+    auto mark = [&]() { if (timeKernels) cudaEventRecord(c->evPool[ev++], s); };
+
+    launchClearCtrl(c->pb, s);
+    mark();
+    launchRaygen(sc, fr, c->pb, s);
+    mark();
+    for (int it = 0; it < iterations; ++it) {
+        launchTraceClosest(sc, c->pb, it, lc, s); mark();
+        launchShade(sc, fr, c->pb, it, lc, s);    mark();
+        launchTraceAny(sc, fr, c->pb, it, lc, s); mark();
+    }
+    launchFinishPass(c->pb, iterations, s);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return failCuda(c, e, "kernel launch");
+    if (launches) { launches[0] = iterations; launches[1] = iterations; launches[2] = iterations; }
+    if (timeKernels && kernelMs) {
+        CU(c, cudaStreamSynchronize(s));
+        float ms = 0; kernelMs[0] = kernelMs[1] = kernelMs[2] = kernelMs[3] = 0;
+        cudaEventElapsedTime(&ms, c->evPool[0], c->evPool[1]); kernelMs[0] = ms;
+        for (int it = 0; it < iterations; ++it) {
+            cudaEventElapsedTime(&ms, c->evPool[1 + 3 * it], c->evPool[2 + 3 * it]); kernelMs[1] += ms;
+            cudaEventElapsedTime(&ms, c->evPool[2 + 3 * it], c->evPool[3 + 3 * it]); kernelMs[2] += ms;
+            cudaEventElapsedTime(&ms, c->evPool[3 + 3 * it], c->evPool[4 + 3 * it]); kernelMs[3] += ms;
+        }
+    }
+    return HRC_OK;
+}
+
+static int readStats(HrcContext c, DeviceStats* out) {
+    CU(c, cudaMemcpyAsync(out, c->pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return HRC_OK;
+}
+
+HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* stats) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    cudaSetDevice(c->device);
+    float kms[4] = {0, 0, 0, 0}; int launches[3] = {0, 0, 0};
+    DeviceStats before; int r = readStats(c, &before); if (r) return r;
+    CU(c, cudaEventRecord(c->evStart, c->stream));
+    r = enqueuePass(c, fp, c->collectStats && stats, kms, launches); if (r) return r;
+    CU(c, cudaEventRecord(c->evStop, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return failCuda(c, e, "render pass");
+    if (stats) {
+        DeviceStats after; r = readStats(c, &after); if (r) return r;
+        std::memset(stats, 0, sizeof(*stats));
+        cudaEventElapsedTime(&stats->gpuMs, c->evStart, c->evStop);
+        stats->raysPrimary = after.raysPrimary - before.raysPrimary; stats->raysExtension = after.raysExtension - before.raysExtension;
+        stats->raysOcclusion = after.raysOcclusion - before.raysOcclusion;
+        stats->nodesVisited = after.nodesVisited - before.nodesVisited; stats->trianglesTested = after.trianglesTested - before.trianglesTested;
+        stats->closestLaunches = launches[0]; stats->shadeLaunches = launches[1]; stats->anyLaunches = launches[2];
+        stats->msRaygen = kms[0]; stats->msClosest = kms[1]; stats->msShade = kms[2]; stats->msAny = kms[3];
+        if (after.stackOverflows != before.stackOverflows) return fail(c, HRC_ERR_INVALID_OPERATION, "traversal stack overflow");
+    }
+    return HRC_OK;
+}
+HRC_API int hrcEnqueuePass(HrcContext c, const HrcFrameParams* fp) { return enqueuePass(c, fp, false, nullptr, nullptr); }
+HRC_API int hrcSynchronize(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    return HRC_OK;
+}
+HRC_API int hrcResetStats(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    cudaSetDevice(c->device);
+    CU(c, cudaMemsetAsync(c->pb.stats, 0, sizeof(DeviceStats), c->stream));
+    return HRC_OK;
+}
+HRC_API int hrcGetStats(HrcContext c, HrcPassStats* stats) {
+    if (!c || !stats) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    cudaSetDevice(c->device);
+    DeviceStats d; int r = readStats(c, &d); if (r) return r;
+    std::memset(stats, 0, sizeof(*stats));
+    stats->raysPrimary = d.raysPrimary; stats->raysExtension = d.raysExtension; stats->raysOcclusion = d.raysOcclusion;
+    stats->nodesVisited = d.nodesVisited; stats->trianglesTested = d.trianglesTested;
+    return HRC_OK;
+}
+
+HRC_API int hrcTraceRays(HrcContext c, int32_t n, const HrcRay* rays, int32_t anyHit, HrcHit* hits) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (!c->committed) return fail(c, HRC_ERR_INVALID_OPERATION, "trace without a committed scene");
+    if (n < 0 || (n && (!rays || !hits))) return fail(c, HRC_ERR_INVALID_VALUE, "bad ray buffers");
+    if (n == 0) return HRC_OK;
+    cudaSetDevice(c->device);
+    HrcRay* dr = nullptr; HrcHit* dh = nullptr;
+    CU(c, cudaMalloc(&dr, (size_t)n * sizeof(HrcRay)));
+    cudaError_t e = cudaMalloc(&dh, (size_t)n * sizeof(HrcHit));
+    if (e != cudaSuccess) { cudaFree(dr); return failCuda(c, e, "cudaMalloc"); }
+    cudaMemcpyAsync(dr, rays, (size_t)n * sizeof(HrcRay), cudaMemcpyHostToDevice, c->stream);
+    launchTraceRays(sceneOf(c), dr, dh, n, anyHit != 0, configOf(c), c->stream);
+    cudaMemcpyAsync(hits, dh, (size_t)n * sizeof(HrcHit), cudaMemcpyDeviceToHost, c->stream);
+    e = cudaStreamSynchronize(c->stream);
+    cudaFree(dr); cudaFree(dh);
+    if (e != cudaSuccess) return failCuda(c, e, "hrcTraceRays");
+    return HRC_OK;
+}
+
+HRC_API int hrcGetSceneInfo(HrcContext c, HrcSceneInfo* info) {
+    if (!c || !info) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    *info = c->info; return HRC_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,978 @@
+// kernels.cu — the wavefront path-tracing kernels (sm_100a).
+//
+// What each kernel replaces in the reference (all of it ran inside the closed OpenRL library):
+//   k_raygen        frame shader          Resources/shaders/perspective.rlsl:39-93
+//   k_trace<false>  closest-hit traversal OpenRL internal (policy A-9 in SURVEY.md)
+//   k_trace<true>   occlusion traversal + the four light ("miss") shaders
+//                   environmentLight.rlsl:19-34, directionalLight.rlsl:20-26, pointLight.rlsl:20-29, spotLight.rlsl:20-36
+//   k_shade         material shaders      physicallyBased.rlsl:55-331, glass.rlsl:138-280 (+ microfacet.rlsl,
+//                   brdfs.rlsl, lightSampling.rlsl, utility.rlsl, sequence.rlsl, accumulator.rlsl)
+//
+// No tensor cores: this is pointer chasing + fp32 ALU, bound by the memory system.
+#include "device_types.h"
+
+#include <cfloat>
+#include <cstdio>
+
+namespace hr {
+namespace {
+
+// ---------------------------------------------------------------------------------------
+// float3 helpers
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+__device__ __forceinline__ float3 f3(float s) { return make_float3(s, s, s); }
+__device__ __forceinline__ float3 f3(const float* p) { return make_float3(p[0], p[1], p[2]); }
+__device__ __forceinline__ float3 xyz(float4 v) { return make_float3(v.x, v.y, v.z); }
+__device__ __forceinline__ float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ float3 operator-(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float3 operator/(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ float dot(float3 a, float3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ float3 cross(float3 a, float3 b) { return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ float3 normalize(float3 a) { return a * (1.0f / sqrtf(dot(a, a))); }
+__device__ __forceinline__ float length(float3 a) { return sqrtf(dot(a, a)); }
+struct M3 { float3 c0, c1, c2; };
+__device__ __forceinline__ float3 mul(const M3& m, float3 v) { return (m.c0 * v.x + m.c1 * v.y) + m.c2 * v.z; }
+__device__ __forceinline__ float3 mulT(const M3& m, float3 v) { return f3(dot(m.c0, v), dot(m.c1, v), dot(m.c2, v)); }
+
+// ---------------------------------------------------------------------------------------
+// utility.rlsl / brdfs.rlsl
+// ---------------------------------------------------------------------------------------
+#define K_PI 3.14159265359f
+#define K_TWO_PI (2.0f * K_PI)
+#define K_ONE_OVER_PI (1.0f / K_PI)
+
+__device__ __forceinline__ float saturate(float f) { return fminf(fmaxf(f, 0.0f), 1.0f); }     // utility.rlsl:20-23
+__device__ __forceinline__ float square(float x) { return x * x; }
+__device__ __forceinline__ float pow5(float x) { return x * square(x) * square(x); }            // :146-149
+__device__ __forceinline__ float greaterThanZero(float f) { return fmaxf(1e-5f, f); }           // :158-161
+__device__ __forceinline__ float luminosity(float3 c) { return dot(c, f3(0.33f, 0.59f, 0.11f)); } // :168-171
+
+__device__ __forceinline__ M3 orthonormalFrame(float3 N) {                                      // :45-61
+    float3 l = f3(N.x, N.z, N.y);
+    float s = l.z < 0.f ? -1.f : 1.f;
+    float a = -1.0f / (s + l.z);
+    float b = l.x * l.y * a;
+    float3 X = f3(1.0f + s * l.x * l.x * a, s * b, -s * l.x);
+    float3 Z = f3(b, s + l.y * l.y * a, -l.y);
+    M3 m; m.c0 = f3(X.x, X.z, X.y); m.c1 = N; m.c2 = f3(Z.x, Z.z, Z.y);
+    return m;
+}
+__device__ __forceinline__ float3 cosineWeightedSample(float u1, float u2) {                    // :65-76
+    float theta = sqrtf(u1);
+    float phi = K_TWO_PI * u2;
+    float sp, cp; sincosf(phi, &sp, &cp);
+    return normalize(f3(theta * cp, sqrtf(fmaxf(0.0f, 1.0f - u1)), theta * sp));
+}
+__device__ __forceinline__ float3 sampleVisibleGGX(float3 localV, float u1, float u2, float alpha) {   // :112-144
+    float3 zUpV = f3(localV.x, localV.z, localV.y);
+    float3 Vh = normalize(f3(zUpV.x * alpha, zUpV.y * alpha, zUpV.z));
+    float lengthSquared = (Vh.x * Vh.x) + (Vh.y * Vh.y);
+    float3 T1 = (lengthSquared > 0.0f) ? f3(-Vh.y, Vh.x, 0.0f) * (1.0f / sqrtf(lengthSquared)) : f3(1.0f, 0.0f, 0.0f);
+    float3 T2 = cross(Vh, T1);
+    float r = sqrtf(u1);
+    float phi = K_TWO_PI * u2;
+    float sp, cp; sincosf(phi, &sp, &cp);
+    float t1 = r * cp, t2 = r * sp;
+    float s = 0.5f * (1.0f + Vh.z);
+    float t1Squared = square(t1);
+    t2 = (1.0f - s) * sqrtf(1.0f - t1Squared) + (s * t2);
+    float3 Nh = (t1 * T1) + (t2 * T2) + sqrtf(fmaxf(0.0f, 1.0f - t1Squared - square(t2))) * Vh;
+    float3 zUp = normalize(f3(alpha * Nh.x, alpha * Nh.y, fmaxf(0.0f, Nh.z)));
+    return f3(zUp.x, zUp.z, zUp.y);
+}
+__device__ __forceinline__ float3 F_Schlick3(float3 Cspec, float cosTheta) { return Cspec + (f3(1.0f) - Cspec) * pow5(1.0f - cosTheta); }   // brdfs.rlsl:47-51
+__device__ __forceinline__ float F_Schlick1(float f0, float cosTheta) { return f0 + (1.0f - f0) * pow5(1.0f - cosTheta); }                  // :54-58
+__device__ __forceinline__ float F_Fresnel(float eta, float cosThetaI) {                                                                    // :60-72
+    float sinThetaT2 = square(eta) * (1.0f - square(cosThetaI));
+    if (sinThetaT2 < 1.0f) {
+        float cosThetaT = sqrtf(1.0f - sinThetaT2);
+        float perpendicular = square((eta * cosThetaI - cosThetaT) / (eta * cosThetaI + cosThetaT));
+        float parallel = square((cosThetaI - eta * cosThetaT) / (cosThetaI + eta * cosThetaT));
+        return 0.5f * (perpendicular + parallel);
+    }
+    return 1.0f;
+}
+__device__ __forceinline__ float D_GGX(float NdotH, float alpha) {                               // :74-79
+    float alpha2 = square(alpha);
+    float denominator = square(square(NdotH) * (alpha2 - 1.0f) + 1.0f);
+    return K_ONE_OVER_PI * (alpha2 / greaterThanZero(denominator));
+}
+__device__ __forceinline__ float G1_Smith_GGX(float NdotI, float alpha) {                        // :89-94
+    float alpha2 = square(alpha);
+    float denom = sqrtf(alpha2 + (1.0f - alpha2) * greaterThanZero(square(NdotI))) + NdotI;
+    return (2.0f * NdotI) / greaterThanZero(denom);
+}
+__device__ __forceinline__ float G2_Smith_GGX(float NdotO, float NdotI, float alpha) { return G1_Smith_GGX(NdotO, alpha) * G1_Smith_GGX(NdotI, alpha); }   // :96-99
+__device__ __forceinline__ float glslSmoothstep(float e0, float e1, float x) {                   // policy A-16
+    float t = saturate((x - e0) / (e1 - e0));
+    return t * t * (3.0f - 2.0f * t);
+}
+__device__ __forceinline__ float3 mix3(float3 a, float3 b, float t) { return a * (1.0f - t) + b * t; }
+
+// ---------------------------------------------------------------------------------------
+// Texture fetch: level-0 bilinear in fp32 over RGBA32F texels (policy A-12). Manual filtering keeps
+// full fp32 weights (the texture unit would use 9-bit fixed point) so the oracle can be matched.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ int wrapCoord(int i, int n, int mode) {
+    if (mode == HRC_WRAP_REPEAT) { i %= n; if (i < 0) i += n; return i; }
+    return min(max(i, 0), n - 1);
+}
+__device__ __forceinline__ float4 texFetch(const DTexture& t, float u, float v) {
+    float x = u * (float)t.w - 0.5f, y = v * (float)t.h - 0.5f;
+    float fx0 = floorf(x), fy0 = floorf(y);
+    float fx = x - fx0, fy = y - fy0;
+    int x0 = wrapCoord((int)fx0, t.w, t.wrapS), x1 = wrapCoord((int)fx0 + 1, t.w, t.wrapS);
+    int y0 = wrapCoord((int)fy0, t.h, t.wrapT), y1 = wrapCoord((int)fy0 + 1, t.h, t.wrapT);
+    float4 p00 = __ldg(&t.texels[(size_t)y0 * t.w + x0]);
+    float4 p10 = __ldg(&t.texels[(size_t)y0 * t.w + x1]);
+    float4 p01 = __ldg(&t.texels[(size_t)y1 * t.w + x0]);
+    float4 p11 = __ldg(&t.texels[(size_t)y1 * t.w + x1]);
+    float4 r;
+    r.x = (p00.x * (1.0f - fx) + p10.x * fx) * (1.0f - fy) + (p01.x * (1.0f - fx) + p11.x * fx) * fy;
+    r.y = (p00.y * (1.0f - fx) + p10.y * fx) * (1.0f - fy) + (p01.y * (1.0f - fx) + p11.y * fx) * fy;
+    r.z = (p00.z * (1.0f - fx) + p10.z * fx) * (1.0f - fy) + (p01.z * (1.0f - fx) + p11.z * fx) * fy;
+    r.w = (p00.w * (1.0f - fx) + p10.w * fx) * (1.0f - fy) + (p01.w * (1.0f - fx) + p11.w * fx) * fy;
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------
+// accumulator.rlsl:12-28. One thread owns a pixel inside any one kernel, so plain RMW is exclusive.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void performAccumulate(const HrcGlobals& g, float4* accum, uint32_t pixel, float3 color) {
+    float3 value = f3(0.0f);
+    if (g.enableAccumulatorVisualizer == 1) {
+        if (g.showNANs == 1) {
+            bool any = isnan(color.x) || isnan(color.y) || isnan(color.z);
+            value = any ? f3(100.0f) : f3(fminf(color.x, 1.0f), fminf(color.y, 1.0f), fminf(color.z, 1.0f)) * 0.1f;
+        } else if (g.showInf == 1) {
+            bool any = isinf(color.x) || isinf(color.y) || isinf(color.z);
+            value = any ? f3(100.0f) : f3(fminf(color.x, 1.0f), fminf(color.y, 1.0f), fminf(color.z, 1.0f)) * 0.1f;
+        }
+    } else {
+        value = f3(fminf(g.maxChannelValue, color.x), fminf(g.maxChannelValue, color.y), fminf(g.maxChannelValue, color.z));
+    }
+    float4 p = accum[pixel];
+    p.x += value.x; p.y += value.y; p.z += value.z;
+    accum[pixel] = p;
+}
+__device__ __forceinline__ void accumulate4(float4* accum, uint32_t pixel, float3 rgb, float a) {
+    float4 p = accum[pixel];
+    p.x += rgb.x; p.y += rgb.y; p.z += rgb.z; p.w += a;
+    accum[pixel] = p;
+}
+
+// sequence.rlsl:18-28
+__device__ __forceinline__ float2 getSequenceValue(const DScene& sc, const DFrame& fr, int sequenceIndex, int sampleIndex) {
+    int ws = sequenceIndex % fr.numSequences;
+    int wv = sampleIndex % fr.sequenceLength;
+    return __ldg(&sc.seq[ws * fr.sequenceLength + wv]);
+}
+
+// ---------------------------------------------------------------------------------------
+// Light ("miss") shaders
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void shadeMiss(const DScene& sc, const DFrame& fr, float4* accum, uint32_t pixel,
+                                          uint32_t missKind, uint32_t missIndex, float3 dir, float3 weight, float tmax, float extraT) {
+    const DLights& L = fr.lights;
+    switch (missKind) {
+    case kMissEnv: {                                                    // environmentLight.rlsl:19-34
+        if (!L.envEnabled) return;
+        float theta = atan2f(dir.x, -dir.z) + L.envTheta;
+        if (theta > K_TWO_PI) theta = theta - K_TWO_PI;
+        float phi = atan2f(dir.y, sqrtf(dir.x * dir.x + dir.z * dir.z));
+        float u = (theta / K_TWO_PI) + 0.5f;
+        float v = (-phi * K_ONE_OVER_PI) + 0.5f;
+        float3 sample = f3(0.0f);
+        if (L.envTex >= 0) sample = xyz(texFetch(sc.textures[L.envTex], u, 1.0f - v));
+        sample = sample * L.envExposure;
+        performAccumulate(fr.g, accum, pixel, weight * sample);
+        break; }
+    case kMissDir:                                                      // directionalLight.rlsl:20-26
+        performAccumulate(fr.g, accum, pixel, weight * f3(L.dirColor[missIndex]));
+        break;
+    case kMissPoint: {                                                  // pointLight.rlsl:20-29 (rl_IntersectionT = maxT, policy A-7)
+        float attenuation = 1.0f / square(tmax + extraT);
+        performAccumulate(fr.g, accum, pixel, weight * f3(L.pointColor[missIndex]) * attenuation);
+        break; }
+    case kMissSpot: {                                                   // spotLight.rlsl:20-36
+        float rayAngle = dot(-dir, f3(L.spotDirection[missIndex]));
+        if (rayAngle >= 0.0f) {
+            float attenuation = 1.0f / square(tmax + extraT);
+            float3 result = weight * f3(L.spotColor[missIndex]) * attenuation;
+            result = result * (1.0f - glslSmoothstep(L.spotAngles[missIndex][0], L.spotAngles[missIndex][1], rayAngle));
+            performAccumulate(fr.g, accum, pixel, result);
+        }
+        break; }
+    default: break;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Traversal of the 8-wide compressed BVH
+// ---------------------------------------------------------------------------------------
+struct HitRec { float t, u, v; int prim; bool back; };
+
+__device__ __forceinline__ uint32_t byteOf(uint32_t x, int i) { return (x >> (i * 8)) & 0xffu; }
+
+// Möller–Trumbore with a FIXED operation order and no FMA contraction: the CPU oracle performs the very
+// same IEEE operations, so hit/miss decisions and (t,u,v) agree bit for bit (policy A-9).
+__device__ __forceinline__ float dotRn(float ax, float ay, float az, float bx, float by, float bz) {
+    return __fadd_rn(__fadd_rn(__fmul_rn(ax, bx), __fmul_rn(ay, by)), __fmul_rn(az, bz));
+}
+__device__ __forceinline__ bool triangleTest(float4 a, float4 b, float4 c, float3 o, float3 d, float tmin, float tmax,
+                                             float& t, float& u, float& v, bool& back) {
+    // pv = cross(d, e2)
+    float pvx = __fsub_rn(__fmul_rn(d.y, c.z), __fmul_rn(d.z, c.y));
+    float pvy = __fsub_rn(__fmul_rn(d.z, c.x), __fmul_rn(d.x, c.z));
+    float pvz = __fsub_rn(__fmul_rn(d.x, c.y), __fmul_rn(d.y, c.x));
+    float det = dotRn(b.x, b.y, b.z, pvx, pvy, pvz);
+    if (det == 0.0f) return false;
+    float inv = __fdiv_rn(1.0f, det);
+    float tvx = __fsub_rn(o.x, a.x), tvy = __fsub_rn(o.y, a.y), tvz = __fsub_rn(o.z, a.z);
+    u = __fmul_rn(dotRn(tvx, tvy, tvz, pvx, pvy, pvz), inv);
+    if (!(u >= 0.0f && u <= 1.0f)) return false;
+    // qv = cross(tv, e1)
+    float qvx = __fsub_rn(__fmul_rn(tvy, b.z), __fmul_rn(tvz, b.y));
+    float qvy = __fsub_rn(__fmul_rn(tvz, b.x), __fmul_rn(tvx, b.z));
+    float qvz = __fsub_rn(__fmul_rn(tvx, b.y), __fmul_rn(tvy, b.x));
+    v = __fmul_rn(dotRn(d.x, d.y, d.z, qvx, qvy, qvz), inv);
+    if (!(v >= 0.0f && __fadd_rn(u, v) <= 1.0f)) return false;
+    t = __fmul_rn(dotRn(c.x, c.y, c.z, qvx, qvy, qvz), inv);
+    if (!(t > tmin && t < tmax)) return false;
+    back = det < 0.0f;
+    return true;
+}
+
+struct TraceCounters { uint32_t nodes, tris, overflow; };
+
+template <bool ANY, bool STATS>
+__device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const float4* __restrict__ tris,
+                                         float3 o, float3 d, float tmin, float tmaxRay, HitRec& best, TraceCounters& tc) {
+    // guard the slab arithmetic against zero direction components (box tests only)
+    const float tiny = 1e-20f;
+    float3 dd = f3(fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x,
+                   fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
+                   fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
+    const float3 idir = f3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
+    // slot bit set = positive side; a ray going positive must visit negative-side children first
+    const bool negX = dd.x < 0.0f, negY = dd.y < 0.0f, negZ = dd.z < 0.0f;
+    const uint32_t octInv = (negX ? 0u : 4u) | (negY ? 0u : 2u) | (negZ ? 0u : 1u);
+    const uint32_t octInv4 = octInv * 0x01010101u;
+
+    best.t = tmaxRay; best.prim = 0x7fffffff; best.u = 0.f; best.v = 0.f; best.back = false;
+    bool found = false;
+
+    uint2 stack[kTraceStack];
+    int sp = 0;
+    uint2 group = make_uint2(0u, 0x80000000u);     // root: "child 7 of a virtual parent whose childBase is 0"
+
+    while (true) {
+        uint2 triGroup;
+        if (group.y & 0xff000000u) {
+            const uint32_t hits = group.y;
+            const uint32_t bit = 31u - __clz(hits);                  // highest set bit = nearest remaining child
+            group.y &= ~(1u << bit);
+            if (group.y & 0xff000000u) {
+                if (sp < kTraceStack) stack[sp++] = group; else if (STATS) tc.overflow++;
+            }
+            const uint32_t slot = (bit - 24u) ^ (octInv & 7u);
+            const uint32_t rel = __popc(hits & ~(0xffffffffu << slot));   // internal children stored before this slot
+            const uint32_t nodeIdx = group.x + rel;
+
+            const float4* np = nodes + (size_t)nodeIdx * 5;
+            const float4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            if (STATS) tc.nodes++;
+
+            const uint32_t eimask = __float_as_uint(n0.w);
+            const float3 adjDir = f3(__uint_as_float(byteOf(eimask, 0) << 23) * idir.x,
+                                     __uint_as_float(byteOf(eimask, 1) << 23) * idir.y,
+                                     __uint_as_float(byteOf(eimask, 2) << 23) * idir.z);
+            const float3 adjOrg = f3((n0.x - o.x) * idir.x, (n0.y - o.y) * idir.y, (n0.z - o.z) * idir.z);
+            const float tfar = best.t;
+
+            uint32_t hitMask = 0;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const uint32_t meta4 = __float_as_uint(half == 0 ? n1.z : n1.w);
+                const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;       // 0xff in every byte whose slot holds an internal child
+                const uint32_t bitIndex4 = (meta4 ^ (octInv4 & innerMask4)) & 0x1f1f1f1fu;
+                const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t qlox = __float_as_uint(half == 0 ? n2.x : n2.y), qloy = __float_as_uint(half == 0 ? n2.z : n2.w);
+                const uint32_t qloz = __float_as_uint(half == 0 ? n3.x : n3.y), qhix = __float_as_uint(half == 0 ? n3.z : n3.w);
+                const uint32_t qhiy = __float_as_uint(half == 0 ? n4.x : n4.y), qhiz = __float_as_uint(half == 0 ? n4.z : n4.w);
+                const uint32_t nx = negX ? qhix : qlox, fx = negX ? qlox : qhix;
+                const uint32_t ny = negY ? qhiy : qloy, fy = negY ? qloy : qhiy;
+                const uint32_t nz = negZ ? qhiz : qloz, fz = negZ ? qloz : qhiz;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float tnx = fmaf((float)byteOf(nx, j), adjDir.x, adjOrg.x), tfx = fmaf((float)byteOf(fx, j), adjDir.x, adjOrg.x);
+                    const float tny = fmaf((float)byteOf(ny, j), adjDir.y, adjOrg.y), tfy = fmaf((float)byteOf(fy, j), adjDir.y, adjOrg.y);
+                    const float tnz = fmaf((float)byteOf(nz, j), adjDir.z, adjOrg.z), tfz = fmaf((float)byteOf(fz, j), adjDir.z, adjOrg.z);
+                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar));
+                    if (tn <= tf * 1.000001f) {                      // conservative: rounding must never cull an exact tie
+                        hitMask |= byteOf(childBits4, j) << byteOf(bitIndex4, j);
+                    }
+                }
+            }
+            group.x = __float_as_uint(n1.x);
+            group.y = (hitMask & 0xff000000u) | (eimask >> 24);
+            triGroup.x = __float_as_uint(n1.y);
+            triGroup.y = hitMask & 0x00ffffffu;
+        } else {
+            triGroup = group;
+            group = make_uint2(0u, 0u);
+        }
+
+        while (triGroup.y) {
+            const uint32_t ti = 31u - __clz(triGroup.y);
+            triGroup.y &= ~(1u << ti);
+            const float4* tp = tris + (size_t)(triGroup.x + ti) * 3;
+            const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            if (STATS) tc.tris++;
+            float t, u, v; bool back;
+            if (triangleTest(a, b, c, o, d, tmin, tmaxRay, t, u, v, back)) {
+                if (ANY) return true;
+                const int prim = __float_as_int(a.w);
+                if (t < best.t || (t == best.t && prim < best.prim)) {
+                    best.t = t; best.u = u; best.v = v; best.prim = prim; best.back = back; found = true;
+                }
+            }
+        }
+
+        if ((group.y & 0xff000000u) == 0u) {
+            if (sp == 0) break;
+            group = stack[--sp];
+        }
+    }
+    return found;
+}
+
+// ---------------------------------------------------------------------------------------
+// Kernels
+// ---------------------------------------------------------------------------------------
+__global__ void k_clear_ctrl(IterCtrl* ctrl) {
+    int i = threadIdx.x;
+    if (i < kMaxIterations) ctrl[i] = IterCtrl{0u, 0u, 0u, 0u};
+}
+
+// perspective.rlsl:39-93 — one thread per pixel of this context's screen bands.
+__global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_constant__ DFrame fr, RayQueue q, float4* accum, IterCtrl* ctrl, uint32_t total) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) ctrl[0].extCount = total;
+    if (i >= total) return;
+    const int W = fr.w, H = fr.h;
+    const int lr = i / W, x = i - lr * W;
+    int y = lr;
+    if (fr.bandCount > 1) { const int lb = lr / fr.bandHeight; y = (lb * fr.bandCount + fr.bandIndex) * fr.bandHeight + (lr - lb * fr.bandHeight); }
+    const uint32_t pixel = (uint32_t)y * W + x;
+    const float fx = (float)x + 0.5f, fy = (float)y + 0.5f;               // rl_FrameCoord (policy A-1)
+
+    float4 px = accum[pixel]; px.w += 1.0f; accum[pixel] = px;            // accumulate(vec4(0,0,0,1)), :60
+
+    const int sequenceID = sc.sequenceId[pixel];                           // :62 via the host table (quirk B-Q2)
+    const uint32_t oi = (uint32_t)(int)__fadd_rn(__fmul_rn(fy, (float)H), fx);   // :64 (quirk B-Q1)
+    const float rnd = __ldg(&sc.seqOffsetX[min(oi, fr.offsetCount - 1)]);
+    const int sequenceIndex = (int)floorf(rnd * fr.maxSampleIndex);       // :65
+    const float2 so = getSequenceValue(sc, fr, sequenceID, fr.g.sampleIndex + sequenceIndex);   // :67
+    const float spx = (fx - 0.5f) + so.x, spy = (fy - 0.5f) + so.y;       // :68
+    const float u = spx / (float)W, v = spy / (float)H;                   // :69
+    const float cx = (2.0f * u - 1.0f) * fr.aspectRatio * fr.fovTan;      // :72
+    const float cy = (1.0f - 2.0f * v) * fr.fovTan * -1.0f;               // :73
+    const float3 dirCam = normalize(f3(cx, cy, -1.0f));                   // :74
+    const float3 focal = fr.focusDistance * dirCam;                       // :77
+    const uint32_t tableSize = (uint32_t)fr.numSequences * (uint32_t)fr.sequenceLength;
+    const uint32_t ai = ((uint32_t)sequenceID * (uint32_t)fr.sequenceLength + (uint32_t)fr.g.sampleIndex) % tableSize;   // :78 (quirk B-Q3)
+    float2 ap = __ldg(&sc.aperture[ai]);
+    ap.x = ((ap.x * 2.0f) - 1.0f) * fr.apertureRadius;                    // :80
+    ap.y = ((ap.y * 2.0f) - 1.0f) * fr.apertureRadius;
+    const float3 org = f3(ap.x, ap.y, 0.0f);
+    const float3 dir = focal - org;
+    const float* M = fr.view;
+    const float3 wo = f3((M[0] * org.x + M[4] * org.y) + (M[8] * org.z + M[12]),
+                         (M[1] * org.x + M[5] * org.y) + (M[9] * org.z + M[13]),
+                         (M[2] * org.x + M[6] * org.y) + (M[10] * org.z + M[14]));   // :85
+    const float3 wd = normalize(f3((M[0] * dir.x + M[4] * dir.y) + M[8] * dir.z,
+                                   (M[1] * dir.x + M[5] * dir.y) + M[9] * dir.z,
+                                   (M[2] * dir.x + M[6] * dir.y) + M[10] * dir.z)); // :86 (normalised on emit, A-11)
+    q.o[i] = make_float4(wo.x, wo.y, wo.z, __int_as_float(0x7f800000));   // tmax = +inf
+    q.d[i] = make_float4(wd.x, wd.y, wd.z, 0.0f);                         // extraT = 0
+    q.w[i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
+    const uint32_t missKind = fr.lights.envEnabled ? kMissEnv : kMissNone;   // defaultPrimitive = env light, :87
+    q.m[i] = make_uint2(0u | (missKind << 8) | ((uint32_t)sequenceID << 16), (uint32_t)sequenceIndex);
+}
+
+// Persistent traversal kernel: warps pull batches of 32 rays from the queue with one atomic per warp.
+template <bool ANY, bool STATS>
+__global__ void __launch_bounds__(128) k_trace(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
+    const uint32_t lane = threadIdx.x & 31u;
+    IterCtrl* ctrl = pb.ctrl + iter;
+    const uint32_t count = ANY ? ctrl->shadowCount : ctrl->extCount;
+    uint32_t* head = ANY ? &ctrl->shadowHead : &ctrl->extHead;
+    const RayQueue& rq = pb.ext[iter & 1];
+    TraceCounters tc{0u, 0u, 0u};
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(head, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= count) break;
+        const uint32_t i = base + lane;
+        if (i < count) {
+            const float4 ro = ANY ? pb.shadow.o[i] : rq.o[i];
+            const float4 rd = ANY ? pb.shadow.d[i] : rq.d[i];
+            HitRec h;
+            const bool hit = traverse<ANY, STATS>(sc.nodes, sc.tris, xyz(ro), xyz(rd), 0.0f, ro.w, h, tc);
+            if (ANY) {
+                if (!hit) {   // the ray reached its light: run the light shader (policy A-5/A-6)
+                    const float4 w = pb.shadow.w[i];
+                    const uint32_t bits = __float_as_uint(w.w);
+                    shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, xyz(rd), xyz(w), ro.w, rd.w);
+                }
+            } else {
+                pb.hits[i] = hit ? make_float4(h.t, h.u, h.v, __int_as_float(h.prim | (h.back ? HRC_HIT_BACKFACE : 0)))
+                                 : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+            }
+        }
+    }
+    if (STATS) {
+        uint32_t n = tc.nodes, t = tc.tris, ov = tc.overflow;
+        for (int s = 16; s > 0; s >>= 1) { n += __shfl_xor_sync(0xffffffffu, n, s); t += __shfl_xor_sync(0xffffffffu, t, s); ov += __shfl_xor_sync(0xffffffffu, ov, s); }
+        if (lane == 0) {
+            atomicAdd(&pb.stats->nodesVisited, (unsigned long long)n);
+            atomicAdd(&pb.stats->trianglesTested, (unsigned long long)t);
+            if (ov) atomicAdd(&pb.stats->stackOverflows, (unsigned long long)ov);
+        }
+    }
+}
+
+// ---- material shading ------------------------------------------------------------------
+struct Surface { float3 P, Ng; float T; };
+struct InRay { float3 o, d, weight; float tmax; uint32_t depth, sequenceID, pixel; int sequenceIndexOffset; };
+struct Emit {
+    bool hasOcc, hasExt;
+    float3 occO, occD, occW; float occTmax; uint32_t occMissKind, occMissIndex;
+    float3 extO, extD, extW; uint32_t extMissKind;
+};
+
+__device__ __forceinline__ float3 offsetOrigin(const Surface& s, float3 dir) {          // ray epsilon policy A-8
+    float m = fmaxf(1.0f, fmaxf(fabsf(s.P.x), fmaxf(fabsf(s.P.y), fabsf(s.P.z))));
+    float eps = 1e-4f * m;
+    float sgn = dot(s.Ng, dir) >= 0.0f ? 1.0f : -1.0f;
+    return s.P + s.Ng * (sgn * eps);
+}
+__device__ __forceinline__ void emitOcc(Emit& e, const Surface& s, float3 dir, float3 w, uint32_t kind, uint32_t idx, float tmax) {
+    e.hasOcc = true; e.occO = offsetOrigin(s, dir); e.occD = dir; e.occW = w; e.occTmax = tmax; e.occMissKind = kind; e.occMissIndex = idx;
+}
+__device__ __forceinline__ void emitExt(Emit& e, const Surface& s, float3 dir, float3 w, uint32_t kind) {
+    e.hasExt = true; e.extO = offsetOrigin(s, dir); e.extD = dir; e.extW = w; e.extMissKind = kind;
+}
+
+struct LightSample { float3 dir; uint32_t missKind, missIndex; float probability, maxDistance; int lightType; };
+#define LIGHT_TYPE_DIRECTIONAL 1
+#define LIGHT_TYPE_POINT 2
+#define LIGHT_TYPE_SPOT 3
+#define LIGHT_TYPE_ENVIRONMENT 4
+
+// lightSampling.rlsl:11-161
+__device__ void computeLightSample(const DLights& L, float3 P, float3 N, float lightProbability, LightSample& ls) {
+    const int MAXL = HRC_MAX_LIGHTS_PER_TYPE;
+    float probabilitySum = 0.0f;
+    float directional[MAXL], point[MAXL], spot[MAXL];
+    float3 pointDir[MAXL], spotDir[MAXL];
+#pragma unroll
+    for (int i = 0; i < MAXL; ++i) {
+        directional[i] = 0.f; point[i] = 0.f; spot[i] = 0.f;
+        if (i < L.nDir) {
+            directional[i] = saturate(dot(N, f3(L.dirDirection[i]))) * luminosity(f3(L.dirColor[i]));
+            probabilitySum += directional[i];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < MAXL; ++i) if (i < L.nPoint) {
+        pointDir[i] = normalize(f3(L.pointPosition[i]) - P);
+        point[i] = saturate(dot(N, pointDir[i])) * luminosity(f3(L.pointColor[i]));
+        probabilitySum += point[i];
+    }
+#pragma unroll
+    for (int i = 0; i < MAXL; ++i) if (i < L.nSpot) {
+        spotDir[i] = normalize(f3(L.spotPosition[i]) - P);
+        float rayAngle = dot(f3(L.spotDirection[i]), -spotDir[i]);
+        spot[i] = saturate(dot(N, spotDir[i])) * luminosity(f3(L.spotColor[i])) *
+                  ((rayAngle > 0.0f) ? 1.0f : 0.0f) *
+                  ((rayAngle < L.spotAngles[i][1]) ? 0.0f : 1.0f) *
+                  (1.0f - glslSmoothstep(L.spotAngles[i][0], L.spotAngles[i][1], rayAngle));
+        probabilitySum += spot[i];
+    }
+    float environment = 0.0f;
+    if (L.envEnabled) { environment = 50.0f * L.envExposure; probabilitySum += environment; }   // :77
+    const float norm = 1.0f / greaterThanZero(probabilitySum);
+    environment *= norm;
+#pragma unroll
+    for (int i = 0; i < MAXL; ++i) { directional[i] *= norm; point[i] *= norm; spot[i] *= norm; }
+
+    float current = 0.0f;
+#pragma unroll
+    for (int i = 0; i < MAXL; ++i) if (i < L.nDir) {
+        current += directional[i];
+        if (directional[i] > 0.0f && lightProbability <= current) {
+            ls.dir = f3(L.dirDirection[i]); ls.missKind = kMissDir; ls.missIndex = i; ls.probability = directional[i];
+            ls.lightType = LIGHT_TYPE_DIRECTIONAL; return;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < MAXL; ++i) if (i < L.nPoint) {
+        current += point[i];
+        if (point[i] > 0.0f && lightProbability <= current) {
+            ls.dir = pointDir[i]; ls.missKind = kMissPoint; ls.missIndex = i; ls.probability = point[i];
+            ls.maxDistance = length(f3(L.pointPosition[i]) - P); ls.lightType = LIGHT_TYPE_POINT; return;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < MAXL; ++i) if (i < L.nSpot) {
+        current += spot[i];
+        if (spot[i] > 0.0f && lightProbability <= current) {
+            ls.dir = spotDir[i]; ls.missKind = kMissSpot; ls.missIndex = i; ls.probability = spot[i];
+            ls.maxDistance = length(f3(L.spotPosition[i]) - P); ls.lightType = LIGHT_TYPE_SPOT; return;
+        }
+    }
+    ls.lightType = LIGHT_TYPE_ENVIRONMENT;
+    ls.probability = environment;
+}
+
+__device__ __forceinline__ float3 computeMultiscattering(const DScene& sc, int lut, float3 Cspec, float NdotI, float roughness) {   // microfacet.rlsl:17-23
+    float ms = 0.0f;
+    if (lut >= 0) ms = texFetch(sc.textures[lut], NdotI, roughness).x;
+    return f3(1.0f) + Cspec * ms;
+}
+
+// microfacet.rlsl:25-51
+__device__ void indirectDiffuseSample(const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 Cdiff,
+                                      float sampleProbability, float optLightProb, float2 rnd, const M3& frame, bool missEnv) {
+    float3 O = mul(frame, cosineWeightedSample(rnd.x, rnd.y));
+    float NdotO = dot(N, O);
+    if (NdotO > 0.0f) {
+        float3 reflectance = Cdiff * inWeight;
+        reflectance = reflectance / sampleProbability;
+        reflectance = reflectance / optLightProb;
+        if (dot(reflectance, reflectance) > 1e-5f) {
+            if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, __int_as_float(0x7f800000)); }
+            else emitExt(e, s, O, reflectance, kMissNone);
+        }
+    }
+}
+// microfacet.rlsl:53-98
+__device__ void directDiffuseSample(const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 Cdiff,
+                                    float sampleProbability, float lightProbability, float2 rnd, const M3& frame) {
+    LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
+    computeLightSample(fr.lights, s.P, N, lightProbability, ls);
+    if (ls.lightType != LIGHT_TYPE_ENVIRONMENT && lightProbability > 0.0f) {
+        float NdotO = dot(N, ls.dir);
+        if (NdotO > 0.0f) {
+            NdotO = saturate(NdotO);
+            float3 reflectance = ((Cdiff / K_PI) * NdotO) * inWeight;
+            reflectance = reflectance / sampleProbability;
+            reflectance = reflectance / ls.probability;
+            if (dot(reflectance, reflectance) > 1e-5f) {
+                float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : __int_as_float(0x7f800000);
+                emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
+            }
+        }
+    } else if (ls.probability > 0.0f) {
+        indirectDiffuseSample(fr, e, s, inWeight, N, Cdiff, sampleProbability, ls.probability, rnd, frame, true);
+    }
+}
+// microfacet.rlsl:100-153
+__device__ void indirectSpecularSample(const DScene& sc, const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 I, float NdotI,
+                                       float3 Cspec, float alpha, int lut, float roughness, float sampleProbability, float optLightProb,
+                                       float2 rnd, const M3& frame, bool missEnv) {
+    float3 H = mul(frame, sampleVisibleGGX(mulT(frame, I), rnd.x, rnd.y, alpha));
+    float IdotH = saturate(dot(I, H));
+    float3 O = normalize(2.0f * IdotH * H - I);
+    float NdotO = dot(N, O);
+    if (NdotO > 0.0f) {
+        NdotO = saturate(NdotO);
+        float3 F = F_Schlick3(Cspec, IdotH);
+        float G2 = G2_Smith_GGX(NdotI, NdotO, alpha);
+        float G1 = G1_Smith_GGX(NdotI, alpha);
+        float3 specular = (F * G2) / greaterThanZero(G1);
+        specular = specular * computeMultiscattering(sc, lut, Cspec, NdotI, roughness);
+        float3 reflectance = specular * inWeight;
+        reflectance = reflectance / sampleProbability;
+        reflectance = reflectance / optLightProb;
+        if (dot(reflectance, reflectance) > 1e-5f) {
+            if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, __int_as_float(0x7f800000)); }
+            else emitExt(e, s, O, reflectance, kMissNone);
+        }
+    }
+}
+// microfacet.rlsl:155-220
+__device__ void directSpecularSample(const DScene& sc, const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 I, float NdotI,
+                                     float3 Cspec, float alpha, int lut, float roughness, float sampleProbability, float lightProbability,
+                                     float2 rnd, const M3& frame) {
+    LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
+    computeLightSample(fr.lights, s.P, N, lightProbability, ls);
+    if (ls.lightType != LIGHT_TYPE_ENVIRONMENT && lightProbability > 0.0f) {
+        float NdotO = dot(N, ls.dir);
+        if (NdotO > 0.0f) {
+            NdotO = saturate(NdotO);
+            float3 H = normalize(I + ls.dir);
+            float NdotH = saturate(dot(N, H));
+            float IdotH = saturate(dot(I, H));
+            float D = D_GGX(NdotH, alpha);
+            float3 F = F_Schlick3(Cspec, IdotH);
+            float G = G2_Smith_GGX(NdotO, NdotI, alpha);
+            float3 specular = (D * F * G) / greaterThanZero(4.0f * NdotI);
+            specular = specular * computeMultiscattering(sc, lut, Cspec, NdotI, roughness);
+            float3 reflectance = specular * inWeight;
+            reflectance = reflectance / sampleProbability;
+            reflectance = reflectance / ls.probability;
+            if (dot(reflectance, reflectance) > 1e-5f) {
+                float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : __int_as_float(0x7f800000);
+                emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
+            }
+        }
+    } else if (ls.probability > 0.0f) {
+        indirectSpecularSample(sc, fr, e, s, inWeight, N, I, NdotI, Cspec, alpha, lut, roughness, sampleProbability, ls.probability, rnd, frame, true);
+    }
+}
+
+// physicallyBased.rlsl:55-331. Returns true when the ray is re-emitted unchanged (single-sided back face).
+__device__ void shadePBR(const DScene& sc, const DFrame& fr, float4* accum, const InRay& in, const DMaterial& m, const Surface& s,
+                         float3 interpNormal, bool frontFacing, Emit& e) {
+    const HrcGlobals& g = fr.g;
+    const uint32_t flags = m.typeFlags >> 4;
+    float3 baseColor = f3(m.baseColor);
+    float3 N = normalize(interpNormal);
+    if (flags & HRC_MAT_DOUBLE_SIDED) { if (!frontFacing) N = -N; }          // :96-100
+    else if (!frontFacing) {                                                  // :102-107 pass-through re-emit
+        e.hasExt = true; e.extO = offsetOrigin(s, in.d); e.extD = in.d; e.extW = in.weight; e.extMissKind = 0xffu;   // 0xff: keep the incoming miss shader
+        return;
+    }
+    const float3 clearCoatN = N;
+    const M3 frame = orthonormalFrame(N);
+    const float3 V = -in.d;
+    const float NdotV = saturate(dot(N, V));
+    const float3 emissive = f3(m.emissive);
+
+    if (g.enableDebugVisualizer == 1) {                                       // :159-203
+        if (g.showGeometricNormals == 1) accumulate4(accum, in.pixel, (interpNormal + f3(1.0f)) * 0.5f, 1.0f);
+        else if (g.showFinalNormals == 1) accumulate4(accum, in.pixel, (N + f3(1.0f)) * 0.5f, 1.0f);
+        else if (g.showBaseColor == 1) accumulate4(accum, in.pixel, baseColor, 1.0f);
+        else if (g.showEmissive == 1) accumulate4(accum, in.pixel, emissive, 1.0f);
+        else if (g.showRoughness == 1) accumulate4(accum, in.pixel, f3(m.roughness), 1.0f);
+        else if (g.showMetallic == 1) accumulate4(accum, in.pixel, f3(m.metallic), 1.0f);
+        else if (g.showClearcoat == 1) accumulate4(accum, in.pixel, f3(m.clearCoat), 1.0f);
+        else if (g.showClearcoatRoughness == 1) accumulate4(accum, in.pixel, f3(m.clearCoatRoughness), 1.0f);
+        else if (g.showShader == 1) accumulate4(accum, in.pixel, f3(1.0f, 0.0f, 0.0f), 1.0f);
+        return;
+    }
+
+    float3 weight = in.weight;
+    performAccumulate(g, accum, in.pixel, weight * emissive);                // :205
+    const float clearCoatNdotV = saturate(dot(clearCoatN, V));
+    const float clearCoatScale = F_Schlick1(0.04f, clearCoatNdotV) * m.clearCoat;
+    const float bottom = 1.0f - clearCoatScale;
+    const float3 Cdiff = (baseColor * (1.0f - m.metallic)) * bottom;         // :214
+    const float3 Cspec = mix3(f3(m.specularF0), baseColor, m.metallic) * bottom;   // :220
+    const float diffuseLuminance = luminosity(Cdiff), specularLuminance = luminosity(Cspec);
+    const float pn = 1.0f / greaterThanZero(diffuseLuminance + specularLuminance + clearCoatScale);
+    const float diffuseProbability = diffuseLuminance * pn, specularProbability = specularLuminance * pn, clearCoatProbability = clearCoatScale * pn;
+    const int sidx = g.sampleIndex + in.sequenceIndexOffset;
+    const int sq = (int)in.sequenceID + (int)in.depth;
+
+    {   // direct lighting, :236-274
+        const float2 rnd = getSequenceValue(sc, fr, sq, sidx);
+        const float2 pr = getSequenceValue(sc, fr, sq + 1, sidx);
+        if (pr.x <= diffuseProbability)
+            directDiffuseSample(fr, e, s, weight, N, Cdiff, diffuseProbability, pr.y, rnd, frame);
+        else if (pr.x <= (diffuseProbability + clearCoatProbability))
+            directSpecularSample(sc, fr, e, s, weight, clearCoatN, V, clearCoatNdotV, f3(clearCoatScale), m.clearCoatRoughnessAlpha, m.lutTex,
+                                 m.clearCoatRoughness, clearCoatProbability, pr.y, rnd, frame);
+        else if (pr.x <= (diffuseProbability + clearCoatProbability + specularProbability))
+            directSpecularSample(sc, fr, e, s, weight, N, V, NdotV, Cspec, m.roughnessAlpha, m.lutTex, m.roughness, specularProbability, pr.y, rnd, frame);
+    }
+    if ((int)in.depth < g.maxRayDepth) {                                      // :277-329
+        if (in.depth > 3) {
+            const float2 rr = getSequenceValue(sc, fr, sq + 2, sidx);
+            const float probability = fmaxf(weight.x, fmaxf(weight.y, weight.z));
+            if (rr.x >= probability) return;
+            weight = weight / probability;
+        }
+        const float2 rnd = getSequenceValue(sc, fr, sq + 3, sidx);
+        const float2 pr = getSequenceValue(sc, fr, sq + 4, sidx);
+        if (pr.x <= diffuseProbability)
+            indirectDiffuseSample(fr, e, s, weight, N, Cdiff, diffuseProbability, 1.0f, rnd, frame, false);
+        else if (pr.x <= (diffuseProbability + clearCoatProbability))
+            indirectSpecularSample(sc, fr, e, s, weight, clearCoatN, V, clearCoatNdotV, f3(clearCoatScale), m.clearCoatRoughnessAlpha, m.lutTex,
+                                   m.clearCoatRoughness, clearCoatProbability, 1.0f, rnd, frame, false);
+        else if (pr.x <= (diffuseProbability + clearCoatProbability + specularProbability))
+            indirectSpecularSample(sc, fr, e, s, weight, N, V, NdotV, Cspec, m.roughnessAlpha, m.lutTex, m.roughness, specularProbability, 1.0f, rnd, frame, false);
+    }
+}
+
+// glass.rlsl:47-78
+__device__ void indirectSpecularGlassSample(const DFrame& fr, Emit& e, const Surface& s, float3 N, float3 I, float NdotI, float3 weight, float3 baseColor,
+                                            float alpha, float matAlpha, float optLightProb, float2 rnd, const M3& frame, bool missEnv) {
+    float3 H = mul(frame, sampleVisibleGGX(mulT(frame, I), rnd.x, rnd.y, alpha));
+    float IdotH = saturate(dot(I, H));
+    float3 O = normalize(2.0f * IdotH * H - I);
+    float NdotO = dot(N, O);
+    if (NdotO > 0.0f) {
+        NdotO = saturate(NdotO);
+        float NdotH = saturate(dot(N, H));
+        float G = G2_Smith_GGX(NdotO, NdotI, matAlpha);                      // Material.roughnessAlpha (quirk B-Q20)
+        float3 reflectance = baseColor * ((G * IdotH) / (NdotH * NdotI));
+        reflectance = reflectance * weight;
+        reflectance = reflectance / optLightProb;
+        if (dot(reflectance, reflectance) > 1e-5f) {
+            if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, __int_as_float(0x7f800000)); }
+            else emitExt(e, s, O, reflectance, kMissNone);
+        }
+    }
+}
+// glass.rlsl:80-129
+__device__ void directSpecularGlassSample(const DFrame& fr, Emit& e, const Surface& s, float3 N, float3 I, float NdotI, float3 weight, float3 baseColor,
+                                          float alpha, float matAlpha, float lightProbability, float2 rnd, const M3& frame) {
+    LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
+    computeLightSample(fr.lights, s.P, N, lightProbability, ls);
+    if (ls.lightType != LIGHT_TYPE_ENVIRONMENT) {
+        float NdotO = dot(N, ls.dir);
+        if (NdotO > 0.0f) {
+            NdotO = saturate(NdotO);
+            float3 H = normalize(I + ls.dir);
+            float NdotH = saturate(dot(N, H));
+            float D = D_GGX(NdotH, alpha);
+            float G = G2_Smith_GGX(NdotO, NdotI, alpha);
+            float specular = (D * G) / greaterThanZero(4.0f * NdotI);
+            float3 reflectance = specular * baseColor;
+            reflectance = reflectance * weight;
+            reflectance = reflectance / ls.probability;
+            if (dot(reflectance, reflectance) > 1e-5f) {
+                float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : __int_as_float(0x7f800000);
+                emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
+            }
+        }
+    } else if (ls.probability > 0.0f) {
+        indirectSpecularGlassSample(fr, e, s, N, I, NdotI, weight, baseColor, alpha, matAlpha, ls.probability, rnd, frame, true);
+    }
+}
+// glass.rlsl:138-280
+__device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, const InRay& in, const DMaterial& m, const Surface& s,
+                           float3 interpNormal, bool frontFacing, Emit& e) {
+    const HrcGlobals& g = fr.g;
+    float3 N = normalize(interpNormal);
+    float nIn = 1.0f, nOut = m.ior;
+    float3 weight = in.weight;
+    const float3 baseColor = f3(m.baseColor);
+    if (!frontFacing) {                                                       // :161-167
+        N = -N; nIn = m.ior; nOut = 1.0f;
+        const float3 absorption = f3(1.0f) - baseColor;                       // beersLaw :131-136
+        const float k = m.density * -s.T;
+        weight = in.weight * f3(expf(absorption.x * k), expf(absorption.y * k), expf(absorption.z * k));
+    }
+    const float roughness = m.roughness, roughnessAlpha = m.roughnessAlpha;
+    if (g.enableDebugVisualizer == 1) {                                       // :179-211
+        if (g.showGeometricNormals == 1) accumulate4(accum, in.pixel, (interpNormal + f3(1.0f)) * 0.5f, 1.0f);
+        else if (g.showFinalNormals == 1) accumulate4(accum, in.pixel, (N + f3(1.0f)) * 0.5f, 1.0f);
+        else if (g.showBaseColor == 1) accumulate4(accum, in.pixel, baseColor, 1.0f);
+        else if (g.showRoughness == 1) accumulate4(accum, in.pixel, f3(roughness), 1.0f);
+        else if (g.showShader == 1) accumulate4(accum, in.pixel, f3(0.0f, 1.0f, 0.0f), 1.0f);
+        return;
+    }
+    const M3 frame = orthonormalFrame(N);
+    const float3 I = -in.d;
+    const float eta = nIn / nOut;
+    const int sidx = g.sampleIndex + in.sequenceIndexOffset;
+    const int sq = (int)in.sequenceID + (int)in.depth;
+    float2 rnd = getSequenceValue(sc, fr, sq, sidx);
+    const float3 H = mul(frame, sampleVisibleGGX(mulT(frame, I), rnd.x, rnd.y, roughnessAlpha));
+    const float HdotI = saturate(dot(H, I));
+    float2 rp = getSequenceValue(sc, fr, sq + 1, sidx);
+    const float F = F_Fresnel(eta, HdotI);
+    const float NdotI = saturate(dot(N, I));
+    if (!frontFacing) rp.y = 0.0f;                                            // :227-231
+    if (rp.y < (1.0f - F)) {                                                  // :234-256 refraction
+        const float3 mI = -I;
+        const float dNI = dot(H, mI);
+        const float k = 1.0f - eta * eta * (1.0f - dNI * dNI);
+        if (k < 0.0f) return;                                                 // refract() == 0 (policy A-16)
+        const float3 R = eta * mI - (eta * dNI + sqrtf(k)) * H;
+        if (dot(R, R) == 0.0f) return;
+        const float3 O = normalize(R);
+        const float NdotO = fabsf(dot(N, O));
+        const float G2 = G2_Smith_GGX(NdotI, NdotO, roughnessAlpha);
+        const float G1 = G1_Smith_GGX(NdotI, roughnessAlpha);
+        float3 transmission = baseColor * G2 / greaterThanZero(G1);
+        transmission = transmission * weight;
+        if (dot(transmission, transmission) > 1e-5f && (int)in.depth < g.maxRayDepth)
+            emitExt(e, s, O, transmission, fr.lights.envEnabled ? kMissEnv : kMissNone);
+    } else {                                                                  // :257-279 reflection
+        rnd = getSequenceValue(sc, fr, sq + 2, sidx);
+        directSpecularGlassSample(fr, e, s, N, I, NdotI, weight, baseColor, roughnessAlpha, m.roughnessAlpha, rp.x, rnd, frame);
+        if ((int)in.depth < g.maxRayDepth) {
+            if (in.depth > 3) {
+                const float2 rr = getSequenceValue(sc, fr, sq + 3, sidx);
+                const float probability = fmaxf(weight.x, fmaxf(weight.y, weight.z));
+                if (rr.x >= probability) return;
+                weight = weight / probability;
+            }
+            rnd = getSequenceValue(sc, fr, sq + 4, sidx);
+            indirectSpecularGlassSample(fr, e, s, N, I, NdotI, weight, baseColor, roughnessAlpha, m.roughnessAlpha, 1.0f, rnd, frame, false);
+        }
+    }
+}
+
+// One thread per ray of iteration `iter`: miss shader or material shader, then warp-aggregated appends of the
+// (<= 1) occlusion ray and (<= 1) extension ray into the next queues — this is the compaction of live rays.
+__global__ void __launch_bounds__(128) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warpsTotal = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    IterCtrl* ctrl = pb.ctrl + iter;
+    const uint32_t count = ctrl->extCount;
+    const RayQueue& rq = pb.ext[iter & 1];
+    const RayQueue& nq = pb.ext[(iter + 1) & 1];
+    const int hardCap = fr.g.maxRayDepth + 16;                                // policy A-14
+    const bool lastIter = (iter + 1 >= kMaxIterations);
+
+    for (uint32_t base = warpId * 32u; base < count; base += warpsTotal * 32u) {
+        const uint32_t i = base + lane;
+        Emit e; e.hasOcc = false; e.hasExt = false;
+        InRay in; in.depth = 0; in.pixel = 0; in.sequenceID = 0; in.sequenceIndexOffset = 0;
+        uint32_t inMissKind = 0;
+        if (i < count) {
+            const float4 ro = rq.o[i], rd = rq.d[i], rw = rq.w[i];
+            const uint2 rm = rq.m[i];
+            const float4 hr = pb.hits[i];
+            in.o = xyz(ro); in.d = xyz(rd); in.weight = xyz(rw); in.tmax = ro.w;
+            in.pixel = __float_as_uint(rw.w);
+            in.depth = rm.x & 0xffu; inMissKind = (rm.x >> 8) & 0xfu; in.sequenceID = rm.x >> 16; in.sequenceIndexOffset = (int)rm.y;
+            const int primBits = __float_as_int(hr.w);
+            if (primBits < 0) {
+                shadeMiss(sc, fr, pb.accum, in.pixel, inMissKind, 0u, in.d, in.weight, in.tmax, rd.w);
+            } else {
+                const int prim = primBits & 0x3fffffff;
+                const bool back = (primBits & HRC_HIT_BACKFACE) != 0;
+                const float4* sp = sc.shade + (size_t)prim * 4;
+                const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2), s3 = __ldg(sp + 3);
+                Surface s;
+                s.P = in.o + in.d * hr.x;
+                s.Ng = xyz(s3);
+                s.T = hr.x;
+                const bool frontFacing = __float_as_int(s1.w) ? back : !back;   // policy A-10
+                const float bw = (1.0f - hr.y) - hr.z;
+                const float3 n = (xyz(s0) * bw + xyz(s1) * hr.y) + xyz(s2) * hr.z;
+                const DMaterial m = sc.materials[__float_as_int(s0.w)];
+                if ((m.typeFlags & 0xfu) == HRC_MATERIAL_PBR) shadePBR(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
+                else                                          shadeGlass(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
+                if (e.hasExt && ((int)in.depth + 1 > hardCap || lastIter)) e.hasExt = false;
+            }
+        }
+        // ---- compaction: one atomic per warp per queue ------------------------------------
+        const uint32_t occMask = __ballot_sync(0xffffffffu, e.hasOcc);
+        const uint32_t extMask = __ballot_sync(0xffffffffu, e.hasExt);
+        uint32_t occBase = 0, extBase = 0;
+        if (lane == 0) {
+            if (occMask) occBase = atomicAdd(&ctrl->shadowCount, (uint32_t)__popc(occMask));
+            if (extMask) extBase = atomicAdd(&ctrl[1].extCount, (uint32_t)__popc(extMask));
+        }
+        occBase = __shfl_sync(0xffffffffu, occBase, 0);
+        extBase = __shfl_sync(0xffffffffu, extBase, 0);
+        const uint32_t below = (1u << lane) - 1u;
+        if (e.hasOcc) {
+            const uint32_t k = occBase + __popc(occMask & below);
+            pb.shadow.o[k] = make_float4(e.occO.x, e.occO.y, e.occO.z, e.occTmax);
+            pb.shadow.d[k] = make_float4(e.occD.x, e.occD.y, e.occD.z, 0.0f);
+            pb.shadow.w[k] = make_float4(e.occW.x, e.occW.y, e.occW.z, __uint_as_float(in.pixel | (e.occMissKind << 24) | (e.occMissIndex << 27)));
+        }
+        if (e.hasExt) {
+            const uint32_t k = extBase + __popc(extMask & below);
+            const uint32_t mk = e.extMissKind == 0xffu ? inMissKind : e.extMissKind;
+            nq.o[k] = make_float4(e.extO.x, e.extO.y, e.extO.z, __int_as_float(0x7f800000));
+            nq.d[k] = make_float4(e.extD.x, e.extD.y, e.extD.z, 0.0f);
+            nq.w[k] = make_float4(e.extW.x, e.extW.y, e.extW.z, __uint_as_float(in.pixel));
+            nq.m[k] = make_uint2((in.depth + 1u) | (mk << 8) | (in.sequenceID << 16), (uint32_t)in.sequenceIndexOffset);
+        }
+    }
+}
+
+__global__ void k_finish_pass(PassBuffers pb, int iterations) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long ext = 0, occ = 0;
+    for (int i = 1; i < iterations; ++i) ext += pb.ctrl[i].extCount;
+    for (int i = 0; i < iterations; ++i) occ += pb.ctrl[i].shadowCount;
+    pb.stats->raysPrimary += pb.ctrl[0].extCount;
+    pb.stats->raysExtension += ext;
+    pb.stats->raysOcclusion += occ;
+}
+
+// hrcTraceRays: the fixed-ray-set parity hook. Same traversal code as the pass kernels.
+template <bool ANY>
+__global__ void __launch_bounds__(128) k_trace_rays(const DScene sc, const HrcRay* __restrict__ rays, HrcHit* __restrict__ hits, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const HrcRay r = rays[i];
+    HitRec h; TraceCounters tc{0u, 0u, 0u};
+    const bool hit = traverse<ANY, false>(sc.nodes, sc.tris, f3(r.origin[0], r.origin[1], r.origin[2]), f3(r.direction[0], r.direction[1], r.direction[2]),
+                                          r.tmin, r.tmax, h, tc);
+    HrcHit out;
+    if (ANY) { out.t = 0.f; out.u = 0.f; out.v = 0.f; out.primId = hit ? 0 : -1; }
+    else if (hit) { out.t = h.t; out.u = h.u; out.v = h.v; out.primId = h.prim | (h.back ? HRC_HIT_BACKFACE : 0); }
+    else { out.t = 0.f; out.u = 0.f; out.v = 0.f; out.primId = -1; }
+    hits[i] = out;
+}
+
+__global__ void k_add_pixels(float4* accum, const float4* src, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { float4 a = accum[i], b = src[i]; a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; accum[i] = a; }
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------
+// Launch wrappers
+// ---------------------------------------------------------------------------------------
+void launchClearCtrl(const PassBuffers& pb, cudaStream_t s) { k_clear_ctrl<<<1, kMaxIterations, 0, s>>>(pb.ctrl); }
+
+void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s) {
+    const uint32_t total = (uint32_t)fr.w * (uint32_t)fr.localRows;
+    if (total == 0) return;
+    k_raygen<<<(total + 255) / 256, 256, 0, s>>>(sc, fr, pb.ext[0], pb.accum, pb.ctrl, total);
+}
+
+void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+    DFrame dummy{};   // closest-hit traversal does not read the frame constants
+    const int grid = lc.smCount * lc.traceBlocksPerSM;
+    if (lc.collectStats) k_trace<false, true><<<grid, 128, 0, s>>>(sc, dummy, pb, iter);
+    else                 k_trace<false, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter);
+}
+
+void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+    const int grid = lc.smCount * lc.traceBlocksPerSM;
+    if (lc.collectStats) k_trace<true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
+    else                 k_trace<true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
+}
+
+void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+    k_shade<<<lc.smCount * 8, 128, 0, s>>>(sc, fr, pb, iter);
+}
+
+void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s) { k_finish_pass<<<1, 32, 0, s>>>(pb, iterations); }
+
+void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig&, cudaStream_t s) {
+    if (n <= 0) return;
+    if (anyHit) k_trace_rays<true><<<(n + 127) / 128, 128, 0, s>>>(sc, rays, hits, n);
+    else        k_trace_rays<false><<<(n + 127) / 128, 128, 0, s>>>(sc, rays, hits, n);
+}
+
+void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s) {
+    if (n) k_add_pixels<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(accum, src, n);
+}
+
+} // namespace hr

@@ -1,0 +1,316 @@
+"""Procedural bench/test scenes — the concrete synthetic inputs of BASELINE.json's configs.
+
+Geometry comes from the host layer's mesh providers (hrhPlaneMesh / hrhSphereMesh, the restated
+PlaneMeshProvider / SphereMeshProvider) plus numpy generators for boxes and terrain. Placement and material
+parameters are drawn from SplitMix64(seed = config number). The reference's studio.hdr environment is not
+copied into this repository; `studio_environment()` synthesises a lat-long HDR map of the same size.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import capi
+
+
+class SplitMix64:
+    def __init__(self, seed: int):
+        self.s = seed & 0xFFFFFFFFFFFFFFFF
+
+    def next(self) -> int:
+        self.s = (self.s + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+        z = self.s
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+        return z ^ (z >> 31)
+
+    def uniform(self, lo=0.0, hi=1.0) -> float:
+        return lo + (hi - lo) * ((self.next() >> 11) * (1.0 / (1 << 53)))
+
+
+@dataclass
+class MeshSpec:
+    positions: np.ndarray
+    normals: np.ndarray
+    indices: np.ndarray
+    material: int
+    transform: np.ndarray = field(default_factory=lambda: np.eye(4, dtype=np.float32))
+    draw_mode: int = capi.DRAW_TRIANGLES
+
+    @property
+    def triangle_count(self):
+        n = self.indices.size
+        return n // 3 if self.draw_mode == capi.DRAW_TRIANGLES else max(0, n - 2)
+
+
+@dataclass
+class MaterialSpec:
+    kind: str                      # "pbr" | "glass"
+    params: dict
+
+
+@dataclass
+class SceneSpec:
+    name: str
+    width: int
+    height: int
+    passes: int
+    max_depth: int
+    meshes: list
+    materials: list
+    env: dict                      # {"enabled": bool, "solid": (r,g,b) | None, "map": ndarray | None, "ev": float, "theta": float}
+    dir_lights: list = field(default_factory=list)     # dicts: color, illuminance, theta, phi
+    point_lights: list = field(default_factory=list)   # dicts: color, intensity, position
+    spot_lights: list = field(default_factory=list)    # dicts: color, intensity, position, theta, phi, inner, outer
+    camera: dict = field(default_factory=dict)         # distance, phi, theta, target, focal_length, fstop, focus_distance
+    bokeh: int = capi.BOKEH_CIRCULAR
+    max_channel_value: float = math.pi
+
+    @property
+    def triangle_count(self):
+        return sum(m.triangle_count for m in self.meshes)
+
+
+# ---- transforms (row-major mathematical matrices; capi transposes into glm layout) ---------------
+def translate(x, y, z):
+    m = np.eye(4, dtype=np.float32)
+    m[:3, 3] = (x, y, z)
+    return m
+
+
+def scale(x, y, z):
+    return np.diag([x, y, z, 1.0]).astype(np.float32)
+
+
+def rotate(axis, angle):
+    c, s = math.cos(angle), math.sin(angle)
+    m = np.eye(4, dtype=np.float32)
+    if axis == "x":
+        m[1, 1], m[1, 2], m[2, 1], m[2, 2] = c, -s, s, c
+    elif axis == "y":
+        m[0, 0], m[0, 2], m[2, 0], m[2, 2] = c, s, -s, c
+    else:
+        m[0, 0], m[0, 1], m[1, 0], m[1, 1] = c, -s, s, c
+    return m
+
+
+# ---- mesh providers -------------------------------------------------------------------------------
+def plane_mesh(width, length):
+    lib = capi.load_library()
+    pos, nrm, uv, idx = np.zeros((4, 3), np.float32), np.zeros((4, 3), np.float32), np.zeros((4, 2), np.float32), np.zeros(4, np.uint32)
+    lib.hrhPlaneMesh(width, length, capi._ptr(pos), capi._ptr(nrm), capi._ptr(uv), capi._ptr(idx))
+    return pos, nrm, idx
+
+
+_sphere_cache = {}
+
+
+def sphere_mesh(u_slices, v_slices, radius):
+    key = (u_slices, v_slices, radius)
+    if key not in _sphere_cache:
+        lib = capi.load_library()
+        nv, ni = C.c_uint32(), C.c_uint32()
+        lib.hrhSphereMesh(u_slices, v_slices, radius, None, None, None, None, C.byref(nv), C.byref(ni))
+        pos, nrm = np.zeros((nv.value, 3), np.float32), np.zeros((nv.value, 3), np.float32)
+        uv, idx = np.zeros((nv.value, 2), np.float32), np.zeros(ni.value, np.uint32)
+        lib.hrhSphereMesh(u_slices, v_slices, radius, capi._ptr(pos), capi._ptr(nrm), capi._ptr(uv), capi._ptr(idx), None, None)
+        _sphere_cache[key] = (pos, nrm, idx)
+    return _sphere_cache[key]
+
+
+def box_mesh(sx, sy, sz):
+    """Axis-aligned box centred at the origin: 6 faces x 2 triangles with per-face normals (CCW outward)."""
+    hx, hy, hz = sx / 2, sy / 2, sz / 2
+    faces = [((1, 0, 0), (0, 1, 0), (0, 0, 1)), ((-1, 0, 0), (0, 0, 1), (0, 1, 0)),
+             ((0, 1, 0), (0, 0, 1), (1, 0, 0)), ((0, -1, 0), (1, 0, 0), (0, 0, 1)),
+             ((0, 0, 1), (1, 0, 0), (0, 1, 0)), ((0, 0, -1), (0, 1, 0), (1, 0, 0))]
+    h = np.array([hx, hy, hz], np.float32)
+    pos, nrm, idx = [], [], []
+    for n, u, v in faces:
+        n, u, v = np.array(n, np.float32), np.array(u, np.float32), np.array(v, np.float32)
+        base = len(pos)
+        for a, b in ((-1, -1), (1, -1), (1, 1), (-1, 1)):
+            pos.append((n + a * u + b * v) * h)
+            nrm.append(n)
+        idx += [base, base + 1, base + 2, base, base + 2, base + 3]
+    return np.array(pos, np.float32), np.array(nrm, np.float32), np.array(idx, np.uint32)
+
+
+def _value_noise(x, y, seed):
+    """Deterministic lattice value noise on float64 arrays (hash of integer lattice points, smoothstep blend)."""
+    xi, yi = np.floor(x).astype(np.int64), np.floor(y).astype(np.int64)
+    fx, fy = x - xi, y - yi
+
+    def h(a, b):
+        v = (a * 374761393 + b * 668265263 + seed * 1442695040888963407) & 0xFFFFFFFF
+        v = ((v ^ (v >> 13)) * 1274126177) & 0xFFFFFFFF
+        return ((v ^ (v >> 16)) & 0xFFFF) / 65535.0
+
+    sx, sy = fx * fx * (3 - 2 * fx), fy * fy * (3 - 2 * fy)
+    a, b = h(xi, yi), h(xi + 1, yi)
+    c, d = h(xi, yi + 1), h(xi + 1, yi + 1)
+    return (a * (1 - sx) + b * sx) * (1 - sy) + (c * (1 - sx) + d * sx) * sy
+
+
+def terrain_mesh(n, size, height, seed):
+    """n x n vertex heightfield over [-size/2, size/2]^2 displaced by 5-octave value noise; 2*(n-1)^2 triangles."""
+    g = np.linspace(0.0, 1.0, n)
+    u, v = np.meshgrid(g, g, indexing="xy")
+    hgt = np.zeros_like(u)
+    amp, freq = 1.0, 4.0
+    for o in range(5):
+        hgt += amp * _value_noise(u * freq, v * freq, seed + o)
+        amp *= 0.5
+        freq *= 2.0
+    hgt = (hgt / 1.9375 - 0.5) * height
+    x, z = (u - 0.5) * size, (v - 0.5) * size
+    pos = np.stack([x, hgt, z], -1).astype(np.float32)
+    dx = np.gradient(hgt, size / (n - 1), axis=1)
+    dz = np.gradient(hgt, size / (n - 1), axis=0)
+    nrm = np.stack([-dx, np.ones_like(dx), -dz], -1)
+    nrm = (nrm / np.linalg.norm(nrm, axis=-1, keepdims=True)).astype(np.float32)
+    i = (np.arange(n - 1)[:, None] * n + np.arange(n - 1)[None, :]).reshape(-1).astype(np.uint32)
+    idx = np.stack([i, i + n, i + 1, i + 1, i + n, i + n + 1], -1).reshape(-1)
+    return pos.reshape(-1, 3), nrm.reshape(-1, 3), idx.astype(np.uint32)
+
+
+def studio_environment(width=2048, height=1024):
+    """Synthetic stand-in for Resources/Environments/studio.hdr (2048x1024): dim grey room, bright ceiling softboxes,
+    a warm key light and a cool fill. Row 0 is the bottom row (t = 0)."""
+    t = (np.arange(height, dtype=np.float32) + 0.5) / height
+    s = (np.arange(width, dtype=np.float32) + 0.5) / width
+    S, T = np.meshgrid(s, t, indexing="xy")
+    img = np.empty((height, width, 3), np.float32)
+    base = 0.08 + 0.25 * T
+    img[..., 0], img[..., 1], img[..., 2] = base, base, base * 1.05
+
+    def softbox(cs, ct, ws, wt, col):
+        m = np.clip(1 - np.abs(S - cs) / ws, 0, 1) * np.clip(1 - np.abs(T - ct) / wt, 0, 1)
+        m = np.minimum(1.0, m * 4.0)
+        for k in range(3):
+            img[..., k] += m * col[k]
+
+    softbox(0.25, 0.80, 0.06, 0.08, (18.0, 17.0, 15.0))
+    softbox(0.62, 0.85, 0.10, 0.06, (9.0, 9.5, 11.0))
+    softbox(0.85, 0.55, 0.03, 0.15, (5.0, 4.0, 3.0))
+    softbox(0.45, 0.60, 0.02, 0.04, (30.0, 28.0, 24.0))
+    return img
+
+
+# ---- the configs -----------------------------------------------------------------------------------
+def _pbr(base, rough=1.0, metal=0.0, f0=0.5, emissive=(0, 0, 0), cc=0.0, ccr=0.0, double_sided=True):
+    return MaterialSpec("pbr", dict(baseColor=base, emissiveColor=emissive, metallic=metal, roughness=rough, specularF0=f0,
+                                    clearCoat=cc, clearCoatRoughness=ccr, doubleSided=double_sided))
+
+
+def _glass(base, rough, ior, density):
+    return MaterialSpec("glass", dict(baseColor=base, roughness=rough, ior=ior, density=density))
+
+
+def cornell_box(width=512, height=512, passes=64, max_depth=4):
+    """Config #1: 5 walls (10 tris) + tall box (12) + short box (12) + ceiling emitter quad (2) = 36 triangles,
+    one point light just below the ceiling, no environment."""
+    mats = [_pbr((0.73, 0.73, 0.73)), _pbr((0.65, 0.05, 0.05)), _pbr((0.12, 0.45, 0.15)),
+            _pbr((0.0, 0.0, 0.0), emissive=(1.0, 1.0, 1.0))]
+    p, n, i = plane_mesh(2.0, 2.0)
+    strip = capi.DRAW_TRIANGLE_STRIP
+    hp = math.pi / 2
+    meshes = [
+        MeshSpec(p, n, i, 0, translate(0, 0, 0), strip),                                  # floor
+        MeshSpec(p, n, i, 0, translate(0, 2, 0) @ rotate("x", math.pi), strip),           # ceiling
+        MeshSpec(p, n, i, 0, translate(0, 1, -1) @ rotate("x", hp), strip),               # back wall
+        MeshSpec(p, n, i, 1, translate(-1, 1, 0) @ rotate("z", -hp), strip),              # left (red)
+        MeshSpec(p, n, i, 2, translate(1, 1, 0) @ rotate("z", hp), strip),                # right (green)
+    ]
+    bp, bn, bi = box_mesh(0.6, 1.2, 0.6)
+    meshes.append(MeshSpec(bp, bn, bi, 0, translate(-0.35, 0.6, -0.3) @ rotate("y", 0.3)))
+    bp, bn, bi = box_mesh(0.6, 0.6, 0.6)
+    meshes.append(MeshSpec(bp, bn, bi, 0, translate(0.35, 0.3, 0.35) @ rotate("y", -0.3)))
+    ep, en, ei = plane_mesh(0.5, 0.5)
+    meshes.append(MeshSpec(ep, en, ei, 3, translate(0, 1.995, 0) @ rotate("x", math.pi), strip))
+    return SceneSpec("cornell", width, height, passes, max_depth, meshes, mats,
+                     env=dict(enabled=False, solid=None, map=None, ev=0.0, theta=0.0),
+                     point_lights=[dict(color=(1.0, 1.0, 1.0), intensity=683.0 * 0.5, position=(0.0, 1.9, 0.0))],
+                     camera=dict(distance=5.4, phi=0.0, theta=0.0, target=(0.0, 1.0, 0.0), focal_length=50.0, fstop=None, focus_distance=5.4))
+
+
+def sphere_grid(width=1920, height=1080, passes=32, max_depth=8, grid=8, u_slices=64, v_slices=32, seed=2, env_size=(2048, 1024)):
+    """Config #2 ("Sponza-scale"): grid x grid lat-long spheres (2*u*v tris each) + floor + 2 walls (6 tris)."""
+    rng = SplitMix64(seed)
+    mats = [_pbr((0.6, 0.6, 0.6), rough=0.9, f0=0.5)]
+    meshes = []
+    p, n, i = plane_mesh(1.0, 1.0)
+    ext = grid * 1.9 + 4.0
+    strip = capi.DRAW_TRIANGLE_STRIP
+    meshes.append(MeshSpec(p, n, i, 0, translate(0, -0.8, 0) @ scale(ext, 1, ext), strip))
+    meshes.append(MeshSpec(p, n, i, 0, translate(0, ext / 4 - 0.8, -ext / 2) @ rotate("x", math.pi / 2) @ scale(ext, 1, ext / 2), strip))
+    meshes.append(MeshSpec(p, n, i, 0, translate(-ext / 2, ext / 4 - 0.8, 0) @ rotate("z", -math.pi / 2) @ scale(ext / 2, 1, ext), strip))
+    sp, sn, si = sphere_mesh(u_slices, v_slices, 0.8)
+    for gz in range(grid):
+        for gx in range(grid):
+            rough = rng.uniform(0.05, 1.0)
+            metal = 1.0 if rng.uniform() < 0.5 else 0.0
+            base = (rng.uniform(0.2, 0.9), rng.uniform(0.2, 0.9), rng.uniform(0.2, 0.9))
+            mats.append(_pbr(base, rough=rough, metal=metal, f0=0.5))
+            x = (gx - (grid - 1) / 2) * 1.9
+            z = (gz - (grid - 1) / 2) * 1.9
+            meshes.append(MeshSpec(sp, sn, si, len(mats) - 1, translate(x, 0.0, z)))
+    return SceneSpec("sphere_grid", width, height, passes, max_depth, meshes, mats,
+                     env=dict(enabled=True, solid=None, map=studio_environment(*env_size), ev=0.0, theta=0.0),
+                     camera=dict(distance=19.0, phi=0.0, theta=0.6, target=(0.0, 0.0, 0.0), focal_length=50.0, fstop=None, focus_distance=19.0))
+
+
+def material_grid(width=1920, height=1080, passes=32, max_depth=8, grid=11, u_slices=64, v_slices=32, seed=3):
+    """Config #3: grid x grid spheres, odd cells glass, even cells clear-coated PBR, ground strip (2 tris);
+    spot + directional light, solid grey environment, f/2.8 with hexagonal bokeh."""
+    rng = SplitMix64(seed)
+    mats = [_pbr((0.5, 0.5, 0.5), rough=0.8, f0=0.5)]
+    meshes = []
+    p, n, i = plane_mesh(1.0, 1.0)
+    ext = grid * 1.4 + 4.0
+    meshes.append(MeshSpec(p, n, i, 0, translate(0, -0.6, 0) @ scale(ext, 1, ext), capi.DRAW_TRIANGLE_STRIP))
+    sp, sn, si = sphere_mesh(u_slices, v_slices, 0.6)
+    for gz in range(grid):
+        for gx in range(grid):
+            cell = gz * grid + gx
+            base = (rng.uniform(0.3, 0.95), rng.uniform(0.3, 0.95), rng.uniform(0.3, 0.95))
+            if cell & 1:
+                mats.append(_glass(base, rng.uniform(0.0, 0.5), rng.uniform(1.1, 2.0), rng.uniform(0.0, 1.0)))
+            else:
+                mats.append(_pbr(base, rough=rng.uniform(0.1, 0.9), metal=0.0, f0=0.5, cc=rng.uniform(0.0, 1.0), ccr=rng.uniform(0.0, 0.5)))
+            x = (gx - (grid - 1) / 2) * 1.4
+            z = (gz - (grid - 1) / 2) * 1.4
+            meshes.append(MeshSpec(sp, sn, si, len(mats) - 1, translate(x, 0.0, z)))
+    return SceneSpec("material_grid", width, height, passes, max_depth, meshes, mats,
+                     env=dict(enabled=True, solid=(0.5, 0.5, 0.5), map=None, ev=0.0, theta=0.0),
+                     dir_lights=[dict(color=(1.0, 0.95, 0.9), illuminance=683.0 * 2.0, theta=math.pi / 3, phi=0.4)],
+                     spot_lights=[dict(color=(1.0, 1.0, 1.0), intensity=683.0 * 40.0, position=(0.0, 8.0, 0.0), theta=math.pi / 2, phi=0.0,
+                                       inner=math.radians(20.0), outer=math.radians(40.0))],
+                     camera=dict(distance=16.0, phi=0.0, theta=0.55, target=(0.0, 0.0, 0.0), focal_length=50.0, fstop=2.8, focus_distance=16.0),
+                     bokeh=capi.BOKEH_HEXAGON)
+
+
+def terrain(width=3840, height=2160, passes=16, max_depth=8, n=2048, blobs=400, seed=4, env_size=(2048, 1024)):
+    """Config #4: n x n displaced heightfield (2(n-1)^2 tris) + `blobs` flattened 4096-triangle foliage spheres."""
+    rng = SplitMix64(seed)
+    mats = [_pbr((0.35, 0.3, 0.22), rough=0.95, f0=0.3), _pbr((0.15, 0.4, 0.12), rough=0.7, f0=0.5)]
+    tp, tn, ti = terrain_mesh(n, 60.0, 6.0, seed)
+    meshes = [MeshSpec(tp, tn, ti, 0)]
+    sp, sn, si = sphere_mesh(64, 32, 1.0)
+    grid = tp.reshape(n, n, 3)
+    for _ in range(blobs):
+        gx, gz = int(rng.uniform(0.05, 0.95) * (n - 1)), int(rng.uniform(0.05, 0.95) * (n - 1))
+        c = grid[gz, gx]
+        r = rng.uniform(0.25, 0.7)
+        meshes.append(MeshSpec(sp, sn, si, 1, translate(float(c[0]), float(c[1]) + r * 0.8, float(c[2])) @ scale(r, r * 1.3, r)))
+    return SceneSpec("terrain", width, height, passes, max_depth, meshes, mats,
+                     env=dict(enabled=True, solid=None, map=studio_environment(*env_size), ev=0.0, theta=0.0),
+                     dir_lights=[dict(color=(1.0, 0.96, 0.9), illuminance=683.0 * 3.0, theta=math.pi / 3.5, phi=0.7)],
+                     camera=dict(distance=55.0, phi=0.3, theta=0.45, target=(0.0, 0.0, 0.0), focal_length=35.0, fstop=None, focus_distance=55.0))
+
+
+def build(name: str, **kw) -> SceneSpec:
+    return {"cornell": cornell_box, "sphere_grid": sphere_grid, "material_grid": material_grid, "terrain": terrain}[name](**kw)
