@@ -22,6 +22,7 @@ TEX_R32F, TEX_RGB32F, TEX_RGBA32F, TEX_RGBA8 = 0, 1, 2, 3
 WRAP_CLAMP, WRAP_REPEAT = 0, 1
 DRAW_TRIANGLES, DRAW_TRIANGLE_STRIP = 0, 1
 HIT_BACKFACE = 0x40000000
+OPT_TRAVERSAL_COUNTERS, OPT_KERNEL_TIMING = 0, 1
 SAMPLE_RANDOM, SAMPLE_HALTON, SAMPLE_HAMMERSLEY, SAMPLE_BLUE_NOISE, SAMPLE_SOBOL = range(5)
 BOKEH_CIRCULAR, BOKEH_PENTAGON, BOKEH_HEXAGON, BOKEH_OCTAGON = range(4)
 
@@ -96,7 +97,7 @@ class FrameParams(C.Structure):
 
 class PassStats(C.Structure):
     _fields_ = [("gpuMs", f32), ("raysPrimary", u64), ("raysExtension", u64), ("raysOcclusion", u64), ("nodesVisited", u64),
-                ("trianglesTested", u64), ("closestLaunches", u64), ("anyLaunches", u64), ("shadeLaunches", u64),
+                ("trianglesTested", u64), ("nodesVisitedAny", u64), ("trianglesTestedAny", u64), ("closestLaunches", u64), ("anyLaunches", u64), ("shadeLaunches", u64),
                 ("msClosest", f32), ("msAny", f32), ("msShade", f32), ("msRaygen", f32)]
 
     @property
@@ -123,10 +124,10 @@ class HrhGlassMaterial(C.Structure):
 
 # names of every exported symbol of the backend C-ABI (checked by tests/test_abi.py against the header)
 BACKEND_SYMBOLS = [
-    "CreateContext", "DestroyContext", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels",
+    "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels",
     "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "ClearScene", "CommitScene",
     "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetGlobals",
-    "RenderPass", "EnqueuePass", "Synchronize", "ResetStats", "GetStats", "TraceRays", "GetSceneInfo",
+    "RenderPass", "EnqueuePass", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo",
 ]
 
 _lib = None
@@ -215,6 +216,9 @@ class Backend:
 
     def __exit__(self, *exc):
         self.close()
+
+    def set_option(self, option: int, value: int):
+        self._call("SetOption", i32(option), i32(value))
 
     # -- framebuffer ------------------------------------------------------------------------
     def resize(self, w, h):
@@ -341,6 +345,14 @@ class Backend:
 
     def synchronize(self):
         self._call("Synchronize")
+
+    def timer_start(self):
+        self._call("TimerStart")
+
+    def timer_stop(self) -> float:
+        ms = f32()
+        self._call("TimerStop", C.byref(ms))
+        return ms.value
 
     def reset_stats(self):
         self._call("ResetStats")

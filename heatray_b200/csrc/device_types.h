@@ -64,7 +64,7 @@ struct ShadowQueue {
 struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; };
 
 struct DeviceStats {                       // accumulated by k_finish_pass
-    unsigned long long raysPrimary, raysExtension, raysOcclusion, nodesVisited, trianglesTested, stackOverflows;
+    unsigned long long raysPrimary, raysExtension, raysOcclusion, nodesVisited, trianglesTested, nodesVisitedAny, trianglesTestedAny, stackOverflows;
 };
 
 struct DScene {

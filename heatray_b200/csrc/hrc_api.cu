@@ -28,9 +28,9 @@ thread_local std::string g_err;
 
 struct HrcContext_t {
     int device = 0;
-    bool collectStats = false;
+    bool counters = false, kernelTiming = false;
     cudaStream_t stream = nullptr;
-    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr, evTimer0 = nullptr, evTimer1 = nullptr;
     std::vector<cudaEvent_t> evPool;
     std::string err;
     int smCount = 148;
@@ -80,7 +80,7 @@ DScene sceneOf(HrcContext c) {
     s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId;
     return s;
 }
-LaunchConfig configOf(HrcContext c) { LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->collectStats; return lc; }
+LaunchConfig configOf(HrcContext c) { LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters; return lc; }
 
 int uploadMaterials(HrcContext c) {
     if (!c->materialsDirty) return HRC_OK;
@@ -156,13 +156,13 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     int dev = desc ? desc->device : 0;
     if (dev < 0 || dev >= count) return fail(nullptr, HRC_ERR_INVALID_VALUE, "bad CUDA device ordinal");
     HrcContext c = new HrcContext_t();
-    c->device = dev; c->collectStats = desc && desc->collectStats;
+    c->device = dev; c->counters = c->kernelTiming = desc && desc->collectStats;
     if ((e = cudaSetDevice(dev)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaSetDevice"); delete c; return r; }
     cudaDeviceProp prop;
     if ((e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaGetDeviceProperties"); delete c; return r; }
     c->smCount = prop.multiProcessorCount;
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaStreamCreate"); delete c; return r; }
-    cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop);
+    cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop); cudaEventCreate(&c->evTimer0); cudaEventCreate(&c->evTimer1);
     cudaMalloc(&c->pb.ctrl, sizeof(IterCtrl) * kMaxIterations);
     cudaMalloc(&c->pb.stats, sizeof(DeviceStats));
     cudaMemsetAsync(c->pb.stats, 0, sizeof(DeviceStats), c->stream);
@@ -186,9 +186,17 @@ HRC_API int hrcDestroyContext(HrcContext c) {
     freeDev(c->dSeq); freeDev(c->dAperture); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
     freeDev(c->pb.ctrl); freeDev(c->pb.stats);
     for (auto ev : c->evPool) cudaEventDestroy(ev);
-    cudaEventDestroy(c->evStart); cudaEventDestroy(c->evStop);
+    cudaEventDestroy(c->evStart); cudaEventDestroy(c->evStop); cudaEventDestroy(c->evTimer0); cudaEventDestroy(c->evTimer1);
     cudaStreamDestroy(c->stream);
     delete c;
+    return HRC_OK;
+}
+
+HRC_API int hrcSetOption(HrcContext c, int32_t option, int32_t value) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (option == HRC_OPT_TRAVERSAL_COUNTERS) c->counters = value != 0;
+    else if (option == HRC_OPT_KERNEL_TIMING) c->kernelTiming = value != 0;
+    else return fail(c, HRC_ERR_INVALID_VALUE, "unknown option");
     return HRC_OK;
 }
 
@@ -543,7 +551,7 @@ HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* 
     float kms[4] = {0, 0, 0, 0}; int launches[3] = {0, 0, 0};
     DeviceStats before; int r = readStats(c, &before); if (r) return r;
     CU(c, cudaEventRecord(c->evStart, c->stream));
-    r = enqueuePass(c, fp, c->collectStats && stats, kms, launches); if (r) return r;
+    r = enqueuePass(c, fp, c->kernelTiming && stats, kms, launches); if (r) return r;
     CU(c, cudaEventRecord(c->evStop, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return failCuda(c, e, "render pass");
@@ -554,6 +562,7 @@ HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* 
         stats->raysPrimary = after.raysPrimary - before.raysPrimary; stats->raysExtension = after.raysExtension - before.raysExtension;
         stats->raysOcclusion = after.raysOcclusion - before.raysOcclusion;
         stats->nodesVisited = after.nodesVisited - before.nodesVisited; stats->trianglesTested = after.trianglesTested - before.trianglesTested;
+        stats->nodesVisitedAny = after.nodesVisitedAny - before.nodesVisitedAny; stats->trianglesTestedAny = after.trianglesTestedAny - before.trianglesTestedAny;
         stats->closestLaunches = launches[0]; stats->shadeLaunches = launches[1]; stats->anyLaunches = launches[2];
         stats->msRaygen = kms[0]; stats->msClosest = kms[1]; stats->msShade = kms[2]; stats->msAny = kms[3];
         if (after.stackOverflows != before.stackOverflows) return fail(c, HRC_ERR_INVALID_OPERATION, "traversal stack overflow");
@@ -573,6 +582,20 @@ HRC_API int hrcResetStats(HrcContext c) {
     CU(c, cudaMemsetAsync(c->pb.stats, 0, sizeof(DeviceStats), c->stream));
     return HRC_OK;
 }
+HRC_API int hrcTimerStart(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    cudaSetDevice(c->device);
+    CU(c, cudaEventRecord(c->evTimer0, c->stream));
+    return HRC_OK;
+}
+HRC_API int hrcTimerStop(HrcContext c, float* ms) {
+    if (!c || !ms) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    cudaSetDevice(c->device);
+    CU(c, cudaEventRecord(c->evTimer1, c->stream));
+    CU(c, cudaEventSynchronize(c->evTimer1));
+    CU(c, cudaEventElapsedTime(ms, c->evTimer0, c->evTimer1));
+    return HRC_OK;
+}
 HRC_API int hrcGetStats(HrcContext c, HrcPassStats* stats) {
     if (!c || !stats) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     cudaSetDevice(c->device);
@@ -580,6 +603,7 @@ HRC_API int hrcGetStats(HrcContext c, HrcPassStats* stats) {
     std::memset(stats, 0, sizeof(*stats));
     stats->raysPrimary = d.raysPrimary; stats->raysExtension = d.raysExtension; stats->raysOcclusion = d.raysOcclusion;
     stats->nodesVisited = d.nodesVisited; stats->trianglesTested = d.trianglesTested;
+    stats->nodesVisitedAny = d.nodesVisitedAny; stats->trianglesTestedAny = d.trianglesTestedAny;
     return HRC_OK;
 }
 

@@ -444,8 +444,8 @@ __global__ void __launch_bounds__(128) k_trace(const DScene sc, const __grid_con
         uint32_t n = tc.nodes, t = tc.tris, ov = tc.overflow;
         for (int s = 16; s > 0; s >>= 1) { n += __shfl_xor_sync(0xffffffffu, n, s); t += __shfl_xor_sync(0xffffffffu, t, s); ov += __shfl_xor_sync(0xffffffffu, ov, s); }
         if (lane == 0) {
-            atomicAdd(&pb.stats->nodesVisited, (unsigned long long)n);
-            atomicAdd(&pb.stats->trianglesTested, (unsigned long long)t);
+            atomicAdd(ANY ? &pb.stats->nodesVisitedAny : &pb.stats->nodesVisited, (unsigned long long)n);
+            atomicAdd(ANY ? &pb.stats->trianglesTestedAny : &pb.stats->trianglesTested, (unsigned long long)t);
             if (ov) atomicAdd(&pb.stats->stackOverflows, (unsigned long long)ov);
         }
     }

@@ -58,10 +58,16 @@ typedef int32_t HrcTexture;   /* ↔ RLtexture */
 /* ---- context (↔ OpenRLCreateContext / OpenRLDestroyContext, PassGenerator.cpp:164,432) */
 typedef struct HrcContextDesc {
     int32_t device;          /* CUDA ordinal */
-    int32_t collectStats;    /* 1: traversal counters (nodes visited / triangles tested) are kept */
+    int32_t collectStats;    /* 1: start with HRC_OPT_TRAVERSAL_COUNTERS and HRC_OPT_KERNEL_TIMING on */
 } HrcContextDesc;
 
 HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out);
+/* Runtime switches (no reference equivalent; OpenRL exposes RL_PROFILE-style enums it never uses, rl.h:346-355). */
+enum {
+    HRC_OPT_TRAVERSAL_COUNTERS = 0,  /* count nodes visited / triangles tested (slightly slower kernels) */
+    HRC_OPT_KERNEL_TIMING = 1        /* CUDA events between kernels: HrcPassStats.ms* are filled by hrcRenderPass */
+};
+HRC_API int hrcSetOption(HrcContext ctx, int32_t option, int32_t value);
 HRC_API int hrcDestroyContext(HrcContext ctx);
 /* ctx may be NULL for errors raised before a context exists. */
 HRC_API const char* hrcGetLastError(HrcContext ctx);
@@ -210,9 +216,10 @@ typedef struct HrcFrameParams {
 typedef struct HrcPassStats {
     float    gpuMs;                 /* CUDA-event time of the pass on the context's stream */
     uint64_t raysPrimary, raysExtension, raysOcclusion;   /* segments submitted to traversal */
-    uint64_t nodesVisited, trianglesTested;               /* only when collectStats */
+    uint64_t nodesVisited, trianglesTested;               /* closest-hit kernel; only with HRC_OPT_TRAVERSAL_COUNTERS */
+    uint64_t nodesVisitedAny, trianglesTestedAny;         /* occlusion kernel; only with HRC_OPT_TRAVERSAL_COUNTERS */
     uint64_t closestLaunches, anyLaunches, shadeLaunches; /* kernels launched by this pass */
-    float    msClosest, msAny, msShade, msRaygen;         /* only when collectStats (per-kernel events) */
+    float    msClosest, msAny, msShade, msRaygen;         /* only with HRC_OPT_KERNEL_TIMING (per-kernel events, summed over the pass) */
 } HrcPassStats;
 /* Enqueues and completes one pass; stats may be NULL. */
 HRC_API int hrcRenderPass(HrcContext ctx, const HrcFrameParams* frame, HrcPassStats* stats);
@@ -221,6 +228,9 @@ HRC_API int hrcRenderPass(HrcContext ctx, const HrcFrameParams* frame, HrcPassSt
 HRC_API int hrcEnqueuePass(HrcContext ctx, const HrcFrameParams* frame);
 HRC_API int hrcSynchronize(HrcContext ctx);
 HRC_API int hrcResetStats(HrcContext ctx);
+/* CUDA-event stopwatch on the context's stream: Start records, Stop records + waits and returns the device time between them. */
+HRC_API int hrcTimerStart(HrcContext ctx);
+HRC_API int hrcTimerStop(HrcContext ctx, float* milliseconds);
 HRC_API int hrcGetStats(HrcContext ctx, HrcPassStats* stats);
 
 /* ---- parity hooks (no reference equivalent; the fixed-ray-set test) ---- */
