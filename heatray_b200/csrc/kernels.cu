@@ -250,28 +250,45 @@ __device__ __forceinline__ bool triangleTest(float4 a, float4 b, float4 c, float
 
 struct TraceCounters { uint32_t nodes, tris, overflow; };
 
-template <bool ANY, bool STATS>
-__device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const float4* __restrict__ tris,
-                                         float3 o, float3 d, float tmin, float tmaxRay, HitRec& best, TraceCounters& tc) {
-    // guard the slab arithmetic against zero direction components (box tests only)
-    const float tiny = 1e-20f;
-    float3 dd = f3(fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x,
-                   fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
-                   fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
-    const float3 idir = f3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
-    // slot bit set = positive side; a ray going positive must visit negative-side children first
-    const bool negX = dd.x < 0.0f, negY = dd.y < 0.0f, negZ = dd.z < 0.0f;
-    const uint32_t octInv = (negX ? 0u : 4u) | (negY ? 0u : 2u) | (negZ ? 0u : 1u);
-    const uint32_t octInv4 = octInv * 0x01010101u;
+// byte j of q as a float, without the quarter-rate I2F pipe: splice the byte into the mantissa of 2^23 (one PRMT)
+// and subtract 2^23 (one full-rate FADD; exact for 0..255).
+template <int J>
+__device__ __forceinline__ float byteToFloat(uint32_t q) {
+    return __uint_as_float(__byte_perm(q, 0x4B000000u, 0x7440u + J)) - 8388608.0f;
+}
 
-    best.t = tmaxRay; best.prim = 0x7fffffff; best.u = 0.f; best.v = 0.f; best.back = false;
-    bool found = false;
+// Per-lane traversal state of the 8-wide compressed BVH. A lane keeps its state across the refill points of the
+// persistent kernel, so a warp can top itself up with fresh rays while slow rays are still in flight.
+struct Traversal {
+    float3 o, d, idir;
+    float tmin, tmaxRay;
+    uint32_t octInv;
+    bool negX, negY, negZ;
+    HitRec best; bool found;
+    uint2 group;
+    int sp;
 
-    uint2 stack[kTraceStack];
-    int sp = 0;
-    uint2 group = make_uint2(0u, 0x80000000u);     // root: "child 7 of a virtual parent whose childBase is 0"
+    __device__ __forceinline__ void begin(float3 org, float3 dir, float tmin_, float tmax_) {
+        o = org; d = dir; tmin = tmin_; tmaxRay = tmax_;
+        // guard the slab arithmetic against zero direction components (box tests only)
+        const float tiny = 1e-20f;
+        const float3 dd = f3(fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x,
+                             fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
+                             fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
+        idir = f3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
+        negX = dd.x < 0.0f; negY = dd.y < 0.0f; negZ = dd.z < 0.0f;
+        // slot bit set = positive side; a ray going positive must visit negative-side children first
+        octInv = (negX ? 0u : 4u) | (negY ? 0u : 2u) | (negZ ? 0u : 1u);
+        best.t = tmax_; best.prim = 0x7fffffff; best.u = 0.f; best.v = 0.f; best.back = false;
+        found = false;
+        sp = 0;
+        group = make_uint2(0u, 0x80000000u);     // root: "child 7 of a virtual parent whose childBase is 0"
+    }
 
-    while (true) {
+    // One traversal step: pop one node (or one postponed triangle group), test its children / triangles.
+    // Returns false when the ray is finished.
+    template <bool ANY, bool STATS>
+    __device__ __forceinline__ bool step(const float4* __restrict__ nodes, const float4* __restrict__ tris, uint2* stack, TraceCounters& tc) {
         uint2 triGroup;
         if (group.y & 0xff000000u) {
             const uint32_t hits = group.y;
@@ -294,6 +311,7 @@ __device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const
                                      __uint_as_float(byteOf(eimask, 2) << 23) * idir.z);
             const float3 adjOrg = f3((n0.x - o.x) * idir.x, (n0.y - o.y) * idir.y, (n0.z - o.z) * idir.z);
             const float tfar = best.t;
+            const uint32_t octInv4 = octInv * 0x01010101u;
 
             uint32_t hitMask = 0;
 #pragma unroll
@@ -309,17 +327,18 @@ __device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const
                 const uint32_t nx = negX ? qhix : qlox, fx = negX ? qlox : qhix;
                 const uint32_t ny = negY ? qhiy : qloy, fy = negY ? qloy : qhiy;
                 const uint32_t nz = negZ ? qhiz : qloz, fz = negZ ? qloz : qhiz;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float tnx = fmaf((float)byteOf(nx, j), adjDir.x, adjOrg.x), tfx = fmaf((float)byteOf(fx, j), adjDir.x, adjOrg.x);
-                    const float tny = fmaf((float)byteOf(ny, j), adjDir.y, adjOrg.y), tfy = fmaf((float)byteOf(fy, j), adjDir.y, adjOrg.y);
-                    const float tnz = fmaf((float)byteOf(nz, j), adjDir.z, adjOrg.z), tfz = fmaf((float)byteOf(fz, j), adjDir.z, adjOrg.z);
-                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar));
-                    if (tn <= tf * 1.000001f) {                      // conservative: rounding must never cull an exact tie
-                        hitMask |= byteOf(childBits4, j) << byteOf(bitIndex4, j);
-                    }
+#define HR_CHILD(J)                                                                                                    \
+                {                                                                                                      \
+                    const float tnx = fmaf(byteToFloat<J>(nx), adjDir.x, adjOrg.x), tfx = fmaf(byteToFloat<J>(fx), adjDir.x, adjOrg.x); \
+                    const float tny = fmaf(byteToFloat<J>(ny), adjDir.y, adjOrg.y), tfy = fmaf(byteToFloat<J>(fy), adjDir.y, adjOrg.y); \
+                    const float tnz = fmaf(byteToFloat<J>(nz), adjDir.z, adjOrg.z), tfz = fmaf(byteToFloat<J>(fz), adjDir.z, adjOrg.z); \
+                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                          \
+                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar));                                          \
+                    if (tn <= tf * 1.000001f) /* conservative: rounding must never cull an exact tie */                 \
+                        hitMask |= byteOf(childBits4, J) << byteOf(bitIndex4, J);                                       \
                 }
+                HR_CHILD(0) HR_CHILD(1) HR_CHILD(2) HR_CHILD(3)
+#undef HR_CHILD
             }
             group.x = __float_as_uint(n1.x);
             group.y = (hitMask & 0xff000000u) | (eimask >> 24);
@@ -338,7 +357,7 @@ __device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const
             if (STATS) tc.tris++;
             float t, u, v; bool back;
             if (triangleTest(a, b, c, o, d, tmin, tmaxRay, t, u, v, back)) {
-                if (ANY) return true;
+                if (ANY) { found = true; return false; }
                 const int prim = __float_as_int(a.w);
                 if (t < best.t || (t == best.t && prim < best.prim)) {
                     best.t = t; best.u = u; best.v = v; best.prim = prim; best.back = back; found = true;
@@ -347,11 +366,21 @@ __device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const
         }
 
         if ((group.y & 0xff000000u) == 0u) {
-            if (sp == 0) break;
+            if (sp == 0) return false;
             group = stack[--sp];
         }
+        return true;
     }
-    return found;
+};
+
+template <bool ANY, bool STATS>
+__device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const float4* __restrict__ tris,
+                                         float3 o, float3 d, float tmin, float tmaxRay, HitRec& best, TraceCounters& tc) {
+    Traversal tr; uint2 stack[kTraceStack];
+    tr.begin(o, d, tmin, tmaxRay);
+    while (tr.step<ANY, STATS>(nodes, tris, stack, tc)) {}
+    best = tr.best;
+    return tr.found;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -408,36 +437,66 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_co
     q.m[i] = make_uint2(0u | (missKind << 8) | ((uint32_t)sequenceID << 16), (uint32_t)sequenceIndex);
 }
 
-// Persistent traversal kernel: warps pull batches of 32 rays from the queue with one atomic per warp.
+// Persistent traversal kernel with dynamic refill: every lane owns one ray; when the number of lanes still traversing
+// drops below kRefillThreshold the warp pauses, the idle lanes pull fresh rays from the queue (one atomic per warp per
+// refill) and traversal resumes with the paused lanes' state intact. This keeps SIMT lanes busy on incoherent rays.
+constexpr int kRefillThreshold = 22;
+
 template <bool ANY, bool STATS>
 __global__ void __launch_bounds__(128) k_trace(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
     const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t below = (1u << lane) - 1u;
     IterCtrl* ctrl = pb.ctrl + iter;
     const uint32_t count = ANY ? ctrl->shadowCount : ctrl->extCount;
     uint32_t* head = ANY ? &ctrl->shadowHead : &ctrl->extHead;
     const RayQueue& rq = pb.ext[iter & 1];
+    const float4* __restrict__ qo = ANY ? pb.shadow.o : rq.o;
+    const float4* __restrict__ qd = ANY ? pb.shadow.d : rq.d;
     TraceCounters tc{0u, 0u, 0u};
+    Traversal tr;
+    uint2 stack[kTraceStack];
+    bool active = false, exhausted = false;
+    uint32_t rayIdx = 0;
+    float extraT = 0.f;
+
     for (;;) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(head, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= count) break;
-        const uint32_t i = base + lane;
-        if (i < count) {
-            const float4 ro = ANY ? pb.shadow.o[i] : rq.o[i];
-            const float4 rd = ANY ? pb.shadow.d[i] : rq.d[i];
-            HitRec h;
-            const bool hit = traverse<ANY, STATS>(sc.nodes, sc.tris, xyz(ro), xyz(rd), 0.0f, ro.w, h, tc);
-            if (ANY) {
-                if (!hit) {   // the ray reached its light: run the light shader (policy A-5/A-6)
-                    const float4 w = pb.shadow.w[i];
-                    const uint32_t bits = __float_as_uint(w.w);
-                    shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, xyz(rd), xyz(w), ro.w, rd.w);
+        if (!exhausted) {
+            const uint32_t need = __ballot_sync(0xffffffffu, !active);
+            if (need) {
+                const uint32_t n = __popc(need);
+                const int leader = __ffs(need) - 1;
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(head, n);
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (!active) {
+                    const uint32_t i = base + __popc(need & below);
+                    if (i < count) {
+                        const float4 ro = qo[i], rd = qd[i];
+                        rayIdx = i; extraT = rd.w;
+                        tr.begin(xyz(ro), xyz(rd), 0.0f, ro.w);
+                        active = true;
+                    }
                 }
-            } else {
-                pb.hits[i] = hit ? make_float4(h.t, h.u, h.v, __int_as_float(h.prim | (h.back ? HRC_HIT_BACKFACE : 0)))
-                                 : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                if (base + n >= count) exhausted = true;
             }
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+        while (active) {
+            if (!tr.step<ANY, STATS>(sc.nodes, sc.tris, stack, tc)) {
+                active = false;
+                if (ANY) {
+                    if (!tr.found) {   // the ray reached its light: run the light shader (policy A-5/A-6)
+                        const float4 w = pb.shadow.w[rayIdx];
+                        const uint32_t bits = __float_as_uint(w.w);
+                        shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, extraT);
+                    }
+                } else {
+                    pb.hits[rayIdx] = tr.found ? make_float4(tr.best.t, tr.best.u, tr.best.v, __int_as_float(tr.best.prim | (tr.best.back ? HRC_HIT_BACKFACE : 0)))
+                                               : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                }
+                break;
+            }
+            if (!exhausted && __popc(__activemask()) < kRefillThreshold) break;
         }
     }
     if (STATS) {
