@@ -1,4 +1,4 @@
-"""In-tree build of libheatray_cuda.so (sm_100a only) and of the CPU oracle used by the tests.
+"""In-tree build of libheatray_cuda.so (sm_100a only).
 
     python -m heatray_b200.build            # build everything that is out of date
     python -m heatray_b200.build --force
@@ -68,28 +68,8 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     return LIB
 
 
-def build_oracle(force: bool = False) -> None:
-    odir = ROOT / "oracle"
-    args = ["make", "-C", str(odir)]
-    if force:
-        args.append("-B")
-    res = subprocess.run(args, capture_output=True, text=True)
-    if res.returncode != 0:
-        sys.stderr.write(res.stdout + res.stderr)
-        raise RuntimeError("oracle build failed")
-    ref = odir / "ref_probe" / "build_ref.sh"
-    if Path("/root/reference/Source").is_dir() and ref.exists():
-        have = all((odir / "_ref" / n).exists() for n in ("libref_qmc.so", "libref_lut.so", "libref_rlsl.so"))
-        if force or not have:
-            res = subprocess.run(["sh", str(ref)], capture_output=True, text=True)
-            if res.returncode != 0:
-                sys.stderr.write(res.stdout + res.stderr)
-                raise RuntimeError("oracle/_ref build failed")
-
-
 def build_all(force: bool = False, verbose: bool = False) -> None:
     build_cuda(force, verbose)
-    build_oracle(force)
 
 
 if __name__ == "__main__":

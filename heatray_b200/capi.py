@@ -122,6 +122,20 @@ class HrhGlassMaterial(C.Structure):
     _fields_ = [("baseColor", f32 * 3), ("roughness", f32), ("ior", f32), ("density", f32)]
 
 
+class RenderOptions(C.Structure):       # HrhRenderOptions ↔ PassGenerator::RenderOptions (PassGenerator.h:49-150)
+    _fields_ = [("enableInteractiveMode", i32), ("enableOfflineMode", i32), ("resetInternalState", i32),
+                ("maxRenderPasses", u32), ("maxRayDepth", u32), ("maxChannelValue", f32),
+                ("envEnabled", i32), ("envUseSolidColor", i32), ("envSolidColor", f32 * 3), ("envTexture", i32),
+                ("envExposureCompensation", f32), ("envThetaRotation", f32),
+                ("aspectRatio", f32), ("focusDistance", f32), ("focalLength", f32), ("apertureRadius", f32), ("fstop", f32),
+                ("viewMatrix", f32 * 16), ("sampleMode", i32), ("bokehShape", i32), ("debugVisMode", i32),
+                ("debugPassRendering", i32), ("debugPassIndex", i32)]
+
+
+PASS_COMPLETE_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, i32, fp, i32, i32, f32, u64)
+CONTEXT_TASK = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p)
+
+
 # names of every exported symbol of the backend C-ABI (checked by tests/test_abi.py against the header)
 BACKEND_SYMBOLS = [
     "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels",
@@ -170,6 +184,15 @@ def _declare_host(lib):
     lib.hrhFovTan.argtypes = [f32]
     lib.hrhApertureRadius.restype = f32
     lib.hrhApertureRadius.argtypes = [f32, f32]
+    lib.hrhDefaultRenderOptions.argtypes = [C.POINTER(RenderOptions)]
+    lib.hrhPassGeneratorCreate.argtypes = [i32, i32, i32, C.POINTER(C.c_void_p)]
+    lib.hrhPassGeneratorDestroy.argtypes = [C.c_void_p]
+    lib.hrhPassGeneratorResize.argtypes = [C.c_void_p, i32, i32]
+    lib.hrhPassGeneratorRenderPass.argtypes = [C.c_void_p, C.POINTER(RenderOptions), PASS_COMPLETE_CALLBACK, C.c_void_p]
+    lib.hrhPassGeneratorRunTask.argtypes = [C.c_void_p, CONTEXT_TASK, C.c_void_p]
+    lib.hrhPassGeneratorWaitIdle.argtypes = [C.c_void_p]
+    lib.hrhPassGeneratorLastError.restype = C.c_char_p
+    lib.hrhPassGeneratorLastError.argtypes = [C.c_void_p]
     lib.hrhPlaneMesh.argtypes = [f32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.hrhSphereMesh.argtypes = [i32, i32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(u32), C.POINTER(u32)]
 
@@ -181,9 +204,10 @@ def _ptr(a):
 class Backend:
     """Object view of one backend context: the calls a reference-side RLWrapper shim would make."""
 
-    def __init__(self, lib: C.CDLL, prefix: str = "hrc", device: int = 0, collect_stats: bool = False):
+    def __init__(self, lib: C.CDLL, prefix: str = "hrc", device: int = 0, collect_stats: bool = False, borrowed_ctx=None):
         self.lib, self.prefix = lib, prefix
         self._fn = {}
+        self._owns = borrowed_ctx is None
         for name in BACKEND_SYMBOLS:
             try:
                 self._fn[name] = getattr(lib, prefix + name)
@@ -192,12 +216,15 @@ class Backend:
                     raise
         self._fn["GetLastError"].restype = C.c_char_p
         self._fn["GetLastError"].argtypes = [C.c_void_p]
+        self.width = self.height = 0
+        if borrowed_ctx is not None:          # a context owned by hr::PassGenerator (inside a task callback)
+            self.ctx = C.c_void_p(borrowed_ctx)
+            return
         self.ctx = C.c_void_p()
         desc = ContextDesc(device, int(collect_stats))
         rc = self._fn["CreateContext"](C.byref(desc), C.byref(self.ctx))
         if rc != HRC_OK:
             raise HrcError(rc, (self._fn["GetLastError"](None) or b"").decode())
-        self.width = self.height = 0
         self._keep = []
 
     # -- plumbing ---------------------------------------------------------------------------
@@ -207,7 +234,7 @@ class Backend:
             raise HrcError(rc, (self._fn["GetLastError"](self.ctx) or b"").decode())
 
     def close(self):
-        if self.ctx:
+        if self.ctx and self._owns:
             self._fn["DestroyContext"](self.ctx)
             self.ctx = C.c_void_p()
 

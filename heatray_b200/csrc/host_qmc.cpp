@@ -10,7 +10,7 @@
 // them through hrcSetSequences()/hrcSetPixelTables().
 //
 // Bit-exactness against the reference generators is checked by tests/test_qmc.py against
-// tests/golden/qmc_ref.json (written by oracle/ref_probe from the reference's own Random.h).
+// tests/golden/qmc_ref.json (tables written by the reference's own Random.h compiled in place).
 
 #include "host_api.h"
 

@@ -144,10 +144,12 @@ def _value_noise(x, y, seed):
     xi, yi = np.floor(x).astype(np.int64), np.floor(y).astype(np.int64)
     fx, fy = x - xi, y - yi
 
+    k = np.uint64((seed * 2654435761) & 0xFFFFFFFF)
+
     def h(a, b):
-        v = (a * 374761393 + b * 668265263 + seed * 1442695040888963407) & 0xFFFFFFFF
-        v = ((v ^ (v >> 13)) * 1274126177) & 0xFFFFFFFF
-        return ((v ^ (v >> 16)) & 0xFFFF) / 65535.0
+        v = (a.astype(np.uint64) * np.uint64(374761393) + b.astype(np.uint64) * np.uint64(668265263) + k) & np.uint64(0xFFFFFFFF)
+        v = ((v ^ (v >> np.uint64(13))) * np.uint64(1274126177)) & np.uint64(0xFFFFFFFF)
+        return ((v ^ (v >> np.uint64(16))) & np.uint64(0xFFFF)).astype(np.float64) / 65535.0
 
     sx, sy = fx * fx * (3 - 2 * fx), fy * fy * (3 - 2 * fy)
     a, b = h(xi, yi), h(xi + 1, yi)

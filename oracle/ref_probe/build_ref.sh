@@ -15,4 +15,5 @@ g++ $FL -shared ref_lut.cpp ref_lut_stubs.cpp /tmp/ref_c_stubs.o -o "$OUT/libref
 grep -v '^#include' "$REF/Resources/shaders/utility.rlsl" | sed 's/dot(st\.xy,/dot(st,/' > /tmp/ref_rlsl_utility.inc
 grep -v '^#include' "$REF/Resources/shaders/brdfs.rlsl" > /tmp/ref_rlsl_brdfs.inc
 g++ -std=c++20 -O2 -fPIC -shared -fsingle-precision-constant -I$REF/3rdParty -I$REF/3rdParty/glm -w ref_rlsl.cpp -o "$OUT/libref_rlsl.so"
+g++ $FL -DGLM_ENABLE_EXPERIMENTAL -shared ref_host.cpp -o "$OUT/libref_host.so"
 echo "oracle/_ref built"

@@ -1,0 +1,98 @@
+"""hr::PassGenerator (the C++ pass interface, heatray_b200/csrc/host_pass_generator.cpp) driven the way HeatrayRenderer
+drives the reference's PassGenerator (HeatrayRenderer.cpp:366-408): async enqueue, worker-thread callbacks, mapped pixels."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+
+from heatray_b200 import capi, renderer, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def _options(lib, spec, w, h, **kw):
+    o = capi.RenderOptions()
+    lib.hrhDefaultRenderOptions(C.byref(o))
+    o.enableInteractiveMode = 0
+    o.maxRenderPasses, o.maxRayDepth = spec.passes, spec.max_depth
+    o.envEnabled = 0
+    cam = spec.camera
+    o.aspectRatio, o.focusDistance, o.focalLength = w / h, cam["focus_distance"], cam["focal_length"]
+    vm = (C.c_float * 16)()
+    lib.hrhOrbitCameraViewMatrix(cam["distance"], cam["phi"], cam["theta"], (C.c_float * 3)(*cam["target"]), vm)
+    o.viewMatrix = vm
+    for k, v in kw.items():
+        setattr(o, k, v)
+    return o
+
+
+def test_pass_generator_matches_direct_backend(lib, gpu_backend):
+    spec = scenes.cornell_box(width=64, height=48, passes=4)
+    w, h = spec.width, spec.height
+    # direct path
+    rg = renderer.Renderer(gpu_backend)
+    rg.load_scene(spec)
+    for _ in range(3):
+        rg.render_pass()
+    want = rg.pixels()
+
+    pg = C.c_void_p()
+    assert lib.hrhPassGeneratorCreate(0, w, h, C.byref(pg)) == 0, lib.hrhPassGeneratorLastError(pg)
+    try:
+        def load(user, ctx):                                   # ↔ loadScene callback on the worker thread
+            b = capi.Backend(lib, "hrc", borrowed_ctx=ctx)
+            b.width, b.height = w, h
+            renderer.Renderer(b).upload_scene(spec, set_environment=False)
+        task = capi.CONTEXT_TASK(load)
+        lib.hrhPassGeneratorRunTask(pg, task, None)
+        got = []
+
+        def done(user, available, pixels, pw, ph, seconds, index):
+            got.append((available, index, np.ctypeslib.as_array(pixels, shape=(ph, pw, 4)).copy() if available else None, seconds))
+        cb = capi.PASS_COMPLETE_CALLBACK(done)
+        o = _options(lib, spec, w, h)
+        for i in range(3):
+            o.resetInternalState = 1 if i == 0 else 0
+            lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)      # returns immediately (asynchronous enqueue)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert lib.hrhPassGeneratorLastError(pg) == b""
+        assert [g[0] for g in got] == [1, 1, 1] and [g[1] for g in got] == [1, 2, 3]
+        assert np.array_equal(got[-1][2], want)
+        assert (got[0][2][..., 3] == 1).all()
+
+        # offline mode: all passes inside one job, pixels only at the end (PassGenerator.cpp:346-400)
+        got.clear()
+        o.enableOfflineMode, o.resetInternalState = 1, 1
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert [g[0] for g in got] == [0, 0, 0, 1] and (got[-1][2][..., 3] == 4).all()
+
+        # debug pass rendering: exactly pass k (PassGenerator.cpp:570-572) and a debug visualiser (showShader: red for PBR)
+        got.clear()
+        o.enableOfflineMode, o.resetInternalState, o.debugPassRendering, o.debugPassIndex = 0, 1, 1, 2
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        o.debugPassRendering, o.debugVisMode = 0, 14
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert got[0][1] == 3
+        vis = got[1][2]
+        hit = vis[..., 3] == 2
+        assert hit.any() and np.allclose(vis[hit][:, :3], [1, 0, 0])
+
+        # resize forces a reset and new pixel tables (PassGenerator.cpp:301-323)
+        got.clear()
+        lib.hrhPassGeneratorResize(pg, 32, 32)
+        o = _options(lib, spec, 32, 32)
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert got[0][2].shape == (32, 32, 4) and (got[0][2][..., 3] == 1).all()
+
+        # interactive block mode is reported, not silently ignored
+        got.clear()
+        o.enableInteractiveMode = 1
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert got[0][0] == 0 and b"interactive" in lib.hrhPassGeneratorLastError(pg)
+    finally:
+        lib.hrhPassGeneratorDestroy(pg)
