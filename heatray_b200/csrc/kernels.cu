@@ -30,7 +30,7 @@ __device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a
 __device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ float3 operator/(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ float3 operator/(float3 a, float s) { const float r = 1.0f / s; return f3(a.x * r, a.y * r, a.z * r); }   // one IEEE reciprocal, <= 1 ulp from a true division
 __device__ __forceinline__ float dot(float3 a, float3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 __device__ __forceinline__ float3 cross(float3 a, float3 b) { return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 __device__ __forceinline__ float3 normalize(float3 a) { return a * (1.0f / sqrtf(dot(a, a))); }
@@ -172,6 +172,18 @@ __device__ __forceinline__ float2 getSequenceValue(const DScene& sc, const DFram
     int wv = sampleIndex % fr.sequenceLength;
     return __ldg(&sc.seq[ws * fr.sequenceLength + wv]);
 }
+// The material shaders read sequences (id + depth + k), k = 0..4, at one sample index: the two integer modulos
+// (by run-time divisors) are hoisted out of the five lookups.
+struct SeqCursor {
+    const float2* col; int base, ns, len;
+    __device__ __forceinline__ SeqCursor(const DScene& sc, const DFrame& fr, int sequenceIndex, int sampleIndex)
+        : col(sc.seq + sampleIndex % fr.sequenceLength), base(sequenceIndex % fr.numSequences), ns(fr.numSequences), len(fr.sequenceLength) {}
+    __device__ __forceinline__ float2 at(int k) const {
+        int r = base + k;
+        while (r >= ns) r -= ns;
+        return __ldg(col + r * len);
+    }
+};
 
 // ---------------------------------------------------------------------------------------
 // Light ("miss") shaders
@@ -538,66 +550,53 @@ struct LightSample { float3 dir; uint32_t missKind, missIndex; float probability
 #define LIGHT_TYPE_SPOT 3
 #define LIGHT_TYPE_ENVIRONMENT 4
 
-// lightSampling.rlsl:11-161
-__device__ void computeLightSample(const DLights& L, float3 P, float3 N, float lightProbability, LightSample& ls) {
-    const int MAXL = HRC_MAX_LIGHTS_PER_TYPE;
+// lightSampling.rlsl:11-161. The shader fills three 5-entry weight arrays, normalises them and walks the CDF; here the
+// weights are evaluated twice (sum, then walk) by one small function instead, so nothing lives in local memory and the
+// loops stay rolled: identical fp32 values, a fraction of the code.
+__device__ __forceinline__ float lightWeight(const DLights& L, int type, int i, float3 P, float3 N, float3& dir) {
+    if (type == 0) {
+        dir = f3(L.dirDirection[i]);
+        return saturate(dot(N, dir)) * luminosity(f3(L.dirColor[i]));
+    }
+    if (type == 1) {
+        dir = normalize(f3(L.pointPosition[i]) - P);
+        return saturate(dot(N, dir)) * luminosity(f3(L.pointColor[i]));
+    }
+    dir = normalize(f3(L.spotPosition[i]) - P);
+    const float rayAngle = dot(f3(L.spotDirection[i]), -dir);
+    return saturate(dot(N, dir)) * luminosity(f3(L.spotColor[i])) *
+           ((rayAngle > 0.0f) ? 1.0f : 0.0f) *
+           ((rayAngle < L.spotAngles[i][1]) ? 0.0f : 1.0f) *
+           (1.0f - glslSmoothstep(L.spotAngles[i][0], L.spotAngles[i][1], rayAngle));
+}
+__device__ __noinline__ void computeLightSample(const DLights& L, float3 P, float3 N, float lightProbability, LightSample& ls) {
     float probabilitySum = 0.0f;
-    float directional[MAXL], point[MAXL], spot[MAXL];
-    float3 pointDir[MAXL], spotDir[MAXL];
-#pragma unroll
-    for (int i = 0; i < MAXL; ++i) {
-        directional[i] = 0.f; point[i] = 0.f; spot[i] = 0.f;
-        if (i < L.nDir) {
-            directional[i] = saturate(dot(N, f3(L.dirDirection[i]))) * luminosity(f3(L.dirColor[i]));
-            probabilitySum += directional[i];
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < MAXL; ++i) if (i < L.nPoint) {
-        pointDir[i] = normalize(f3(L.pointPosition[i]) - P);
-        point[i] = saturate(dot(N, pointDir[i])) * luminosity(f3(L.pointColor[i]));
-        probabilitySum += point[i];
-    }
-#pragma unroll
-    for (int i = 0; i < MAXL; ++i) if (i < L.nSpot) {
-        spotDir[i] = normalize(f3(L.spotPosition[i]) - P);
-        float rayAngle = dot(f3(L.spotDirection[i]), -spotDir[i]);
-        spot[i] = saturate(dot(N, spotDir[i])) * luminosity(f3(L.spotColor[i])) *
-                  ((rayAngle > 0.0f) ? 1.0f : 0.0f) *
-                  ((rayAngle < L.spotAngles[i][1]) ? 0.0f : 1.0f) *
-                  (1.0f - glslSmoothstep(L.spotAngles[i][0], L.spotAngles[i][1], rayAngle));
-        probabilitySum += spot[i];
+    float3 dir;
+#pragma unroll 1
+    for (int type = 0; type < 3; ++type) {
+        const int n = type == 0 ? L.nDir : (type == 1 ? L.nPoint : L.nSpot);
+#pragma unroll 1
+        for (int i = 0; i < n; ++i) probabilitySum += lightWeight(L, type, i, P, N, dir);
     }
     float environment = 0.0f;
     if (L.envEnabled) { environment = 50.0f * L.envExposure; probabilitySum += environment; }   // :77
     const float norm = 1.0f / greaterThanZero(probabilitySum);
     environment *= norm;
-#pragma unroll
-    for (int i = 0; i < MAXL; ++i) { directional[i] *= norm; point[i] *= norm; spot[i] *= norm; }
-
     float current = 0.0f;
-#pragma unroll
-    for (int i = 0; i < MAXL; ++i) if (i < L.nDir) {
-        current += directional[i];
-        if (directional[i] > 0.0f && lightProbability <= current) {
-            ls.dir = f3(L.dirDirection[i]); ls.missKind = kMissDir; ls.missIndex = i; ls.probability = directional[i];
-            ls.lightType = LIGHT_TYPE_DIRECTIONAL; return;
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < MAXL; ++i) if (i < L.nPoint) {
-        current += point[i];
-        if (point[i] > 0.0f && lightProbability <= current) {
-            ls.dir = pointDir[i]; ls.missKind = kMissPoint; ls.missIndex = i; ls.probability = point[i];
-            ls.maxDistance = length(f3(L.pointPosition[i]) - P); ls.lightType = LIGHT_TYPE_POINT; return;
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < MAXL; ++i) if (i < L.nSpot) {
-        current += spot[i];
-        if (spot[i] > 0.0f && lightProbability <= current) {
-            ls.dir = spotDir[i]; ls.missKind = kMissSpot; ls.missIndex = i; ls.probability = spot[i];
-            ls.maxDistance = length(f3(L.spotPosition[i]) - P); ls.lightType = LIGHT_TYPE_SPOT; return;
+#pragma unroll 1
+    for (int type = 0; type < 3; ++type) {
+        const int n = type == 0 ? L.nDir : (type == 1 ? L.nPoint : L.nSpot);
+#pragma unroll 1
+        for (int i = 0; i < n; ++i) {
+            const float w = lightWeight(L, type, i, P, N, dir) * norm;
+            current += w;
+            if (w > 0.0f && lightProbability <= current) {
+                ls.dir = dir; ls.missIndex = i; ls.probability = w;
+                if (type == 0) { ls.missKind = kMissDir; ls.lightType = LIGHT_TYPE_DIRECTIONAL; }
+                else if (type == 1) { ls.missKind = kMissPoint; ls.lightType = LIGHT_TYPE_POINT; ls.maxDistance = length(f3(L.pointPosition[i]) - P); }
+                else { ls.missKind = kMissSpot; ls.lightType = LIGHT_TYPE_SPOT; ls.maxDistance = length(f3(L.spotPosition[i]) - P); }
+                return;
+            }
         }
     }
     ls.lightType = LIGHT_TYPE_ENVIRONMENT;
@@ -610,98 +609,13 @@ __device__ __forceinline__ float3 computeMultiscattering(const DScene& sc, int l
     return f3(1.0f) + Cspec * ms;
 }
 
-// microfacet.rlsl:25-51
-__device__ void indirectDiffuseSample(const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 Cdiff,
-                                      float sampleProbability, float optLightProb, float2 rnd, const M3& frame, bool missEnv) {
-    float3 O = mul(frame, cosineWeightedSample(rnd.x, rnd.y));
-    float NdotO = dot(N, O);
-    if (NdotO > 0.0f) {
-        float3 reflectance = Cdiff * inWeight;
-        reflectance = reflectance / sampleProbability;
-        reflectance = reflectance / optLightProb;
-        if (dot(reflectance, reflectance) > 1e-5f) {
-            if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, __int_as_float(0x7f800000)); }
-            else emitExt(e, s, O, reflectance, kMissNone);
-        }
-    }
-}
-// microfacet.rlsl:53-98
-__device__ void directDiffuseSample(const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 Cdiff,
-                                    float sampleProbability, float lightProbability, float2 rnd, const M3& frame) {
-    LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
-    computeLightSample(fr.lights, s.P, N, lightProbability, ls);
-    if (ls.lightType != LIGHT_TYPE_ENVIRONMENT && lightProbability > 0.0f) {
-        float NdotO = dot(N, ls.dir);
-        if (NdotO > 0.0f) {
-            NdotO = saturate(NdotO);
-            float3 reflectance = ((Cdiff / K_PI) * NdotO) * inWeight;
-            reflectance = reflectance / sampleProbability;
-            reflectance = reflectance / ls.probability;
-            if (dot(reflectance, reflectance) > 1e-5f) {
-                float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : __int_as_float(0x7f800000);
-                emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
-            }
-        }
-    } else if (ls.probability > 0.0f) {
-        indirectDiffuseSample(fr, e, s, inWeight, N, Cdiff, sampleProbability, ls.probability, rnd, frame, true);
-    }
-}
-// microfacet.rlsl:100-153
-__device__ void indirectSpecularSample(const DScene& sc, const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 I, float NdotI,
-                                       float3 Cspec, float alpha, int lut, float roughness, float sampleProbability, float optLightProb,
-                                       float2 rnd, const M3& frame, bool missEnv) {
-    float3 H = mul(frame, sampleVisibleGGX(mulT(frame, I), rnd.x, rnd.y, alpha));
-    float IdotH = saturate(dot(I, H));
-    float3 O = normalize(2.0f * IdotH * H - I);
-    float NdotO = dot(N, O);
-    if (NdotO > 0.0f) {
-        NdotO = saturate(NdotO);
-        float3 F = F_Schlick3(Cspec, IdotH);
-        float G2 = G2_Smith_GGX(NdotI, NdotO, alpha);
-        float G1 = G1_Smith_GGX(NdotI, alpha);
-        float3 specular = (F * G2) / greaterThanZero(G1);
-        specular = specular * computeMultiscattering(sc, lut, Cspec, NdotI, roughness);
-        float3 reflectance = specular * inWeight;
-        reflectance = reflectance / sampleProbability;
-        reflectance = reflectance / optLightProb;
-        if (dot(reflectance, reflectance) > 1e-5f) {
-            if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, __int_as_float(0x7f800000)); }
-            else emitExt(e, s, O, reflectance, kMissNone);
-        }
-    }
-}
-// microfacet.rlsl:155-220
-__device__ void directSpecularSample(const DScene& sc, const DFrame& fr, Emit& e, const Surface& s, float3 inWeight, float3 N, float3 I, float NdotI,
-                                     float3 Cspec, float alpha, int lut, float roughness, float sampleProbability, float lightProbability,
-                                     float2 rnd, const M3& frame) {
-    LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
-    computeLightSample(fr.lights, s.P, N, lightProbability, ls);
-    if (ls.lightType != LIGHT_TYPE_ENVIRONMENT && lightProbability > 0.0f) {
-        float NdotO = dot(N, ls.dir);
-        if (NdotO > 0.0f) {
-            NdotO = saturate(NdotO);
-            float3 H = normalize(I + ls.dir);
-            float NdotH = saturate(dot(N, H));
-            float IdotH = saturate(dot(I, H));
-            float D = D_GGX(NdotH, alpha);
-            float3 F = F_Schlick3(Cspec, IdotH);
-            float G = G2_Smith_GGX(NdotO, NdotI, alpha);
-            float3 specular = (D * F * G) / greaterThanZero(4.0f * NdotI);
-            specular = specular * computeMultiscattering(sc, lut, Cspec, NdotI, roughness);
-            float3 reflectance = specular * inWeight;
-            reflectance = reflectance / sampleProbability;
-            reflectance = reflectance / ls.probability;
-            if (dot(reflectance, reflectance) > 1e-5f) {
-                float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : __int_as_float(0x7f800000);
-                emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
-            }
-        }
-    } else if (ls.probability > 0.0f) {
-        indirectSpecularSample(sc, fr, e, s, inWeight, N, I, NdotI, Cspec, alpha, lut, roughness, sampleProbability, ls.probability, rnd, frame, true);
-    }
-}
+// One BSDF lobe of the PBR material as the sample functions of microfacet.rlsl see it.
+struct Lobe { bool diffuse; float3 N; float NdotI; float3 C; float alpha, roughness, probability; };
+__device__ __forceinline__ float kInf() { return __int_as_float(0x7f800000); }
 
-// physicallyBased.rlsl:55-331. Returns true when the ray is re-emitted unchanged (single-sided back face).
+// physicallyBased.rlsl:55-331 with microfacet.rlsl:25-220 folded in. The direct (:236-274) and indirect (:277-329) halves
+// run as two trips of ONE loop so that every sample function exists once in the instruction stream: the first version
+// inlined each of them at 2-3 call sites, the kernel grew to ~200 KB of SASS and stalled on instruction fetch.
 __device__ void shadePBR(const DScene& sc, const DFrame& fr, float4* accum, const InRay& in, const DMaterial& m, const Surface& s,
                          float3 interpNormal, bool frontFacing, Emit& e) {
     const HrcGlobals& g = fr.g;
@@ -742,86 +656,98 @@ __device__ void shadePBR(const DScene& sc, const DFrame& fr, float4* accum, cons
     const float diffuseLuminance = luminosity(Cdiff), specularLuminance = luminosity(Cspec);
     const float pn = 1.0f / greaterThanZero(diffuseLuminance + specularLuminance + clearCoatScale);
     const float diffuseProbability = diffuseLuminance * pn, specularProbability = specularLuminance * pn, clearCoatProbability = clearCoatScale * pn;
-    const int sidx = g.sampleIndex + in.sequenceIndexOffset;
-    const int sq = (int)in.sequenceID + (int)in.depth;
+    const SeqCursor seq(sc, fr, (int)in.sequenceID + (int)in.depth, g.sampleIndex + in.sequenceIndexOffset);
 
-    {   // direct lighting, :236-274
-        const float2 rnd = getSequenceValue(sc, fr, sq, sidx);
-        const float2 pr = getSequenceValue(sc, fr, sq + 1, sidx);
-        if (pr.x <= diffuseProbability)
-            directDiffuseSample(fr, e, s, weight, N, Cdiff, diffuseProbability, pr.y, rnd, frame);
-        else if (pr.x <= (diffuseProbability + clearCoatProbability))
-            directSpecularSample(sc, fr, e, s, weight, clearCoatN, V, clearCoatNdotV, f3(clearCoatScale), m.clearCoatRoughnessAlpha, m.lutTex,
-                                 m.clearCoatRoughness, clearCoatProbability, pr.y, rnd, frame);
-        else if (pr.x <= (diffuseProbability + clearCoatProbability + specularProbability))
-            directSpecularSample(sc, fr, e, s, weight, N, V, NdotV, Cspec, m.roughnessAlpha, m.lutTex, m.roughness, specularProbability, pr.y, rnd, frame);
-    }
-    if ((int)in.depth < g.maxRayDepth) {                                      // :277-329
-        if (in.depth > 3) {
-            const float2 rr = getSequenceValue(sc, fr, sq + 2, sidx);
-            const float probability = fmaxf(weight.x, fmaxf(weight.y, weight.z));
-            if (rr.x >= probability) return;
-            weight = weight / probability;
+#pragma unroll 1
+    for (int phase = 0; phase < 2; ++phase) {                                 // 0: direct lighting :236-274, 1: indirect :277-329
+        if (phase == 1) {
+            if (!((int)in.depth < g.maxRayDepth)) return;
+            if (in.depth > 3) {                                               // Russian roulette, :279-288 (quirk B-Q12)
+                const float2 rr = seq.at(2);
+                const float probability = fmaxf(weight.x, fmaxf(weight.y, weight.z));
+                if (rr.x >= probability) return;
+                weight = weight / probability;
+            }
         }
-        const float2 rnd = getSequenceValue(sc, fr, sq + 3, sidx);
-        const float2 pr = getSequenceValue(sc, fr, sq + 4, sidx);
-        if (pr.x <= diffuseProbability)
-            indirectDiffuseSample(fr, e, s, weight, N, Cdiff, diffuseProbability, 1.0f, rnd, frame, false);
-        else if (pr.x <= (diffuseProbability + clearCoatProbability))
-            indirectSpecularSample(sc, fr, e, s, weight, clearCoatN, V, clearCoatNdotV, f3(clearCoatScale), m.clearCoatRoughnessAlpha, m.lutTex,
-                                   m.clearCoatRoughness, clearCoatProbability, 1.0f, rnd, frame, false);
-        else if (pr.x <= (diffuseProbability + clearCoatProbability + specularProbability))
-            indirectSpecularSample(sc, fr, e, s, weight, N, V, NdotV, Cspec, m.roughnessAlpha, m.lutTex, m.roughness, specularProbability, 1.0f, rnd, frame, false);
-    }
-}
+        const float2 rnd = seq.at(phase ? 3 : 0);
+        const float2 pr = seq.at(phase ? 4 : 1);
+        Lobe lb;
+        if (pr.x <= diffuseProbability) {
+            lb.diffuse = true; lb.N = N; lb.NdotI = NdotV; lb.C = Cdiff; lb.alpha = 0.f; lb.roughness = 0.f; lb.probability = diffuseProbability;
+        } else if (pr.x <= (diffuseProbability + clearCoatProbability)) {
+            lb.diffuse = false; lb.N = clearCoatN; lb.NdotI = clearCoatNdotV; lb.C = f3(clearCoatScale); lb.alpha = m.clearCoatRoughnessAlpha;
+            lb.roughness = m.clearCoatRoughness; lb.probability = clearCoatProbability;
+        } else if (pr.x <= (diffuseProbability + clearCoatProbability + specularProbability)) {
+            lb.diffuse = false; lb.N = N; lb.NdotI = NdotV; lb.C = Cspec; lb.alpha = m.roughnessAlpha; lb.roughness = m.roughness; lb.probability = specularProbability;
+        } else continue;
 
-// glass.rlsl:47-78
-__device__ void indirectSpecularGlassSample(const DFrame& fr, Emit& e, const Surface& s, float3 N, float3 I, float NdotI, float3 weight, float3 baseColor,
-                                            float alpha, float matAlpha, float optLightProb, float2 rnd, const M3& frame, bool missEnv) {
-    float3 H = mul(frame, sampleVisibleGGX(mulT(frame, I), rnd.x, rnd.y, alpha));
-    float IdotH = saturate(dot(I, H));
-    float3 O = normalize(2.0f * IdotH * H - I);
-    float NdotO = dot(N, O);
-    if (NdotO > 0.0f) {
-        NdotO = saturate(NdotO);
-        float NdotH = saturate(dot(N, H));
-        float G = G2_Smith_GGX(NdotO, NdotI, matAlpha);                      // Material.roughnessAlpha (quirk B-Q20)
-        float3 reflectance = baseColor * ((G * IdotH) / (NdotH * NdotI));
-        reflectance = reflectance * weight;
+        float optLightProb = 1.0f;
+        bool missEnv = false;
+        if (phase == 0) {                                                     // directDiffuseSample :53-98 / directSpecularSample :155-220
+            LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
+            computeLightSample(fr.lights, s.P, lb.N, pr.y, ls);
+            if (ls.lightType != LIGHT_TYPE_ENVIRONMENT && pr.y > 0.0f) {      // quirk B-Q11
+                float NdotO = dot(lb.N, ls.dir);
+                if (NdotO > 0.0f) {
+                    NdotO = saturate(NdotO);
+                    float3 reflectance;
+                    if (lb.diffuse) {
+                        reflectance = ((lb.C / K_PI) * NdotO) * weight;
+                    } else {
+                        const float3 H = normalize(V + ls.dir);
+                        const float NdotH = saturate(dot(lb.N, H));
+                        const float IdotH = saturate(dot(V, H));
+                        const float D = D_GGX(NdotH, lb.alpha);
+                        const float3 F = F_Schlick3(lb.C, IdotH);
+                        const float G = G2_Smith_GGX(NdotO, lb.NdotI, lb.alpha);
+                        float3 specular = (D * F * G) / greaterThanZero(4.0f * lb.NdotI);
+                        specular = specular * computeMultiscattering(sc, m.lutTex, lb.C, lb.NdotI, lb.roughness);
+                        reflectance = specular * weight;
+                    }
+                    reflectance = reflectance / lb.probability;
+                    reflectance = reflectance / ls.probability;
+                    if (dot(reflectance, reflectance) > 1e-5f) {
+                        const float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : kInf();
+                        emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
+                    }
+                }
+                continue;
+            }
+            if (!(ls.probability > 0.0f)) continue;
+            optLightProb = ls.probability;                                    // environment: BSDF-sampled occlusion ray (quirk B-Q8)
+            missEnv = true;
+        }
+        // indirectDiffuseSample :25-51 / indirectSpecularSample :100-153
+        float3 O, reflectance;
+        if (lb.diffuse) {
+            O = mul(frame, cosineWeightedSample(rnd.x, rnd.y));
+            if (!(dot(lb.N, O) > 0.0f)) continue;
+            reflectance = lb.C * weight;
+        } else {
+            const float3 H = mul(frame, sampleVisibleGGX(mulT(frame, V), rnd.x, rnd.y, lb.alpha));
+            const float IdotH = saturate(dot(V, H));
+            O = normalize(2.0f * IdotH * H - V);
+            float NdotO = dot(lb.N, O);
+            if (!(NdotO > 0.0f)) continue;
+            NdotO = saturate(NdotO);
+            const float3 F = F_Schlick3(lb.C, IdotH);
+            const float G2 = G2_Smith_GGX(lb.NdotI, NdotO, lb.alpha);
+            const float G1 = G1_Smith_GGX(lb.NdotI, lb.alpha);
+            float3 specular = (F * G2) / greaterThanZero(G1);
+            specular = specular * computeMultiscattering(sc, m.lutTex, lb.C, lb.NdotI, lb.roughness);
+            reflectance = specular * weight;
+        }
+        reflectance = reflectance / lb.probability;
         reflectance = reflectance / optLightProb;
         if (dot(reflectance, reflectance) > 1e-5f) {
-            if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, __int_as_float(0x7f800000)); }
+            if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, kInf()); }
             else emitExt(e, s, O, reflectance, kMissNone);
         }
     }
 }
-// glass.rlsl:80-129
-__device__ void directSpecularGlassSample(const DFrame& fr, Emit& e, const Surface& s, float3 N, float3 I, float NdotI, float3 weight, float3 baseColor,
-                                          float alpha, float matAlpha, float lightProbability, float2 rnd, const M3& frame) {
-    LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
-    computeLightSample(fr.lights, s.P, N, lightProbability, ls);
-    if (ls.lightType != LIGHT_TYPE_ENVIRONMENT) {
-        float NdotO = dot(N, ls.dir);
-        if (NdotO > 0.0f) {
-            NdotO = saturate(NdotO);
-            float3 H = normalize(I + ls.dir);
-            float NdotH = saturate(dot(N, H));
-            float D = D_GGX(NdotH, alpha);
-            float G = G2_Smith_GGX(NdotO, NdotI, alpha);
-            float specular = (D * G) / greaterThanZero(4.0f * NdotI);
-            float3 reflectance = specular * baseColor;
-            reflectance = reflectance * weight;
-            reflectance = reflectance / ls.probability;
-            if (dot(reflectance, reflectance) > 1e-5f) {
-                float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : __int_as_float(0x7f800000);
-                emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
-            }
-        }
-    } else if (ls.probability > 0.0f) {
-        indirectSpecularGlassSample(fr, e, s, N, I, NdotI, weight, baseColor, alpha, matAlpha, ls.probability, rnd, frame, true);
-    }
-}
-// glass.rlsl:138-280
+
+// glass.rlsl:138-280 with the sample functions (:47-129) folded in; the reflection branch runs its direct and indirect
+// halves as two trips of one loop (see shadePBR).
 __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, const InRay& in, const DMaterial& m, const Surface& s,
                            float3 interpNormal, bool frontFacing, Emit& e) {
     const HrcGlobals& g = fr.g;
@@ -846,22 +772,22 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
     }
     const M3 frame = orthonormalFrame(N);
     const float3 I = -in.d;
+    const float3 localI = mulT(frame, I);
     const float eta = nIn / nOut;
-    const int sidx = g.sampleIndex + in.sequenceIndexOffset;
-    const int sq = (int)in.sequenceID + (int)in.depth;
-    float2 rnd = getSequenceValue(sc, fr, sq, sidx);
-    const float3 H = mul(frame, sampleVisibleGGX(mulT(frame, I), rnd.x, rnd.y, roughnessAlpha));
-    const float HdotI = saturate(dot(H, I));
-    float2 rp = getSequenceValue(sc, fr, sq + 1, sidx);
+    const SeqCursor seq(sc, fr, (int)in.sequenceID + (int)in.depth, g.sampleIndex + in.sequenceIndexOffset);
+    float2 rnd = seq.at(0);
+    const float3 H0 = mul(frame, sampleVisibleGGX(localI, rnd.x, rnd.y, roughnessAlpha));
+    const float HdotI = saturate(dot(H0, I));
+    float2 rp = seq.at(1);
     const float F = F_Fresnel(eta, HdotI);
     const float NdotI = saturate(dot(N, I));
     if (!frontFacing) rp.y = 0.0f;                                            // :227-231
     if (rp.y < (1.0f - F)) {                                                  // :234-256 refraction
         const float3 mI = -I;
-        const float dNI = dot(H, mI);
+        const float dNI = dot(H0, mI);
         const float k = 1.0f - eta * eta * (1.0f - dNI * dNI);
         if (k < 0.0f) return;                                                 // refract() == 0 (policy A-16)
-        const float3 R = eta * mI - (eta * dNI + sqrtf(k)) * H;
+        const float3 R = eta * mI - (eta * dNI + sqrtf(k)) * H0;
         if (dot(R, R) == 0.0f) return;
         const float3 O = normalize(R);
         const float NdotO = fabsf(dot(N, O));
@@ -871,18 +797,64 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
         transmission = transmission * weight;
         if (dot(transmission, transmission) > 1e-5f && (int)in.depth < g.maxRayDepth)
             emitExt(e, s, O, transmission, fr.lights.envEnabled ? kMissEnv : kMissNone);
-    } else {                                                                  // :257-279 reflection
-        rnd = getSequenceValue(sc, fr, sq + 2, sidx);
-        directSpecularGlassSample(fr, e, s, N, I, NdotI, weight, baseColor, roughnessAlpha, m.roughnessAlpha, rp.x, rnd, frame);
-        if ((int)in.depth < g.maxRayDepth) {
-            if (in.depth > 3) {
-                const float2 rr = getSequenceValue(sc, fr, sq + 3, sidx);
+        return;
+    }
+    // :257-279 reflection
+#pragma unroll 1
+    for (int phase = 0; phase < 2; ++phase) {
+        float optLightProb = 1.0f;
+        bool missEnv = false;
+        if (phase == 0) {                                                     // directSpecularGlassSample :80-129
+            rnd = seq.at(2);
+            LightSample ls; ls.maxDistance = 0.f; ls.missKind = 0; ls.missIndex = 0; ls.dir = f3(0.f);
+            computeLightSample(fr.lights, s.P, N, rp.x, ls);
+            if (ls.lightType != LIGHT_TYPE_ENVIRONMENT) {
+                float NdotO = dot(N, ls.dir);
+                if (NdotO > 0.0f) {
+                    NdotO = saturate(NdotO);
+                    const float3 H = normalize(I + ls.dir);
+                    const float NdotH = saturate(dot(N, H));
+                    const float D = D_GGX(NdotH, roughnessAlpha);
+                    const float G = G2_Smith_GGX(NdotO, NdotI, roughnessAlpha);
+                    const float specular = (D * G) / greaterThanZero(4.0f * NdotI);
+                    float3 reflectance = specular * baseColor;
+                    reflectance = reflectance * weight;
+                    reflectance = reflectance / ls.probability;
+                    if (dot(reflectance, reflectance) > 1e-5f) {
+                        const float maxT = (ls.lightType == LIGHT_TYPE_POINT || ls.lightType == LIGHT_TYPE_SPOT) ? ls.maxDistance : kInf();
+                        emitOcc(e, s, ls.dir, reflectance, ls.missKind, ls.missIndex, maxT);
+                    }
+                }
+                continue;
+            }
+            if (!(ls.probability > 0.0f)) continue;
+            optLightProb = ls.probability; missEnv = true;
+        } else {
+            if (!((int)in.depth < g.maxRayDepth)) return;
+            if (in.depth > 3) {                                               // :265-274
+                const float2 rr = seq.at(3);
                 const float probability = fmaxf(weight.x, fmaxf(weight.y, weight.z));
                 if (rr.x >= probability) return;
                 weight = weight / probability;
             }
-            rnd = getSequenceValue(sc, fr, sq + 4, sidx);
-            indirectSpecularGlassSample(fr, e, s, N, I, NdotI, weight, baseColor, roughnessAlpha, m.roughnessAlpha, 1.0f, rnd, frame, false);
+            rnd = seq.at(4);
+        }
+        // indirectSpecularGlassSample :47-78
+        const float3 H = mul(frame, sampleVisibleGGX(localI, rnd.x, rnd.y, roughnessAlpha));
+        const float IdotH = saturate(dot(I, H));
+        const float3 O = normalize(2.0f * IdotH * H - I);
+        float NdotO = dot(N, O);
+        if (NdotO > 0.0f) {
+            NdotO = saturate(NdotO);
+            const float NdotH = saturate(dot(N, H));
+            const float G = G2_Smith_GGX(NdotO, NdotI, m.roughnessAlpha);     // Material.roughnessAlpha (quirk B-Q20)
+            float3 reflectance = baseColor * ((G * IdotH) / (NdotH * NdotI));
+            reflectance = reflectance * weight;
+            reflectance = reflectance / optLightProb;
+            if (dot(reflectance, reflectance) > 1e-5f) {
+                if (missEnv) { if (fr.lights.envEnabled) emitOcc(e, s, O, reflectance, kMissEnv, 0, kInf()); }
+                else emitExt(e, s, O, reflectance, kMissNone);
+            }
         }
     }
 }
