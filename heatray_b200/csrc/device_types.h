@@ -48,11 +48,11 @@ struct DFrame {
 };
 
 // Wavefront queues (structure of arrays; one slot per in-flight ray).
+// Extension rays are two arrays of 32-byte records (one L2 sector each), because the shade kernels gather them through
+// the per-class index lists while the traversal kernel streams only the first one:
 struct RayQueue {
-    float4* o;     // origin.xyz, tmax
-    float4* d;     // direction.xyz, extraT
-    float4* w;     // weight.xyz, pixel index (int bits)
-    uint2*  m;     // x: depth | missKind<<8 | missIndex<<12 | sequenceID<<16 ; y: sequenceIndexOffset
+    float4* od;    // [2i]   origin.xyz, tmax            [2i+1] direction.xyz, extraT
+    float4* wm;    // [2i]   weight.xyz, pixel (bits)    [2i+1] x: depth | missKind<<8 | sequenceID<<16 (bits), y: sequenceIndexOffset (bits)
 };
 struct ShadowQueue {
     float4* o;     // origin.xyz, tmax
@@ -61,7 +61,7 @@ struct ShadowQueue {
 };
 
 // Per-iteration control words, zeroed at the start of every pass.
-struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; };
+struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; uint32_t classCount[3]; uint32_t pad; };   // class 0: miss, 1: PBR, 2: glass
 
 struct DeviceStats {                       // accumulated by k_finish_pass
     unsigned long long raysPrimary, raysExtension, raysOcclusion, nodesVisited, trianglesTested, nodesVisitedAny, trianglesTestedAny, stackOverflows;
@@ -69,7 +69,7 @@ struct DeviceStats {                       // accumulated by k_finish_pass
 
 struct DScene {
     const float4* nodes;      // 5 x float4 per wide node
-    const float4* tris;       // 3 x float4 per triangle, leaf order: (v0, primId) (e1, 0) (e2, 0)
+    const float4* tris;       // 3 x float4 per triangle, leaf order: (v0, primId) (e1, material type) (e2, 0)
     const float4* shade;      // 4 x float4 per triangle, primId order: (n0, material) (n1, frontFaceCW) (n2, 0) (Ng, 0)
     const DMaterial* materials;
     const DTexture* textures;
@@ -83,14 +83,15 @@ struct DScene {
 struct PassBuffers {
     RayQueue ext[2];
     ShadowQueue shadow;
-    float4* hits;
+    float4* hits;             // t, u, v, primId | material class << 28 | HRC_HIT_BACKFACE  (-1: miss)
+    uint32_t* classIdx[3];    // per-class lists of ray indices of the current iteration, filled by k_trace<closest>
     IterCtrl* ctrl;           // kMaxIterations entries
     DeviceStats* stats;
     float4* accum;
     uint32_t capacity;        // rays per queue
 };
 
-struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; };
+struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool shadeMiss, shadePbr, shadeGlass; int refillIdle; };
 
 void launchClearCtrl(const PassBuffers& pb, cudaStream_t s);
 void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s);

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -34,6 +35,7 @@ struct HrcContext_t {
     std::vector<cudaEvent_t> evPool;
     std::string err;
     int smCount = 148;
+    int tuneRefillIdle = 10, tuneBlocksPerSM = 8;   // traversal scheduling knobs (HRC_TUNE_* environment overrides, for experiments)
 
     int w = 0, h = 0;
     float4* accum = nullptr;
@@ -44,7 +46,7 @@ struct HrcContext_t {
     std::vector<MaterialRec> materials;
     std::vector<MeshRec> meshes;
     bool committed = false, materialsDirty = true, texturesDirty = true;
-    bool anySingleSided = false;
+    bool anySingleSided = false, anyPbr = false, anyGlass = false;
 
     float4 *dNodes = nullptr, *dTris = nullptr, *dShade = nullptr;
     DMaterial* dMaterials = nullptr; size_t dMaterialsCap = 0;
@@ -70,7 +72,8 @@ int failCuda(HrcContext c, cudaError_t e, const char* what) {
 template <class T> void freeDev(T*& p) { if (p) { cudaFree(p); p = nullptr; } }
 
 void freeQueues(HrcContext c) {
-    for (int k = 0; k < 2; ++k) { freeDev(c->pb.ext[k].o); freeDev(c->pb.ext[k].d); freeDev(c->pb.ext[k].w); freeDev(c->pb.ext[k].m); }
+    for (int k = 0; k < 2; ++k) { freeDev(c->pb.ext[k].od); freeDev(c->pb.ext[k].wm); }
+    for (int k = 0; k < 3; ++k) freeDev(c->pb.classIdx[k]);
     freeDev(c->pb.shadow.o); freeDev(c->pb.shadow.d); freeDev(c->pb.shadow.w); freeDev(c->pb.hits);
     c->pb.capacity = 0;
 }
@@ -80,16 +83,22 @@ DScene sceneOf(HrcContext c) {
     s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId;
     return s;
 }
-LaunchConfig configOf(HrcContext c) { LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters; return lc; }
+LaunchConfig configOf(HrcContext c) {
+    LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters;
+    lc.refillIdle = c->tuneRefillIdle; lc.traceBlocksPerSM = c->tuneBlocksPerSM;
+    lc.shadeMiss = c->lights.envEnabled != 0; lc.shadePbr = c->anyPbr; lc.shadeGlass = c->anyGlass;
+    return lc;
+}
 
 int uploadMaterials(HrcContext c) {
     if (!c->materialsDirty) return HRC_OK;
     size_t n = std::max<size_t>(1, c->materials.size());
     if (n > c->dMaterialsCap) { freeDev(c->dMaterials); CU(c, cudaMalloc(&c->dMaterials, n * sizeof(DMaterial))); c->dMaterialsCap = n; }
     std::vector<DMaterial> host(n);
-    c->anySingleSided = false;
+    c->anySingleSided = c->anyPbr = c->anyGlass = false;
     for (size_t i = 0; i < c->materials.size(); ++i) {
         host[i] = c->materials[i].d;
+        if (c->materials[i].type == HRC_MATERIAL_PBR) c->anyPbr = true; else c->anyGlass = true;
         if (c->materials[i].type == HRC_MATERIAL_PBR && !(c->materials[i].flags & HRC_MAT_DOUBLE_SIDED)) c->anySingleSided = true;
     }
     CU(c, cudaMemcpyAsync(c->dMaterials, host.data(), n * sizeof(DMaterial), cudaMemcpyHostToDevice, c->stream));
@@ -171,6 +180,8 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     std::memset(&c->globals, 0, sizeof(c->globals));
     c->globals.maxRayDepth = 5; c->globals.maxChannelValue = 3.14159265358979f;   // GlobalData defaults, PassGenerator.h:270-272
     c->lights.envTex = -1;
+    if (const char* e = std::getenv("HRC_TUNE_REFILL_IDLE")) c->tuneRefillIdle = std::max(1, std::min(32, std::atoi(e)));
+    if (const char* e = std::getenv("HRC_TUNE_BLOCKS_PER_SM")) c->tuneBlocksPerSM = std::max(1, std::min(16, std::atoi(e)));
     *out = c;
     return HRC_OK;
 }
@@ -217,9 +228,9 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
     CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));
     CU(c, cudaMallocHost(&c->pinned, n * sizeof(float4))); c->pinnedBytes = n * sizeof(float4);
     for (int k = 0; k < 2; ++k) {
-        CU(c, cudaMalloc(&c->pb.ext[k].o, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.ext[k].d, n * sizeof(float4)));
-        CU(c, cudaMalloc(&c->pb.ext[k].w, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.ext[k].m, n * sizeof(uint2)));
+        CU(c, cudaMalloc(&c->pb.ext[k].od, 2 * n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.ext[k].wm, 2 * n * sizeof(float4)));
     }
+    for (int k = 0; k < 3; ++k) CU(c, cudaMalloc(&c->pb.classIdx[k], n * sizeof(uint32_t)));
     CU(c, cudaMalloc(&c->pb.shadow.o, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.shadow.d, n * sizeof(float4)));
     CU(c, cudaMalloc(&c->pb.shadow.w, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.hits, n * sizeof(float4)));
     c->pb.capacity = (uint32_t)n; c->pb.accum = c->accum;
@@ -353,9 +364,10 @@ HRC_API int hrcCommitScene(HrcContext c) {
     // 1. flatten to world space; primitive id = running triangle index in (mesh, element) order (policy A-9)
     std::vector<BuildTriangle> bt;
     std::vector<float4> shade;      // 4 per triangle
+    std::vector<int32_t> primType;  // material type per triangle: selects the shade kernel (ray class) at hit time
     size_t triTotal = 0;
     for (const MeshRec& m : c->meshes) if (m.alive) triTotal += m.drawMode == HRC_DRAW_TRIANGLES ? m.idx.size() / 3 : (m.idx.size() >= 3 ? m.idx.size() - 2 : 0);
-    if (triTotal >= (1u << 30)) return fail(c, HRC_ERR_UNSUPPORTED, "more than 2^30 triangles");
+    if (triTotal >= (1u << 28)) return fail(c, HRC_ERR_UNSUPPORTED, "more than 2^28 triangles");
     bt.reserve(triTotal); shade.reserve(triTotal * 4);
     for (const MeshRec& m : c->meshes) {
         if (!m.alive) continue;
@@ -366,6 +378,7 @@ HRC_API int hrcCommitScene(HrcContext c) {
             BuildTriangle t;
             for (int k = 0; k < 3; ++k) { t.v0[k] = wp[3 * a + k]; t.v1[k] = wp[3 * b + k]; t.v2[k] = wp[3 * cc + k]; }
             bt.push_back(t);
+            primType.push_back(c->materials[m.material].type);
             // geometric normal = normalize(cross(e1, e2)) with the same fp32 operation order as the shaders' restatement
             float e1[3], e2[3];
             for (int k = 0; k < 3; ++k) { e1[k] = t.v1[k] - t.v0[k]; e2[k] = t.v2[k] - t.v0[k]; }
@@ -395,7 +408,7 @@ HRC_API int hrcCommitScene(HrcContext c) {
         const uint32_t prim = bvh.triOrder[s];
         const BuildTriangle& t = bt[prim];
         tris[3 * s + 0] = make_float4(t.v0[0], t.v0[1], t.v0[2], __builtin_bit_cast(float, (int32_t)prim));
-        tris[3 * s + 1] = make_float4(t.v1[0] - t.v0[0], t.v1[1] - t.v0[1], t.v1[2] - t.v0[2], 0.0f);
+        tris[3 * s + 1] = make_float4(t.v1[0] - t.v0[0], t.v1[1] - t.v0[1], t.v1[2] - t.v0[2], __builtin_bit_cast(float, primType[prim]));
         tris[3 * s + 2] = make_float4(t.v2[0] - t.v0[0], t.v2[1] - t.v0[1], t.v2[2] - t.v0[2], 0.0f);
     }
     if (shade.empty()) shade.resize(4, make_float4(0, 0, 0, 0));
@@ -525,7 +538,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     launchFinishPass(c->pb, iterations, s);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return failCuda(c, e, "kernel launch");
-    if (launches) { launches[0] = iterations; launches[1] = iterations; launches[2] = iterations; }
+    if (launches) { launches[0] = iterations; launches[1] = iterations * ((int)lc.shadeMiss + (int)lc.shadePbr + (int)lc.shadeGlass); launches[2] = iterations; }
     if (timeKernels && kernelMs) {
         CU(c, cudaStreamSynchronize(s));
         float ms = 0; kernelMs[0] = kernelMs[1] = kernelMs[2] = kernelMs[3] = 0;

@@ -227,8 +227,6 @@ __device__ __forceinline__ void shadeMiss(const DScene& sc, const DFrame& fr, fl
 // ---------------------------------------------------------------------------------------
 // Traversal of the 8-wide compressed BVH
 // ---------------------------------------------------------------------------------------
-struct HitRec { float t, u, v; int prim; bool back; };
-
 __device__ __forceinline__ uint32_t byteOf(uint32_t x, int i) { return (x >> (i * 8)) & 0xffu; }
 
 // Möller–Trumbore with a FIXED operation order and no FMA contraction: the CPU oracle performs the very
@@ -262,22 +260,25 @@ __device__ __forceinline__ bool triangleTest(float4 a, float4 b, float4 c, float
 
 struct TraceCounters { uint32_t nodes, tris, overflow; };
 
-// byte j of q as a float, without the quarter-rate I2F pipe: splice the byte into the mantissa of 2^23 (one PRMT)
-// and subtract 2^23 (one full-rate FADD; exact for 0..255).
+// Byte J of q spliced into mantissa bits 8..15 of 1.0f with one PRMT: the float 1 + q * 2^-15. The child-plane distance
+// (origin + q*cell - o) / d is then ONE FMA, f * A + B with A = cell/d * 2^15 and B = (origin - o)/d - A: no I2F (quarter
+// rate) and no separate subtract. B absorbs a rounding error of at most 2^-9 cell, which the conservative bias on B
+// (nodeSetup) covers.
 template <int J>
-__device__ __forceinline__ float byteToFloat(uint32_t q) {
-    return __uint_as_float(__byte_perm(q, 0x4B000000u, 0x7440u + J)) - 8388608.0f;
+__device__ __forceinline__ float byteToUnitFloat(uint32_t q) {
+    return __uint_as_float(__byte_perm(q, 0x3F800000u, 0x7604u + (J << 4)));
 }
 
-// Per-lane traversal state of the 8-wide compressed BVH. A lane keeps its state across the refill points of the
-// persistent kernel, so a warp can top itself up with fresh rays while slow rays are still in flight.
+// Per-lane traversal state. A lane keeps it across the warp-synchronous phases of k_trace (node step, triangle rounds,
+// refill), so a warp tops itself up with fresh rays while slow rays are still in flight.
 struct Traversal {
     float3 o, d, idir;
     float tmin, tmaxRay;
     uint32_t octInv;
-    bool negX, negY, negZ;
-    HitRec best; bool found;
-    uint2 group;
+    float bestT, bestU, bestV; int bestPrim;      // bestPrim carries HRC_HIT_BACKFACE and, in bits 28..29, the material class
+    bool found;
+    uint2 group;       // x: first child node index; y: bits 24..31 pending internal children (octant order), bits 0..7 imask
+    uint2 tri;         // leaf triangles hit by the last node step (x: first triangle, y: bit mask)
     int sp;
 
     __device__ __forceinline__ void begin(float3 org, float3 dir, float tmin_, float tmax_) {
@@ -288,111 +289,121 @@ struct Traversal {
                              fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
                              fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
         idir = f3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
-        negX = dd.x < 0.0f; negY = dd.y < 0.0f; negZ = dd.z < 0.0f;
         // slot bit set = positive side; a ray going positive must visit negative-side children first
-        octInv = (negX ? 0u : 4u) | (negY ? 0u : 2u) | (negZ ? 0u : 1u);
-        best.t = tmax_; best.prim = 0x7fffffff; best.u = 0.f; best.v = 0.f; best.back = false;
+        octInv = (dd.x < 0.0f ? 0u : 4u) | (dd.y < 0.0f ? 0u : 2u) | (dd.z < 0.0f ? 0u : 1u);
+        bestT = tmax_; bestPrim = 0x0fffffff; bestU = 0.f; bestV = 0.f;
         found = false;
         sp = 0;
         group = make_uint2(0u, 0x80000000u);     // root: "child 7 of a virtual parent whose childBase is 0"
+        tri = make_uint2(0u, 0u);
     }
+    __device__ __forceinline__ bool hasNodeWork() const { return (group.y & 0xff000000u) != 0u; }
 
-    // One traversal step: pop one node (or one postponed triangle group), test its children / triangles.
-    // Returns false when the ray is finished.
-    template <bool ANY, bool STATS>
-    __device__ __forceinline__ bool step(const float4* __restrict__ nodes, const float4* __restrict__ tris, uint2* stack, TraceCounters& tc) {
-        uint2 triGroup;
+    // Pops the nearest pending child of `group`, tests its 8 children, leaves the hit internal children in `group` and
+    // files the hit leaf triangles as a pending triangle group.
+    template <bool STATS>
+    __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, uint2* stack, TraceCounters& tc) {
+        const uint32_t hits = group.y;
+        const uint32_t bit = 31u - __clz(hits);                  // highest set bit = nearest remaining child
+        group.y &= ~(1u << bit);
         if (group.y & 0xff000000u) {
-            const uint32_t hits = group.y;
-            const uint32_t bit = 31u - __clz(hits);                  // highest set bit = nearest remaining child
-            group.y &= ~(1u << bit);
-            if (group.y & 0xff000000u) {
-                if (sp < kTraceStack) stack[sp++] = group; else if (STATS) tc.overflow++;
-            }
-            const uint32_t slot = (bit - 24u) ^ (octInv & 7u);
-            const uint32_t rel = __popc(hits & ~(0xffffffffu << slot));   // internal children stored before this slot
-            const uint32_t nodeIdx = group.x + rel;
+            if (sp < kTraceStack) stack[sp++] = group; else if (STATS) tc.overflow++;
+        }
+        const uint32_t slot = (bit - 24u) ^ (octInv & 7u);
+        const uint32_t rel = __popc(hits & ~(0xffffffffu << slot));   // internal children stored before this slot
+        const uint32_t nodeIdx = group.x + rel;
 
-            const float4* np = nodes + (size_t)nodeIdx * 5;
-            const float4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-            if (STATS) tc.nodes++;
+        const float4* np = nodes + (size_t)nodeIdx * 5;
+        const float4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+        if (STATS) tc.nodes++;
 
-            const uint32_t eimask = __float_as_uint(n0.w);
-            const float3 adjDir = f3(__uint_as_float(byteOf(eimask, 0) << 23) * idir.x,
-                                     __uint_as_float(byteOf(eimask, 1) << 23) * idir.y,
-                                     __uint_as_float(byteOf(eimask, 2) << 23) * idir.z);
-            const float3 adjOrg = f3((n0.x - o.x) * idir.x, (n0.y - o.y) * idir.y, (n0.z - o.z) * idir.z);
-            const float tfar = best.t;
-            const uint32_t octInv4 = octInv * 0x01010101u;
+        const uint32_t eimask = __float_as_uint(n0.w);
+        // A = cell * 2^15 / d  (cell = 2^(e-127); e == 0 marks a flat axis with cell size 0)
+        const uint32_t ex = byteOf(eimask, 0), ey = byteOf(eimask, 1), ez = byteOf(eimask, 2);
+        const float Ax = __uint_as_float(ex ? (ex + 15u) << 23 : 0u) * idir.x;
+        const float Ay = __uint_as_float(ey ? (ey + 15u) << 23 : 0u) * idir.y;
+        const float Az = __uint_as_float(ez ? (ez + 15u) << 23 : 0u) * idir.z;
+        const float Bx = (n0.x - o.x) * idir.x - Ax, By = (n0.y - o.y) * idir.y - Ay, Bz = (n0.z - o.z) * idir.z - Az;
+        // conservative bias: entry planes a little earlier, exit planes a little later (2^-7 cell >> the 2^-9 cell rounding of B)
+        const float kBias = 1.0f / 4194304.0f;   // 2^-22 * 2^15 cells
+        const float ex_ = fabsf(Ax) * kBias, ey_ = fabsf(Ay) * kBias, ez_ = fabsf(Az) * kBias;
+        const float Bnx = Bx - ex_, Bny = By - ey_, Bnz = Bz - ez_;
+        const float Bfx = Bx + ex_, Bfy = By + ey_, Bfz = Bz + ez_;
+        const bool negX = !(octInv & 4u), negY = !(octInv & 2u), negZ = !(octInv & 1u);
+        const float tfar = bestT;
+        const uint32_t octInv4 = octInv * 0x01010101u;
 
-            uint32_t hitMask = 0;
+        uint32_t hitMask = 0;
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const uint32_t meta4 = __float_as_uint(half == 0 ? n1.z : n1.w);
-                const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;       // 0xff in every byte whose slot holds an internal child
-                const uint32_t bitIndex4 = (meta4 ^ (octInv4 & innerMask4)) & 0x1f1f1f1fu;
-                const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = __float_as_uint(half == 0 ? n2.x : n2.y), qloy = __float_as_uint(half == 0 ? n2.z : n2.w);
-                const uint32_t qloz = __float_as_uint(half == 0 ? n3.x : n3.y), qhix = __float_as_uint(half == 0 ? n3.z : n3.w);
-                const uint32_t qhiy = __float_as_uint(half == 0 ? n4.x : n4.y), qhiz = __float_as_uint(half == 0 ? n4.z : n4.w);
-                const uint32_t nx = negX ? qhix : qlox, fx = negX ? qlox : qhix;
-                const uint32_t ny = negY ? qhiy : qloy, fy = negY ? qloy : qhiy;
-                const uint32_t nz = negZ ? qhiz : qloz, fz = negZ ? qloz : qhiz;
+        for (int half = 0; half < 2; ++half) {
+            const uint32_t meta4 = __float_as_uint(half == 0 ? n1.z : n1.w);
+            const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+            const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;       // 0xff in every byte whose slot holds an internal child
+            const uint32_t bitIndex4 = (meta4 ^ (octInv4 & innerMask4)) & 0x1f1f1f1fu;
+            const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+            const uint32_t qlox = __float_as_uint(half == 0 ? n2.x : n2.y), qloy = __float_as_uint(half == 0 ? n2.z : n2.w);
+            const uint32_t qloz = __float_as_uint(half == 0 ? n3.x : n3.y), qhix = __float_as_uint(half == 0 ? n3.z : n3.w);
+            const uint32_t qhiy = __float_as_uint(half == 0 ? n4.x : n4.y), qhiz = __float_as_uint(half == 0 ? n4.z : n4.w);
+            const uint32_t nx = negX ? qhix : qlox, fx = negX ? qlox : qhix;
+            const uint32_t ny = negY ? qhiy : qloy, fy = negY ? qloy : qhiy;
+            const uint32_t nz = negZ ? qhiz : qloz, fz = negZ ? qloz : qhiz;
 #define HR_CHILD(J)                                                                                                    \
-                {                                                                                                      \
-                    const float tnx = fmaf(byteToFloat<J>(nx), adjDir.x, adjOrg.x), tfx = fmaf(byteToFloat<J>(fx), adjDir.x, adjOrg.x); \
-                    const float tny = fmaf(byteToFloat<J>(ny), adjDir.y, adjOrg.y), tfy = fmaf(byteToFloat<J>(fy), adjDir.y, adjOrg.y); \
-                    const float tnz = fmaf(byteToFloat<J>(nz), adjDir.z, adjOrg.z), tfz = fmaf(byteToFloat<J>(fz), adjDir.z, adjOrg.z); \
-                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                          \
-                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar));                                          \
-                    if (tn <= tf * 1.000001f) /* conservative: rounding must never cull an exact tie */                 \
-                        hitMask |= byteOf(childBits4, J) << byteOf(bitIndex4, J);                                       \
-                }
-                HR_CHILD(0) HR_CHILD(1) HR_CHILD(2) HR_CHILD(3)
+            {                                                                                                          \
+                const float tnx = fmaf(byteToUnitFloat<J>(nx), Ax, Bnx), tfx = fmaf(byteToUnitFloat<J>(fx), Ax, Bfx);   \
+                const float tny = fmaf(byteToUnitFloat<J>(ny), Ay, Bny), tfy = fmaf(byteToUnitFloat<J>(fy), Ay, Bfy);   \
+                const float tnz = fmaf(byteToUnitFloat<J>(nz), Az, Bnz), tfz = fmaf(byteToUnitFloat<J>(fz), Az, Bfz);   \
+                const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                              \
+                const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar));                                              \
+                if (tn <= tf * 1.000001f) /* conservative: rounding must never cull an exact tie */                     \
+                    hitMask |= byteOf(childBits4, J) << byteOf(bitIndex4, J);                                           \
+            }
+            HR_CHILD(0) HR_CHILD(1) HR_CHILD(2) HR_CHILD(3)
 #undef HR_CHILD
-            }
-            group.x = __float_as_uint(n1.x);
-            group.y = (hitMask & 0xff000000u) | (eimask >> 24);
-            triGroup.x = __float_as_uint(n1.y);
-            triGroup.y = hitMask & 0x00ffffffu;
-        } else {
-            triGroup = group;
-            group = make_uint2(0u, 0u);
         }
-
-        while (triGroup.y) {
-            const uint32_t ti = 31u - __clz(triGroup.y);
-            triGroup.y &= ~(1u << ti);
-            const float4* tp = tris + (size_t)(triGroup.x + ti) * 3;
-            const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
-            if (STATS) tc.tris++;
-            float t, u, v; bool back;
-            if (triangleTest(a, b, c, o, d, tmin, tmaxRay, t, u, v, back)) {
-                if (ANY) { found = true; return false; }
-                const int prim = __float_as_int(a.w);
-                if (t < best.t || (t == best.t && prim < best.prim)) {
-                    best.t = t; best.u = u; best.v = v; best.prim = prim; best.back = back; found = true;
-                }
-            }
-        }
-
-        if ((group.y & 0xff000000u) == 0u) {
-            if (sp == 0) return false;
-            group = stack[--sp];
-        }
-        return true;
+        group.x = __float_as_uint(n1.x);
+        group.y = (hitMask & 0xff000000u) | (eimask >> 24);
+        const uint32_t triBits = hitMask & 0x00ffffffu;
+        tri = make_uint2(__float_as_uint(n1.y), triBits);
     }
+
+    // Takes the next node group from the stack when the current one is used up.
+    __device__ __forceinline__ void popIfEmpty(const uint2* stack) {
+        if (!hasNodeWork() && sp > 0) group = stack[--sp];
+    }
+
+    // Tests ONE pending triangle. Returns true when an any-hit ray is finished.
+    template <bool ANY, bool STATS>
+    __device__ __forceinline__ bool triStep(const float4* __restrict__ tris, TraceCounters& tc) {
+        const uint32_t ti = 31u - __clz(tri.y);
+        tri.y &= ~(1u << ti);
+        const float4* tp = tris + (size_t)(tri.x + ti) * 3;
+        const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+        if (STATS) tc.tris++;
+        float t, u, v; bool back;
+        if (triangleTest(a, b, c, o, d, tmin, tmaxRay, t, u, v, back)) {
+            if (ANY) { found = true; return true; }
+            const int prim = __float_as_int(a.w);
+            if (t < bestT || (t == bestT && prim < (bestPrim & 0x0fffffff))) {
+                bestT = t; bestU = u; bestV = v; found = true;
+                bestPrim = prim | (back ? HRC_HIT_BACKFACE : 0) | (__float_as_int(b.w) << 28);
+            }
+        }
+        return false;
+    }
+    __device__ __forceinline__ bool finished() const { return !hasNodeWork() && tri.y == 0u && sp == 0; }
 };
 
-template <bool ANY, bool STATS>
-__device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const float4* __restrict__ tris,
-                                         float3 o, float3 d, float tmin, float tmaxRay, HitRec& best, TraceCounters& tc) {
-    Traversal tr; uint2 stack[kTraceStack];
-    tr.begin(o, d, tmin, tmaxRay);
-    while (tr.step<ANY, STATS>(nodes, tris, stack, tc)) {}
-    best = tr.best;
-    return tr.found;
+// Plain per-thread traversal (the hrcTraceRays parity hook): same steps, no warp scheduling.
+template <bool ANY>
+__device__ __forceinline__ void traverseSimple(const float4* __restrict__ nodes, const float4* __restrict__ tris, Traversal& tr) {
+    uint2 stack[kTraceStack];
+    TraceCounters tc{0u, 0u, 0u};
+    for (;;) {
+        if (tr.hasNodeWork()) tr.nodeStep<false>(nodes, stack, tc);
+        while (tr.tri.y) if (tr.triStep<ANY, false>(tris, tc)) return;
+        tr.popIfEmpty(stack);
+        if (tr.finished()) return;
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -400,7 +411,7 @@ __device__ __forceinline__ bool traverse(const float4* __restrict__ nodes, const
 // ---------------------------------------------------------------------------------------
 __global__ void k_clear_ctrl(IterCtrl* ctrl) {
     int i = threadIdx.x;
-    if (i < kMaxIterations) ctrl[i] = IterCtrl{0u, 0u, 0u, 0u};
+    if (i < kMaxIterations) ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};
 }
 
 // perspective.rlsl:39-93 — one thread per pixel of this context's screen bands.
@@ -442,78 +453,103 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_co
     const float3 wd = normalize(f3((M[0] * dir.x + M[4] * dir.y) + M[8] * dir.z,
                                    (M[1] * dir.x + M[5] * dir.y) + M[9] * dir.z,
                                    (M[2] * dir.x + M[6] * dir.y) + M[10] * dir.z)); // :86 (normalised on emit, A-11)
-    q.o[i] = make_float4(wo.x, wo.y, wo.z, __int_as_float(0x7f800000));   // tmax = +inf
-    q.d[i] = make_float4(wd.x, wd.y, wd.z, 0.0f);                         // extraT = 0
-    q.w[i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
+    q.od[2 * (size_t)i] = make_float4(wo.x, wo.y, wo.z, __int_as_float(0x7f800000));   // tmax = +inf
+    q.od[2 * (size_t)i + 1] = make_float4(wd.x, wd.y, wd.z, 0.0f);                     // extraT = 0
+    q.wm[2 * (size_t)i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
     const uint32_t missKind = fr.lights.envEnabled ? kMissEnv : kMissNone;   // defaultPrimitive = env light, :87
-    q.m[i] = make_uint2(0u | (missKind << 8) | ((uint32_t)sequenceID << 16), (uint32_t)sequenceIndex);
+    q.wm[2 * (size_t)i + 1] = make_float4(__uint_as_float(0u | (missKind << 8) | ((uint32_t)sequenceID << 16)), __int_as_float(sequenceIndex), 0.0f, 0.0f);
 }
 
-// Persistent traversal kernel with dynamic refill: every lane owns one ray; when the number of lanes still traversing
-// drops below kRefillThreshold the warp pauses, the idle lanes pull fresh rays from the queue (one atomic per warp per
-// refill) and traversal resumes with the paused lanes' state intact. This keeps SIMT lanes busy on incoherent rays.
-constexpr int kRefillThreshold = 22;
+// Persistent traversal kernel. Every lane owns one ray and runs the classic while-while loop (one 8-wide node step, then
+// that node's leaf triangles at once). When kRefillIdle lanes of a warp have finished, the warp pauses at a
+// warp-synchronous point: finished rays are appended to the per-material-class index lists (one atomic per warp per
+// class: the compaction that lets each shade kernel run one material) and the idle lanes pull fresh rays from the queue
+// (one atomic per warp) while the other lanes keep their traversal state.
+// Tried and measured slower on B200 (profiles/r01_v3_notes.md): parking leaf triangles in a per-lane ring and testing
+// them in warp-wide rounds (triangle-test lane utilisation doubled, node-step utilisation and scheduling overhead ate the
+// gain), and "one node step or one triangle per trip".
+constexpr uint32_t kFull = 0xffffffffu;
 
 template <bool ANY, bool STATS>
-__global__ void __launch_bounds__(128) k_trace(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
+__global__ void __launch_bounds__(128, 8) k_trace(const DScene sc, const __grid_constant__ DFrame fr, const PassBuffers pb, int iter, int kRefillIdle) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t below = (1u << lane) - 1u;
     IterCtrl* ctrl = pb.ctrl + iter;
     const uint32_t count = ANY ? ctrl->shadowCount : ctrl->extCount;
     uint32_t* head = ANY ? &ctrl->shadowHead : &ctrl->extHead;
-    const RayQueue& rq = pb.ext[iter & 1];
-    const float4* __restrict__ qo = ANY ? pb.shadow.o : rq.o;
-    const float4* __restrict__ qd = ANY ? pb.shadow.d : rq.d;
+    const float4* __restrict__ qod = (iter & 1) ? pb.ext[1].od : pb.ext[0].od;   // no dynamic indexing of kernel parameters (it forces a local copy)
+    const float4* __restrict__ nodes = sc.nodes;
+    const float4* __restrict__ tris = sc.tris;
     TraceCounters tc{0u, 0u, 0u};
     Traversal tr;
     uint2 stack[kTraceStack];
     bool active = false, exhausted = false;
-    uint32_t rayIdx = 0;
-    float extraT = 0.f;
+    uint32_t rayIdx = 0, doneIdx = 0;
+    int doneClass = -1;                      // closest-hit only: class of a finished ray not yet appended to its list
 
     for (;;) {
-        if (!exhausted) {
-            const uint32_t need = __ballot_sync(0xffffffffu, !active);
-            if (need) {
-                const uint32_t n = __popc(need);
-                const int leader = __ffs(need) - 1;
+        const uint32_t idle = __ballot_sync(kFull, !active);
+        if (idle == kFull || (!exhausted && __popc(idle) >= kRefillIdle)) {
+            if (!ANY) {                                                   // retire: append finished rays to the class lists
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const uint32_t m = __ballot_sync(kFull, doneClass == c);
+                    if (m) {
+                        const int leader = __ffs(m) - 1;
+                        uint32_t base = 0;
+                        if ((int)lane == leader) base = atomicAdd(&ctrl->classCount[c], (uint32_t)__popc(m));
+                        base = __shfl_sync(kFull, base, leader);
+                        if (doneClass == c) pb.classIdx[c][base + __popc(m & below)] = doneIdx;
+                    }
+                }
+                doneClass = -1;
+            }
+            if (!exhausted) {                                             // refill
+                const uint32_t n = __popc(idle);
+                const int leader = __ffs(idle) - 1;
                 uint32_t base = 0;
                 if ((int)lane == leader) base = atomicAdd(head, n);
-                base = __shfl_sync(0xffffffffu, base, leader);
+                base = __shfl_sync(kFull, base, leader);
                 if (!active) {
-                    const uint32_t i = base + __popc(need & below);
+                    const uint32_t i = base + __popc(idle & below);
                     if (i < count) {
-                        const float4 ro = qo[i], rd = qd[i];
-                        rayIdx = i; extraT = rd.w;
+                        const float4 ro = __ldcs(ANY ? pb.shadow.o + i : qod + 2 * (size_t)i), rd = __ldcs(ANY ? pb.shadow.d + i : qod + 2 * (size_t)i + 1);   // streamed: keep the BVH in L2
+                        rayIdx = i;
                         tr.begin(xyz(ro), xyz(rd), 0.0f, ro.w);
                         active = true;
                     }
                 }
                 if (base + n >= count) exhausted = true;
             }
+            if (!__any_sync(kFull, active)) break;
         }
-        if (!__any_sync(0xffffffffu, active)) break;
+
         while (active) {
-            if (!tr.step<ANY, STATS>(sc.nodes, sc.tris, stack, tc)) {
+            if (tr.hasNodeWork()) tr.nodeStep<STATS>(nodes, stack, tc);
+            bool occluded = false;
+            while (tr.tri.y) if (tr.triStep<ANY, STATS>(tris, tc)) { occluded = true; break; }
+            tr.popIfEmpty(stack);
+            if (occluded) { active = false; break; }                       // any-hit: nothing to shade
+            if (tr.finished()) {
                 active = false;
-                if (ANY) {
-                    if (!tr.found) {   // the ray reached its light: run the light shader (policy A-5/A-6)
-                        const float4 w = pb.shadow.w[rayIdx];
-                        const uint32_t bits = __float_as_uint(w.w);
-                        shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, extraT);
-                    }
+                if (ANY) {             // the ray reached its light: run the light shader (policy A-5/A-6)
+                    const float4 w = __ldcs(pb.shadow.w + rayIdx);
+                    const uint32_t bits = __float_as_uint(w.w);
+                    shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, pb.shadow.d[rayIdx].w);
                 } else {
-                    pb.hits[rayIdx] = tr.found ? make_float4(tr.best.t, tr.best.u, tr.best.v, __int_as_float(tr.best.prim | (tr.best.back ? HRC_HIT_BACKFACE : 0)))
-                                               : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                    __stcs(pb.hits + rayIdx, tr.found ? make_float4(tr.bestT, tr.bestU, tr.bestV, __int_as_float(tr.bestPrim))
+                                                      : make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));
+                    doneIdx = rayIdx;
+                    doneClass = tr.found ? 1 + ((tr.bestPrim >> 28) & 3) : 0;
                 }
                 break;
             }
-            if (!exhausted && __popc(__activemask()) < kRefillThreshold) break;
+            if (!exhausted && 32 - __popc(__activemask()) >= kRefillIdle) break;
         }
     }
     if (STATS) {
         uint32_t n = tc.nodes, t = tc.tris, ov = tc.overflow;
-        for (int s = 16; s > 0; s >>= 1) { n += __shfl_xor_sync(0xffffffffu, n, s); t += __shfl_xor_sync(0xffffffffu, t, s); ov += __shfl_xor_sync(0xffffffffu, ov, s); }
+        for (int s = 16; s > 0; s >>= 1) { n += __shfl_xor_sync(kFull, n, s); t += __shfl_xor_sync(kFull, t, s); ov += __shfl_xor_sync(kFull, ov, s); }
         if (lane == 0) {
             atomicAdd(ANY ? &pb.stats->nodesVisitedAny : &pb.stats->nodesVisited, (unsigned long long)n);
             atomicAdd(ANY ? &pb.stats->trianglesTestedAny : &pb.stats->trianglesTested, (unsigned long long)t);
@@ -859,36 +895,44 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
     }
 }
 
-// One thread per ray of iteration `iter`: miss shader or material shader, then warp-aggregated appends of the
-// (<= 1) occlusion ray and (<= 1) extension ray into the next queues — this is the compaction of live rays.
+// Material / miss shading, one kernel per ray class (CLS 0: miss, 1: PBR, 2: glass) over the index list k_trace<closest>
+// compacted for that class: a warp runs ONE material program, and each kernel's code stays small enough for the
+// instruction cache (the single all-materials kernel of the first version stalled on instruction fetch).
+// The (<= 1) occlusion ray and (<= 1) extension ray of every hit are appended to the next queues with warp-aggregated
+// atomics (ballot + popc prefix) — the compaction of live rays.
+template <int CLS>
 __global__ void __launch_bounds__(128) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = (gridDim.x * blockDim.x) >> 5;
     const uint32_t warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     IterCtrl* ctrl = pb.ctrl + iter;
-    const uint32_t count = ctrl->extCount;
-    const RayQueue& rq = pb.ext[iter & 1];
-    const RayQueue& nq = pb.ext[(iter + 1) & 1];
+    const uint32_t count = ctrl->classCount[CLS];
+    const uint32_t* __restrict__ list = pb.classIdx[CLS];
+    const RayQueue rq = (iter & 1) ? pb.ext[1] : pb.ext[0];
+    const RayQueue nq = (iter & 1) ? pb.ext[0] : pb.ext[1];
     const int hardCap = fr.g.maxRayDepth + 16;                                // policy A-14
     const bool lastIter = (iter + 1 >= kMaxIterations);
 
     for (uint32_t base = warpId * 32u; base < count; base += warpsTotal * 32u) {
-        const uint32_t i = base + lane;
+        const uint32_t k = base + lane;
         Emit e; e.hasOcc = false; e.hasExt = false;
         InRay in; in.depth = 0; in.pixel = 0; in.sequenceID = 0; in.sequenceIndexOffset = 0;
         uint32_t inMissKind = 0;
-        if (i < count) {
-            const float4 ro = rq.o[i], rd = rq.d[i], rw = rq.w[i];
-            const uint2 rm = rq.m[i];
-            const float4 hr = pb.hits[i];
-            in.o = xyz(ro); in.d = xyz(rd); in.weight = xyz(rw); in.tmax = ro.w;
+        if (k < count) {
+            const size_t i = list[k];
+            const float4 rd = __ldcs(rq.od + 2 * i + 1), rw = __ldcs(rq.wm + 2 * i), rm = __ldcs(rq.wm + 2 * i + 1);
+            const uint32_t mx = __float_as_uint(rm.x);
+            in.d = xyz(rd); in.weight = xyz(rw);
             in.pixel = __float_as_uint(rw.w);
-            in.depth = rm.x & 0xffu; inMissKind = (rm.x >> 8) & 0xfu; in.sequenceID = rm.x >> 16; in.sequenceIndexOffset = (int)rm.y;
-            const int primBits = __float_as_int(hr.w);
-            if (primBits < 0) {
-                shadeMiss(sc, fr, pb.accum, in.pixel, inMissKind, 0u, in.d, in.weight, in.tmax, rd.w);
+            in.depth = mx & 0xffu; inMissKind = (mx >> 8) & 0xfu; in.sequenceID = mx >> 16; in.sequenceIndexOffset = __float_as_int(rm.y);
+            if (CLS == 0) {
+                shadeMiss(sc, fr, pb.accum, in.pixel, inMissKind, 0u, in.d, in.weight, 0.0f, 0.0f);   // extension rays only miss into the environment
             } else {
-                const int prim = primBits & 0x3fffffff;
+                const float4 ro = __ldcs(rq.od + 2 * i);
+                const float4 hr = __ldcs(pb.hits + i);
+                in.o = xyz(ro); in.tmax = ro.w;
+                const int primBits = __float_as_int(hr.w);
+                const int prim = primBits & 0x0fffffff;
                 const bool back = (primBits & HRC_HIT_BACKFACE) != 0;
                 const float4* sp = sc.shade + (size_t)prim * 4;
                 const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2), s3 = __ldg(sp + 3);
@@ -900,11 +944,12 @@ __global__ void __launch_bounds__(128) k_shade(const DScene sc, const __grid_con
                 const float bw = (1.0f - hr.y) - hr.z;
                 const float3 n = (xyz(s0) * bw + xyz(s1) * hr.y) + xyz(s2) * hr.z;
                 const DMaterial m = sc.materials[__float_as_int(s0.w)];
-                if ((m.typeFlags & 0xfu) == HRC_MATERIAL_PBR) shadePBR(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
-                else                                          shadeGlass(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
+                if (CLS == 1) shadePBR(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
+                else          shadeGlass(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
                 if (e.hasExt && ((int)in.depth + 1 > hardCap || lastIter)) e.hasExt = false;
             }
         }
+        if (CLS == 0) continue;
         // ---- compaction: one atomic per warp per queue ------------------------------------
         const uint32_t occMask = __ballot_sync(0xffffffffu, e.hasOcc);
         const uint32_t extMask = __ballot_sync(0xffffffffu, e.hasExt);
@@ -917,18 +962,18 @@ __global__ void __launch_bounds__(128) k_shade(const DScene sc, const __grid_con
         extBase = __shfl_sync(0xffffffffu, extBase, 0);
         const uint32_t below = (1u << lane) - 1u;
         if (e.hasOcc) {
-            const uint32_t k = occBase + __popc(occMask & below);
-            pb.shadow.o[k] = make_float4(e.occO.x, e.occO.y, e.occO.z, e.occTmax);
-            pb.shadow.d[k] = make_float4(e.occD.x, e.occD.y, e.occD.z, 0.0f);
-            pb.shadow.w[k] = make_float4(e.occW.x, e.occW.y, e.occW.z, __uint_as_float(in.pixel | (e.occMissKind << 24) | (e.occMissIndex << 27)));
+            const uint32_t j = occBase + __popc(occMask & below);
+            __stcs(pb.shadow.o + j, make_float4(e.occO.x, e.occO.y, e.occO.z, e.occTmax));
+            __stcs(pb.shadow.d + j, make_float4(e.occD.x, e.occD.y, e.occD.z, 0.0f));
+            __stcs(pb.shadow.w + j, make_float4(e.occW.x, e.occW.y, e.occW.z, __uint_as_float(in.pixel | (e.occMissKind << 24) | (e.occMissIndex << 27))));
         }
         if (e.hasExt) {
-            const uint32_t k = extBase + __popc(extMask & below);
+            const size_t j = extBase + __popc(extMask & below);
             const uint32_t mk = e.extMissKind == 0xffu ? inMissKind : e.extMissKind;
-            nq.o[k] = make_float4(e.extO.x, e.extO.y, e.extO.z, __int_as_float(0x7f800000));
-            nq.d[k] = make_float4(e.extD.x, e.extD.y, e.extD.z, 0.0f);
-            nq.w[k] = make_float4(e.extW.x, e.extW.y, e.extW.z, __uint_as_float(in.pixel));
-            nq.m[k] = make_uint2((in.depth + 1u) | (mk << 8) | (in.sequenceID << 16), (uint32_t)in.sequenceIndexOffset);
+            __stcs(nq.od + 2 * j, make_float4(e.extO.x, e.extO.y, e.extO.z, __int_as_float(0x7f800000)));
+            __stcs(nq.od + 2 * j + 1, make_float4(e.extD.x, e.extD.y, e.extD.z, 0.0f));
+            __stcs(nq.wm + 2 * j, make_float4(e.extW.x, e.extW.y, e.extW.z, __uint_as_float(in.pixel)));
+            __stcs(nq.wm + 2 * j + 1, make_float4(__uint_as_float((in.depth + 1u) | (mk << 8) | (in.sequenceID << 16)), __int_as_float(in.sequenceIndexOffset), 0.0f, 0.0f));
         }
     }
 }
@@ -943,18 +988,18 @@ __global__ void k_finish_pass(PassBuffers pb, int iterations) {
     pb.stats->raysOcclusion += occ;
 }
 
-// hrcTraceRays: the fixed-ray-set parity hook. Same traversal code as the pass kernels.
+// hrcTraceRays: the fixed-ray-set parity hook. Same node / triangle steps as the pass kernels.
 template <bool ANY>
 __global__ void __launch_bounds__(128) k_trace_rays(const DScene sc, const HrcRay* __restrict__ rays, HrcHit* __restrict__ hits, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const HrcRay r = rays[i];
-    HitRec h; TraceCounters tc{0u, 0u, 0u};
-    const bool hit = traverse<ANY, false>(sc.nodes, sc.tris, f3(r.origin[0], r.origin[1], r.origin[2]), f3(r.direction[0], r.direction[1], r.direction[2]),
-                                          r.tmin, r.tmax, h, tc);
+    Traversal tr;
+    tr.begin(f3(r.origin[0], r.origin[1], r.origin[2]), f3(r.direction[0], r.direction[1], r.direction[2]), r.tmin, r.tmax);
+    traverseSimple<ANY>(sc.nodes, sc.tris, tr);
     HrcHit out;
-    if (ANY) { out.t = 0.f; out.u = 0.f; out.v = 0.f; out.primId = hit ? 0 : -1; }
-    else if (hit) { out.t = h.t; out.u = h.u; out.v = h.v; out.primId = h.prim | (h.back ? HRC_HIT_BACKFACE : 0); }
+    if (ANY) { out.t = 0.f; out.u = 0.f; out.v = 0.f; out.primId = tr.found ? 0 : -1; }
+    else if (tr.found) { out.t = tr.bestT; out.u = tr.bestU; out.v = tr.bestV; out.primId = tr.bestPrim & (0x0fffffff | HRC_HIT_BACKFACE); }
     else { out.t = 0.f; out.u = 0.f; out.v = 0.f; out.primId = -1; }
     hits[i] = out;
 }
@@ -980,18 +1025,21 @@ void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cud
 void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     DFrame dummy{};   // closest-hit traversal does not read the frame constants
     const int grid = lc.smCount * lc.traceBlocksPerSM;
-    if (lc.collectStats) k_trace<false, true><<<grid, 128, 0, s>>>(sc, dummy, pb, iter);
-    else                 k_trace<false, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter);
+    if (lc.collectStats) k_trace<false, true><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
+    else                 k_trace<false, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
 }
 
 void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     const int grid = lc.smCount * lc.traceBlocksPerSM;
-    if (lc.collectStats) k_trace<true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
-    else                 k_trace<true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
+    if (lc.collectStats) k_trace<true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+    else                 k_trace<true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
 }
 
 void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
-    k_shade<<<lc.smCount * 8, 128, 0, s>>>(sc, fr, pb, iter);
+    const int grid = lc.smCount * 8;
+    if (lc.shadeMiss)  k_shade<0><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
+    if (lc.shadePbr)   k_shade<1><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
+    if (lc.shadeGlass) k_shade<2><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
 }
 
 void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s) { k_finish_pass<<<1, 32, 0, s>>>(pb, iterations); }
