@@ -115,11 +115,27 @@ HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), (
 
 class HrhPbrMaterial(C.Structure):
     _fields_ = [("baseColor", f32 * 3), ("emissiveColor", f32 * 3), ("metallic", f32), ("roughness", f32), ("specularF0", f32),
-                ("clearCoat", f32), ("clearCoatRoughness", f32), ("doubleSided", i32), ("alphaMask", i32)]
+                ("clearCoat", f32), ("clearCoatRoughness", f32), ("doubleSided", i32), ("alphaMask", i32),
+                ("baseColorTexture", i32), ("metallicRoughnessTexture", i32), ("emissiveTexture", i32), ("normalmap", i32),
+                ("clearCoatTexture", i32), ("clearCoatRoughnessTexture", i32), ("clearCoatNormalmap", i32),
+                ("forceEnableAllTextures", i32), ("enableVertexColors", i32)]
+    _TEX = ("baseColorTexture", "metallicRoughnessTexture", "emissiveTexture", "normalmap", "clearCoatTexture", "clearCoatRoughnessTexture", "clearCoatNormalmap")
+
+    def __init__(self, *a, **kw):
+        for t in self._TEX[max(0, len(a) - 9):]:
+            kw.setdefault(t, -1)              # HRC_NULL_TEXTURE
+        super().__init__(*a, **kw)
 
 
 class HrhGlassMaterial(C.Structure):
-    _fields_ = [("baseColor", f32 * 3), ("roughness", f32), ("ior", f32), ("density", f32)]
+    _fields_ = [("baseColor", f32 * 3), ("roughness", f32), ("ior", f32), ("density", f32),
+                ("baseColorTexture", i32), ("normalmap", i32), ("metallicRoughnessTexture", i32), ("forceEnableAllTextures", i32)]
+    _TEX = ("baseColorTexture", "normalmap", "metallicRoughnessTexture")
+
+    def __init__(self, *a, **kw):
+        for t in self._TEX[max(0, len(a) - 4):]:
+            kw.setdefault(t, -1)
+        super().__init__(*a, **kw)
 
 
 class RenderOptions(C.Structure):       # HrhRenderOptions ↔ PassGenerator::RenderOptions (PassGenerator.h:49-150)
@@ -299,7 +315,7 @@ class Backend:
         self._call("UpdateMaterial", i32(mat), C.byref(params), C.c_size_t(C.sizeof(params)))
 
     def create_mesh(self, positions, normals, indices, material, transform=None, draw_mode=DRAW_TRIANGLES,
-                    front_face_cw=None, is_occluder=True) -> int:
+                    front_face_cw=None, is_occluder=True, uvs=None, tangents=None, bitangents=None, colors=None) -> int:
         pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
         nrm = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
         idx = np.ascontiguousarray(indices, np.uint32).reshape(-1)
@@ -308,6 +324,14 @@ class Backend:
         d.positions, d.positionStride = _ptr(pos), 12
         d.normals, d.normalStride = _ptr(nrm), 12
         d.vertexCount, d.indices, d.elementCount, d.drawMode = pos.shape[0], _ptr(idx), idx.shape[0], draw_mode
+        keep = []
+        for name, arr, comps in (("texCoords", uvs, 2), ("tangents", tangents, 3), ("bitangents", bitangents, 3), ("colors", colors, 3)):
+            if arr is not None:
+                a = np.ascontiguousarray(arr, np.float32).reshape(-1, comps)
+                assert a.shape[0] == pos.shape[0], f"{name}: one entry per vertex"
+                keep.append(a)
+                setattr(d, name, _ptr(a))
+                setattr(d, name[:-1] + "Stride", comps * 4)
         # `transform` is given as a mathematical 4x4 (row-major numpy); the ABI wants glm column-major
         d.worldFromEntity = (f32 * 16)(*M.T.reshape(-1))
         if front_face_cw is None:

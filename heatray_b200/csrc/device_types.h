@@ -13,13 +13,20 @@ constexpr int kTraceStack = 32;           // per-thread traversal stack entries 
 // miss-shader selector carried by a ray (policy A-6)
 enum : uint32_t { kMissNone = 0, kMissEnv = 1, kMissDir = 2, kMissPoint = 3, kMissSpot = 4 };
 
-struct alignas(16) DMaterial {            // 80 B, one per HrcMaterial
-    float baseColor[3]; uint32_t typeFlags;       // bits 0..3 type, bits 4.. feature flags
+struct alignas(16) DMaterial {            // 96 B, one per HrcMaterial
+    float baseColor[3]; uint32_t typeFlags;       // bits 0..3 type, bits 4.. feature flags (HRC_MAT_*)
     float emissive[3];  float metallic;
     float roughness, specularF0, roughnessAlpha, clearCoat;
     float clearCoatRoughness, clearCoatRoughnessAlpha, ior, density;
-    int32_t lutTex; int32_t pad[3];
+    int32_t lutTex, baseColorTex, metallicRoughnessTex, emissiveTex;      // texture handles, -1 = the 1x1 white dummy (Texture.h:178-192)
+    int32_t normalTex, clearCoatTex, clearCoatRoughnessTex, clearCoatNormalTex;
 };
+constexpr uint32_t kMatAnyTexture = HRC_MAT_HAS_BASE_COLOR_TEXTURE | HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE | HRC_MAT_HAS_EMISSIVE_TEXTURE | HRC_MAT_HAS_NORMALMAP |
+                                    HRC_MAT_HAS_CLEARCOAT_TEXTURE | HRC_MAT_HAS_CLEARCOAT_ROUGHNESS_TEXTURE | HRC_MAT_HAS_CLEARCOAT_NORMALMAP;   // HAS_TEXTURES
+constexpr uint32_t kMatTangentSpace = HRC_MAT_HAS_NORMALMAP | HRC_MAT_HAS_CLEARCOAT_NORMALMAP;                                                   // USE_TANGENT_SPACE
+constexpr int kAttrStride = 11;           // float4 per triangle in DScene::attr
+constexpr int kMaxMaskedSurfaces = 16;    // alpha-mask pass-throughs per occlusion ray (policy A-14)
+constexpr uint32_t kTriNonOccluder = 4u;  // bit 2 of the triangle record's e1.w (bits 0..1: material type)
 
 struct DTexture {                          // all textures are expanded to RGBA32F
     const float4* texels; int32_t w, h, wrapS, wrapT;
@@ -61,7 +68,7 @@ struct ShadowQueue {
 };
 
 // Per-iteration control words, zeroed at the start of every pass.
-struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; uint32_t classCount[3]; uint32_t pad; };   // class 0: miss, 1: PBR, 2: glass
+struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; uint32_t classCount[3]; uint32_t maskedContinuations; };   // class 0: miss, 1: PBR, 2: glass
 
 struct DeviceStats {                       // accumulated by k_finish_pass
     unsigned long long raysPrimary, raysExtension, raysOcclusion, nodesVisited, trianglesTested, nodesVisitedAny, trianglesTestedAny, stackOverflows;
@@ -71,6 +78,8 @@ struct DScene {
     const float4* nodes;      // 5 x float4 per wide node
     const float4* tris;       // 3 x float4 per triangle, leaf order: (v0, primId) (e1, material type) (e2, 0)
     const float4* shade;      // 4 x float4 per triangle, primId order: (n0, material) (n1, frontFaceCW) (n2, 0) (Ng, 0)
+    const float4* attr;       // optional varyings, kAttrStride x float4 per triangle, primId order (nullptr when no mesh has any):
+                              // (uv0, uv1) (uv2, -, -) (tangent0..2) (bitangent0..2) (colour0..2)
     const DMaterial* materials;
     const DTexture* textures;
     const float2* seq;        // RandomSequences
@@ -91,7 +100,7 @@ struct PassBuffers {
     uint32_t capacity;        // rays per queue
 };
 
-struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool shadeMiss, shadePbr, shadeGlass; int refillIdle; };
+struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle; };
 
 void launchClearCtrl(const PassBuffers& pb, cudaStream_t s);
 void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s);

@@ -95,9 +95,21 @@ uint32_t packPbrMaterial(const HrhPbrMaterial& in, HrcTexture lut, HrcPbrParams&
     out.clearCoat = in.clearCoat * kMaxClearcoat;
     out.clearCoatRoughness = std::max(saturate(in.clearCoatRoughness), kMinRoughness);
     out.clearCoatRoughnessAlpha = out.clearCoatRoughness * out.clearCoatRoughness;
+    out.baseColorTexture = in.baseColorTexture; out.metallicRoughnessTexture = in.metallicRoughnessTexture;
+    out.emissiveTexture = in.emissiveTexture; out.normalmap = in.normalmap; out.clearCoatTexture = in.clearCoatTexture;
+    out.clearCoatRoughnessTexture = in.clearCoatRoughnessTexture; out.clearCoatNormalmap = in.clearCoatNormalmap;
     uint32_t flags = 0;                                               // feature #defines, PhysicallyBasedMaterial.cpp:49-113
+    const bool force = in.forceEnableAllTextures != 0;
+    if (in.baseColorTexture >= 0 || force) flags |= HRC_MAT_HAS_BASE_COLOR_TEXTURE;
+    if (in.metallicRoughnessTexture >= 0 || force) flags |= HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE;
+    if (in.emissiveTexture >= 0) flags |= HRC_MAT_HAS_EMISSIVE_TEXTURE;
+    if (in.normalmap >= 0) flags |= HRC_MAT_HAS_NORMALMAP;
+    if (in.clearCoatTexture >= 0 || force) flags |= HRC_MAT_HAS_CLEARCOAT_TEXTURE;
+    if (in.clearCoatRoughnessTexture >= 0 || force) flags |= HRC_MAT_HAS_CLEARCOAT_ROUGHNESS_TEXTURE;
+    if (in.clearCoatNormalmap >= 0) flags |= HRC_MAT_HAS_CLEARCOAT_NORMALMAP;
     if (in.doubleSided) flags |= HRC_MAT_DOUBLE_SIDED;
     if (in.alphaMask) flags |= HRC_MAT_ALPHA_MASK;
+    if (in.enableVertexColors) flags |= HRC_MAT_VERTEX_COLORS;
     return flags;
 }
 
@@ -111,7 +123,13 @@ uint32_t packGlassMaterial(const HrhGlassMaterial& in, HrcGlassParams& out) {   
     out.ior = std::max(0.0f, in.ior);
     const float f0 = std::fabs((1.0f - out.ior) / (1.0f + out.ior));
     out.specularF0 = f0 * f0;
-    return 0;
+    out.baseColorTexture = in.baseColorTexture; out.normalmap = in.normalmap; out.metallicRoughnessTexture = in.metallicRoughnessTexture;
+    uint32_t flags = 0;                                               // GlassMaterial.cpp:40-74
+    const bool force = in.forceEnableAllTextures != 0;
+    if (in.baseColorTexture >= 0 || force) flags |= HRC_MAT_HAS_BASE_COLOR_TEXTURE;
+    if (in.metallicRoughnessTexture >= 0 || force) flags |= HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE;
+    if (in.normalmap >= 0) flags |= HRC_MAT_HAS_NORMALMAP;
+    return flags;
 }
 
 void generateMultiscatterLUT(float* out, int dim, int sampleCount, int threads) {           // MultiScatterUtil.cpp:91-139

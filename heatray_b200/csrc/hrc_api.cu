@@ -19,6 +19,7 @@ struct MaterialRec { DMaterial d; int type; uint32_t flags; };
 struct MeshRec {
     bool alive = false;
     std::vector<float> pos, nrm;       // entity space, tightly packed xyz
+    std::vector<float> uv, tan, bit, col;   // optional attributes (empty when absent): 2 / 3 / 3 / 3 floats per vertex
     std::vector<uint32_t> idx;
     int drawMode = 0; float M[16]; int frontFaceCW = 0, isOccluder = 1, material = 0;
 };
@@ -48,7 +49,8 @@ struct HrcContext_t {
     bool committed = false, materialsDirty = true, texturesDirty = true;
     bool anySingleSided = false, anyPbr = false, anyGlass = false;
 
-    float4 *dNodes = nullptr, *dTris = nullptr, *dShade = nullptr;
+    float4 *dNodes = nullptr, *dTris = nullptr, *dShade = nullptr, *dAttr = nullptr;
+    bool anyMasked = false;
     DMaterial* dMaterials = nullptr; size_t dMaterialsCap = 0;
     DTexture* dTextures = nullptr; size_t dTexturesCap = 0;
     float2 *dSeq = nullptr, *dAperture = nullptr; float* dSeqOffsetX = nullptr; uint8_t* dSequenceId = nullptr;
@@ -79,13 +81,14 @@ void freeQueues(HrcContext c) {
 }
 
 DScene sceneOf(HrcContext c) {
-    DScene s; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.materials = c->dMaterials; s.textures = c->dTextures;
+    DScene s; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.attr = c->dAttr; s.materials = c->dMaterials; s.textures = c->dTextures;
     s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId;
     return s;
 }
 LaunchConfig configOf(HrcContext c) {
     LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters;
     lc.refillIdle = c->tuneRefillIdle; lc.traceBlocksPerSM = c->tuneBlocksPerSM;
+    lc.masked = c->anyMasked;
     lc.shadeMiss = c->lights.envEnabled != 0; lc.shadePbr = c->anyPbr; lc.shadeGlass = c->anyGlass;
     return lc;
 }
@@ -127,14 +130,24 @@ int packMaterial(HrcContext c, MaterialRec& m, int type, const void* params, siz
         d.metallic = p->metallic; d.roughness = p->roughness; d.specularF0 = p->specularF0; d.roughnessAlpha = p->roughnessAlpha;
         d.clearCoat = p->clearCoat; d.clearCoatRoughness = p->clearCoatRoughness; d.clearCoatRoughnessAlpha = p->clearCoatRoughnessAlpha;
         d.lutTex = p->multiscatterLUT;
+        d.baseColorTex = p->baseColorTexture; d.metallicRoughnessTex = p->metallicRoughnessTexture; d.emissiveTex = p->emissiveTexture;
+        d.normalTex = p->normalmap; d.clearCoatTex = p->clearCoatTexture; d.clearCoatRoughnessTex = p->clearCoatRoughnessTexture;
+        d.clearCoatNormalTex = p->clearCoatNormalmap;
     } else if (type == HRC_MATERIAL_GLASS) {
         if (bytes != sizeof(HrcGlassParams)) return fail(c, HRC_ERR_INVALID_VALUE, "glass parameter block has the wrong size");
         const HrcGlassParams* p = (const HrcGlassParams*)params;
         for (int k = 0; k < 3; ++k) d.baseColor[k] = p->baseColor[k];
         d.roughness = p->roughness; d.roughnessAlpha = p->roughnessAlpha; d.ior = p->ior; d.density = p->density; d.specularF0 = p->specularF0;
         d.lutTex = -1;
+        d.baseColorTex = p->baseColorTexture; d.metallicRoughnessTex = p->metallicRoughnessTexture; d.normalTex = p->normalmap;
+        d.emissiveTex = d.clearCoatTex = d.clearCoatRoughnessTex = d.clearCoatNormalTex = -1;
     } else return fail(c, HRC_ERR_INVALID_VALUE, "unknown material type");
-    if (d.lutTex >= (int)c->textures.size() || (d.lutTex >= 0 && !c->textures[d.lutTex].alive)) return fail(c, HRC_ERR_INVALID_VALUE, "bad multiscatter LUT texture handle");
+    for (int32_t* h : {&d.lutTex, &d.baseColorTex, &d.metallicRoughnessTex, &d.emissiveTex, &d.normalTex, &d.clearCoatTex, &d.clearCoatRoughnessTex, &d.clearCoatNormalTex}) {
+        if (*h < 0) { *h = -1; continue; }
+        if (*h >= (int)c->textures.size() || !c->textures[*h].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad material texture handle");
+    }
+    if (type == HRC_MATERIAL_GLASS && (m.flags & ~(uint32_t)(HRC_MAT_HAS_BASE_COLOR_TEXTURE | HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE | HRC_MAT_HAS_NORMALMAP)))
+        return fail(c, HRC_ERR_INVALID_VALUE, "glass materials take only the base-colour, metallic-roughness and normal-map flags (GlassMaterial.cpp:40-74)");
     d.typeFlags = (uint32_t)type | (m.flags << 4);
     m.d = d; m.type = type;
     return HRC_OK;
@@ -193,7 +206,7 @@ HRC_API int hrcDestroyContext(HrcContext c) {
     freeQueues(c);
     freeDev(c->accum); freeDev(c->staging); if (c->pinned) cudaFreeHost(c->pinned);
     for (auto& t : c->textures) freeDev(t.dev);
-    freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade); freeDev(c->dMaterials); freeDev(c->dTextures);
+    freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade); freeDev(c->dAttr); freeDev(c->dMaterials); freeDev(c->dTextures);
     freeDev(c->dSeq); freeDev(c->dAperture); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
     freeDev(c->pb.ctrl); freeDev(c->pb.stats);
     for (auto ev : c->evPool) cudaEventDestroy(ev);
@@ -313,8 +326,7 @@ HRC_API int hrcDestroyTexture(HrcContext c, HrcTexture tex) {
 
 HRC_API int hrcCreateMaterial(HrcContext c, int32_t type, uint32_t flags, const void* params, size_t bytes, HrcMaterial* out) {
     if (!c || !params || !out) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
-    const uint32_t unsupported = ~(uint32_t)(HRC_MAT_DOUBLE_SIDED);
-    if (flags & unsupported) return fail(c, HRC_ERR_UNSUPPORTED, "material textures / alpha mask / vertex colours are not built yet");
+    if (flags >> 10) return fail(c, HRC_ERR_INVALID_VALUE, "unknown material feature flags");
     MaterialRec m; m.flags = flags;
     int r = packMaterial(c, m, type, params, bytes); if (r) return r;
     c->materials.push_back(m); c->materialsDirty = true;
@@ -331,7 +343,6 @@ HRC_API int hrcCreateMesh(HrcContext c, const HrcMeshDesc* d, HrcMesh* out) {
     if (!c || !d || !out || !d->positions || !d->normals || !d->indices) return fail(c, HRC_ERR_INVALID_VALUE, "mesh needs positions, normals and indices");
     if (d->material < 0 || d->material >= (int)c->materials.size()) return fail(c, HRC_ERR_INVALID_VALUE, "bad material handle");
     if (d->drawMode != HRC_DRAW_TRIANGLES && d->drawMode != HRC_DRAW_TRIANGLE_STRIP) return fail(c, HRC_ERR_INVALID_VALUE, "bad draw mode");
-    if (!d->isOccluder) return fail(c, HRC_ERR_UNSUPPORTED, "non-occluder (alpha-masked) primitives are not built yet");
     MeshRec m; m.alive = true;
     m.pos.resize((size_t)3 * d->vertexCount); m.nrm.resize((size_t)3 * d->vertexCount);
     const int ps = d->positionStride ? d->positionStride : 12, ns = d->normalStride ? d->normalStride : 12;
@@ -339,6 +350,14 @@ HRC_API int hrcCreateMesh(HrcContext c, const HrcMeshDesc* d, HrcMesh* out) {
         std::memcpy(&m.pos[3 * (size_t)i], (const char*)d->positions + (size_t)i * ps, 12);
         std::memcpy(&m.nrm[3 * (size_t)i], (const char*)d->normals + (size_t)i * ns, 12);
     }
+    auto copyAttr = [&](const float* src, int stride, int comps, std::vector<float>& dst) {
+        if (!src) return;
+        dst.resize((size_t)comps * d->vertexCount);
+        const int st = stride ? stride : comps * 4;
+        for (uint32_t i = 0; i < d->vertexCount; ++i) std::memcpy(&dst[(size_t)comps * i], (const char*)src + (size_t)i * st, (size_t)comps * 4);
+    };
+    copyAttr(d->texCoords, d->texCoordStride, 2, m.uv); copyAttr(d->tangents, d->tangentStride, 3, m.tan);
+    copyAttr(d->bitangents, d->bitangentStride, 3, m.bit); copyAttr(d->colors, d->colorStride, 3, m.col);
     m.idx.assign(d->indices, d->indices + d->elementCount);
     for (uint32_t i : m.idx) if (i >= d->vertexCount) return fail(c, HRC_ERR_INVALID_VALUE, "index out of range");
     m.drawMode = d->drawMode; std::memcpy(m.M, d->worldFromEntity, sizeof(m.M));
@@ -369,16 +388,36 @@ HRC_API int hrcCommitScene(HrcContext c) {
     for (const MeshRec& m : c->meshes) if (m.alive) triTotal += m.drawMode == HRC_DRAW_TRIANGLES ? m.idx.size() / 3 : (m.idx.size() >= 3 ? m.idx.size() - 2 : 0);
     if (triTotal >= (1u << 28)) return fail(c, HRC_ERR_UNSUPPORTED, "more than 2^28 triangles");
     bt.reserve(triTotal); shade.reserve(triTotal * 4);
+    std::vector<float4> attr;       // kAttrStride per triangle, only when some mesh carries uv / tangent / bitangent / colour
+    bool anyAttr = false;
+    for (const MeshRec& m : c->meshes) if (m.alive && (!m.uv.empty() || !m.tan.empty() || !m.bit.empty() || !m.col.empty())) anyAttr = true;
+    if (anyAttr) attr.reserve(triTotal * kAttrStride);
+    c->anyMasked = false;
     for (const MeshRec& m : c->meshes) {
         if (!m.alive) continue;
         const size_t nv = m.pos.size() / 3;
-        std::vector<float> wp(3 * nv), wn(3 * nv);
+        std::vector<float> wp(3 * nv), wn(3 * nv), wt(m.tan.size()), wb(m.bit.size());
         for (size_t i = 0; i < nv; ++i) { xformPoint(m.M, &m.pos[3 * i], &wp[3 * i]); xformNormal(m.M, &m.nrm[3 * i], &wn[3 * i]); }
+        for (size_t i = 0; i < m.tan.size() / 3; ++i) xformNormal(m.M, &m.tan[3 * i], &wt[3 * i]);     // vertex.rlsl:36-37
+        for (size_t i = 0; i < m.bit.size() / 3; ++i) xformNormal(m.M, &m.bit[3 * i], &wb[3 * i]);
+        if (!m.isOccluder) c->anyMasked = true;
         auto emit = [&](uint32_t a, uint32_t b, uint32_t cc) {
             BuildTriangle t;
             for (int k = 0; k < 3; ++k) { t.v0[k] = wp[3 * a + k]; t.v1[k] = wp[3 * b + k]; t.v2[k] = wp[3 * cc + k]; }
             bt.push_back(t);
-            primType.push_back(c->materials[m.material].type);
+            primType.push_back(c->materials[m.material].type | (m.isOccluder ? 0 : (int32_t)kTriNonOccluder));
+            if (anyAttr) {
+                const uint32_t vi[3] = {a, b, cc};
+                float4 rec[kAttrStride];
+                for (auto& r : rec) r = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!m.uv.empty()) { rec[0] = make_float4(m.uv[2 * a], m.uv[2 * a + 1], m.uv[2 * b], m.uv[2 * b + 1]); rec[1] = make_float4(m.uv[2 * cc], m.uv[2 * cc + 1], 0.f, 0.f); }
+                for (int k = 0; k < 3; ++k) {
+                    if (!wt.empty()) rec[2 + k] = make_float4(wt[3 * vi[k]], wt[3 * vi[k] + 1], wt[3 * vi[k] + 2], 0.f);
+                    if (!wb.empty()) rec[5 + k] = make_float4(wb[3 * vi[k]], wb[3 * vi[k] + 1], wb[3 * vi[k] + 2], 0.f);
+                    if (!m.col.empty()) rec[8 + k] = make_float4(m.col[3 * vi[k]], m.col[3 * vi[k] + 1], m.col[3 * vi[k] + 2], 0.f);
+                }
+                attr.insert(attr.end(), rec, rec + kAttrStride);
+            }
             // geometric normal = normalize(cross(e1, e2)) with the same fp32 operation order as the shaders' restatement
             float e1[3], e2[3];
             for (int k = 0; k < 3; ++k) { e1[k] = t.v1[k] - t.v0[k]; e2[k] = t.v2[k] - t.v0[k]; }
@@ -413,7 +452,11 @@ HRC_API int hrcCommitScene(HrcContext c) {
     }
     if (shade.empty()) shade.resize(4, make_float4(0, 0, 0, 0));
     // 4. upload
-    freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade);
+    freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade); freeDev(c->dAttr);
+    if (!attr.empty()) {
+        CU(c, cudaMalloc(&c->dAttr, attr.size() * sizeof(float4)));
+        CU(c, cudaMemcpyAsync(c->dAttr, attr.data(), attr.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    }
     CU(c, cudaMalloc(&c->dNodes, bvh.nodes.size() * sizeof(WideNode)));
     CU(c, cudaMalloc(&c->dTris, tris.size() * sizeof(float4)));
     CU(c, cudaMalloc(&c->dShade, shade.size() * sizeof(float4)));
@@ -422,7 +465,7 @@ HRC_API int hrcCommitScene(HrcContext c) {
     CU(c, cudaMemcpyAsync(c->dShade, shade.data(), shade.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     c->info.triangleCount = bt.size(); c->info.nodeCount = bvh.nodes.size();
-    c->info.nodeBytes = bvh.nodes.size() * sizeof(WideNode); c->info.triangleBytes = bt.size() * 48; c->info.shadingBytes = bt.size() * 64;
+    c->info.nodeBytes = bvh.nodes.size() * sizeof(WideNode); c->info.triangleBytes = bt.size() * 48; c->info.shadingBytes = bt.size() * 64 + attr.size() * sizeof(float4);
     c->info.buildSeconds = (float)bvh.buildSeconds;
     c->committed = true;
     return HRC_OK;

@@ -140,6 +140,31 @@ __device__ __forceinline__ float4 texFetch(const DTexture& t, float u, float v) 
     return r;
 }
 
+struct Surface { float3 P, Ng; float T; float2 uv; float3 tangent, bitangent, color; };   // + interpolated varyings (vertex.rlsl:31-42), zero when absent
+__device__ __forceinline__ float3 offsetOrigin(const Surface& s, float3 dir) {          // ray epsilon policy A-8
+    float m = fmaxf(1.0f, fmaxf(fabsf(s.P.x), fmaxf(fabsf(s.P.y), fabsf(s.P.z))));
+    float eps = 1e-4f * m;
+    float sgn = dot(s.Ng, dir) >= 0.0f ? 1.0f : -1.0f;
+    return s.P + s.Ng * (sgn * eps);
+}
+// texture2D(sampler, texCoord) of a material texture; handle -1 samples the 1x1 white dummy (Texture.h:178-192)
+__device__ __forceinline__ float4 sampleMaterialTexture(const DScene& sc, int handle, float2 uv) {
+    if (handle < 0) return make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    return texFetch(sc.textures[handle], uv.x, uv.y);
+}
+// Barycentric interpolation of the optional varyings of triangle `prim` (same operation order as the normals).
+__device__ __forceinline__ void loadVaryings(const DScene& sc, int prim, float u, float v, bool wantTangents, bool wantColor, Surface& s) {
+    const float4* ap = sc.attr + (size_t)prim * kAttrStride;
+    const float bw = (1.0f - u) - v;
+    const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+    s.uv = make_float2((a0.x * bw + a0.z * u) + a1.x * v, (a0.y * bw + a0.w * u) + a1.y * v);
+    if (wantTangents) {
+        s.tangent = (xyz(__ldg(ap + 2)) * bw + xyz(__ldg(ap + 3)) * u) + xyz(__ldg(ap + 4)) * v;
+        s.bitangent = (xyz(__ldg(ap + 5)) * bw + xyz(__ldg(ap + 6)) * u) + xyz(__ldg(ap + 7)) * v;
+    }
+    if (wantColor) s.color = (xyz(__ldg(ap + 8)) * bw + xyz(__ldg(ap + 9)) * u) + xyz(__ldg(ap + 10)) * v;
+}
+
 // ---------------------------------------------------------------------------------------
 // accumulator.rlsl:12-28. One thread owns a pixel inside any one kernel, so plain RMW is exclusive.
 // ---------------------------------------------------------------------------------------
@@ -301,7 +326,7 @@ struct Traversal {
 
     // Pops the nearest pending child of `group`, tests its 8 children, leaves the hit internal children in `group` and
     // files the hit leaf triangles as a pending triangle group.
-    template <bool STATS>
+    template <bool STATS, bool ANY>
     __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, uint2* stack, TraceCounters& tc) {
         const uint32_t hits = group.y;
         const uint32_t bit = 31u - __clz(hits);                  // highest set bit = nearest remaining child
@@ -330,7 +355,7 @@ struct Traversal {
         const float Bnx = Bx - ex_, Bny = By - ey_, Bnz = Bz - ez_;
         const float Bfx = Bx + ex_, Bfy = By + ey_, Bfz = Bz + ez_;
         const bool negX = !(octInv & 4u), negY = !(octInv & 2u), negZ = !(octInv & 1u);
-        const float tfar = bestT;
+        const float tfar = ANY ? tmaxRay : bestT;   // occlusion rays cull against maxT only: bestT then tracks the nearest alpha-masked hit, which must not hide occluders
         const uint32_t octInv4 = octInv * 0x01010101u;
 
         uint32_t hitMask = 0;
@@ -372,7 +397,7 @@ struct Traversal {
     }
 
     // Tests ONE pending triangle. Returns true when an any-hit ray is finished.
-    template <bool ANY, bool STATS>
+    template <bool ANY, bool STATS, bool MASKED>
     __device__ __forceinline__ bool triStep(const float4* __restrict__ tris, TraceCounters& tc) {
         const uint32_t ti = 31u - __clz(tri.y);
         tri.y &= ~(1u << ti);
@@ -381,11 +406,11 @@ struct Traversal {
         if (STATS) tc.tris++;
         float t, u, v; bool back;
         if (triangleTest(a, b, c, o, d, tmin, tmaxRay, t, u, v, back)) {
-            if (ANY) { found = true; return true; }
+            if (ANY && !(MASKED && (__float_as_uint(b.w) & kTriNonOccluder))) { found = true; return true; }
             const int prim = __float_as_int(a.w);
             if (t < bestT || (t == bestT && prim < (bestPrim & 0x0fffffff))) {
                 bestT = t; bestU = u; bestV = v; found = true;
-                bestPrim = prim | (back ? HRC_HIT_BACKFACE : 0) | (__float_as_int(b.w) << 28);
+                bestPrim = prim | (back ? HRC_HIT_BACKFACE : 0) | ((__float_as_int(b.w) & 3) << 28);
             }
         }
         return false;
@@ -399,8 +424,8 @@ __device__ __forceinline__ void traverseSimple(const float4* __restrict__ nodes,
     uint2 stack[kTraceStack];
     TraceCounters tc{0u, 0u, 0u};
     for (;;) {
-        if (tr.hasNodeWork()) tr.nodeStep<false>(nodes, stack, tc);
-        while (tr.tri.y) if (tr.triStep<ANY, false>(tris, tc)) return;
+        if (tr.hasNodeWork()) tr.nodeStep<false, ANY>(nodes, stack, tc);
+        while (tr.tri.y) if (tr.triStep<ANY, false, false>(tris, tc)) return;
         tr.popIfEmpty(stack);
         if (tr.finished()) return;
     }
@@ -470,7 +495,7 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_co
 // gain), and "one node step or one triangle per trip".
 constexpr uint32_t kFull = 0xffffffffu;
 
-template <bool ANY, bool STATS>
+template <bool ANY, bool STATS, bool MASKED>
 __global__ void __launch_bounds__(128, 8) k_trace(const DScene sc, const __grid_constant__ DFrame fr, const PassBuffers pb, int iter, int kRefillIdle) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t below = (1u << lane) - 1u;
@@ -486,6 +511,7 @@ __global__ void __launch_bounds__(128, 8) k_trace(const DScene sc, const __grid_
     bool active = false, exhausted = false;
     uint32_t rayIdx = 0, doneIdx = 0;
     int doneClass = -1;                      // closest-hit only: class of a finished ray not yet appended to its list
+    float extraT = 0.0f; int maskedPasses = 0;   // MASKED only: distance already travelled through alpha-masked surfaces
 
     for (;;) {
         const uint32_t idle = __ballot_sync(kFull, !active);
@@ -516,6 +542,7 @@ __global__ void __launch_bounds__(128, 8) k_trace(const DScene sc, const __grid_
                         const float4 ro = __ldcs(ANY ? pb.shadow.o + i : qod + 2 * (size_t)i), rd = __ldcs(ANY ? pb.shadow.d + i : qod + 2 * (size_t)i + 1);   // streamed: keep the BVH in L2
                         rayIdx = i;
                         tr.begin(xyz(ro), xyz(rd), 0.0f, ro.w);
+                        if (MASKED) { extraT = rd.w; maskedPasses = 0; }
                         active = true;
                     }
                 }
@@ -525,17 +552,39 @@ __global__ void __launch_bounds__(128, 8) k_trace(const DScene sc, const __grid_
         }
 
         while (active) {
-            if (tr.hasNodeWork()) tr.nodeStep<STATS>(nodes, stack, tc);
+            if (tr.hasNodeWork()) tr.nodeStep<STATS, ANY>(nodes, stack, tc);
             bool occluded = false;
-            while (tr.tri.y) if (tr.triStep<ANY, STATS>(tris, tc)) { occluded = true; break; }
+            while (tr.tri.y) if (tr.triStep<ANY, STATS, MASKED>(tris, tc)) { occluded = true; break; }
             tr.popIfEmpty(stack);
             if (occluded) { active = false; break; }                       // any-hit: nothing to shade
             if (tr.finished()) {
+                if (ANY && MASKED && (tr.bestPrim & 0x0fffffff) != 0x0fffffff) {
+                    // No occluder on the way, but an alpha-masked (non-occluder) surface: physicallyBased.rlsl:70-90 (policy A-5).
+                    const int prim = tr.bestPrim & 0x0fffffff;
+                    const float4* sp = sc.shade + (size_t)prim * 4;
+                    const int mat = __float_as_int(__ldg(sp).w);
+                    const uint32_t tf = sc.materials[mat].typeFlags;
+                    float alpha = 1.0f;
+                    if ((tf & 0xfu) == HRC_MATERIAL_PBR && ((tf >> 4) & HRC_MAT_HAS_BASE_COLOR_TEXTURE) && sc.attr) {
+                        Surface sv; loadVaryings(sc, prim, tr.bestU, tr.bestV, false, false, sv);
+                        alpha = sampleMaterialTexture(sc, sc.materials[mat].baseColorTex, sv.uv).w;
+                    }
+                    if ((tf & 0xfu) == HRC_MATERIAL_PBR && ((tf >> 4) & HRC_MAT_ALPHA_MASK) && alpha < 1.0f && maskedPasses < kMaxMaskedSurfaces) {
+                        Surface sv; sv.P = tr.o + tr.d * tr.bestT; sv.Ng = xyz(__ldg(sp + 3));
+                        const float t = tr.bestT;
+                        extraT += t; ++maskedPasses;                                     // :84
+                        atomicAdd(&ctrl->maskedContinuations, 1u);
+                        tr.begin(offsetOrigin(sv, tr.d), tr.d, 0.0f, tr.tmaxRay - t);    // :80
+                        continue;
+                    }
+                    active = false;                                                      // :88-90 shadowed
+                    break;
+                }
                 active = false;
                 if (ANY) {             // the ray reached its light: run the light shader (policy A-5/A-6)
                     const float4 w = __ldcs(pb.shadow.w + rayIdx);
                     const uint32_t bits = __float_as_uint(w.w);
-                    shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, pb.shadow.d[rayIdx].w);
+                    shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, MASKED ? extraT : pb.shadow.d[rayIdx].w);
                 } else {
                     __stcs(pb.hits + rayIdx, tr.found ? make_float4(tr.bestT, tr.bestU, tr.bestV, __int_as_float(tr.bestPrim))
                                                       : make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));
@@ -559,7 +608,6 @@ __global__ void __launch_bounds__(128, 8) k_trace(const DScene sc, const __grid_
 }
 
 // ---- material shading ------------------------------------------------------------------
-struct Surface { float3 P, Ng; float T; };
 struct InRay { float3 o, d, weight; float tmax; uint32_t depth, sequenceID, pixel; int sequenceIndexOffset; };
 struct Emit {
     bool hasOcc, hasExt;
@@ -567,12 +615,6 @@ struct Emit {
     float3 extO, extD, extW; uint32_t extMissKind;
 };
 
-__device__ __forceinline__ float3 offsetOrigin(const Surface& s, float3 dir) {          // ray epsilon policy A-8
-    float m = fmaxf(1.0f, fmaxf(fabsf(s.P.x), fmaxf(fabsf(s.P.y), fabsf(s.P.z))));
-    float eps = 1e-4f * m;
-    float sgn = dot(s.Ng, dir) >= 0.0f ? 1.0f : -1.0f;
-    return s.P + s.Ng * (sgn * eps);
-}
 __device__ __forceinline__ void emitOcc(Emit& e, const Surface& s, float3 dir, float3 w, uint32_t kind, uint32_t idx, float tmax) {
     e.hasOcc = true; e.occO = offsetOrigin(s, dir); e.occD = dir; e.occW = w; e.occTmax = tmax; e.occMissKind = kind; e.occMissIndex = idx;
 }
@@ -657,38 +699,82 @@ __device__ void shadePBR(const DScene& sc, const DFrame& fr, float4* accum, cons
     const HrcGlobals& g = fr.g;
     const uint32_t flags = m.typeFlags >> 4;
     float3 baseColor = f3(m.baseColor);
+    float alpha = 1.0f;
+    if (flags & HRC_MAT_HAS_BASE_COLOR_TEXTURE) {                             // :59-65
+        const float4 t = sampleMaterialTexture(sc, m.baseColorTex, s.uv);
+        baseColor = baseColor * xyz(t); alpha = t.w;
+    }
+    if (flags & HRC_MAT_VERTEX_COLORS) baseColor = baseColor * s.color;       // :66-68
+    if ((flags & HRC_MAT_ALPHA_MASK) && alpha < 1.0f) {                       // :70-87 (extension rays; occlusion rays: k_trace<any>)
+        e.hasExt = true; e.extO = offsetOrigin(s, in.d); e.extD = in.d; e.extW = in.weight; e.extMissKind = 0xffu;
+        return;
+    }
     float3 N = normalize(interpNormal);
     if (flags & HRC_MAT_DOUBLE_SIDED) { if (!frontFacing) N = -N; }          // :96-100
     else if (!frontFacing) {                                                  // :102-107 pass-through re-emit
         e.hasExt = true; e.extO = offsetOrigin(s, in.d); e.extD = in.d; e.extW = in.weight; e.extMissKind = 0xffu;   // 0xff: keep the incoming miss shader
         return;
     }
-    const float3 clearCoatN = N;
+    float3 clearCoatN = N;
+    float3 nmSample = f3(0.0f), ccnmSample = f3(0.0f);
+    float metallic = m.metallic, roughness = m.roughness, roughnessAlpha = m.roughnessAlpha;
+    float clearCoat = m.clearCoat, clearCoatRoughness = m.clearCoatRoughness, clearCoatRoughnessAlpha = m.clearCoatRoughnessAlpha;
+    float3 emissive = f3(m.emissive);
+    if (flags & kMatAnyTexture) {
+        if (flags & kMatTangentSpace) {
+            const float3 T = normalize(s.tangent), B = normalize(s.bitangent);
+            if (flags & HRC_MAT_HAS_NORMALMAP) {                              // :112-118
+                nmSample = xyz(sampleMaterialTexture(sc, m.normalTex, s.uv));
+                const float3 ts = nmSample * 2.0f - f3(1.0f);
+                N = normalize((T * ts.x + B * ts.y) + N * ts.z);
+            }
+            if (flags & HRC_MAT_HAS_CLEARCOAT_NORMALMAP) {                    // :120-126
+                ccnmSample = xyz(sampleMaterialTexture(sc, m.clearCoatNormalTex, s.uv));
+                const float3 ts = ccnmSample * 2.0f - f3(1.0f);
+                clearCoatN = normalize((T * ts.x + B * ts.y) + clearCoatN * ts.z);
+            }
+        }
+        if (flags & HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE) {                 // :135-140 (.bg)
+            const float4 t = sampleMaterialTexture(sc, m.metallicRoughnessTex, s.uv);
+            metallic *= t.z; roughness *= t.y; roughnessAlpha = roughness * roughness;
+        }
+        if (flags & HRC_MAT_HAS_CLEARCOAT_TEXTURE) clearCoat *= sampleMaterialTexture(sc, m.clearCoatTex, s.uv).x;            // :145-147
+        if (flags & HRC_MAT_HAS_CLEARCOAT_ROUGHNESS_TEXTURE) {                // :148-151
+            clearCoatRoughness *= sampleMaterialTexture(sc, m.clearCoatRoughnessTex, s.uv).x;
+            clearCoatRoughnessAlpha = clearCoatRoughness * clearCoatRoughness;
+        }
+        if (flags & HRC_MAT_HAS_EMISSIVE_TEXTURE) emissive = xyz(sampleMaterialTexture(sc, m.emissiveTex, s.uv));             // :153-156 (replaces)
+    }
     const M3 frame = orthonormalFrame(N);
     const float3 V = -in.d;
     const float NdotV = saturate(dot(N, V));
-    const float3 emissive = f3(m.emissive);
 
     if (g.enableDebugVisualizer == 1) {                                       // :159-203
+        const bool ht = (flags & kMatAnyTexture) != 0, uts = (flags & kMatTangentSpace) != 0;
         if (g.showGeometricNormals == 1) accumulate4(accum, in.pixel, (interpNormal + f3(1.0f)) * 0.5f, 1.0f);
+        else if (ht && g.showUVs == 1) accumulate4(accum, in.pixel, f3(s.uv.x, s.uv.y, 0.0f), 1.0f);
+        else if (uts && g.showTangents == 1) accumulate4(accum, in.pixel, (s.tangent + f3(1.0f)) * 0.5f, 1.0f);
+        else if (uts && g.showBitangents == 1) accumulate4(accum, in.pixel, (s.bitangent + f3(1.0f)) * 0.5f, 1.0f);
+        else if ((flags & HRC_MAT_HAS_NORMALMAP) && g.showNormalmap == 1) accumulate4(accum, in.pixel, nmSample, 1.0f);
         else if (g.showFinalNormals == 1) accumulate4(accum, in.pixel, (N + f3(1.0f)) * 0.5f, 1.0f);
         else if (g.showBaseColor == 1) accumulate4(accum, in.pixel, baseColor, 1.0f);
         else if (g.showEmissive == 1) accumulate4(accum, in.pixel, emissive, 1.0f);
-        else if (g.showRoughness == 1) accumulate4(accum, in.pixel, f3(m.roughness), 1.0f);
-        else if (g.showMetallic == 1) accumulate4(accum, in.pixel, f3(m.metallic), 1.0f);
-        else if (g.showClearcoat == 1) accumulate4(accum, in.pixel, f3(m.clearCoat), 1.0f);
-        else if (g.showClearcoatRoughness == 1) accumulate4(accum, in.pixel, f3(m.clearCoatRoughness), 1.0f);
+        else if (g.showRoughness == 1) accumulate4(accum, in.pixel, f3(roughness), 1.0f);
+        else if (g.showMetallic == 1) accumulate4(accum, in.pixel, f3(metallic), 1.0f);
+        else if (g.showClearcoat == 1) accumulate4(accum, in.pixel, f3(clearCoat), 1.0f);
+        else if (g.showClearcoatRoughness == 1) accumulate4(accum, in.pixel, f3(clearCoatRoughness), 1.0f);
         else if (g.showShader == 1) accumulate4(accum, in.pixel, f3(1.0f, 0.0f, 0.0f), 1.0f);
+        else if ((flags & HRC_MAT_HAS_CLEARCOAT_NORMALMAP) && g.showClearcoatNormalmap == 1) accumulate4(accum, in.pixel, ccnmSample, 1.0f);
         return;
     }
 
     float3 weight = in.weight;
     performAccumulate(g, accum, in.pixel, weight * emissive);                // :205
     const float clearCoatNdotV = saturate(dot(clearCoatN, V));
-    const float clearCoatScale = F_Schlick1(0.04f, clearCoatNdotV) * m.clearCoat;
+    const float clearCoatScale = F_Schlick1(0.04f, clearCoatNdotV) * clearCoat;
     const float bottom = 1.0f - clearCoatScale;
-    const float3 Cdiff = (baseColor * (1.0f - m.metallic)) * bottom;         // :214
-    const float3 Cspec = mix3(f3(m.specularF0), baseColor, m.metallic) * bottom;   // :220
+    const float3 Cdiff = (baseColor * (1.0f - metallic)) * bottom;         // :214
+    const float3 Cspec = mix3(f3(m.specularF0), baseColor, metallic) * bottom;   // :220
     const float diffuseLuminance = luminosity(Cdiff), specularLuminance = luminosity(Cspec);
     const float pn = 1.0f / greaterThanZero(diffuseLuminance + specularLuminance + clearCoatScale);
     const float diffuseProbability = diffuseLuminance * pn, specularProbability = specularLuminance * pn, clearCoatProbability = clearCoatScale * pn;
@@ -711,10 +797,10 @@ __device__ void shadePBR(const DScene& sc, const DFrame& fr, float4* accum, cons
         if (pr.x <= diffuseProbability) {
             lb.diffuse = true; lb.N = N; lb.NdotI = NdotV; lb.C = Cdiff; lb.alpha = 0.f; lb.roughness = 0.f; lb.probability = diffuseProbability;
         } else if (pr.x <= (diffuseProbability + clearCoatProbability)) {
-            lb.diffuse = false; lb.N = clearCoatN; lb.NdotI = clearCoatNdotV; lb.C = f3(clearCoatScale); lb.alpha = m.clearCoatRoughnessAlpha;
-            lb.roughness = m.clearCoatRoughness; lb.probability = clearCoatProbability;
+            lb.diffuse = false; lb.N = clearCoatN; lb.NdotI = clearCoatNdotV; lb.C = f3(clearCoatScale); lb.alpha = clearCoatRoughnessAlpha;
+            lb.roughness = clearCoatRoughness; lb.probability = clearCoatProbability;
         } else if (pr.x <= (diffuseProbability + clearCoatProbability + specularProbability)) {
-            lb.diffuse = false; lb.N = N; lb.NdotI = NdotV; lb.C = Cspec; lb.alpha = m.roughnessAlpha; lb.roughness = m.roughness; lb.probability = specularProbability;
+            lb.diffuse = false; lb.N = N; lb.NdotI = NdotV; lb.C = Cspec; lb.alpha = roughnessAlpha; lb.roughness = roughness; lb.probability = specularProbability;
         } else continue;
 
         float optLightProb = 1.0f;
@@ -787,23 +873,41 @@ __device__ void shadePBR(const DScene& sc, const DFrame& fr, float4* accum, cons
 __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, const InRay& in, const DMaterial& m, const Surface& s,
                            float3 interpNormal, bool frontFacing, Emit& e) {
     const HrcGlobals& g = fr.g;
+    const uint32_t flags = m.typeFlags >> 4;
     float3 N = normalize(interpNormal);
     float nIn = 1.0f, nOut = m.ior;
     float3 weight = in.weight;
-    const float3 baseColor = f3(m.baseColor);
+    float3 nmSample = f3(0.0f);
+    if (flags & HRC_MAT_HAS_NORMALMAP) {                                      // :145-151
+        const float3 T = normalize(s.tangent), B = normalize(s.bitangent);
+        nmSample = xyz(sampleMaterialTexture(sc, m.normalTex, s.uv));
+        const float3 ts = nmSample * 2.0f - f3(1.0f);
+        N = normalize((T * ts.x + B * ts.y) + N * ts.z);
+    }
+    float3 baseColor = f3(m.baseColor);
+    if (flags & HRC_MAT_HAS_BASE_COLOR_TEXTURE) baseColor = baseColor * xyz(sampleMaterialTexture(sc, m.baseColorTex, s.uv));   // :154-156
     if (!frontFacing) {                                                       // :161-167
         N = -N; nIn = m.ior; nOut = 1.0f;
         const float3 absorption = f3(1.0f) - baseColor;                       // beersLaw :131-136
         const float k = m.density * -s.T;
         weight = in.weight * f3(expf(absorption.x * k), expf(absorption.y * k), expf(absorption.z * k));
     }
-    const float roughness = m.roughness, roughnessAlpha = m.roughnessAlpha;
+    float roughness = m.roughness, roughnessAlpha = m.roughnessAlpha;
+    if (flags & HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE) {                     // :171-176 (.g; metallic ignored)
+        roughness *= sampleMaterialTexture(sc, m.metallicRoughnessTex, s.uv).y;
+        roughnessAlpha = roughness * roughness;
+    }
     if (g.enableDebugVisualizer == 1) {                                       // :179-211
+        const bool ht = (flags & kMatAnyTexture) != 0, uts = (flags & kMatTangentSpace) != 0;
         if (g.showGeometricNormals == 1) accumulate4(accum, in.pixel, (interpNormal + f3(1.0f)) * 0.5f, 1.0f);
         else if (g.showFinalNormals == 1) accumulate4(accum, in.pixel, (N + f3(1.0f)) * 0.5f, 1.0f);
         else if (g.showBaseColor == 1) accumulate4(accum, in.pixel, baseColor, 1.0f);
         else if (g.showRoughness == 1) accumulate4(accum, in.pixel, f3(roughness), 1.0f);
         else if (g.showShader == 1) accumulate4(accum, in.pixel, f3(0.0f, 1.0f, 0.0f), 1.0f);
+        else if (ht && g.showUVs == 1) accumulate4(accum, in.pixel, f3(s.uv.x, s.uv.y, 0.0f), 1.0f);
+        else if (uts && g.showTangents == 1) accumulate4(accum, in.pixel, (s.tangent + f3(1.0f)) * 0.5f, 1.0f);
+        else if (uts && g.showBitangents == 1) accumulate4(accum, in.pixel, (s.bitangent + f3(1.0f)) * 0.5f, 1.0f);
+        else if ((flags & HRC_MAT_HAS_NORMALMAP) && g.showNormalmap == 1) accumulate4(accum, in.pixel, nmSample, 1.0f);
         return;
     }
     const M3 frame = orthonormalFrame(N);
@@ -944,6 +1048,10 @@ __global__ void __launch_bounds__(128) k_shade(const DScene sc, const __grid_con
                 const float bw = (1.0f - hr.y) - hr.z;
                 const float3 n = (xyz(s0) * bw + xyz(s1) * hr.y) + xyz(s2) * hr.z;
                 const DMaterial m = sc.materials[__float_as_int(s0.w)];
+                s.uv = make_float2(0.f, 0.f); s.tangent = f3(0.f); s.bitangent = f3(0.f); s.color = f3(0.f);
+                const uint32_t mflags = m.typeFlags >> 4;
+                if (sc.attr && (mflags & (kMatAnyTexture | HRC_MAT_VERTEX_COLORS)))
+                    loadVaryings(sc, prim, hr.y, hr.z, (mflags & kMatTangentSpace) != 0, (mflags & HRC_MAT_VERTEX_COLORS) != 0, s);
                 if (CLS == 1) shadePBR(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
                 else          shadeGlass(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
                 if (e.hasExt && ((int)in.depth + 1 > hardCap || lastIter)) e.hasExt = false;
@@ -982,7 +1090,7 @@ __global__ void k_finish_pass(PassBuffers pb, int iterations) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     unsigned long long ext = 0, occ = 0;
     for (int i = 1; i < iterations; ++i) ext += pb.ctrl[i].extCount;
-    for (int i = 0; i < iterations; ++i) occ += pb.ctrl[i].shadowCount;
+    for (int i = 0; i < iterations; ++i) occ += pb.ctrl[i].shadowCount + pb.ctrl[i].maskedContinuations;
     pb.stats->raysPrimary += pb.ctrl[0].extCount;
     pb.stats->raysExtension += ext;
     pb.stats->raysOcclusion += occ;
@@ -1025,14 +1133,19 @@ void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cud
 void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     DFrame dummy{};   // closest-hit traversal does not read the frame constants
     const int grid = lc.smCount * lc.traceBlocksPerSM;
-    if (lc.collectStats) k_trace<false, true><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
-    else                 k_trace<false, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
+    if (lc.collectStats) k_trace<false, true, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
+    else                 k_trace<false, false, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
 }
 
 void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     const int grid = lc.smCount * lc.traceBlocksPerSM;
-    if (lc.collectStats) k_trace<true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
-    else                 k_trace<true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+    if (lc.masked) {
+        if (lc.collectStats) k_trace<true, true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+        else                 k_trace<true, false, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+    } else {
+        if (lc.collectStats) k_trace<true, true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+        else                 k_trace<true, false, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+    }
 }
 
 void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {

@@ -39,6 +39,10 @@ class MeshSpec:
     material: int
     transform: np.ndarray = field(default_factory=lambda: np.eye(4, dtype=np.float32))
     draw_mode: int = capi.DRAW_TRIANGLES
+    uvs: np.ndarray = None          # optional per-vertex attributes (MeshProvider.h VertexBufferUsage)
+    tangents: np.ndarray = None
+    bitangents: np.ndarray = None
+    colors: np.ndarray = None
 
     @property
     def triangle_count(self):
@@ -50,6 +54,7 @@ class MeshSpec:
 class MaterialSpec:
     kind: str                      # "pbr" | "glass"
     params: dict
+    textures: dict = field(default_factory=dict)   # slot name (HrhPbrMaterial field) -> float32 array (H, W, 4), row 0 = t = 0
 
 
 @dataclass
@@ -98,14 +103,26 @@ def rotate(axis, angle):
 
 
 # ---- mesh providers -------------------------------------------------------------------------------
-def plane_mesh(width, length):
+def plane_mesh(width, length, with_uv=False):
     lib = capi.load_library()
     pos, nrm, uv, idx = np.zeros((4, 3), np.float32), np.zeros((4, 3), np.float32), np.zeros((4, 2), np.float32), np.zeros(4, np.uint32)
     lib.hrhPlaneMesh(width, length, capi._ptr(pos), capi._ptr(nrm), capi._ptr(uv), capi._ptr(idx))
-    return pos, nrm, idx
+    return (pos, nrm, idx, uv) if with_uv else (pos, nrm, idx)
 
 
 _sphere_cache = {}
+
+
+def sphere_mesh_uv(u_slices, v_slices, radius):
+    """Sphere with texture coordinates plus a tangent frame (tangent = d position / d longitude, bitangent = n x t)."""
+    pos, nrm, idx = sphere_mesh(u_slices, v_slices, radius)
+    uv = _sphere_cache[(u_slices, v_slices, radius, "uv")]
+    up = np.array([0.0, 1.0, 0.0], np.float32)
+    tan = np.cross(up, nrm)
+    ln = np.linalg.norm(tan, axis=1, keepdims=True)
+    tan = np.where(ln > 1e-6, tan / np.maximum(ln, 1e-6), np.array([1.0, 0.0, 0.0], np.float32)).astype(np.float32)
+    bit = np.cross(nrm, tan).astype(np.float32)
+    return pos, nrm, idx, uv, tan, bit
 
 
 def sphere_mesh(u_slices, v_slices, radius):
@@ -118,6 +135,7 @@ def sphere_mesh(u_slices, v_slices, radius):
         uv, idx = np.zeros((nv.value, 2), np.float32), np.zeros(ni.value, np.uint32)
         lib.hrhSphereMesh(u_slices, v_slices, radius, capi._ptr(pos), capi._ptr(nrm), capi._ptr(uv), capi._ptr(idx), None, None)
         _sphere_cache[key] = (pos, nrm, idx)
+        _sphere_cache[key + ("uv",)] = uv
     return _sphere_cache[key]
 
 
@@ -203,13 +221,15 @@ def studio_environment(width=2048, height=1024):
 
 
 # ---- the configs -----------------------------------------------------------------------------------
-def _pbr(base, rough=1.0, metal=0.0, f0=0.5, emissive=(0, 0, 0), cc=0.0, ccr=0.0, double_sided=True):
+def _pbr(base, rough=1.0, metal=0.0, f0=0.5, emissive=(0, 0, 0), cc=0.0, ccr=0.0, double_sided=True, alpha_mask=False,
+         vertex_colors=False, force_textures=False, textures=None):
     return MaterialSpec("pbr", dict(baseColor=base, emissiveColor=emissive, metallic=metal, roughness=rough, specularF0=f0,
-                                    clearCoat=cc, clearCoatRoughness=ccr, doubleSided=double_sided))
+                                    clearCoat=cc, clearCoatRoughness=ccr, doubleSided=double_sided, alphaMask=alpha_mask,
+                                    vertexColors=vertex_colors, forceEnableAllTextures=force_textures), textures or {})
 
 
-def _glass(base, rough, ior, density):
-    return MaterialSpec("glass", dict(baseColor=base, roughness=rough, ior=ior, density=density))
+def _glass(base, rough, ior, density, textures=None):
+    return MaterialSpec("glass", dict(baseColor=base, roughness=rough, ior=ior, density=density), textures or {})
 
 
 def cornell_box(width=512, height=512, passes=64, max_depth=4):
@@ -314,5 +334,71 @@ def terrain(width=3840, height=2160, passes=16, max_depth=8, n=2048, blobs=400, 
                      camera=dict(distance=55.0, phi=0.3, theta=0.45, target=(0.0, 0.0, 0.0), focal_length=35.0, fstop=None, focus_distance=55.0))
 
 
+def _checker(n, cells, a, b):
+    """n x n RGBA checker of `cells` squares per side between colours a and b (4 floats each)."""
+    g = (np.arange(n) * cells // n)
+    m = ((g[:, None] + g[None, :]) & 1).astype(np.float32)[..., None]
+    return (np.asarray(a, np.float32) * (1 - m) + np.asarray(b, np.float32) * m).astype(np.float32)
+
+
+def _bump_normalmap(n, waves):
+    """Tangent-space normal map of a sinusoidal egg-crate height field, encoded (n*0.5+0.5), alpha 1."""
+    t = (np.arange(n, dtype=np.float32) + 0.5) / n
+    x, y = np.meshgrid(t, t, indexing="xy")
+    dx = 0.6 * np.cos(2 * np.pi * waves * x) * np.abs(np.sin(2 * np.pi * waves * y))
+    dy = 0.6 * np.cos(2 * np.pi * waves * y) * np.abs(np.sin(2 * np.pi * waves * x))
+    nrm = np.stack([-dx, -dy, np.ones_like(dx)], -1)
+    nrm /= np.linalg.norm(nrm, axis=-1, keepdims=True)
+    return np.concatenate([nrm * 0.5 + 0.5, np.ones_like(dx)[..., None]], -1).astype(np.float32)
+
+
+def _gradient(n, c0, c1):
+    t = ((np.arange(n, dtype=np.float32) + 0.5) / n)[None, :, None]
+    img = np.asarray(c0, np.float32) * (1 - t) + np.asarray(c1, np.float32) * t
+    return np.broadcast_to(img, (n, n, 4)).astype(np.float32).copy()
+
+
+def textured_showcase(width=192, height=128, passes=4, max_depth=5, u_slices=32, v_slices=16):
+    """Every texture slot, vertex colours, an alpha-masked (non-occluder) fence and textured glass in one small scene:
+    the parity case for physicallyBased.rlsl:57-156 / glass.rlsl:145-176 (not one of BASELINE.json's bench configs)."""
+    tex_base = _checker(64, 8, (0.9, 0.85, 0.8, 1.0), (0.25, 0.3, 0.6, 1.0))
+    tex_mr = _gradient(32, (0.0, 0.15, 0.0, 1.0), (0.0, 1.0, 1.0, 1.0))                 # .g roughness, .b metallic
+    tex_nm = _bump_normalmap(64, 4)
+    tex_fence = _checker(32, 8, (0.8, 0.7, 0.3, 1.0), (0.0, 0.0, 0.0, 0.0))              # alpha 0 holes
+    tex_em = _checker(16, 4, (0.0, 0.0, 0.0, 1.0), (0.9, 0.4, 0.1, 1.0))
+    tex_cc = _gradient(16, (0.2, 0.0, 0.0, 1.0), (1.0, 0.0, 0.0, 1.0))
+    tex_ccr = _gradient(16, (0.1, 0.0, 0.0, 1.0), (0.9, 0.0, 0.0, 1.0))
+    tex_ccn = _bump_normalmap(32, 2)
+    tex_glass = _checker(32, 6, (0.95, 0.95, 0.95, 1.0), (0.6, 0.9, 0.7, 1.0))
+    mats = [
+        _pbr((1.0, 1.0, 1.0), rough=0.9, f0=0.5, textures=dict(baseColorTexture=tex_base, metallicRoughnessTexture=tex_mr, normalmap=tex_nm)),      # 0 ground
+        _pbr((1.0, 1.0, 1.0), rough=0.8, f0=0.5, alpha_mask=True, textures=dict(baseColorTexture=tex_fence)),                                        # 1 fence
+        _pbr((0.7, 0.7, 0.75), rough=0.5, f0=0.5, cc=1.0, ccr=0.4,
+             textures=dict(emissiveTexture=tex_em, clearCoatTexture=tex_cc, clearCoatRoughnessTexture=tex_ccr, clearCoatNormalmap=tex_ccn, normalmap=tex_nm)),   # 2
+        _pbr((1.0, 1.0, 1.0), rough=0.6, metal=0.0, f0=0.5, vertex_colors=True, force_textures=True),                                                # 3 vertex colours + forced dummy textures
+        _glass((1.0, 1.0, 1.0), 0.3, 1.5, 0.5, textures=dict(baseColorTexture=tex_glass, metallicRoughnessTexture=tex_mr, normalmap=tex_nm)),        # 4
+        _pbr((0.6, 0.6, 0.6), rough=1.0, f0=0.5, double_sided=False),                                                                                # 5 single-sided back wall
+    ]
+    meshes = []
+    p, n, i, uv = plane_mesh(1.0, 1.0, with_uv=True)
+    strip = capi.DRAW_TRIANGLE_STRIP
+    tx = np.tile(np.array([1.0, 0.0, 0.0], np.float32), (4, 1))
+    bz = np.tile(np.array([0.0, 0.0, -1.0], np.float32), (4, 1))
+    meshes.append(MeshSpec(p, n, i, 0, scale(8, 1, 8), strip, uvs=uv * 4.0, tangents=tx, bitangents=bz))
+    meshes.append(MeshSpec(p, n, i, 1, translate(0.0, 1.0, 1.2) @ rotate("x", math.pi / 2) @ scale(5, 1, 2), strip, uvs=uv, tangents=tx, bitangents=bz))
+    meshes.append(MeshSpec(p, n, i, 5, translate(0.0, 1.5, -3.0) @ rotate("x", math.pi / 2) @ scale(8, 1, 3), strip))
+    sp, sn, si, suv, st, sb = sphere_mesh_uv(u_slices, v_slices, 0.7)
+    meshes.append(MeshSpec(sp, sn, si, 2, translate(-1.7, 0.7, -0.3), uvs=suv, tangents=st, bitangents=sb))
+    col = (sn * 0.5 + 0.5).astype(np.float32)
+    meshes.append(MeshSpec(sp, sn, si, 3, translate(0.0, 0.7, -0.6), uvs=suv, colors=col))
+    meshes.append(MeshSpec(sp, sn, si, 4, translate(1.7, 0.7, -0.3) @ scale(1.0, 1.1, 1.0), uvs=suv, tangents=st, bitangents=sb))
+    return SceneSpec("textured_showcase", width, height, passes, max_depth, meshes, mats,
+                     env=dict(enabled=True, solid=(0.35, 0.4, 0.5), map=None, ev=0.0, theta=0.0),
+                     dir_lights=[dict(color=(1.0, 0.95, 0.9), illuminance=683.0 * 1.5, theta=math.pi / 3, phi=0.6)],
+                     point_lights=[dict(color=(1.0, 0.9, 0.8), intensity=683.0 * 1.2, position=(0.0, 2.2, 3.0))],
+                     camera=dict(distance=6.5, phi=0.15, theta=0.35, target=(0.0, 0.6, 0.0), focal_length=35.0, fstop=None, focus_distance=6.5))
+
+
 def build(name: str, **kw) -> SceneSpec:
-    return {"cornell": cornell_box, "sphere_grid": sphere_grid, "material_grid": material_grid, "terrain": terrain}[name](**kw)
+    return {"cornell": cornell_box, "sphere_grid": sphere_grid, "material_grid": material_grid, "terrain": terrain,
+            "textured_showcase": textured_showcase}[name](**kw)

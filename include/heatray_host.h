@@ -41,9 +41,16 @@ typedef struct HrhPbrMaterial {       /* PhysicallyBasedMaterial.h Parameters (u
     float baseColor[3]; float emissiveColor[3];
     float metallic, roughness, specularF0, clearCoat, clearCoatRoughness;
     int32_t doubleSided, alphaMask;
+    /* textures: HRC_NULL_TEXTURE = none (the shader then sees the 1x1 white dummy, Texture.h:178-192) */
+    HrcTexture baseColorTexture, metallicRoughnessTexture, emissiveTexture, normalmap;
+    HrcTexture clearCoatTexture, clearCoatRoughnessTexture, clearCoatNormalmap;
+    int32_t forceEnableAllTextures;   /* PhysicallyBasedMaterial.h Parameters::forceEnableAllTextures */
+    int32_t enableVertexColors;       /* Material::m_enableVertexColors (Material.h) */
 } HrhPbrMaterial;
 typedef struct HrhGlassMaterial {     /* GlassMaterial.h Parameters */
     float baseColor[3]; float roughness, ior, density;
+    HrcTexture baseColorTexture, normalmap, metallicRoughnessTexture;
+    int32_t forceEnableAllTextures;
 } HrhGlassMaterial;
 /* modify(): clamps and derived values (PhysicallyBasedMaterial.cpp:127-145, quirk B-Q16); returns the feature flags. */
 HRC_API uint32_t hrhPackPbrMaterial(const HrhPbrMaterial* in, HrcTexture multiscatterLUT, HrcPbrParams* out);

@@ -31,6 +31,8 @@ SMALL = {
     "cornell": lambda: scenes.cornell_box(width=128, height=128, passes=4),
     "sphere_grid": lambda: scenes.sphere_grid(width=160, height=90, passes=2, grid=3, u_slices=24, v_slices=12, env_size=(256, 128)),
     "material_grid": lambda: scenes.material_grid(width=160, height=90, passes=2, grid=3, u_slices=24, v_slices=12),
+    # every texture slot, vertex colours, an alpha-masked non-occluder fence, textured glass, a single-sided wall
+    "textured_showcase": lambda: scenes.textured_showcase(width=160, height=96, passes=2),
 }
 
 
@@ -172,8 +174,47 @@ def test_error_paths(gpu_backend):
     with pytest.raises(capi.HrcError):
         b.unmap_pixels()
     with pytest.raises(capi.HrcError) as e:
-        b.create_material(capi.MATERIAL_PBR, 1 << 2, capi.PbrParams())
-    assert e.value.code == 5      # textures: not built yet, reported loudly
+        b.create_material(capi.MATERIAL_PBR, 1 << 12, capi.PbrParams())
+    assert e.value.code == 1      # unknown feature flag
+    with pytest.raises(capi.HrcError) as e:
+        b.create_material(capi.MATERIAL_PBR, 1 << 2, capi.PbrParams())      # base-colour texture flag with a dead handle (0)
+    assert e.value.code == 1
+    f = capi.FrameParams(); f.interactiveMode = 0
+    with pytest.raises(capi.HrcError) as e:
+        b.create_material(capi.MATERIAL_GLASS, 1 << 1, capi.GlassParams(-1, -1, -1))   # alpha mask is a PBR-only feature
+    assert e.value.code == 1
+
+
+@pytest.mark.parametrize("debug", ["showUVs", "showTangents", "showBitangents", "showNormalmap", "showBaseColor", "showFinalNormals",
+                                   "showRoughness", "showMetallic", "showEmissive", "showClearcoat", "showClearcoatRoughness",
+                                   "showClearcoatNormalmap", "showGeometricNormals", "showShader"])
+def test_debug_visualizers_match_oracle(debug, oracle_backend, gpu_backend):
+    """physicallyBased.rlsl:159-203 / glass.rlsl:179-211: primary-hit visualisations read the textured, interpolated inputs
+    of the shaders, so they pin the varyings and the texture fetches one by one (no bounce, no transcendental drift)."""
+    spec = SMALL["textured_showcase"]()
+    ro, rg = _pair(oracle_backend, gpu_backend, spec)
+    ro.reset(debug=debug); rg.reset(debug=debug)
+    ro.render_pass(); rg.render_pass()
+    po, pg = ro.pixels(), rg.pixels()
+    assert np.array_equal(po[..., 3], pg[..., 3])
+    assert po[..., :3].any(), "visualiser wrote nothing"
+    # The kernels contract a*b+c into FMAs, the oracle does not (-ffp-contract=off): interpolated varyings differ by a few ulp,
+    # texture coordinates are scaled by the texture size before filtering, so fetched values differ by up to ~1e-4.
+    close = np.isclose(pg[..., :3], po[..., :3], rtol=1e-4, atol=2e-4).all(-1)
+    assert close.mean() >= 0.999, f"{(~close).sum()} pixels differ, max diff {np.abs(pg - po).max()}"
+
+
+def test_masked_occlusion_rays(oracle_mod, oracle_backend, gpu_backend):
+    """Occlusion rays through the alpha-masked fence (policy A-5): light reaches the ground only through the holes.
+    Same rays on both sides => identical shadow pattern; compare the per-pixel direct light of one pass at depth 0."""
+    spec = SMALL["textured_showcase"]()
+    ro, rg = _pair(oracle_backend, gpu_backend, spec, )
+    ro.reset(max_depth=0); rg.reset(max_depth=0)
+    so, sg = ro.render_pass(), rg.render_pass()
+    po, pg = ro.pixels(), rg.pixels()
+    assert so.raysOcclusion == sg.raysOcclusion and so.raysOcclusion > spec.width * spec.height * 0.5
+    close = np.isclose(pg[..., :3], po[..., :3], rtol=1e-3, atol=1e-4).all(-1)
+    assert close.mean() >= 0.995, f"only {close.mean():.4f} of pixels match"
 
 
 def test_empty_scene_and_misses(gpu_backend, oracle_backend):

@@ -36,6 +36,24 @@ def test_pbr_material_packing(lib):
     assert out.multiscatterLUT == 7 and out.baseColorTexture == -1
 
 
+def test_material_feature_flags(lib):
+    """The #define selection of PhysicallyBasedMaterial.cpp:49-113 / GlassMaterial.cpp:40-74 as HRC_MAT_* flags."""
+    def pbr(**kw):
+        src = capi.HrhPbrMaterial(_f3((1, 1, 1)), _f3((0, 0, 0)), 0.0, 0.5, 0.5, 0.0, 0.0, 0, 0, **kw)
+        out = capi.PbrParams()
+        return lib.hrhPackPbrMaterial(C.byref(src), -1, C.byref(out)), out
+    assert pbr()[0] == 0
+    f, out = pbr(baseColorTexture=3, normalmap=5)
+    assert f == (1 << 2) | (1 << 5) and out.baseColorTexture == 3 and out.normalmap == 5 and out.emissiveTexture == -1
+    assert pbr(forceEnableAllTextures=1)[0] == (1 << 2) | (1 << 3) | (1 << 6) | (1 << 7)      # emissive / normal maps are never forced
+    assert pbr(emissiveTexture=0, clearCoatNormalmap=1, enableVertexColors=1)[0] == (1 << 4) | (1 << 8) | (1 << 9)
+    src = capi.HrhPbrMaterial(_f3((1, 1, 1)), _f3((0, 0, 0)), 0.0, 0.5, 0.5, 0.0, 0.0, 1, 1)
+    assert lib.hrhPackPbrMaterial(C.byref(src), -1, C.byref(capi.PbrParams())) == 1 | 2
+    g = capi.HrhGlassMaterial(_f3((1, 1, 1)), 0.1, 1.5, 0.0, baseColorTexture=2, metallicRoughnessTexture=4)
+    out = capi.GlassParams()
+    assert lib.hrhPackGlassMaterial(C.byref(g), C.byref(out)) == (1 << 2) | (1 << 3) and out.baseColorTexture == 2 and out.normalmap == -1
+
+
 def test_glass_material_packing(lib):
     src = capi.HrhGlassMaterial(_f3((0.9, 1.6, 0.6)), 0.0, 1.57, 0.5)
     out = capi.GlassParams()
