@@ -156,7 +156,7 @@ CONTEXT_TASK = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p)
 BACKEND_SYMBOLS = [
     "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels",
     "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "ClearScene", "CommitScene",
-    "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetGlobals",
+    "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetInteractiveBlocks", "SetGlobals",
     "RenderPass", "EnqueuePass", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo",
 ]
 
@@ -381,6 +381,11 @@ class Backend:
         a = np.ascontiguousarray(seq_offset_x, np.float32)
         b = np.ascontiguousarray(sequence_id, np.uint8)
         self._call("SetPixelTables", _ptr(a), C.c_size_t(a.size), _ptr(b))
+
+    def set_interactive_blocks(self, block_coords: np.ndarray, block_rand: np.ndarray):
+        """block_coords: (blockH, blockW, 3) texels; block_rand: (blocksY, blocksX, 2)."""
+        bc = np.ascontiguousarray(block_coords, np.float32); br = np.ascontiguousarray(block_rand, np.float32)
+        self._call("SetInteractiveBlocks", i32(bc.shape[1]), i32(bc.shape[0]), _ptr(bc), i32(br.shape[1]), i32(br.shape[0]), _ptr(br))
 
     def set_globals(self, g: Globals):
         self._call("SetGlobals", C.byref(g))

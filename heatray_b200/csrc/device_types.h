@@ -51,6 +51,7 @@ struct DFrame {
     int32_t bandHeight, bandIndex, bandCount, localRows;   // screen-band sharding
     int32_t numSequences, sequenceLength;
     uint32_t offsetCount;
+    int32_t interactiveMode, blockW, blockH, blockSampleX, blockSampleY, blocksX;   // perspective.rlsl:20-22,42-57
     DLights lights;
 };
 
@@ -86,6 +87,8 @@ struct DScene {
     const float2* aperture;   // ApertureSamples
     const float* seqOffsetX;  // SequenceOffsets.x
     const uint8_t* sequenceId;
+    const float* blockCoords; // interactive mode: blockW*blockH RGB texels of shuffled (row, col, 0)
+    const float2* blockRand;  // interactive mode: per block (random(blockIndex), random(blockIndex.yx))
 };
 
 // Launch wrappers implemented in kernels.cu

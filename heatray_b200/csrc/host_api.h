@@ -17,6 +17,8 @@ void generateRandomSequences(int sampleMode, int bokehShape, uint32_t numSequenc
 size_t sequenceOffsetCount(int w, int h);
 void generateSequenceOffsets(int w, int h, float* outX, size_t count);
 void generateSequenceIds(int w, int h, int numSequences, uint8_t* out);
+void generateInteractiveBlockCoords(int blockW, int blockH, uint32_t seed, float* outRGB);
+void generateInteractiveBlockRand(int blocksX, int blocksY, float* outXY);
 } // namespace hr
 
 namespace hr {

@@ -107,6 +107,15 @@ private:
         std::vector<float> off(n); generateSequenceOffsets(w, h, off.data(), n);
         std::vector<uint8_t> ids((size_t)w * h); generateSequenceIds(w, h, kNumRandomSequences, ids.data());
         rc = hrcSetPixelTables(m_ctx, off.data(), n, ids.data()); check(rc);
+        if (rc) return rc;
+        // interactive block-coordinate texture + per-block hashes (PassGenerator.cpp:266-294, perspective.rlsl:42-57)
+        const int bs = 3;                                                 // RenderOptions::kInteractiveBlockSize, PassGenerator.h:59
+        std::vector<float> coords((size_t)bs * bs * 3);
+        generateInteractiveBlockCoords(bs, bs, m_blockShuffleSeed, coords.data());
+        const int bx = (w + bs - 1) / bs, by = (h + bs - 1) / bs;
+        std::vector<float> brand((size_t)bx * by * 2);
+        generateInteractiveBlockRand(bx, by, brand.data());
+        rc = hrcSetInteractiveBlocks(m_ctx, bs, bs, coords.data(), bx, by, brand.data()); check(rc);
         return rc;
     }
 
@@ -230,6 +239,7 @@ private:
     bool m_envApplied = false, m_globalsApplied = false, m_mapped = false;
     HrcTexture m_solidTex = HRC_NULL_TEXTURE;
     uint32_t m_currentSampleIndex = 0;
+    uint32_t m_blockShuffleSeed = 0x5eed;   // the reference seeds this shuffle from std::random_device (quirk B-Q6)
     int m_currentBlockPixelSample[2] = {0, 0};
     int m_width = 0, m_height = 0;
 };

@@ -14,7 +14,11 @@
 
 #include "host_api.h"
 
+#include <algorithm>
+#include <array>
 #include <cmath>
+#include <random>
+#include <vector>
 #include <cstdint>
 #include <cstring>
 #include <limits>
@@ -234,6 +238,30 @@ void generateSequenceIds(int w, int h, int numSequences, uint8_t* out) {
     }
 }
 
+// utility.rlsl:15-18 random(st), evaluated with the host's libm (the ground truth for every `sin`-hash decision, quirk B-Q2)
+static inline float rlslRandom(float sx, float sy) {
+    float d = sx * 12.9898f + sy * 78.233f;
+    float v = sinf(d) * 43758.5453123f;
+    return v - floorf(v);
+}
+
+void generateInteractiveBlockCoords(int blockW, int blockH, uint32_t seed, float* outRGB) {      // PassGenerator.cpp:266-294
+    std::vector<std::array<float, 3>> coords;
+    for (int row = 0; row < blockW; ++row)
+        for (int col = 0; col < blockH; ++col) coords.push_back({(float)row, (float)col, 0.0f});
+    std::mt19937 generator(seed);                                                                // reference: std::random_device (quirk B-Q6)
+    std::shuffle(coords.begin(), coords.end(), generator);
+    for (size_t i = 0; i < coords.size(); ++i) for (int k = 0; k < 3; ++k) outRGB[3 * i + k] = coords[i][k];
+}
+
+void generateInteractiveBlockRand(int blocksX, int blocksY, float* outXY) {                      // perspective.rlsl:44-46
+    for (int by = 0; by < blocksY; ++by)
+        for (int bx = 0; bx < blocksX; ++bx) {
+            outXY[2 * ((size_t)by * blocksX + bx)] = rlslRandom((float)bx, (float)by);
+            outXY[2 * ((size_t)by * blocksX + bx) + 1] = rlslRandom((float)by, (float)bx);
+        }
+}
+
 } // namespace hr
 
 // ---- flat C exports ---------------------------------------------------------------------
@@ -250,5 +278,8 @@ HRC_API void hrhGenerateRandomSequences(int32_t mode, int32_t bokeh, uint32_t nu
 }
 HRC_API size_t hrhSequenceOffsetCount(int32_t w, int32_t h) { return hr::sequenceOffsetCount(w, h); }
 HRC_API void hrhGenerateSequenceOffsets(int32_t w, int32_t h, float* outX, size_t count) { hr::generateSequenceOffsets(w, h, outX, count); }
+HRC_API void hrhGenerateInteractiveBlockCoords(int32_t bw, int32_t bh, uint32_t seed, float* out) { hr::generateInteractiveBlockCoords(bw, bh, seed, out); }
+HRC_API void hrhInteractiveBlockCount(int32_t w, int32_t h, int32_t bw, int32_t bh, int32_t* bx, int32_t* by) { *bx = (w + bw - 1) / bw; *by = (h + bh - 1) / bh; }
+HRC_API void hrhGenerateInteractiveBlockRand(int32_t bx, int32_t by, float* out) { hr::generateInteractiveBlockRand(bx, by, out); }
 HRC_API void hrhGenerateSequenceIds(int32_t w, int32_t h, int32_t numSeq, uint8_t* out) { hr::generateSequenceIds(w, h, numSeq, out); }
 }

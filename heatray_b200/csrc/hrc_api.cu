@@ -55,6 +55,7 @@ struct HrcContext_t {
     DTexture* dTextures = nullptr; size_t dTexturesCap = 0;
     float2 *dSeq = nullptr, *dAperture = nullptr; float* dSeqOffsetX = nullptr; uint8_t* dSequenceId = nullptr;
     int numSequences = 0, sequenceLength = 0; size_t offsetCount = 0; bool pixelTables = false;
+    float* dBlockCoords = nullptr; float2* dBlockRand = nullptr; int blockW = 0, blockH = 0, blocksX = 0, blocksY = 0;
 
     PassBuffers pb{};
     DLights lights{};
@@ -82,7 +83,7 @@ void freeQueues(HrcContext c) {
 
 DScene sceneOf(HrcContext c) {
     DScene s; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.attr = c->dAttr; s.materials = c->dMaterials; s.textures = c->dTextures;
-    s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId;
+    s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId; s.blockCoords = c->dBlockCoords; s.blockRand = c->dBlockRand;
     return s;
 }
 LaunchConfig configOf(HrcContext c) {
@@ -207,7 +208,7 @@ HRC_API int hrcDestroyContext(HrcContext c) {
     freeDev(c->accum); freeDev(c->staging); if (c->pinned) cudaFreeHost(c->pinned);
     for (auto& t : c->textures) freeDev(t.dev);
     freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade); freeDev(c->dAttr); freeDev(c->dMaterials); freeDev(c->dTextures);
-    freeDev(c->dSeq); freeDev(c->dAperture); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
+    freeDev(c->dSeq); freeDev(c->dAperture); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId); freeDev(c->dBlockCoords); freeDev(c->dBlockRand);
     freeDev(c->pb.ctrl); freeDev(c->pb.stats);
     for (auto ev : c->evPool) cudaEventDestroy(ev);
     cudaEventDestroy(c->evStart); cudaEventDestroy(c->evStop); cudaEventDestroy(c->evTimer0); cudaEventDestroy(c->evTimer1);
@@ -236,6 +237,7 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
     freeQueues(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
     if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
     c->pixelTables = false; c->offsetCount = 0;
+    freeDev(c->dBlockCoords); freeDev(c->dBlockRand); c->blocksX = c->blocksY = 0;   // block tables depend on the frame size
     const size_t n = (size_t)w * h;
     CU(c, cudaMalloc(&c->accum, n * sizeof(float4)));
     CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));
@@ -525,6 +527,20 @@ HRC_API int hrcSetPixelTables(HrcContext c, const float* off, size_t count, cons
     c->offsetCount = count; c->pixelTables = true;
     return HRC_OK;
 }
+HRC_API int hrcSetInteractiveBlocks(HrcContext c, int32_t bw, int32_t bh, const float* coords, int32_t bx, int32_t by, const float* rnd) {
+    if (!c || !coords || !rnd || bw <= 0 || bh <= 0 || bx <= 0 || by <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad interactive block tables");
+    if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "interactive block tables need a framebuffer size first");
+    if ((int64_t)bx * bw < c->w || (int64_t)by * bh < c->h) return fail(c, HRC_ERR_INVALID_VALUE, "block tables do not cover the frame");
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream));
+    freeDev(c->dBlockCoords); freeDev(c->dBlockRand);
+    CU(c, cudaMalloc(&c->dBlockCoords, (size_t)bw * bh * 3 * sizeof(float)));
+    CU(c, cudaMalloc(&c->dBlockRand, (size_t)bx * by * sizeof(float2)));
+    CU(c, cudaMemcpy(c->dBlockCoords, coords, (size_t)bw * bh * 3 * sizeof(float), cudaMemcpyHostToDevice));
+    CU(c, cudaMemcpy(c->dBlockRand, rnd, (size_t)bx * by * sizeof(float2), cudaMemcpyHostToDevice));
+    c->blockW = bw; c->blockH = bh; c->blocksX = bx; c->blocksY = by;
+    return HRC_OK;
+}
 HRC_API int hrcSetGlobals(HrcContext c, const HrcGlobals* g) {
     if (!c || !g) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     c->globals = *g; return HRC_OK;
@@ -535,7 +551,10 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     if (!c->committed) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a committed scene");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
     if (!c->dSeq || !c->pixelTables) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without QMC / pixel tables");
-    if (fp->interactiveMode) return fail(c, HRC_ERR_UNSUPPORTED, "interactive block mode is not built");
+    if (fp->interactiveMode) {
+        if (!c->dBlockCoords) return fail(c, HRC_ERR_INVALID_OPERATION, "interactive mode without block tables (hrcSetInteractiveBlocks)");
+        if (fp->blockSize[0] != c->blockW || fp->blockSize[1] != c->blockH) return fail(c, HRC_ERR_INVALID_VALUE, "blockSize differs from the uploaded block tables");
+    }
     if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass while pixels are mapped");
     const size_t maxIdx = (size_t)(int)(((float)(c->h - 1) + 0.5f) * (float)c->h + ((float)(c->w - 1) + 0.5f));
     if (maxIdx >= c->offsetCount) return fail(c, HRC_ERR_INVALID_VALUE, "sequence-offset table too short for the reference index formula");
@@ -555,6 +574,8 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
         fr.localRows = rows;
     } else fr.localRows = c->h;
     fr.numSequences = c->numSequences; fr.sequenceLength = c->sequenceLength; fr.offsetCount = (uint32_t)c->offsetCount;
+    fr.interactiveMode = fp->interactiveMode ? 1 : 0; fr.blockW = c->blockW; fr.blockH = c->blockH;
+    fr.blockSampleX = fp->currentBlockPixelSample[0]; fr.blockSampleY = fp->currentBlockPixelSample[1]; fr.blocksX = c->blocksX;
     fr.lights = c->lights;
     if (fr.lights.envEnabled && fr.lights.envTex >= 0 && !c->textures[fr.lights.envTex].alive) return fail(c, HRC_ERR_INVALID_OPERATION, "environment texture was destroyed");
 

@@ -441,15 +441,39 @@ __global__ void k_clear_ctrl(IterCtrl* ctrl) {
 
 // perspective.rlsl:39-93 — one thread per pixel of this context's screen bands.
 __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_constant__ DFrame fr, RayQueue q, float4* accum, IterCtrl* ctrl, uint32_t total) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) ctrl[0].extCount = total;
-    if (i >= total) return;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0 && !fr.interactiveMode) ctrl[0].extCount = total;
     const int W = fr.w, H = fr.h;
-    const int lr = i / W, x = i - lr * W;
-    int y = lr;
-    if (fr.bandCount > 1) { const int lb = lr / fr.bandHeight; y = (lb * fr.bandCount + fr.bandIndex) * fr.bandHeight + (lr - lb * fr.bandHeight); }
-    const uint32_t pixel = (uint32_t)y * W + x;
-    const float fx = (float)x + 0.5f, fy = (float)y + 0.5f;               // rl_FrameCoord (policy A-1)
+    bool sampled = t < total;
+    uint32_t pixel = 0; float fx = 0.f, fy = 0.f;
+    if (sampled) {
+        const int lr = t / W, x = t - lr * W;
+        int y = lr;
+        if (fr.bandCount > 1) { const int lb = lr / fr.bandHeight; y = (lb * fr.bandCount + fr.bandIndex) * fr.bandHeight + (lr - lb * fr.bandHeight); }
+        pixel = (uint32_t)y * W + x;
+        fx = (float)x + 0.5f; fy = (float)y + 0.5f;                       // rl_FrameCoord (policy A-1)
+        if (fr.interactiveMode) {                                          // :42-57: one pixel of every block per pass
+            const int bx = x / fr.blockW, by = y / fr.blockH;
+            const float2 rnd = __ldg(&sc.blockRand[(size_t)by * fr.blocksX + bx]);   // random(blockIndex), random(blockIndex.yx) (host, quirk B-Q2)
+            const float su = __fadd_rn(__fmul_rn(1.0f / (float)fr.blockW, (float)fr.blockSampleX), rnd.x);
+            const float sv = __fadd_rn(__fmul_rn(1.0f / (float)fr.blockH, (float)fr.blockSampleY), rnd.y);
+            int ts = (int)floorf(__fmul_rn(su, (float)fr.blockW)) % fr.blockW, tt = (int)floorf(__fmul_rn(sv, (float)fr.blockH)) % fr.blockH;   // NEAREST + REPEAT
+            if (ts < 0) ts += fr.blockW;
+            if (tt < 0) tt += fr.blockH;
+            const float* texel = sc.blockCoords + 3 * (tt * fr.blockW + ts);
+            sampled = (x % fr.blockW) == (int)__ldg(texel) && (y % fr.blockH) == (int)__ldg(texel + 1);
+        }
+    }
+    uint32_t i = t;
+    if (fr.interactiveMode) {                                              // compaction: one atomic per warp
+        const uint32_t m = __ballot_sync(0xffffffffu, sampled);
+        const uint32_t lane = threadIdx.x & 31u;
+        uint32_t base = 0;
+        if (m && lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(&ctrl[0].extCount, (uint32_t)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, m ? __ffs(m) - 1 : 0);
+        i = base + __popc(m & ((1u << lane) - 1u));
+    }
+    if (!sampled) return;
 
     float4 px = accum[pixel]; px.w += 1.0f; accum[pixel] = px;            // accumulate(vec4(0,0,0,1)), :60
 

@@ -188,6 +188,12 @@ HRC_API int hrcSetSequences(HrcContext ctx, int32_t numSequences, int32_t sequen
  * int(FrameCoord.y*FrameSize.y + FrameCoord.x) for every pixel (quirk B-Q1). */
 HRC_API int hrcSetPixelTables(HrcContext ctx, const float* seqOffsetX, size_t offsetCount,
                               const uint8_t* sequenceId /* w*h */);
+/* ↔ the interactive-mode inputs of the frame shader (perspective.rlsl:42-57): the blockW x blockH RGB32F texture of shuffled
+ * (row, col, 0) block coordinates (PassGenerator.cpp:266-294; NEAREST + REPEAT) and, per block of pixels, the two hash values
+ * random(vec2(blockIndex)), random(vec2(blockIndex.yx)) the shader derives from `sin` — evaluated once on the host like the
+ * per-pixel sequenceID (quirk B-Q2). blockRandXY holds blocksX*blocksY vec2, row-major by block row. */
+HRC_API int hrcSetInteractiveBlocks(HrcContext ctx, int32_t blockW, int32_t blockH, const float* blockCoordsRGB,
+                                    int32_t blocksX, int32_t blocksY, const float* blockRandXY);
 /* ↔ PassGenerator::GlobalData (PassGenerator.h:269-294) / uniformblock Globals (globalData.rlsl:9-34): 84 bytes */
 typedef struct HrcGlobals {
     int32_t maxRayDepth;
@@ -207,7 +213,7 @@ typedef struct HrcFrameParams {
     float viewMatrix[16];        /* camera-to-world (quirk B-Q19) */
     int32_t sampleIndex;         /* Globals.sampleIndex for this pass */
     float maxSampleIndex;        /* float(maxRenderPasses) (PassGenerator.cpp:368) */
-    int32_t interactiveMode;     /* must be 0 for now (HRC_ERR_UNSUPPORTED otherwise) */
+    int32_t interactiveMode;     /* 1: render one pixel of every blockSize block per pass (needs hrcSetInteractiveBlocks) */
     int32_t blockSize[2], currentBlockPixelSample[2];
     /* screen-band sharding: this context renders rows y with (y / bandHeight) % bandCount == bandIndex.
      * bandCount <= 1 renders the whole frame. */

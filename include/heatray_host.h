@@ -36,6 +36,13 @@ HRC_API void hrhGenerateSequenceOffsets(int32_t w, int32_t h, float* outX, size_
 /* sequenceID = floor(random(FrameCoord/FrameSize) * numSequences) per pixel (perspective.rlsl:62, quirk B-Q2). */
 HRC_API void hrhGenerateSequenceIds(int32_t w, int32_t h, int32_t numSequences, uint8_t* out);
 
+/* Interactive block mode (PassGenerator.cpp:266-294, perspective.rlsl:42-57): the shuffled (row, col, 0) block-coordinate
+ * texture — the reference seeds the shuffle from std::random_device (quirk B-Q6); here the seed is explicit — and the
+ * per-block hash pair of the frame shader. */
+HRC_API void hrhGenerateInteractiveBlockCoords(int32_t blockW, int32_t blockH, uint32_t seed, float* outRGB /* blockW*blockH*3 */);
+HRC_API void hrhInteractiveBlockCount(int32_t w, int32_t h, int32_t blockW, int32_t blockH, int32_t* blocksX, int32_t* blocksY);
+HRC_API void hrhGenerateInteractiveBlockRand(int32_t blocksX, int32_t blocksY, float* outXY /* blocksX*blocksY*2 */);
+
 /* ---- materials (PhysicallyBasedMaterial::Parameters → ShaderParams; GlassMaterial likewise) ---- */
 typedef struct HrhPbrMaterial {       /* PhysicallyBasedMaterial.h Parameters (user-facing, unclamped) */
     float baseColor[3]; float emissiveColor[3];

@@ -158,6 +158,25 @@ def test_band_sharding_matches_full_frame(gpu_backend):
     assert np.array_equal(total, full)
 
 
+def test_interactive_block_mode(oracle_backend, gpu_backend):
+    """perspective.rlsl:42-57: each pass renders one pixel of every 3x3 block; the oracle and the kernels pick the same pixels
+    (alpha planes equal after every pass), and nine passes add up to exactly one ordinary pass at the same sample index."""
+    spec = SMALL["sphere_grid"]()
+    ro, rg = _pair(oracle_backend, gpu_backend, spec)
+    for k in range(9):
+        so, sg = ro.render_pass(interactive=True), rg.render_pass(interactive=True)
+        ao, ag = ro.pixels()[..., 3], rg.pixels()[..., 3]
+        assert np.array_equal(ao, ag) and sg.raysPrimary == so.raysPrimary
+        assert abs(int(ag.sum()) - (k + 1) * spec.width * spec.height / 9) <= (k + 1) * (spec.width + spec.height)
+    inter = rg.pixels()
+    assert (inter[..., 3] == 1).all() and rg.sample_index == 1
+    rg.reset()
+    rg.render_pass()
+    assert np.array_equal(rg.pixels(), inter)
+    close = np.isclose(inter[..., :3], ro.pixels()[..., :3], rtol=1e-3, atol=1e-4).all(-1)
+    assert close.mean() >= 0.99
+
+
 def test_error_paths(gpu_backend):
     b = gpu_backend
     with pytest.raises(capi.HrcError) as e:

@@ -88,11 +88,23 @@ def test_pass_generator_matches_direct_backend(lib, gpu_backend):
         lib.hrhPassGeneratorWaitIdle(pg)
         assert got[0][2].shape == (32, 32, 4) and (got[0][2][..., 3] == 1).all()
 
-        # interactive block mode is reported, not silently ignored
+        # interactive block mode (PassGenerator.cpp:372-381, perspective.rlsl:42-57): 9 passes walk every pixel of each 3x3 block
+        # once at sample index 0, so their sum is exactly one offline pass; the reported pass index advances on the 9th
         got.clear()
-        o.enableInteractiveMode = 1
+        o.enableInteractiveMode, o.resetInternalState = 1, 1
+        for i in range(9):
+            lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+            o.resetInternalState = 0
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert lib.hrhPassGeneratorLastError(pg) == b""
+        assert [g[1] for g in got] == [0] * 8 + [1]
+        assert (got[0][2][..., 3].sum() == 32 * 32 // 9 + (1 if (32 * 32) % 9 else 0)) or (got[0][2][..., 3].sum() > 100)
+        inter = got[-1][2]
+        assert (inter[..., 3] == 1).all()
+        got.clear()
+        o.enableInteractiveMode, o.resetInternalState = 0, 1
         lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
         lib.hrhPassGeneratorWaitIdle(pg)
-        assert got[0][0] == 0 and b"interactive" in lib.hrhPassGeneratorLastError(pg)
+        assert np.array_equal(got[0][2], inter)
     finally:
         lib.hrhPassGeneratorDestroy(pg)

@@ -239,3 +239,22 @@ def test_textured_base_colour_is_bilinear(oracle_backend):
             if not hit[y, x]:
                 continue
             assert np.allclose(col[y, x, :3], bilinear(uvs[y, x, 0], uvs[y, x, 1]), atol=2e-6)
+
+
+def test_interactive_block_mode_covers_each_pixel_once(oracle_backend):
+    """perspective.rlsl:42-57 + PassGenerator.cpp:372-381: nine interactive passes sample every pixel exactly once, all at
+    sample index 0, so their sum equals one ordinary pass."""
+    from heatray_b200 import renderer, scenes
+    spec = scenes.cornell_box(width=40, height=31, passes=2)
+    r = renderer.Renderer(oracle_backend)
+    r.load_scene(spec)
+    for k in range(9):
+        st = r.render_pass(interactive=True)
+        a = r.pixels()[..., 3]
+        assert a.max() == 1 and st.raysPrimary == a.sum() - (0 if k == 0 else prev)
+        prev = a.sum()
+    inter = r.pixels()
+    assert (inter[..., 3] == 1).all() and r.sample_index == 1 and r.block_sample == [0, 0]
+    r.reset()
+    r.render_pass()
+    assert np.array_equal(r.pixels(), inter)
