@@ -31,6 +31,15 @@ from heatray_b200 import capi, renderer, scenes  # noqa: E402
 METRIC, UNIT = "path_tracing_throughput", "Mrays/s"
 
 
+def load_traffic(config, kernel):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json), else None."""
+    p = ROOT / "profiles" / "traffic.json"
+    try:
+        return json.loads(p.read_text())[config][kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def load_peaks():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -94,6 +103,8 @@ def build_spec(name, small=False):
         return scenes.terrain() if not small else scenes.terrain(width=960, height=540, n=256, blobs=20, env_size=(512, 256))
     if name == "cornell":
         return scenes.cornell_box()
+    if name == "convergence":
+        return scenes.sphere_grid(width=3840, height=2160, passes=1024) if not small else scenes.sphere_grid(width=960, height=540, passes=64, grid=4, u_slices=32, v_slices=16, env_size=(512, 256))
     raise SystemExit(f"unknown config {name}")
 
 
@@ -102,14 +113,18 @@ WORKLOAD_NAMES = {
     "material_grid": "configs[2]: 11x11 glass + clearcoat material grid, f/2.8 hexagonal bokeh, spot + directional",
     "terrain": "configs[3]: displaced terrain + flattened foliage",
     "cornell": "configs[0]: Cornell box, 1 point light",
+    "convergence": "configs[4]: convergence run 3840x2160, 1024 spp sharded by sample index, NCCL reduce of the fp32 accumulation buffer",
 }
 
 
-def config_dict(spec, name, n_gpus, extra=None):
+def config_dict(spec, name, n_gpus, extra=None, shard="sample"):
+    par = "single GPU" if n_gpus <= 1 else (f"sample-index sharding x{n_gpus}, one NCCL fp32 sum-reduce of the accumulation buffer" if shard == "sample"
+                                            else f"screen-band sharding x{n_gpus} (interleaved 16-row bands), one NCCL fp32 sum-reduce of the disjoint bands")
     d = {"workload": WORKLOAD_NAMES[name], "scene": spec.name, "triangles": spec.triangle_count, "resolution": f"{spec.width}x{spec.height}",
          "max_ray_depth": spec.max_depth, "spp_per_step": 1, "qmc": "owen-scrambled sobol (16 sequences)",
-         "parallelism": f"sample-index sharding x{n_gpus}" if n_gpus > 1 else "single GPU",
-         "l2_policy": "inputs larger than L2: the ray/hit queues streamed per pass (>400 MB at 1080p) exceed the 126 MB L2; the BVH itself is L2-resident by design"}
+         "parallelism": par,
+         "l2_policy": "inputs larger than L2: every pass streams its ray / hit queues (%d MB at this resolution) through the 126 MB L2; the BVH + triangles are %s" % (
+             spec.width * spec.height * 204 // 1000000, "L2-resident by design (< 126 MB)" if spec.triangle_count < 1000000 else "larger than L2 as well")}
     if extra:
         d.update(extra)
     return d
@@ -187,6 +202,8 @@ def main():
     ap.add_argument("--config", default="sphere_grid", choices=list(WORKLOAD_NAMES))
     ap.add_argument("--small", action="store_true", help="reduced-size scene (debug only; not a valid bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard", default=None, choices=["sample", "bands"],
+                    help="multi-GPU partition (SURVEY 8e): sample-index (default; weak scaling) or interleaved screen bands (default for terrain; strong scaling)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
 
@@ -214,21 +231,49 @@ def main():
 
     lib = capi.load_library()
     spec = build_spec(args.config, args.small)
+    shard = args.shard or ("bands" if args.config == "terrain" else "sample")
     b = capi.Backend(lib, "hrc", device=local_rank, collect_stats=False)
     r = renderer.Renderer(b)
     r.load_scene(spec)
     info = b.scene_info()
     K, W = args.steps, args.warmup
-    # sample-index sharding: rank r renders sample indices r, r + world, ... (wrapped into the QMC table length)
-    passes_total = max(spec.passes, K * world)
+    if shard == "bands" and world > 1:
+        # screen-band sharding: every rank renders every sample index for its interleaved 16-row bands (strong scaling)
+        passes_total = max(spec.passes, K)
+        r.set_band(16, rank, world)
+    else:
+        # sample-index sharding: rank r renders sample indices r, r + world, ... (wrapped into the QMC table length)
+        passes_total = max(spec.passes, K * world)
     r.reset(passes=passes_total)
+    if shard == "bands" and world > 1:
+        r.set_band(16, rank, world)
 
     def sidx(step):
-        return (rank + step * world) % passes_total
+        return step % passes_total if (shard == "bands" and world > 1) else (rank + step * world) % passes_total
+
+    acc = None
+    if world > 1:   # the exchange step: one fp32 sum-reduce of the accumulation buffer, in place on the device pointer
+        ptr = b.device_pixels()
+
+        class _Arr:
+            __cuda_array_interface__ = {"shape": (spec.height, spec.width, 4), "typestr": "<f4", "data": (ptr, False), "version": 2}
+        acc = torch.as_tensor(_Arr(), device=f"cuda:{local_rank}")
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def reduce_timed():
+        """NCCL reduce timed with CUDA events on torch's current stream (the pass stream has been synchronised before)."""
+        if world <= 1:
+            return 0.0
+        ev0.record()
+        dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+        ev1.record()
+        ev1.synchronize()
+        return ev0.elapsed_time(ev1)
 
     # ---- warm-up -----------------------------------------------------------------------------
     for i in range(W):
         r.render_pass(want_stats=False, sample_index=sidx(i))
+    reduce_timed()
     b.clear()
 
     # ---- traversal counters for the roofline numerator (same sample indices as the timed region; not timed) ----
@@ -241,35 +286,33 @@ def main():
     b.clear()
     rays_total = counters.rays
 
-    # ---- timed region: K passes, inputs resident in HBM, CUDA events on the launching stream --------------
-    b.set_option(capi.OPT_KERNEL_TIMING, 1)
+    # ---- timed region: exactly K passes, inputs resident in HBM, enqueued back to back on the context's stream and timed
+    #      with CUDA events on that stream (no host synchronisation inside), then the reduce ------------------------------
     sampler = ClockSampler(local_rank)
     sampler.start()
     time.sleep(0.3)
     barrier()
-    b.timer_start()
     t0 = time.perf_counter()
-    ms_closest = ms_any = ms_shade = ms_raygen = 0.0
-    launches = 0
+    b.timer_start()
     for i in range(K):
-        st = r.render_pass(want_stats=True, sample_index=sidx(i))
-        ms_closest += st.msClosest; ms_any += st.msAny; ms_shade += st.msShade; ms_raygen += st.msRaygen
-        launches += int(st.closestLaunches + st.anyLaunches + st.shadeLaunches) + 3     # + clear, raygen, finish
-    reduce_ms = 0.0
-    if world > 1:   # the exchange step of sample-index sharding: one fp32 sum-reduce of the accumulation buffer
-        ptr = b.device_pixels()
-
-        class _Arr:
-            __cuda_array_interface__ = {"shape": (spec.height, spec.width, 4), "typestr": "<f4", "data": (ptr, False), "version": 2}
-        acc = torch.as_tensor(_Arr(), device=f"cuda:{local_rank}")
-        tr0 = time.perf_counter()
-        dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
-        torch.cuda.synchronize()
-        reduce_ms = (time.perf_counter() - tr0) * 1e3
-    dev_ms = b.timer_stop() + reduce_ms
+        r.enqueue_pass(sample_index=sidx(i))
+    pass_ms = b.timer_stop()
+    reduce_ms = reduce_timed()
+    dev_ms = pass_ms + reduce_ms
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.finish()
+
+    # ---- instrumented replay of the same K passes: CUDA events between the kernels give each kernel's launch durations
+    #      (their sum is within ~2 % of the clean region above; the shares and the roofline use these) ---------------------
+    b.clear()
+    b.set_option(capi.OPT_KERNEL_TIMING, 1)
+    ms_closest = ms_any = ms_shade = ms_raygen = inst_ms = 0.0
+    launches = 0
+    for i in range(K):
+        st = r.render_pass(want_stats=True, sample_index=sidx(i))
+        ms_closest += st.msClosest; ms_any += st.msAny; ms_shade += st.msShade; ms_raygen += st.msRaygen; inst_ms += st.gpuMs
+        launches += int(st.closestLaunches + st.anyLaunches + st.shadeLaunches) + 3     # + clear, raygen, finish
     b.set_option(capi.OPT_KERNEL_TIMING, 0)
 
     # ---- end-to-end region: the reference-facing call sequence with HOST buffers (pass + PixelPackBuffer readback) ----
@@ -282,6 +325,8 @@ def main():
         px = b.map_pixels()                       # D2H of the RGBA32F accumulation buffer into pinned memory, every pass
         checksum += float(px[0, 0, 3])
         b.unmap_pixels()
+    if world > 1:
+        reduce_timed()
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
 
@@ -308,7 +353,8 @@ def main():
         achieved = dom_bytes / (dom_ms / 1e3) / 1e9
         rays_c = counters.raysPrimary + counters.raysExtension
         roof = {"bound": "hbm", "kernel": "k_trace<closest>" if dominant_closest else "k_trace<any>",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": load_traffic(args.config, "k_trace<closest>" if dominant_closest else "k_trace<any>"),
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": dom_bytes / n_launch, "avg_launch_ms": dom_ms / n_launch, "launches": n_launch,
                 "per_ray": {"closest": {"rays": int(rays_c), "nodes": counters.nodesVisited / max(1, rays_c), "tris": counters.trianglesTested / max(1, rays_c),
@@ -318,12 +364,14 @@ def main():
                                     "tris": counters.trianglesTestedAny / max(1, counters.raysOcclusion),
                                     "bytes": bytes_any / max(1, counters.raysOcclusion), "ms": ms_any, "GBps": bytes_any / (max(ms_any, 1e-9) / 1e3) / 1e9,
                                     "Mrays_per_s": counters.raysOcclusion / (max(ms_any, 1e-9) / 1e3) / 1e6}},
-                "kernel_share_of_step": {"closest": ms_closest / dev_ms, "any": ms_any / dev_ms, "shade": ms_shade / dev_ms, "raygen": ms_raygen / dev_ms},
+                "kernel_share_of_step": {"closest": ms_closest / inst_ms, "any": ms_any / inst_ms, "shade": ms_shade / inst_ms, "raygen": ms_raygen / inst_ms},
+                "instrumented_ms_per_step": inst_ms / K,
+                "timing": "value: K passes enqueued back to back, CUDA events on the launching stream; kernel durations: CUDA events between the kernels in a replay of the same K passes",
                 "note": "scene BVH fits L2 for this config, so DRAM traffic is dominated by queue streams; see DESIGN.md"}
         frame_bytes = spec.width * spec.height * 16
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": config_dict(spec, args.config, world, {"bvh_nodes": int(info.nodeCount), "bvh_build_s": float(info.buildSeconds),
+                "higher_is_better": True, "scaling": "strong" if (shard == "bands" and world > 1) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": config_dict(spec, args.config, world, shard=shard, extra={"bvh_nodes": int(info.nodeCount), "bvh_build_s": float(info.buildSeconds),
                                                                  "scene_bytes": int(info.nodeBytes + info.triangleBytes + info.shadingBytes)}),
                 "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K,
                 "clocks": clocks, "roofline": roof,

@@ -31,7 +31,9 @@ thread_local std::string g_err;
 struct HrcContext_t {
     int device = 0;
     bool counters = false, kernelTiming = false;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: occlusion traversal of iteration i overlaps closest-hit traversal of i+1
+    std::vector<cudaEvent_t> evSync;                     // 2 per iteration, timing disabled
+    bool overlap = true;
     cudaEvent_t evStart = nullptr, evStop = nullptr, evTimer0 = nullptr, evTimer1 = nullptr;
     std::vector<cudaEvent_t> evPool;
     std::string err;
@@ -185,6 +187,9 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     if ((e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaGetDeviceProperties"); delete c; return r; }
     c->smCount = prop.multiProcessorCount;
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { int r = failCuda(nullptr, e, "cudaStreamCreate"); delete c; return r; }
+    cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 * kMaxIterations; ++i) { cudaEvent_t ev; cudaEventCreateWithFlags(&ev, cudaEventDisableTiming); c->evSync.push_back(ev); }
+    if (const char* e2 = std::getenv("HRC_TUNE_OVERLAP")) c->overlap = std::atoi(e2) != 0;
     cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop); cudaEventCreate(&c->evTimer0); cudaEventCreate(&c->evTimer1);
     cudaMalloc(&c->pb.ctrl, sizeof(IterCtrl) * kMaxIterations);
     cudaMalloc(&c->pb.stats, sizeof(DeviceStats));
@@ -211,6 +216,8 @@ HRC_API int hrcDestroyContext(HrcContext c) {
     freeDev(c->dSeq); freeDev(c->dAperture); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId); freeDev(c->dBlockCoords); freeDev(c->dBlockRand);
     freeDev(c->pb.ctrl); freeDev(c->pb.stats);
     for (auto ev : c->evPool) cudaEventDestroy(ev);
+    for (auto ev : c->evSync) cudaEventDestroy(ev);
+    if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     cudaEventDestroy(c->evStart); cudaEventDestroy(c->evStop); cudaEventDestroy(c->evTimer0); cudaEventDestroy(c->evTimer1);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -594,10 +601,27 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     mark();
     launchRaygen(sc, fr, c->pb, s);
     mark();
-    for (int it = 0; it < iterations; ++it) {
-        launchTraceClosest(sc, c->pb, it, lc, s); mark();
-        launchShade(sc, fr, c->pb, it, lc, s);    mark();
-        launchTraceAny(sc, fr, c->pb, it, lc, s); mark();
+    if (timeKernels || !c->overlap || iterations < 2) {
+        for (int it = 0; it < iterations; ++it) {
+            launchTraceClosest(sc, c->pb, it, lc, s); mark();
+            launchShade(sc, fr, c->pb, it, lc, s);    mark();
+            launchTraceAny(sc, fr, c->pb, it, lc, s); mark();
+        }
+    } else {
+        // Occlusion rays of iteration i and extension rays of iteration i+1 are independent (both were emitted by shade(i)):
+        // k_trace<any>(i) runs on the second stream next to k_trace<closest>(i+1) and fills the SMs its tail leaves idle.
+        // shade(i+1) waits for both: it reuses the shadow queue and accumulates into the same pixels as the light shaders.
+        cudaStream_t s2 = c->stream2;
+        for (int it = 0; it < iterations; ++it) {
+            launchTraceClosest(sc, c->pb, it, lc, s);
+            if (it > 0) cudaStreamWaitEvent(s, c->evSync[2 * (it - 1) + 1], 0);
+            launchShade(sc, fr, c->pb, it, lc, s);
+            cudaEventRecord(c->evSync[2 * it], s);
+            cudaStreamWaitEvent(s2, c->evSync[2 * it], 0);
+            launchTraceAny(sc, fr, c->pb, it, lc, s2);
+            cudaEventRecord(c->evSync[2 * it + 1], s2);
+        }
+        cudaStreamWaitEvent(s, c->evSync[2 * (iterations - 1) + 1], 0);
     }
     launchFinishPass(c->pb, iterations, s);
     cudaError_t e = cudaGetLastError();
