@@ -11,6 +11,8 @@
 // No tensor cores: this is pointer chasing + fp32 ALU, bound by the memory system.
 #include "device_types.h"
 
+#include <cuda_fp16.h>
+
 #include <cfloat>
 #include <cstdio>
 
@@ -343,14 +345,15 @@ struct Traversal {
         if (STATS) tc.nodes++;
 
         const uint32_t eimask = __float_as_uint(n0.w);
-        // A = cell * 2^15 / d  (cell = 2^(e-127); e == 0 marks a flat axis with cell size 0)
+        // Child plane distance (origin + q*cell - o) / d as ONE FMA on the widened magic number (1024 + q):
+        // A = cell / d (cell = 2^(e-127); e == 0 marks a flat axis with cell size 0), B = (origin - o)/d - 1024 A.
         const uint32_t ex = byteOf(eimask, 0), ey = byteOf(eimask, 1), ez = byteOf(eimask, 2);
-        const float Ax = __uint_as_float(ex ? (ex + 15u) << 23 : 0u) * idir.x;
-        const float Ay = __uint_as_float(ey ? (ey + 15u) << 23 : 0u) * idir.y;
-        const float Az = __uint_as_float(ez ? (ez + 15u) << 23 : 0u) * idir.z;
-        const float Bx = (n0.x - o.x) * idir.x - Ax, By = (n0.y - o.y) * idir.y - Ay, Bz = (n0.z - o.z) * idir.z - Az;
-        // conservative bias: entry planes a little earlier, exit planes a little later (2^-7 cell >> the 2^-9 cell rounding of B)
-        const float kBias = 1.0f / 4194304.0f;   // 2^-22 * 2^15 cells
+        const float Ax = __uint_as_float(ex << 23) * idir.x;
+        const float Ay = __uint_as_float(ey << 23) * idir.y;
+        const float Az = __uint_as_float(ez << 23) * idir.z;
+        const float Bx = fmaf(-1024.0f, Ax, (n0.x - o.x) * idir.x), By = fmaf(-1024.0f, Ay, (n0.y - o.y) * idir.y), Bz = fmaf(-1024.0f, Az, (n0.z - o.z) * idir.z);
+        // conservative bias: entry planes a little earlier, exit planes a little later (2^-9 cell >> the 2^-14 cell rounding of B)
+        const float kBias = 1.0f / 512.0f;
         const float ex_ = fabsf(Ax) * kBias, ey_ = fabsf(Ay) * kBias, ez_ = fabsf(Az) * kBias;
         const float Bnx = Bx - ex_, Bny = By - ey_, Bnz = Bz - ez_;
         const float Bfx = Bx + ex_, Bfy = By + ey_, Bfz = Bz + ez_;
@@ -372,18 +375,28 @@ struct Traversal {
             const uint32_t nx = negX ? qhix : qlox, fx = negX ? qlox : qhix;
             const uint32_t ny = negY ? qhiy : qloy, fy = negY ? qloy : qhiy;
             const uint32_t nz = negZ ? qhiz : qloz, fz = negZ ? qloz : qhiz;
-#define HR_CHILD(J)                                                                                                    \
+#define HR_PLANES(Q, SEL, A, B, LO, HI)                                                                                \
+            { const uint32_t h_ = __byte_perm(Q, 0x64646464u, SEL);   /* two fp16 magic numbers 1024 + q in one PRMT */  \
+              const __half2 hv_ = *reinterpret_cast<const __half2*>(&h_);                                               \
+              LO = fmaf(__low2float(hv_), A, B); HI = fmaf(__high2float(hv_), A, B); }   /* widening on the FMA pipe */
+#define HR_HIT(J, TNX, TNY, TNZ, TFX, TFY, TFZ)                                                                        \
             {                                                                                                          \
-                const float tnx = fmaf(byteToUnitFloat<J>(nx), Ax, Bnx), tfx = fmaf(byteToUnitFloat<J>(fx), Ax, Bfx);   \
-                const float tny = fmaf(byteToUnitFloat<J>(ny), Ay, Bny), tfy = fmaf(byteToUnitFloat<J>(fy), Ay, Bfy);   \
-                const float tnz = fmaf(byteToUnitFloat<J>(nz), Az, Bnz), tfz = fmaf(byteToUnitFloat<J>(fz), Az, Bfz);   \
-                const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                              \
-                const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar));                                              \
+                const float tn = fmaxf(fmaxf(TNX, TNY), fmaxf(TNZ, tmin));                                              \
+                const float tf = fminf(fminf(TFX, TFY), fminf(TFZ, tfar));                                              \
                 if (tn <= tf * 1.000001f) /* conservative: rounding must never cull an exact tie */                     \
                     hitMask |= byteOf(childBits4, J) << byteOf(bitIndex4, J);                                           \
             }
-            HR_CHILD(0) HR_CHILD(1) HR_CHILD(2) HR_CHILD(3)
-#undef HR_CHILD
+#define HR_PAIR(J0, J1, SEL)                                                                                           \
+            {                                                                                                          \
+                float anx, bnx, any_, bny, anz, bnz, afx, bfx, afy, bfy, afz, bfz;                                      \
+                HR_PLANES(nx, SEL, Ax, Bnx, anx, bnx) HR_PLANES(ny, SEL, Ay, Bny, any_, bny) HR_PLANES(nz, SEL, Az, Bnz, anz, bnz) \
+                HR_PLANES(fx, SEL, Ax, Bfx, afx, bfx) HR_PLANES(fy, SEL, Ay, Bfy, afy, bfy) HR_PLANES(fz, SEL, Az, Bfz, afz, bfz) \
+                HR_HIT(J0, anx, any_, anz, afx, afy, afz) HR_HIT(J1, bnx, bny, bnz, bfx, bfy, bfz)                       \
+            }
+            HR_PAIR(0, 1, 0x4140) HR_PAIR(2, 3, 0x4342)
+#undef HR_PAIR
+#undef HR_HIT
+#undef HR_PLANES
         }
         group.x = __float_as_uint(n1.x);
         group.y = (hitMask & 0xff000000u) | (eimask >> 24);
