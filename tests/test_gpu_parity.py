@@ -106,6 +106,26 @@ def test_image_parity_equal_spp(name, oracle_backend, gpu_backend):
     assert sg.nodesVisited > 0 and sg.trianglesTested > 0
 
 
+def test_config1_cornell_converged_image(oracle_backend, gpu_backend):
+    """BASELINE.json configs[0] at full size: Cornell box 512x512, 64 progressive 1-spp passes, 4 bounces, same QMC tables.
+    Stated tolerance for the converged (resolved) images: RMSE <= 2e-3 of the clamp value (pi), PSNR >= 54 dB; sample counts exact."""
+    spec = scenes.cornell_box()
+    assert (spec.width, spec.height, spec.passes, spec.max_depth) == (512, 512, 64, 4)
+    ro, rg = _pair(oracle_backend, gpu_backend, spec)
+    rays_o = rays_g = 0
+    for _ in range(spec.passes):
+        rays_o += ro.render_pass().rays
+        rays_g += rg.render_pass().rays
+    po, pg = ro.pixels(), rg.pixels()
+    assert (po[..., 3] == 64).all() and np.array_equal(po[..., 3], pg[..., 3])
+    io, ig = renderer.resolve(po), renderer.resolve(pg)
+    rmse = float(np.sqrt(np.mean((io - ig) ** 2)))
+    assert rmse <= 2e-3 * spec.max_channel_value, rmse
+    assert _psnr(io, ig, spec.max_channel_value) >= 54.0
+    assert abs(rays_g - rays_o) <= 1e-3 * rays_o
+    assert abs(float(ig.mean()) - float(io.mean())) <= 1e-4 * float(io.mean()) + 1e-6      # no energy drift
+
+
 def test_progressive_contract_and_reset(gpu_backend):
     """Sums in RGB, sample count in A, persistence across passes, clear on reset (PassGenerator.cpp:335-339,437-439)."""
     spec = SMALL["cornell"]()
