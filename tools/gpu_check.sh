@@ -1,0 +1,16 @@
+#!/bin/bash
+# Round-end style GPU check: parity tests, bench lines for the configs, ncu launch list + one full capture of k_trace.
+# usage: tools/gpu_check.sh <tag>     (outputs under gpurun_out/<tag>_*)
+T=${1:-chk}
+O=gpurun_out
+mkdir -p $O
+python -m pytest tests -m gpu -x -q 2>&1 | tail -5 > $O/${T}_pytest.txt; cat $O/${T}_pytest.txt
+python bench.py > $O/${T}_bench_sphere_grid.json 2> $O/${T}_bench_sphere_grid.err || { tail -20 $O/${T}_bench_sphere_grid.err; exit 1; }
+python bench.py --config material_grid --no-cpu-baseline > $O/${T}_bench_material_grid.json 2>/dev/null
+python bench.py --config terrain --steps 8 --no-cpu-baseline > $O/${T}_bench_terrain.json 2>/dev/null
+python bench.py --config cornell --steps 64 --no-cpu-baseline > $O/${T}_bench_cornell.json 2>/dev/null
+python bench.py --impl reference --steps 16 --warmup 1 > $O/${T}_bench_reference.json 2>/dev/null
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/${T}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_list.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_trace -s 60 -c 6 -o $O/${T}_trace_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_shade -s 40 -c 6 -o $O/${T}_shade_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_full2.log 2>&1
+ls -la $O | tail -20
