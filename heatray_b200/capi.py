@@ -89,6 +89,20 @@ class Globals(C.Structure):
                 ("enableAccumulatorVisualizer", i32), ("showNANs", i32), ("showInf", i32)]
 
 
+class PostProcess(C.Structure):        # HrcPostProcess ↔ HeatrayRenderer::PostProcessingParams (HeatrayRenderer.h:104-117)
+    _fields_ = [("tonemappingEnabled", i32), ("cameraExposure", f32), ("brightness", f32), ("contrast", f32), ("hue", f32), ("saturation", f32),
+                ("vibrance", f32), ("red", f32), ("green", f32), ("blue", f32), ("vignetteIntensity", f32), ("vignetteFalloff", f32)]
+
+    def __init__(self, *a, **kw):
+        defaults = dict(tonemappingEnabled=0, cameraExposure=1.0, brightness=0.0, contrast=1.0, hue=1.0, saturation=1.0, vibrance=0.0,
+                        red=1.0, green=1.0, blue=1.0, vignetteIntensity=0.0, vignetteFalloff=1.0)
+        defaults.update(kw)
+        super().__init__(*a, **defaults)
+
+
+RESOLVE_DISPLAY_RGBA32F, RESOLVE_DISPLAY_RGB8, RESOLVE_HDR_RGB32F = 0, 1, 2
+
+
 class FrameParams(C.Structure):
     _fields_ = [("fovTan", f32), ("aspectRatio", f32), ("focusDistance", f32), ("apertureRadius", f32), ("viewMatrix", f32 * 16),
                 ("sampleIndex", i32), ("maxSampleIndex", f32), ("interactiveMode", i32), ("blockSize", i32 * 2),
@@ -154,7 +168,7 @@ CONTEXT_TASK = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p)
 
 # names of every exported symbol of the backend C-ABI (checked by tests/test_abi.py against the header)
 BACKEND_SYMBOLS = [
-    "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels",
+    "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels", "Resolve",
     "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "ClearScene", "CommitScene",
     "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetInteractiveBlocks", "SetGlobals",
     "RenderPass", "EnqueuePass", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo",
@@ -289,6 +303,14 @@ class Backend:
     def add_pixels(self, rgba: np.ndarray):
         a = np.ascontiguousarray(rgba, np.float32)
         self._call("AddPixels", _ptr(a))
+
+    def resolve(self, post: "PostProcess | None" = None, fmt: int = RESOLVE_DISPLAY_RGB8) -> np.ndarray:
+        """hrcResolve: the display colour pipeline (displayGL.frag) or the HDR screenshot divide, rows bottom-up."""
+        shape, dt = {RESOLVE_DISPLAY_RGBA32F: ((self.height, self.width, 4), np.float32), RESOLVE_DISPLAY_RGB8: ((self.height, self.width, 3), np.uint8),
+                     RESOLVE_HDR_RGB32F: ((self.height, self.width, 3), np.float32)}.get(fmt, ((self.height, self.width, 4), np.float32))
+        out = np.empty(shape, dt)
+        self._call("Resolve", C.byref(post) if post is not None else None, i32(fmt), _ptr(out))
+        return out
 
     def device_pixels(self) -> int:
         p = C.c_void_p()

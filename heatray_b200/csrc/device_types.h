@@ -113,5 +113,6 @@ void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, i
 void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s);
 void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig& lc, cudaStream_t s);
 void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s);
+void launchResolve(const float4* accum, const HrcPostProcess& post, int format, int w, int h, void* out, cudaStream_t s);   // resolve.cu
 
 } // namespace hr

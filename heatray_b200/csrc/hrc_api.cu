@@ -44,6 +44,7 @@ struct HrcContext_t {
     float4* accum = nullptr;
     float* pinned = nullptr; size_t pinnedBytes = 0; bool mapped = false;
     float4* staging = nullptr;        // device staging for hrcAddPixels
+    void* resolveDev = nullptr; size_t resolveBytes = 0;   // device output of hrcResolve
 
     std::vector<TextureRec> textures;
     std::vector<MaterialRec> materials;
@@ -210,7 +211,7 @@ HRC_API int hrcDestroyContext(HrcContext c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     freeQueues(c);
-    freeDev(c->accum); freeDev(c->staging); if (c->pinned) cudaFreeHost(c->pinned);
+    freeDev(c->accum); freeDev(c->staging); if (c->resolveDev) { cudaFree(c->resolveDev); c->resolveDev = nullptr; } if (c->pinned) cudaFreeHost(c->pinned);
     for (auto& t : c->textures) freeDev(t.dev);
     freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade); freeDev(c->dAttr); freeDev(c->dMaterials); freeDev(c->dTextures);
     freeDev(c->dSeq); freeDev(c->dAperture); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId); freeDev(c->dBlockCoords); freeDev(c->dBlockRand);
@@ -300,6 +301,29 @@ HRC_API int hrcGetDevicePixels(HrcContext c, void** devPtr) {
     cudaSetDevice(c->device);
     CU(c, cudaStreamSynchronize(c->stream));
     *devPtr = c->accum; return HRC_OK;
+}
+
+HRC_API int hrcResolve(HrcContext c, const HrcPostProcess* post, int32_t format, void* hostOut) {
+    if (!c || !hostOut) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
+    if (format < HRC_RESOLVE_DISPLAY_RGBA32F || format > HRC_RESOLVE_HDR_RGB32F) return fail(c, HRC_ERR_INVALID_VALUE, "unknown resolve format");
+    if (!post && format != HRC_RESOLVE_HDR_RGB32F) return fail(c, HRC_ERR_INVALID_VALUE, "post-processing parameters are required for the display formats");
+    cudaSetDevice(c->device);
+    const size_t n = (size_t)c->w * c->h;
+    const size_t bytes = n * (format == HRC_RESOLVE_DISPLAY_RGBA32F ? 16 : format == HRC_RESOLVE_DISPLAY_RGB8 ? 3 : 12);
+    const size_t padded = (bytes + 15) & ~(size_t)15;
+    if (c->resolveBytes < padded) {
+        CU(c, cudaStreamSynchronize(c->stream));
+        if (c->resolveDev) { cudaFree(c->resolveDev); c->resolveDev = nullptr; } c->resolveBytes = 0;
+        CU(c, cudaMalloc(&c->resolveDev, padded)); c->resolveBytes = padded;
+    }
+    HrcPostProcess pp{}; if (post) pp = *post;
+    launchResolve(c->accum, pp, format, c->w, c->h, c->resolveDev, c->stream);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return failCuda(c, e, "resolve launch");
+    CU(c, cudaMemcpyAsync(hostOut, c->resolveDev, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return HRC_OK;
 }
 
 HRC_API int hrcCreateTexture2D(HrcContext c, const HrcTextureDesc* d, const void* pixels, HrcTexture* out) {

@@ -88,6 +88,27 @@ HRC_API int hrcAddPixels(HrcContext ctx, const float* rgba);
 /* Device pointer of the accumulation buffer (w*h float4), for NCCL reduce without staging. */
 HRC_API int hrcGetDevicePixels(HrcContext ctx, void** devPtr);
 
+/* ---- resolve + colour pipeline (↔ displayGL.frag:28-151 drawn by HeatrayRenderer.h:228-262, and the
+ * screenshot paths of HeatrayRenderer::saveScreenshot, HeatrayRenderer.cpp:1619-1662). The reference runs this as a
+ * GL fragment shader over the window; here it is one CUDA kernel over the accumulation buffer (no graphics API). */
+typedef struct HrcPostProcess {       /* ↔ HeatrayRenderer::PostProcessingParams (HeatrayRenderer.h:104-117) */
+    int32_t tonemappingEnabled;       /* ACES fit, displayGL.frag:82-90 */
+    float   cameraExposure;           /* already 2^exposure (HeatrayRenderer.h:238) */
+    float   brightness, contrast;     /* :95-97 */
+    float   hue, saturation, vibrance;/* :100-129 */
+    float   red, green, blue;         /* :132-136 */
+    float   vignetteIntensity, vignetteFalloff; /* :139-143 */
+} HrcPostProcess;
+enum {
+    HRC_RESOLVE_DISPLAY_RGBA32F = 0,  /* fragColor of displayGL.frag as floats (sRGB-encoded, unclamped), w*h*4 floats */
+    HRC_RESOLVE_DISPLAY_RGB8 = 1,     /* the same quantised like an 8-bit unorm colour buffer: round(clamp(c,0,1)*255), w*h*3 bytes (the LDR screenshot) */
+    HRC_RESOLVE_HDR_RGB32F = 2        /* rgb / alpha only, no colour pipeline (the HDR screenshot path, HeatrayRenderer.cpp:1629-1643); `post` may be NULL */
+};
+/* Rows are written bottom-up like the accumulation buffer (row 0 = bottom row; glReadPixels / FreeImage order).
+ * `hostOut` is caller-owned host memory of the size the format implies. Pixels with alpha == 0 divide by zero exactly as
+ * the shader does (inf/NaN in float formats, 0 or 255 after the 8-bit clamp). */
+HRC_API int hrcResolve(HrcContext ctx, const HrcPostProcess* post, int32_t format, void* hostOut);
+
 /* ---- textures (↔ openrl::Texture::create, Texture.h:59-91) ------------------------- */
 enum { HRC_TEX_R32F = 0, HRC_TEX_RGB32F = 1, HRC_TEX_RGBA32F = 2, HRC_TEX_RGBA8 = 3 };
 enum { HRC_WRAP_CLAMP = 0, HRC_WRAP_REPEAT = 1 };

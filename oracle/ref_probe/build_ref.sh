@@ -16,4 +16,12 @@ grep -v '^#include' "$REF/Resources/shaders/utility.rlsl" | sed 's/dot(st\.xy,/d
 grep -v '^#include' "$REF/Resources/shaders/brdfs.rlsl" > /tmp/ref_rlsl_brdfs.inc
 g++ -std=c++20 -O2 -fPIC -shared -fsingle-precision-constant -I$REF/3rdParty -I$REF/3rdParty/glm -w ref_rlsl.cpp -o "$OUT/libref_rlsl.so"
 g++ $FL -DGLM_ENABLE_EXPERIMENTAL -shared ref_host.cpp -o "$OUT/libref_host.so"
+# displayGL.frag as C++: drop #version, turn uniform/in/out globals into statics, rename main; two swizzle proxies get an explicit
+# vec3() (glm proxies do not convert inside operator/ and mix<>): nothing else is touched. -D_MSC_EXTENSIONS only selects glm's
+# member-swizzle syntax (GLM_LANG_CXXMS_FLAG) without enabling SIMD types.
+sed -e '/^#version/d' -e 's/^uniform sampler2D raytracedTexture;/struct sampler2D {}; static sampler2D raytracedTexture;/' \
+    -e 's/^uniform /static /' -e 's/^in vec2 /static vec2 /' -e 's/^out vec4 /static vec4 /' -e 's/^void main()/static void display_main()/' \
+    -e 's|result\.xyz / result\.w|vec3(result.xyz) / result.w|' -e 's|mix(k\.xxx,|mix(vec3(k.xxx),|' \
+    "$REF/Resources/shaders/displayGL.frag" > /tmp/ref_display.inc
+g++ -std=gnu++20 -D_MSC_EXTENSIONS -O2 -fPIC -shared -fsingle-precision-constant -I$REF/3rdParty -I$REF/3rdParty/glm -w ref_display.cpp -o "$OUT/libref_display.so"
 echo "oracle/_ref built"

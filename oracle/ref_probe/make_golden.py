@@ -89,9 +89,37 @@ def host():
     (OUT / "host_glm_ref.json").write_text(json.dumps({"orbit_view": cams, "light_forward": lights}))
 
 
+def display():
+    """displayGL.frag (compiled as C++) at random texels / uv / parameter sets, plus the defaults and each stage alone."""
+    lib = C.CDLL(str(REF / "libref_display.so"))
+    rng = np.random.default_rng(4242)
+    #          tonemap exposure bright contrast hue  sat  vib  r    g    b    vigI vigF
+    default = [0.0, 1.0, 0.0, 1.0, 1.0, 1.0, 0.0, 1.0, 1.0, 1.0, 0.0, 1.0]      # HeatrayRenderer.h:104-117
+    sets = [default, [1.0] + default[1:]]
+    for i, val in ((1, 2.0), (2, 0.15), (3, 1.4), (4, 0.7), (5, 1.6), (6, 0.8), (7, 0.5), (8, 1.3), (9, 0.6), (10, 1.2), (11, 0.4)):
+        q = list(default); q[i] = val; sets.append(q)
+    for _ in range(12):
+        sets.append([float(rng.integers(0, 2)), float(2.0 ** rng.uniform(-2, 2)), float(rng.uniform(-0.3, 0.3)), float(rng.uniform(0.5, 1.6)), float(rng.uniform(0.3, 1.5)),
+                     float(rng.uniform(0, 2)), float(rng.uniform(0, 1)), float(rng.uniform(0.3, 1.5)), float(rng.uniform(0.3, 1.5)), float(rng.uniform(0.3, 1.5)),
+                     float(rng.uniform(0, 2)), float(rng.uniform(0.2, 1.5))])
+    cases = []
+    for q in sets:
+        for k in range(24):
+            n = float(rng.integers(1, 65))
+            rgb = rng.uniform(0, 1, 3) ** 2 * n * (float(rng.uniform(0, 4)) if k % 3 else 1.0)
+            if k == 0: rgb = np.zeros(3)
+            if k == 1: rgb = np.full(3, 0.5 * n)                      # grey: d == 0 in the HSV conversion
+            texel = np.asarray([*rgb, n], np.float32)
+            uv = np.asarray([rng.uniform(), rng.uniform()], np.float32)
+            pa = np.asarray(q, np.float32); o = np.zeros(4, np.float32)
+            lib.ref_display(texel.ctypes.data_as(C.c_void_p), uv.ctypes.data_as(C.c_void_p), pa.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p))
+            cases.append({"texel": bits(texel), "uv": bits(uv), "params": bits(pa), "out": bits(o)})
+    (OUT / "display_ref.json").write_text(json.dumps(cases))
+
+
 if __name__ == "__main__":
     if not (REF / "libref_qmc.so").exists():
         sys.exit("oracle/_ref is missing: run oracle/ref_probe/build_ref.sh where /root/reference is mounted")
     OUT.mkdir(parents=True, exist_ok=True)
-    qmc(); lut(); rlsl(); host()
+    qmc(); lut(); rlsl(); host(); display()
     print("golden vectors written to", OUT)

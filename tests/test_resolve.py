@@ -1,0 +1,141 @@
+"""Resolve + colour pipeline (displayGL.frag:72-151).
+
+CPU: the oracle's restatement against golden vectors produced by the shader text itself compiled as C++
+(oracle/ref_probe/ref_display.cpp -> tests/golden/display_ref.json), bit for bit.
+GPU: hrcResolve (one CUDA kernel over the accumulation buffer) against the oracle through the same C-ABI call.
+"""
+import ctypes as C
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from heatray_b200 import capi, renderer, scenes
+
+GOLDEN = Path(__file__).resolve().parent / "golden" / "display_ref.json"
+FIELDS = [f for f, _ in capi.PostProcess._fields_]
+
+
+def _post(p):
+    kw = {f: (int(v) if f == "tonemappingEnabled" else float(v)) for f, v in zip(FIELDS, p)}
+    return capi.PostProcess(**kw)
+
+
+def _f32(bits):
+    return np.asarray(bits, np.uint32).view(np.float32)
+
+
+def test_oracle_display_pipeline_matches_shader_text_bit_for_bit(oracle_mod):
+    lib = oracle_mod.load()
+    cases = json.loads(GOLDEN.read_text())
+    assert len(cases) >= 500
+    for c in cases:
+        t, uv, p = _f32(c["texel"]), _f32(c["uv"]), _f32(c["params"])
+        pp = _post(p)
+        o = np.zeros(4, np.float32)
+        lib.orcProbeDisplay(C.byref(pp), t.ctypes.data_as(C.c_void_p), uv.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p))
+        assert np.array_equal(o.view(np.uint32), np.asarray(c["out"], np.uint32)), (p, t, uv, o, _f32(c["out"]))
+
+
+def test_live_display_reference_if_present(oracle_mod):
+    """Where oracle/_ref was built (the container with the reference mounted), re-check fresh random fragments."""
+    ref = Path(oracle_mod.HERE) / "_ref" / "libref_display.so"
+    if not ref.exists():
+        pytest.skip("oracle/_ref not built here")
+    rl, ol = C.CDLL(str(ref)), oracle_mod.load()
+    rng = np.random.default_rng(7)
+    for _ in range(2000):
+        n = float(rng.integers(1, 100))
+        t = np.asarray([*(rng.uniform(0, 3, 3) * n), n], np.float32)
+        uv = rng.uniform(0, 1, 2).astype(np.float32)
+        p = np.asarray([rng.integers(0, 2), 2.0 ** rng.uniform(-2, 2), rng.uniform(-0.2, 0.2), rng.uniform(0.5, 1.5), rng.uniform(0.5, 1.5), rng.uniform(0, 2),
+                        rng.uniform(0, 1), rng.uniform(0.5, 1.5), rng.uniform(0.5, 1.5), rng.uniform(0.5, 1.5), rng.uniform(0, 2), rng.uniform(0.2, 1.5)], np.float32)
+        a, b = np.zeros(4, np.float32), np.zeros(4, np.float32)
+        rl.ref_display(t.ctypes.data_as(C.c_void_p), uv.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p), a.ctypes.data_as(C.c_void_p))
+        pp = _post(p)
+        ol.orcProbeDisplay(C.byref(pp), t.ctypes.data_as(C.c_void_p), uv.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p))
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+def _fill(backend, w, h, seed):
+    """A synthetic accumulation buffer: sums of `n` samples per pixel, n in alpha (the progressive contract)."""
+    rng = np.random.default_rng(seed)
+    n = rng.integers(1, 33, (h, w, 1)).astype(np.float32)
+    rgb = (rng.uniform(0, 1, (h, w, 3)) ** 2.2 * rng.uniform(0, 3.2, (h, w, 1))).astype(np.float32) * n
+    px = np.concatenate([rgb, n], -1).astype(np.float32)
+    backend.resize(w, h)
+    backend.clear()
+    backend.add_pixels(px)
+    return px
+
+
+def test_oracle_resolve_defaults_are_plain_srgb(oracle_backend):
+    """With the default parameters (HeatrayRenderer.h:104-117) every stage but the final LinearToSRGB is an identity up to rounding."""
+    px = _fill(oracle_backend, 37, 23, 1)
+    out = oracle_backend.resolve(capi.PostProcess(), capi.RESOLVE_DISPLAY_RGBA32F)
+    mean = px[..., :3] / px[..., 3:]
+    srgb = np.where(mean <= 0.0031308, 12.92 * mean, 1.055 * np.power(mean, 1 / 2.4) - 0.055)
+    assert np.allclose(out[..., :3], srgb, rtol=2e-4, atol=2e-5)
+    assert (out[..., 3] == 1.0).all()
+    hdr = oracle_backend.resolve(None, capi.RESOLVE_HDR_RGB32F)
+    assert np.allclose(hdr, mean, rtol=1e-6)
+    ldr = oracle_backend.resolve(capi.PostProcess(), capi.RESOLVE_DISPLAY_RGB8)
+    assert np.abs(ldr.astype(np.int32) - np.rint(np.clip(out[..., :3], 0, 1) * 255).astype(np.int32)).max() == 0
+
+
+def test_resolve_argument_errors(oracle_backend):
+    _fill(oracle_backend, 8, 8, 2)
+    with pytest.raises(capi.HrcError):
+        oracle_backend.resolve(None, capi.RESOLVE_DISPLAY_RGB8)
+    with pytest.raises(capi.HrcError):
+        oracle_backend.resolve(capi.PostProcess(), 7)
+
+
+PARAM_SETS = {
+    "defaults": {},
+    "aces": dict(tonemappingEnabled=1),
+    "graded": dict(tonemappingEnabled=1, cameraExposure=1.5, brightness=0.05, contrast=1.2, hue=0.9, saturation=1.3, vibrance=0.4, red=1.1, green=0.95, blue=0.8,
+                   vignetteIntensity=1.2, vignetteFalloff=0.5),
+}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(PARAM_SETS))
+@pytest.mark.parametrize("size", [(64, 48), (253, 131), (1, 1), (3, 1)])     # incl. pixel counts that are not multiples of 4 (the kernel's quad tail)
+def test_gpu_resolve_matches_oracle(name, size, oracle_backend, gpu_backend):
+    w, h = size
+    _fill(oracle_backend, w, h, 11)
+    _fill(gpu_backend, w, h, 11)
+    pp = capi.PostProcess(**PARAM_SETS[name])
+    fo = oracle_backend.resolve(pp, capi.RESOLVE_DISPLAY_RGBA32F)
+    fg = gpu_backend.resolve(pp, capi.RESOLVE_DISPLAY_RGBA32F)
+    # tolerance: CUDA powf/sqrtf vs glibc differ by ulps; the hue wrap (fract) and the step() selects are discontinuous,
+    # so a handful of pixels may land on the other branch: >= 99.5 % within 2e-4 relative (+2e-5 abs), none off by more than 0.02
+    close = np.isclose(fg[..., :3], fo[..., :3], rtol=2e-4, atol=2e-5).all(-1)
+    assert close.mean() >= (0.995 if w * h > 100 else 1.0), close.mean()
+    assert np.abs(fg[..., :3] - fo[..., :3]).max() < 0.02
+    assert (fg[..., 3] == 1.0).all()
+    lo = oracle_backend.resolve(pp, capi.RESOLVE_DISPLAY_RGB8).astype(np.int32)
+    lg = gpu_backend.resolve(pp, capi.RESOLVE_DISPLAY_RGB8).astype(np.int32)
+    assert np.abs(lo - lg).max() <= 1 and (lo != lg).mean() < 0.02          # 8-bit: at most one code value apart, on < 2 % of channels
+    ho = oracle_backend.resolve(None, capi.RESOLVE_HDR_RGB32F)
+    hg = gpu_backend.resolve(None, capi.RESOLVE_HDR_RGB32F)
+    assert np.array_equal(ho, hg)                                           # 1/alpha then multiply: the same two IEEE operations on both sides
+
+
+@pytest.mark.gpu
+def test_gpu_resolve_of_a_rendered_frame(oracle_backend, gpu_backend):
+    """End to end: render the Cornell box on the GPU, resolve it on the GPU, compare with the oracle's resolve of the oracle's render."""
+    spec = scenes.cornell_box(width=96, height=96, passes=4)
+    ro, rg = renderer.Renderer(oracle_backend), renderer.Renderer(gpu_backend)
+    ro.load_scene(spec)
+    rg.load_scene(spec)
+    for _ in range(spec.passes):
+        ro.render_pass()
+        rg.render_pass()
+    pp = capi.PostProcess(tonemappingEnabled=1)
+    lo = oracle_backend.resolve(pp, capi.RESOLVE_DISPLAY_RGB8).astype(np.int32)
+    lg = gpu_backend.resolve(pp, capi.RESOLVE_DISPLAY_RGB8).astype(np.int32)
+    assert (np.abs(lo - lg) <= 2).mean() >= 0.99
+    assert lg.max() > 100 and lg.std() > 10          # an actual picture, not a constant
