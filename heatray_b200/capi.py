@@ -103,6 +103,14 @@ class PostProcess(C.Structure):        # HrcPostProcess ↔ HeatrayRenderer::Pos
 RESOLVE_DISPLAY_RGBA32F, RESOLVE_DISPLAY_RGB8, RESOLVE_HDR_RGB32F = 0, 1, 2
 
 
+class HrhImage(C.Structure):
+    _fields_ = [("width", i32), ("height", i32), ("channels", i32), ("isFloat", i32), ("data", C.c_void_p)]
+
+
+class HrhLoadedTexture(C.Structure):
+    _fields_ = [("image", HrhImage), ("format", i32), ("wrapS", i32), ("wrapT", i32)]
+
+
 class FrameParams(C.Structure):
     _fields_ = [("fovTan", f32), ("aspectRatio", f32), ("focusDistance", f32), ("apertureRadius", f32), ("viewMatrix", f32 * 16),
                 ("sampleIndex", i32), ("maxSampleIndex", f32), ("interactiveMode", i32), ("blockSize", i32 * 2),
@@ -223,6 +231,15 @@ def _declare_host(lib):
     lib.hrhPassGeneratorWaitIdle.argtypes = [C.c_void_p]
     lib.hrhPassGeneratorLastError.restype = C.c_char_p
     lib.hrhPassGeneratorLastError.argtypes = [C.c_void_p]
+    lib.hrhLoadImage.argtypes = [C.c_char_p, i32, C.POINTER(HrhImage)]
+    lib.hrhLoadImageFromMemory.argtypes = [C.c_void_p, C.c_size_t, i32, C.POINTER(HrhImage)]
+    lib.hrhFreeImage.argtypes = [C.POINTER(HrhImage)]
+    lib.hrhLoadTexture.argtypes = [C.c_char_p, i32, i32, C.POINTER(HrhLoadedTexture)]
+    lib.hrhExpandToRGBA8.argtypes = [C.POINTER(HrhImage), C.c_void_p]
+    lib.hrhWritePNG.argtypes = [C.c_char_p, C.c_void_p, i32, i32, i32, i32]
+    lib.hrhWriteHDR.argtypes = [C.c_char_p, C.c_void_p, i32, i32, i32]
+    lib.hrhWritePFM.argtypes = [C.c_char_p, C.c_void_p, i32, i32, i32]
+    lib.hrhImageLastError.restype = C.c_char_p
     lib.hrhPlaneMesh.argtypes = [f32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.hrhSphereMesh.argtypes = [i32, i32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(u32), C.POINTER(u32)]
 
@@ -445,3 +462,60 @@ class Backend:
         hits = np.zeros(r.shape[0], HIT_DTYPE)
         self._call("TraceRays", i32(r.shape[0]), _ptr(r), i32(int(any_hit)), _ptr(hits))
         return hits
+
+
+# ---- images (host_image.cpp) --------------------------------------------------------------------
+def _image_to_numpy(lib, im: HrhImage) -> np.ndarray:
+    n = im.width * im.height * im.channels
+    ct = C.c_float if im.isFloat else C.c_uint8
+    a = np.ctypeslib.as_array(C.cast(im.data, C.POINTER(ct)), shape=(n,)).copy().reshape(im.height, im.width, im.channels)
+    lib.hrhFreeImage(C.byref(im))
+    return a
+
+
+def load_image(path_or_bytes, flip=False) -> np.ndarray:
+    """hrhLoadImage / hrhLoadImageFromMemory -> (h, w, channels) uint8 or float32 array."""
+    lib = load_library()
+    im = HrhImage()
+    if isinstance(path_or_bytes, (bytes, bytearray)):
+        buf = (C.c_uint8 * len(path_or_bytes)).from_buffer_copy(path_or_bytes)
+        rc = lib.hrhLoadImageFromMemory(buf, len(path_or_bytes), int(flip), C.byref(im))
+    else:
+        rc = lib.hrhLoadImage(str(path_or_bytes).encode(), int(flip), C.byref(im))
+    if rc != HRC_OK:
+        raise HrcError(rc, (lib.hrhImageLastError() or b"").decode())
+    return _image_to_numpy(lib, im)
+
+
+def load_texture(path, generate_mips=True, convert_to_linear=False):
+    """util::loadTexture (TextureLoader.cpp:17-137): returns (pixels, HRC_TEX_* format, wrapS, wrapT); uint8 images come back expanded to RGBA8."""
+    lib = load_library()
+    lt = HrhLoadedTexture()
+    rc = lib.hrhLoadTexture(str(path).encode(), int(generate_mips), int(convert_to_linear), C.byref(lt))
+    if rc != HRC_OK:
+        raise HrcError(rc, (lib.hrhImageLastError() or b"").decode())
+    fmt, ws, wt = lt.format, lt.wrapS, lt.wrapT
+    if lt.image.isFloat:
+        return _image_to_numpy(lib, lt.image), fmt, ws, wt
+    out = np.empty((lt.image.height, lt.image.width, 4), np.uint8)
+    lib.hrhExpandToRGBA8(C.byref(lt.image), _ptr(out))
+    lib.hrhFreeImage(C.byref(lt.image))
+    return out, fmt, ws, wt
+
+
+def write_png(path, pixels: np.ndarray, rows_bottom_up=True):
+    a = np.ascontiguousarray(pixels, np.uint8)
+    h, w = a.shape[:2]
+    ch = 1 if a.ndim == 2 else a.shape[2]
+    rc = load_library().hrhWritePNG(str(path).encode(), _ptr(a), w, h, ch, int(rows_bottom_up))
+    if rc != HRC_OK:
+        raise HrcError(rc, (load_library().hrhImageLastError() or b"").decode())
+
+
+def write_hdr(path, rgb: np.ndarray, rows_bottom_up=True, pfm=False):
+    a = np.ascontiguousarray(rgb, np.float32)
+    h, w = a.shape[:2]
+    lib = load_library()
+    rc = (lib.hrhWritePFM if pfm else lib.hrhWriteHDR)(str(path).encode(), _ptr(a), w, h, int(rows_bottom_up))
+    if rc != HRC_OK:
+        raise HrcError(rc, (lib.hrhImageLastError() or b"").decode())

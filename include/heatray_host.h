@@ -111,6 +111,37 @@ HRC_API int  hrhPassGeneratorRunTask(HrhPassGenerator pg, HrhContextTask task, v
 HRC_API int  hrhPassGeneratorWaitIdle(HrhPassGenerator pg);       /* drains the job queue (test/bench helper) */
 HRC_API const char* hrhPassGeneratorLastError(HrhPassGenerator pg);
 
+/* ---- images: texture loading (reference Source/Utility/TextureLoader.cpp:17-159, which decodes with stb_image / FreeImage)
+ * and screenshots (HeatrayRenderer::saveScreenshot, HeatrayRenderer.cpp:1619-1662, FreeImage_Save). Own decoders/encoders:
+ * PNG (all colour types and bit depths, Adam7, tRNS), baseline + progressive JPEG, Radiance .hdr (RGBE, flat and RLE). ---- */
+typedef struct HrhImage {
+    int32_t width, height, channels;   /* channels as stored in the file: 1 (luminance), 2, 3 (RGB) or 4 (RGBA) */
+    int32_t isFloat;                   /* 1: data is float32 (Radiance .hdr; stbi_loadf path); 0: uint8 */
+    void*   data;                      /* width*height*channels elements, rows top-down unless flipped at load; free with hrhFreeImage */
+} HrhImage;
+/* ↔ stbi_load / stbi_loadf with stbi_set_flip_vertically_on_load(flip) (TextureLoader.cpp:90-107); 16-bit PNG samples keep their high byte. */
+HRC_API int  hrhLoadImage(const char* path, int32_t flipVertically, HrhImage* out);
+HRC_API int  hrhLoadImageFromMemory(const void* bytes, size_t size, int32_t flipVertically, HrhImage* out);
+HRC_API void hrhFreeImage(HrhImage* img);
+/* ↔ util::loadTextureInternal (TextureLoader.cpp:17-137): "../" path fallback (:24-35), vertical flip, 8-bit sRGB->linear->8-bit
+ * requantisation of the colour channels when convertToLinear (alpha untouched, :109-133), channel count -> format (:138-151,
+ * 2-channel images are rejected like the reference), sampler = LINEAR + CLAMP_TO_EDGE when !generateMips else the default
+ * REPEAT (+ mip filter, which policy A-12 replaces by level-0 bilinear). */
+typedef struct HrhLoadedTexture {
+    HrhImage image;
+    int32_t  format;                   /* HRC_TEX_* to hand to hrcCreateTexture2D after hrhExpandTexture */
+    int32_t  wrapS, wrapT;             /* HRC_WRAP_* */
+} HrhLoadedTexture;
+HRC_API int  hrhLoadTexture(const char* path, int32_t generateMips, int32_t convertToLinear, HrhLoadedTexture* out);
+/* Expands 1/3/4-channel uint8 or float texels to what hrcCreateTexture2D accepts (RGBA8 or RGBA32F/RGB32F/R32F; luminance replicates to RGB
+ * with alpha 1 like RL_LUMINANCE). `out` must hold width*height*4 bytes (uint8 input) or is the image itself (float input, no copy needed). */
+HRC_API int  hrhExpandToRGBA8(const HrhImage* img, uint8_t* out);
+/* Screenshot writers (rows given bottom-up like hrcResolve output; written top-down as the formats require). */
+HRC_API int  hrhWritePNG(const char* path, const uint8_t* pixels, int32_t width, int32_t height, int32_t channels, int32_t rowsBottomUp);
+HRC_API int  hrhWriteHDR(const char* path, const float* rgb, int32_t width, int32_t height, int32_t rowsBottomUp);   /* Radiance RGBE */
+HRC_API int  hrhWritePFM(const char* path, const float* rgb, int32_t width, int32_t height, int32_t rowsBottomUp);
+HRC_API const char* hrhImageLastError(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,4 +24,5 @@ sed -e '/^#version/d' -e 's/^uniform sampler2D raytracedTexture;/struct sampler2
     -e 's|result\.xyz / result\.w|vec3(result.xyz) / result.w|' -e 's|mix(k\.xxx,|mix(vec3(k.xxx),|' \
     "$REF/Resources/shaders/displayGL.frag" > /tmp/ref_display.inc
 g++ -std=gnu++20 -D_MSC_EXTENSIONS -O2 -fPIC -shared -fsingle-precision-constant -I$REF/3rdParty -I$REF/3rdParty/glm -w ref_display.cpp -o "$OUT/libref_display.so"
+g++ -std=c++17 -O2 -fPIC -shared -I$REF/3rdParty -w ref_stb.cpp -o "$OUT/libref_stb.so"
 echo "oracle/_ref built"
