@@ -4,7 +4,7 @@
 // (stbi_load / stbi_loadf, vertical flip on) and HeatrayRenderer::saveScreenshot (HeatrayRenderer.cpp:1619-1662) writes
 // through FreeImage. Neither library is used here: this file carries its own PNG (zlib inflate, all colour types and bit
 // depths, Adam7, tRNS), JPEG (baseline + progressive Huffman, 8-bit) and Radiance RGBE decoders, and PNG / RGBE / PFM
-// writers. tests/test_images.py pins the decoders against stb_image compiled from the reference tree (oracle/_ref).
+// writers. tests/test_images.py pins the decoders bit for bit against stb_image as vendored by the reference.
 #include "host_api.h"
 
 #include <algorithm>
