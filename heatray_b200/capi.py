@@ -7,6 +7,7 @@ prefix; the tests build the same wrapper around the CPU oracle (see oracle/loade
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
@@ -160,6 +161,24 @@ class HrhGlassMaterial(C.Structure):
         super().__init__(*a, **kw)
 
 
+class HrhSceneInfo(C.Structure):
+    _fields_ = [("materialCount", i32), ("meshCount", i32), ("lightCount", i32), ("aabbMin", f32 * 3), ("aabbMax", f32 * 3)]
+
+
+class HrhSceneMaterial(C.Structure):
+    _fields_ = [("type", i32), ("name", C.c_char_p), ("pbr", HrhPbrMaterial), ("glass", HrhGlassMaterial), ("texturePath", C.c_char_p * 7)]
+
+
+class HrhSceneMesh(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("vertexCount", u32), ("indexCount", u32), ("positions", fp), ("normals", fp), ("texCoords", fp),
+                ("tangents", fp), ("bitangents", fp), ("colors", fp), ("indices", C.POINTER(u32)), ("materialIndex", i32), ("localTransform", f32 * 16)]
+
+
+class HrhSceneLight(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("type", i32), ("color", f32 * 3), ("intensity", f32), ("position", f32 * 3), ("theta", f32), ("phi", f32),
+                ("innerAngle", f32), ("outerAngle", f32)]
+
+
 class RenderOptions(C.Structure):       # HrhRenderOptions ↔ PassGenerator::RenderOptions (PassGenerator.h:49-150)
     _fields_ = [("enableInteractiveMode", i32), ("enableOfflineMode", i32), ("resetInternalState", i32),
                 ("maxRenderPasses", u32), ("maxRayDepth", u32), ("maxChannelValue", f32),
@@ -189,9 +208,10 @@ def load_library() -> C.CDLL:
     """The in-tree CUDA backend. Raises if it has not been built: there is no fallback."""
     global _lib
     if _lib is None:
-        if not LIB_PATH.exists():
-            raise RuntimeError(f"{LIB_PATH} is missing: run `python -m heatray_b200.build` (nvcc, sm_100a). There is no CPU fallback.")
-        _lib = C.CDLL(str(LIB_PATH))
+        path = Path(os.environ.get("HEATRAY_CUDA_LIB", LIB_PATH))      # override: experimental kernel variants (tools/build_variant.sh)
+        if not path.exists():
+            raise RuntimeError(f"{path} is missing: run `python -m heatray_b200.build` (nvcc, sm_100a). There is no CPU fallback.")
+        _lib = C.CDLL(str(path))
         _declare_host(_lib)
     return _lib
 
@@ -240,6 +260,14 @@ def _declare_host(lib):
     lib.hrhWriteHDR.argtypes = [C.c_char_p, C.c_void_p, i32, i32, i32]
     lib.hrhWritePFM.argtypes = [C.c_char_p, C.c_void_p, i32, i32, i32]
     lib.hrhImageLastError.restype = C.c_char_p
+    lib.hrhImportScene.argtypes = [C.c_char_p, i32, C.POINTER(C.c_void_p)]
+    lib.hrhFreeScene.argtypes = [C.c_void_p]
+    lib.hrhSceneGetInfo.argtypes = [C.c_void_p, C.POINTER(HrhSceneInfo)]
+    lib.hrhSceneGetMaterial.argtypes = [C.c_void_p, i32, C.POINTER(HrhSceneMaterial)]
+    lib.hrhSceneGetMesh.argtypes = [C.c_void_p, i32, C.POINTER(HrhSceneMesh)]
+    lib.hrhSceneGetLight.argtypes = [C.c_void_p, i32, C.POINTER(HrhSceneLight)]
+    lib.hrhImportLastError.restype = C.c_char_p
+    lib.hrhLightAnglesFromTransform.argtypes = [fp, fp, fp]
     lib.hrhPlaneMesh.argtypes = [f32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.hrhSphereMesh.argtypes = [i32, i32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(u32), C.POINTER(u32)]
 

@@ -1041,8 +1041,11 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
 // instruction cache (the single all-materials kernel of the first version stalled on instruction fetch).
 // The (<= 1) occlusion ray and (<= 1) extension ray of every hit are appended to the next queues with warp-aggregated
 // atomics (ballot + popc prefix) — the compaction of live rays.
+#ifndef HR_SHADE_MIN_BLOCKS
+#define HR_SHADE_MIN_BLOCKS 4
+#endif
 template <int CLS>
-__global__ void __launch_bounds__(128) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
+__global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = (gridDim.x * blockDim.x) >> 5;
     const uint32_t warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;

@@ -10,6 +10,7 @@ from __future__ import annotations
 import ctypes as C
 import math
 from dataclasses import dataclass, field
+from pathlib import Path
 
 import numpy as np
 
@@ -402,3 +403,129 @@ def textured_showcase(width=192, height=128, passes=4, max_depth=5, u_slices=32,
 def build(name: str, **kw) -> SceneSpec:
     return {"cornell": cornell_box, "sphere_grid": sphere_grid, "material_grid": material_grid, "terrain": terrain,
             "textured_showcase": textured_showcase}[name](**kw)
+
+
+# ---- assets from disk (Scene::loadFromDisk, Scene.cpp:14-27 -> hrhImportScene) -----------------------------------------
+_SLOT_FIELDS = ["baseColorTexture", "metallicRoughnessTexture", "emissiveTexture", "normalmap", "clearCoatTexture", "clearCoatRoughnessTexture", "clearCoatNormalmap"]
+_SLOT_LINEAR = [True, False, True, False, False, False, False]     # convertToLinear per slot (AssimpMeshProvider.cpp:448-505)
+
+
+def import_scene(path, convert_to_meters=False, width=512, height=512, passes=16, max_depth=5, env=None, camera=None, load_textures=True) -> SceneSpec:
+    """OBJ / glTF asset -> SceneSpec through the C++ importer (host_import.cpp) and texture loader (host_image.cpp).
+    Camera framing follows HeatrayRenderer.cpp:302-308: target = AABB centre, distance = 3 x AABB diagonal, focus on the target."""
+    import ctypes as C
+    lib = capi.load_library()
+    h = C.c_void_p()
+    rc = lib.hrhImportScene(str(path).encode(), int(convert_to_meters), C.byref(h))
+    if rc != capi.HRC_OK:
+        raise capi.HrcError(rc, (lib.hrhImportLastError() or b"").decode())
+    try:
+        info = capi.HrhSceneInfo()
+        lib.hrhSceneGetInfo(h, C.byref(info))
+        tex_cache = {}
+
+        def texture(pth, linear):
+            key = (pth, linear)
+            if key not in tex_cache:
+                try:
+                    px, fmt, _, _ = capi.load_texture(pth, True, linear)
+                except capi.HrcError:
+                    tex_cache[key] = None                      # the reference logs and carries on without the texture (TextureLoader.cpp:29-33)
+                else:
+                    if px.dtype == np.uint8:
+                        px = px.astype(np.float32) / np.float32(255.0)
+                    elif px.shape[2] == 3:
+                        px = np.concatenate([px, np.ones(px.shape[:2] + (1,), np.float32)], -1)
+                    elif px.shape[2] == 1:
+                        px = np.concatenate([px, px, px, np.ones_like(px)], -1)
+                    tex_cache[key] = np.ascontiguousarray(px, np.float32)
+            return tex_cache[key]
+        materials = []
+        for i in range(info.materialCount):
+            m = capi.HrhSceneMaterial()
+            lib.hrhSceneGetMaterial(h, i, C.byref(m))
+            textures = {}
+            if load_textures:
+                for s, fld in enumerate(_SLOT_FIELDS):
+                    if m.texturePath[s]:
+                        t = texture(m.texturePath[s].decode(), _SLOT_LINEAR[s])
+                        if t is not None:
+                            textures[fld] = t
+            if m.type == capi.MATERIAL_GLASS:
+                g = m.glass
+                materials.append(_glass(tuple(g.baseColor), g.roughness, g.ior, g.density,
+                                        {k: v for k, v in textures.items() if k in ("baseColorTexture", "normalmap", "metallicRoughnessTexture")}))
+            else:
+                p = m.pbr
+                materials.append(_pbr(tuple(p.baseColor), p.roughness, p.metallic, p.specularF0, tuple(p.emissiveColor), p.clearCoat, p.clearCoatRoughness,
+                                      bool(p.doubleSided), bool(p.alphaMask), bool(p.enableVertexColors), False, textures))
+        meshes = []
+        for i in range(info.meshCount):
+            sm = capi.HrhSceneMesh()
+            lib.hrhSceneGetMesh(h, i, C.byref(sm))
+            nv, ni = sm.vertexCount, sm.indexCount
+
+            def arr(ptr, comps):
+                return np.ctypeslib.as_array(ptr, shape=(nv, comps)).copy() if ptr else None
+            idx = np.ctypeslib.as_array(sm.indices, shape=(ni,)).copy().astype(np.uint32)
+            xf = np.asarray(list(sm.localTransform), np.float32).reshape(4, 4).T          # column-major -> mathematical (row-major) matrix
+            meshes.append(MeshSpec(arr(sm.positions, 3), arr(sm.normals, 3), idx, sm.materialIndex, xf, capi.DRAW_TRIANGLES,
+                                   uvs=arr(sm.texCoords, 2), tangents=arr(sm.tangents, 3), bitangents=arr(sm.bitangents, 3), colors=arr(sm.colors, 3)))
+        dl, pl, sl = [], [], []
+        for i in range(info.lightCount):
+            L = capi.HrhSceneLight()
+            lib.hrhSceneGetLight(h, i, C.byref(L))
+            if L.type == 0:
+                dl.append(dict(color=tuple(L.color), illuminance=L.intensity, theta=L.theta, phi=L.phi))
+            elif L.type == 1:
+                pl.append(dict(color=tuple(L.color), intensity=L.intensity, position=tuple(L.position)))
+            else:
+                sl.append(dict(color=tuple(L.color), intensity=L.intensity, position=tuple(L.position), theta=L.theta, phi=L.phi, inner=L.innerAngle, outer=L.outerAngle))
+        lo, hi = np.asarray(list(info.aabbMin), np.float32), np.asarray(list(info.aabbMax), np.float32)
+        centre, radius = (lo + hi) * 0.5, float(np.linalg.norm(hi - lo))                   # AABB.h:34-44 (radius() is the full diagonal)
+        cam = dict(distance=radius * 3.0, phi=0.0, theta=0.0, target=tuple(float(v) for v in centre), focal_length=50.0, fstop=None, focus_distance=radius * 3.0)
+        cam.update(camera or {})
+        return SceneSpec(Path(str(path)).stem, width, height, passes, max_depth, meshes, materials,
+                         env=env or dict(enabled=True, solid=(0.5, 0.5, 0.5), map=None, ev=0.0, theta=0.0),
+                         dir_lights=dl[:5], point_lights=pl[:5], spot_lights=sl[:5], camera=cam)
+    finally:
+        lib.hrhFreeScene(h)
+
+
+def write_obj(spec: SceneSpec, path) -> Path:
+    """Writes the meshes of `spec`, flattened to world space, as Wavefront OBJ + MTL (BASELINE config #1 names a Cornell-box OBJ).
+    Strips are expanded GL-style; normals are written transformed by mat3(worldFromEntity) like vertex.rlsl:28. PBR parameters go out
+    through the keys Assimp's OBJ importer understands (Kd, Ke, Pr, Pm, Pc, Pcr, Ni with ((1-Ni)/(1+Ni))^2 = specularF0)."""
+    path = Path(path)
+    mtl = path.with_suffix(".mtl")
+    with open(mtl, "w") as f:
+        for i, m in enumerate(spec.materials):
+            p = m.params
+            f.write(f"newmtl m{i}\n")
+            f.write("Kd %.9g %.9g %.9g\nKe %.9g %.9g %.9g\n" % (*p["baseColor"], *p.get("emissiveColor", (0, 0, 0))))
+            s = math.sqrt(max(p.get("specularF0", 0.5), 0.0))
+            f.write("Pr %.9g\nPm %.9g\nPc %.9g\nPcr %.9g\nNi %.9g\n\n" % (p.get("roughness", 1.0), p.get("metallic", 0.0), p.get("clearCoat", 0.0),
+                                                                       p.get("clearCoatRoughness", 0.0), (1 + s) / (1 - s) if s < 1 else 1e9))
+    with open(path, "w") as f:
+        f.write(f"mtllib {mtl.name}\n")
+        base = 1
+        for k, ms in enumerate(spec.meshes):
+            M = np.asarray(ms.transform, np.float64)
+            P = np.asarray(ms.positions, np.float64).reshape(-1, 3) @ M[:3, :3].T + M[:3, 3]
+            N = np.asarray(ms.normals, np.float64).reshape(-1, 3) @ M[:3, :3].T
+            f.write(f"o mesh{k}\nusemtl m{ms.material}\n")
+            for v in P.astype(np.float32):
+                f.write("v %.9g %.9g %.9g\n" % tuple(v))
+            for v in N.astype(np.float32):
+                f.write("vn %.9g %.9g %.9g\n" % tuple(v))
+            idx = np.asarray(ms.indices).reshape(-1)
+            if ms.draw_mode == capi.DRAW_TRIANGLES:
+                tris = idx.reshape(-1, 3)
+            else:
+                tris = np.asarray([(idx[j], idx[j + 1], idx[j + 2]) if j % 2 == 0 else (idx[j + 1], idx[j], idx[j + 2]) for j in range(len(idx) - 2)])
+            if np.linalg.det(M[:3, :3]) < 0:
+                tris = tris[:, ::-1]
+            for a, b, c in tris:
+                f.write("f %d//%d %d//%d %d//%d\n" % (a + base, a + base, b + base, b + base, c + base, c + base))
+            base += len(P)
+    return path

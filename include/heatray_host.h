@@ -142,6 +142,46 @@ HRC_API int  hrhWriteHDR(const char* path, const float* rgb, int32_t width, int3
 HRC_API int  hrhWritePFM(const char* path, const float* rgb, int32_t width, int32_t height, int32_t rowsBottomUp);
 HRC_API const char* hrhImageLastError(void);
 
+/* ---- scene import (reference Scene::loadFromDisk, Scene.cpp:14-27 -> AssimpMeshProvider, AssimpMeshProvider.cpp:65-723).
+ * Own readers for Wavefront OBJ/MTL and glTF 2.0 (.gltf/.glb) that apply the reference's Assimp->Heatray mapping rules and hand
+ * back what MeshProvider exposes (MeshProvider.h:50-81). Pointers stay valid until hrhFreeScene. ---- */
+typedef struct HrhScene_t* HrhScene;
+typedef struct HrhSceneInfo { int32_t materialCount, meshCount, lightCount; float aabbMin[3], aabbMax[3]; } HrhSceneInfo;
+enum { HRH_TEX_BASE_COLOR = 0, HRH_TEX_METALLIC_ROUGHNESS = 1, HRH_TEX_EMISSIVE = 2, HRH_TEX_NORMAL = 3, HRH_TEX_CLEARCOAT = 4,
+       HRH_TEX_CLEARCOAT_ROUGHNESS = 5, HRH_TEX_CLEARCOAT_NORMAL = 6, HRH_TEX_SLOT_COUNT = 7 };
+typedef struct HrhSceneMaterial {
+    int32_t type;                        /* HRC_MATERIAL_PBR or HRC_MATERIAL_GLASS (alphaMode BLEND or transmission != 0, :365-376) */
+    const char* name;
+    HrhPbrMaterial pbr;                  /* user-facing parameters (ProcessMaterial :378-425); texture handles are HRC_NULL_TEXTURE: the caller creates them */
+    HrhGlassMaterial glass;              /* ProcessGlassMaterial :264-283 (uses slots base colour, normal, metallic-roughness) */
+    const char* texturePath[7];          /* HRH_TEX_*: file to load, NULL = none. Base colour and emissive load with convertToLinear = true, the rest false (:448-505) */
+} HrhSceneMaterial;
+typedef struct HrhSceneMesh {            /* one Submesh of the provider (ProcessMesh :100-262 + ProcessNode :73-98) */
+    const char* name;
+    uint32_t vertexCount, indexCount;    /* triangles: indexCount / 3 */
+    const float *positions, *normals;    /* xyz per vertex, always present (smooth normals are generated when the file has none) */
+    const float *texCoords;              /* uv per vertex or NULL */
+    const float *tangents, *bitangents;  /* xyz per vertex or NULL (present whenever texCoords are) */
+    const float *colors;                 /* rgb per vertex or NULL; the material then has enableVertexColors */
+    const uint32_t* indices;
+    int32_t materialIndex;
+    float localTransform[16];            /* column-major world-from-mesh transform of the owning node */
+} HrhSceneMesh;
+typedef struct HrhSceneLight {           /* ProcessLight :516-660; feed hrhPackDirectionalLight / PointLight / SpotLight */
+    const char* name; int32_t type;      /* 0 directional, 1 point, 2 spot */
+    float color[3]; float intensity;     /* |colour * intensity| split as the reference does (:541-545) */
+    float position[3]; float theta, phi, innerAngle, outerAngle;
+} HrhSceneLight;
+HRC_API int  hrhImportScene(const char* path, int32_t convertToMeters, HrhScene* out);
+HRC_API void hrhFreeScene(HrhScene scene);
+HRC_API int  hrhSceneGetInfo(HrhScene scene, HrhSceneInfo* info);
+HRC_API int  hrhSceneGetMaterial(HrhScene scene, int32_t index, HrhSceneMaterial* out);
+HRC_API int  hrhSceneGetMesh(HrhScene scene, int32_t index, HrhSceneMesh* out);
+HRC_API int  hrhSceneGetLight(HrhScene scene, int32_t index, HrhSceneLight* out);
+/* theta/phi of an imported directional or spot light from its node transform (ProcessLight :564-586, incl. its vec4(axis, 1) quirk). */
+HRC_API void hrhLightAnglesFromTransform(const float worldFromLight[16], float* theta, float* phi);
+HRC_API const char* hrhImportLastError(void);
+
 #ifdef __cplusplus
 }
 #endif

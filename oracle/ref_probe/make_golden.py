@@ -86,7 +86,21 @@ def host():
         o = np.zeros(3, np.float32)
         lib.ref_light_forward(f32(th), f32(phi), o.ctypes.data_as(C.c_void_p))
         lights.append({"in": bits([th, phi]), "out": bits(o)})
-    (OUT / "host_glm_ref.json").write_text(json.dumps({"orbit_view": cams, "light_forward": lights}))
+    # ProcessLight's euler-angle recovery for imported lights (AssimpMeshProvider.cpp:564-586) on random rigid + translated node transforms
+    la = []
+    for k in range(24):
+        q = rng.normal(size=4); q /= np.linalg.norm(q)
+        x, y, z, w = q
+        R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                      [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                      [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+        M = np.eye(4); M[:3, :3] = R
+        M[:3, 3] = rng.uniform(-4, 4, 3) if k % 2 else 0.0
+        m = np.ascontiguousarray(M.T, np.float32).reshape(-1)          # column-major
+        o = np.zeros(2, np.float32)
+        lib.ref_light_angles(m.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p))
+        la.append({"in": bits(m), "out": bits(o)})
+    (OUT / "host_glm_ref.json").write_text(json.dumps({"orbit_view": cams, "light_forward": lights, "light_angles": la}))
 
 
 def display():

@@ -1,3 +1,5 @@
+#include <glm/glm/gtx/euler_angles.hpp>
+#include <algorithm>
 // Host-side math of the reference evaluated with the reference's own glm: OrbitCamera::createViewMatrix from the
 // UNMODIFIED header (Source/HeatrayRenderer/OrbitCamera.h) and the light-direction expressions of
 // DirectionalLight.cpp:64-78 / SpotLight.cpp:76-91 written with the same glm calls (the light classes themselves
@@ -23,5 +25,20 @@ void ref_light_forward(float theta, float phi, float* out3) {   // normalize(vie
     glm::vec3 direction = glm::vec3(viewMatrix[2]) * -1.0f;
     glm::vec3 n = glm::normalize(direction);
     out3[0] = n.x; out3[1] = n.y; out3[2] = n.z;
+}
+// ProcessLight's orientation recovery (AssimpMeshProvider.cpp:564-586): local frame with vec4(axis, 1) columns, lightTransform * local,
+// glm::extractEulerAngleXYZ, clamps. in16 = column-major node transform; up/dir as Assimp's glTF importer sets them. out = (theta, phi).
+void ref_light_angles(const float* in16, float* out2) {
+    glm::mat4 lightTransform; for (int c = 0; c < 4; ++c) for (int r = 0; r < 4; ++r) lightTransform[c][r] = in16[4 * c + r];
+    glm::vec4 yAxis = glm::vec4(0.0f, 1.0f, 0.0f, 1.0f);
+    glm::vec4 zAxis = glm::vec4(0.0f, 0.0f, -1.0f, 1.0f);
+    glm::vec4 xAxis = glm::vec4(glm::cross(glm::vec3(yAxis), glm::vec3(zAxis)), 1.0f);
+    glm::mat4x4 localTransform = glm::mat4x4(xAxis, yAxis, zAxis, glm::vec4(0.0f, 0.0f, 0.0f, 1.0f));
+    glm::mat4x4 finalTransform = lightTransform * localTransform;
+    float roll = 0.0f, pitch = 0.0f, yaw = 0.0f;
+    glm::extractEulerAngleXYZ(finalTransform, pitch, yaw, roll);
+    yaw = std::clamp(yaw, 0.0f, glm::two_pi<float>());
+    pitch = std::clamp(pitch, -glm::half_pi<float>(), glm::half_pi<float>());
+    out2[0] = pitch; out2[1] = yaw;
 }
 }
