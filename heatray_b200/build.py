@@ -68,8 +68,24 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     return LIB
 
 
+APP = PKG / "heatray_headless"
+
+
+def build_apps(force: bool = False) -> Path:
+    """heatray_headless: the viewer's render loop without the viewer (csrc/apps/heatray_headless.cpp), linked against the in-tree library."""
+    src = CSRC / "apps" / "heatray_headless.cpp"
+    if force or _stale(APP, [src, LIB] + _headers()):
+        cmd = ["g++", "-std=c++17", "-O2", "-pthread", str(src), "-o", str(APP), f"-L{PKG}", "-lheatray_cuda", "-Wl,-rpath,$ORIGIN"]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            sys.stderr.write(res.stdout + res.stderr)
+            raise RuntimeError("heatray_headless build failed")
+    return APP
+
+
 def build_all(force: bool = False, verbose: bool = False) -> None:
     build_cuda(force, verbose)
+    build_apps(force)
 
 
 if __name__ == "__main__":

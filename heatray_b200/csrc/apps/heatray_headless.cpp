@@ -1,0 +1,156 @@
+// heatray_headless — the viewer's render loop without the viewer: load an asset, kick progressive passes through the pass
+// interface, resolve with the display colour pipeline, write the screenshot. Plain C over include/heatray_host.h only.
+//
+// Reference flow being mirrored: HeatrayRenderer::changeScene -> PassGenerator::loadScene -> Scene::loadFromDisk
+// (HeatrayRenderer.cpp:288-310), camera framing from the scene AABB (:302-308), the pass-kicking loop of
+// HeatrayRenderer::render (:366-408, one renderPass per completed pass until maxRenderPasses), the display pass
+// (displayGL.frag via HeatrayRenderer.h:228-262) and saveScreenshot (:1619-1662). GLFW / ImGui / GL are absent by design.
+#include "../../../include/heatray_host.h"
+
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+struct App {
+    std::string scenePath, outPng = "heatray.png", outHdr, envMap;
+    int width = 800, height = 800, passes = 32, depth = 10, device = 0;          // reference defaults: 800x800 render area (main.cpp:42-43), 32 passes, depth 10
+    bool meters = false, envOff = false; float envColor[3] = {0.5f, 0.5f, 0.5f}, envEV = 0.0f;
+    float phi = 0.0f, theta = 0.0f, distanceScale = 1.0f, fstop = 0.0f, focalLength = 50.0f;
+    HrcPostProcess post{0, 1.0f, 0.0f, 1.0f, 1.0f, 1.0f, 0.0f, 1.0f, 1.0f, 1.0f, 0.0f, 1.0f};
+    // filled on the worker thread
+    HrhSceneInfo info{}; HrhSceneUploadResult upload{}; HrcTexture envTex = HRC_NULL_TEXTURE; int rc = 0; std::string error;
+    std::atomic<int> passesDone{0}; double passSeconds = 0.0;
+};
+
+void loadSceneTask(void* user, HrcContext ctx) {                                 // the LoadSceneCallback body (PassGenerator.cpp:124-136)
+    App& a = *static_cast<App*>(user);
+    HrhScene scene = nullptr;
+    a.rc = hrhImportScene(a.scenePath.c_str(), a.meters ? 1 : 0, &scene);
+    if (a.rc != HRC_OK) { a.error = hrhImportLastError(); return; }
+    hrhSceneGetInfo(scene, &a.info);
+    a.rc = hrhSceneUpload(scene, ctx, 1, HRC_NULL_TEXTURE, &a.upload);
+    if (a.rc != HRC_OK) a.error = hrhImportLastError();
+    hrhFreeScene(scene);
+    if (a.rc == HRC_OK && !a.envMap.empty()) {                                   // EnvironmentLight::changeImageSource -> util::loadTexture(path, true, false) (EnvironmentLight.cpp:36-46)
+        HrhLoadedTexture lt;
+        a.rc = hrhLoadTexture(a.envMap.c_str(), 1, 0, &lt);
+        if (a.rc != HRC_OK) { a.error = hrhImageLastError(); return; }
+        HrcTextureDesc td{lt.image.width, lt.image.height, lt.format, HRC_WRAP_REPEAT, HRC_WRAP_CLAMP};
+        if (lt.image.isFloat) a.rc = hrcCreateTexture2D(ctx, &td, lt.image.data, &a.envTex);
+        else { std::vector<uint8_t> rgba((size_t)lt.image.width * lt.image.height * 4); hrhExpandToRGBA8(&lt.image, rgba.data()); a.rc = hrcCreateTexture2D(ctx, &td, rgba.data(), &a.envTex); }
+        hrhFreeImage(&lt.image);
+        if (a.rc != HRC_OK) a.error = hrcGetLastError(ctx);
+    }
+}
+
+void passComplete(void* user, int32_t, const float*, int32_t, int32_t, float passTime, uint64_t) {
+    App& a = *static_cast<App*>(user);
+    a.passSeconds += passTime; a.passesDone++;
+}
+
+void screenshotTask(void* user, HrcContext ctx) {                                // saveScreenshot, HeatrayRenderer.cpp:1619-1662
+    App& a = *static_cast<App*>(user);
+    const size_t n = (size_t)a.width * a.height;
+    if (!a.outPng.empty()) {
+        std::vector<uint8_t> rgb(n * 3);
+        a.rc = hrcResolve(ctx, &a.post, HRC_RESOLVE_DISPLAY_RGB8, rgb.data());
+        if (a.rc == HRC_OK) a.rc = hrhWritePNG(a.outPng.c_str(), rgb.data(), a.width, a.height, 3, 1);
+        if (a.rc != HRC_OK) { a.error = "screenshot failed"; return; }
+    }
+    if (!a.outHdr.empty()) {
+        std::vector<float> rgb(n * 3);
+        a.rc = hrcResolve(ctx, nullptr, HRC_RESOLVE_HDR_RGB32F, rgb.data());
+        const bool pfm = a.outHdr.size() > 4 && a.outHdr.compare(a.outHdr.size() - 4, 4, ".pfm") == 0;
+        if (a.rc == HRC_OK) a.rc = pfm ? hrhWritePFM(a.outHdr.c_str(), rgb.data(), a.width, a.height, 1) : hrhWriteHDR(a.outHdr.c_str(), rgb.data(), a.width, a.height, 1);
+        if (a.rc != HRC_OK) a.error = "HDR screenshot failed";
+    }
+}
+
+int usage() {
+    std::fprintf(stderr,
+        "usage: heatray_headless <scene.obj|.gltf|.glb> [--size W H] [--passes N] [--depth D] [--meters] [--device K]\n"
+        "       [--env r g b | --env-map file.hdr | --no-env] [--ev EV] [--orbit PHI THETA] [--distance-scale S] [--focal MM] [--fstop F]\n"
+        "       [--out image.png] [--hdr image.hdr|image.pfm] [--tonemap] [--exposure EV]\n");
+    return 2;
+}
+
+} // namespace
+
+int main(int argc, char** argv) {
+    App a;
+    for (int i = 1; i < argc; ++i) {
+        const std::string k = argv[i];
+        auto need = [&](int n) { if (i + n >= argc) { usage(); std::exit(2); } };
+        if (k == "--size") { need(2); a.width = std::atoi(argv[++i]); a.height = std::atoi(argv[++i]); }
+        else if (k == "--passes") { need(1); a.passes = std::atoi(argv[++i]); }
+        else if (k == "--depth") { need(1); a.depth = std::atoi(argv[++i]); }
+        else if (k == "--device") { need(1); a.device = std::atoi(argv[++i]); }
+        else if (k == "--meters") a.meters = true;
+        else if (k == "--no-env") a.envOff = true;
+        else if (k == "--env") { need(3); for (int c = 0; c < 3; ++c) a.envColor[c] = (float)std::atof(argv[++i]); }
+        else if (k == "--env-map") { need(1); a.envMap = argv[++i]; }
+        else if (k == "--ev") { need(1); a.envEV = (float)std::atof(argv[++i]); }
+        else if (k == "--orbit") { need(2); a.phi = (float)std::atof(argv[++i]); a.theta = (float)std::atof(argv[++i]); }
+        else if (k == "--distance-scale") { need(1); a.distanceScale = (float)std::atof(argv[++i]); }
+        else if (k == "--focal") { need(1); a.focalLength = (float)std::atof(argv[++i]); }
+        else if (k == "--fstop") { need(1); a.fstop = (float)std::atof(argv[++i]); }
+        else if (k == "--out") { need(1); a.outPng = argv[++i]; }
+        else if (k == "--hdr") { need(1); a.outHdr = argv[++i]; }
+        else if (k == "--tonemap") a.post.tonemappingEnabled = 1;
+        else if (k == "--exposure") { need(1); a.post.cameraExposure = std::pow(2.0f, (float)std::atof(argv[++i])); }
+        else if (k[0] == '-') return usage();
+        else a.scenePath = k;
+    }
+    if (a.scenePath.empty() || a.width <= 0 || a.height <= 0 || a.passes <= 0) return usage();
+
+    HrhPassGenerator pg = nullptr;
+    if (hrhPassGeneratorCreate(a.device, a.width, a.height, &pg) != HRC_OK) {
+        std::fprintf(stderr, "cannot create the CUDA backend (there is no CPU path): %s\n", pg ? hrhPassGeneratorLastError(pg) : "no device");
+        return 1;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    hrhPassGeneratorRunTask(pg, loadSceneTask, &a);
+    hrhPassGeneratorWaitIdle(pg);
+    if (a.rc != HRC_OK) { std::fprintf(stderr, "scene load failed: %s\n", a.error.c_str()); hrhPassGeneratorDestroy(pg); return 1; }
+    const double loadS = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+
+    HrhRenderOptions o; hrhDefaultRenderOptions(&o);
+    o.enableInteractiveMode = 0; o.enableOfflineMode = 1;                        // no per-pass readback (PassGenerator.cpp:388-396)
+    o.maxRenderPasses = (uint32_t)a.passes; o.maxRayDepth = (uint32_t)a.depth;
+    o.envEnabled = a.envOff ? 0 : 1; o.envExposureCompensation = a.envEV;
+    if (!a.envMap.empty()) { o.envUseSolidColor = 0; o.envTexture = a.envTex; } else std::memcpy(o.envSolidColor, a.envColor, 12);
+    // camera framing, HeatrayRenderer.cpp:302-308 (AABB.h:34-44: radius() is the full diagonal)
+    float centre[3], diag = 0.0f;
+    for (int k = 0; k < 3; ++k) { centre[k] = 0.5f * (a.info.aabbMin[k] + a.info.aabbMax[k]); const float d = a.info.aabbMax[k] - a.info.aabbMin[k]; diag += d * d; }
+    const float distance = std::sqrt(diag) * 3.0f * a.distanceScale;
+    hrhOrbitCameraViewMatrix(distance, a.phi, a.theta, centre, o.viewMatrix);
+    o.aspectRatio = (float)a.width / (float)a.height; o.focusDistance = distance; o.focalLength = a.focalLength;
+    if (a.fstop > 0.0f) { o.fstop = a.fstop; o.apertureRadius = hrhApertureRadius(a.focalLength, a.fstop); }
+
+    const auto t1 = std::chrono::steady_clock::now();
+    for (int p = 0; p < a.passes; ++p) {
+        o.resetInternalState = p == 0;
+        hrhPassGeneratorRenderPass(pg, &o, passComplete, &a);
+    }
+    hrhPassGeneratorWaitIdle(pg);
+    const double renderS = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
+    hrhPassGeneratorRunTask(pg, screenshotTask, &a);
+    hrhPassGeneratorWaitIdle(pg);
+    const char* err = hrhPassGeneratorLastError(pg);
+    const bool ok = a.rc == HRC_OK && a.passesDone.load() == a.passes && (!err || !*err);
+    std::printf("{\"scene\": \"%s\", \"meshes\": %d, \"materials\": %d, \"textures\": %d, \"textures_missing\": %d, \"lights\": [%d, %d, %d], "
+                "\"size\": [%d, %d], \"passes\": %d, \"load_s\": %.3f, \"render_s\": %.3f, \"pass_s_sum\": %.3f, \"out\": \"%s\", \"ok\": %s}\n",
+                a.scenePath.c_str(), a.upload.meshCount, a.upload.materialCount, a.upload.textureCount, a.upload.texturesMissing,
+                a.upload.dirLights, a.upload.pointLights, a.upload.spotLights, a.width, a.height, a.passesDone.load(), loadS, renderS, a.passSeconds,
+                a.outPng.c_str(), ok ? "true" : "false");
+    if (!ok) std::fprintf(stderr, "error: %s %s\n", a.error.c_str(), err ? err : "");
+    hrhPassGeneratorDestroy(pg);
+    return ok ? 0 : 1;
+}

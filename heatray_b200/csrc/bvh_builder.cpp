@@ -7,6 +7,7 @@
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -34,7 +35,11 @@ struct Node2 {
 };
 
 constexpr int kBins = 16;
-constexpr uint32_t kMaxLeaf = 3;           // a child slot encodes at most 3 triangles (unary count in 3 bits)
+constexpr uint32_t kMaxLeafLimit = 3;      // a child slot encodes at most 3 triangles (unary count in 3 bits)
+// Leaf policy: at most g_maxLeaf triangles, made a leaf when n * area <= g_travCost * area + SAH(best split). Defaults measured on B200
+// (profiles/); HRC_TUNE_MAX_LEAF / HRC_TUNE_TRAV_COST override them for experiments.
+uint32_t g_maxLeaf = 3; float g_travCost = 0.5f;
+#define kMaxLeaf g_maxLeaf
 
 struct Builder2 {
     std::vector<Prim>& prims;
@@ -82,7 +87,7 @@ struct Builder2 {
             mid = begin + n / 2;
         } else {
             const float area = bounds.halfArea();
-            if (n <= kMaxLeaf && (float)n * area <= 0.5f * area + bestCost) { node.first = begin; node.count = n; return; }
+            if (n <= kMaxLeaf && (float)n * area <= g_travCost * area + bestCost) { node.first = begin; node.count = n; return; }
             const float cmin = cbounds.lo[bestAxis], cmax = cbounds.hi[bestAxis];
             const float scale = kBins / (cmax - cmin);
             auto it = std::partition(prims.begin() + begin, prims.begin() + end, [&](const Prim& p) {
@@ -130,6 +135,8 @@ void buildWideBVH(const BuildTriangle* tris, size_t count, int threads, WideBVH&
         out.nodes.push_back(root);
         return;
     }
+    if (const char* e = std::getenv("HRC_TUNE_MAX_LEAF")) g_maxLeaf = (uint32_t)std::max(1, std::min((int)kMaxLeafLimit, std::atoi(e)));
+    if (const char* e = std::getenv("HRC_TUNE_TRAV_COST")) g_travCost = (float)std::atof(e);
     if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
     if (threads < 1) threads = 1;
     int spawnDepth = 0; while ((1 << spawnDepth) < threads) ++spawnDepth;

@@ -795,3 +795,109 @@ HRC_API int hrhSceneGetLight(HrhScene s, int32_t i, HrhSceneLight* out) {
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// Upload of an imported scene into a backend context: what Scene::loadFromDisk (Scene.cpp:14-27) triggers in the reference —
+// texture loads (AssimpMeshProvider.cpp:296-357, 433-511 through util::loadTexture), Material::build/modify, Mesh::Mesh
+// (Mesh.cpp:55-155: one primitive per submesh, front face from the transform determinant, PBR + alpha mask = non-occluder),
+// Lighting::clearAllButEnvironment + the imported punctual lights (Scene.cpp:16, ProcessLight).
+// ---------------------------------------------------------------------------------------
+namespace {
+
+float det3(const float* m) {   // upper-left 3x3 of a column-major 4x4
+    return m[0] * (m[5] * m[10] - m[9] * m[6]) - m[4] * (m[1] * m[10] - m[9] * m[2]) + m[8] * (m[1] * m[6] - m[5] * m[2]);
+}
+
+} // namespace
+
+extern "C" HRC_API int hrhSceneUpload(HrhScene s, HrcContext ctx, int32_t clearOldScene, HrcTexture multiscatterLUT, HrhSceneUploadResult* result) {
+    if (!s || !ctx) { g_importErr = "null argument"; return HRC_ERR_INVALID_VALUE; }
+    HrhSceneUploadResult res{}; int rc;
+    auto fail = [&](int code, const char* what) { g_importErr = std::string(what) + ": " + (hrcGetLastError(ctx) ? hrcGetLastError(ctx) : ""); if (result) *result = res; return code; };
+    if (clearOldScene && (rc = hrcClearScene(ctx)) != HRC_OK) return fail(rc, "hrcClearScene");
+    if (multiscatterLUT == HRC_NULL_TEXTURE) {                                    // loadMultiscatterTexture (MultiScatterUtil.cpp:141-150): LINEAR, CLAMP_TO_EDGE
+        std::vector<float> lut(128 * 128);
+        hr::generateMultiscatterLUT(lut.data(), 128, 4096, 0);
+        HrcTextureDesc td{128, 128, HRC_TEX_R32F, HRC_WRAP_CLAMP, HRC_WRAP_CLAMP};
+        if ((rc = hrcCreateTexture2D(ctx, &td, lut.data(), &multiscatterLUT)) != HRC_OK) return fail(rc, "multiscatter LUT");
+    }
+    res.multiscatterLUT = multiscatterLUT;
+
+    std::map<std::pair<std::string, bool>, HrcTexture> cache;
+    auto texture = [&](const std::string& path, bool linear) -> HrcTexture {
+        if (path.empty()) return HRC_NULL_TEXTURE;
+        const auto key = std::make_pair(path, linear);
+        auto it = cache.find(key);
+        if (it != cache.end()) return it->second;
+        HrcTexture handle = HRC_NULL_TEXTURE;
+        HrhLoadedTexture lt;
+        if (hrhLoadTexture(path.c_str(), 1, linear ? 1 : 0, &lt) == HRC_OK) {     // generateMips = true at every call site (:314, :449 ...)
+            HrcTextureDesc td{lt.image.width, lt.image.height, lt.format, lt.wrapS, lt.wrapT};
+            int trc;
+            if (lt.image.isFloat) trc = hrcCreateTexture2D(ctx, &td, lt.image.data, &handle);
+            else {
+                std::vector<uint8_t> rgba((size_t)lt.image.width * lt.image.height * 4);
+                hrhExpandToRGBA8(&lt.image, rgba.data());
+                trc = hrcCreateTexture2D(ctx, &td, rgba.data(), &handle);
+            }
+            hrhFreeImage(&lt.image);
+            if (trc != HRC_OK) handle = HRC_NULL_TEXTURE; else ++res.textureCount;
+        } else ++res.texturesMissing;                                              // the reference logs the error and renders without the map (TextureLoader.cpp:29-33)
+        cache[key] = handle;
+        return handle;
+    };
+
+    std::vector<HrcMaterial> handles;
+    for (const ImpMaterial& m : s->materials) {
+        HrcMaterial h = -1;
+        if (m.type == HRC_MATERIAL_GLASS) {
+            HrhGlassMaterial g{}; std::memcpy(g.baseColor, m.baseColor, 12); g.roughness = m.roughness; g.ior = m.ior; g.density = m.density;
+            g.baseColorTexture = texture(m.tex[kSlotBaseColor], true); g.normalmap = texture(m.tex[kSlotNormal], false);
+            g.metallicRoughnessTexture = texture(m.tex[kSlotMetallicRoughness], false);
+            HrcGlassParams p{}; const uint32_t flags = hr::packGlassMaterial(g, p);
+            rc = hrcCreateMaterial(ctx, HRC_MATERIAL_GLASS, flags, &p, sizeof(p), &h);
+        } else {
+            HrhPbrMaterial b{}; std::memcpy(b.baseColor, m.baseColor, 12); std::memcpy(b.emissiveColor, m.emissive, 12);
+            b.metallic = m.metallic; b.roughness = m.roughness; b.specularF0 = m.specularF0; b.clearCoat = m.clearCoat; b.clearCoatRoughness = m.clearCoatRoughness;
+            b.doubleSided = m.doubleSided; b.alphaMask = m.alphaMask; b.enableVertexColors = m.vertexColors;
+            b.baseColorTexture = texture(m.tex[kSlotBaseColor], true); b.metallicRoughnessTexture = texture(m.tex[kSlotMetallicRoughness], false);
+            b.emissiveTexture = texture(m.tex[kSlotEmissive], true); b.normalmap = texture(m.tex[kSlotNormal], false);
+            b.clearCoatTexture = texture(m.tex[kSlotClearCoat], false); b.clearCoatRoughnessTexture = texture(m.tex[kSlotClearCoatRoughness], false);
+            b.clearCoatNormalmap = texture(m.tex[kSlotClearCoatNormal], false);
+            HrcPbrParams p{}; const uint32_t flags = hr::packPbrMaterial(b, multiscatterLUT, p);
+            rc = hrcCreateMaterial(ctx, HRC_MATERIAL_PBR, flags, &p, sizeof(p), &h);
+        }
+        if (rc != HRC_OK) return fail(rc, "hrcCreateMaterial");
+        handles.push_back(h); ++res.materialCount;
+    }
+    for (const ImpMesh& m : s->meshes) {
+        if (m.idx.empty()) continue;
+        HrcMeshDesc d{};
+        d.positions = m.pos.data(); d.positionStride = 12; d.normals = m.nrm.data(); d.normalStride = 12;
+        if (!m.uv.empty()) { d.texCoords = m.uv.data(); d.texCoordStride = 8; }
+        if (!m.tan.empty()) { d.tangents = m.tan.data(); d.tangentStride = 12; d.bitangents = m.bit.data(); d.bitangentStride = 12; }
+        if (!m.col.empty()) { d.colors = m.col.data(); d.colorStride = 12; }
+        d.vertexCount = (uint32_t)(m.pos.size() / 3); d.indices = m.idx.data(); d.elementCount = (uint32_t)m.idx.size(); d.drawMode = HRC_DRAW_TRIANGLES;
+        std::memcpy(d.worldFromEntity, m.xf, 64);
+        d.frontFaceCW = det3(m.xf) < 0.0f;                                                                     // Mesh.cpp:86-91
+        const ImpMaterial& mat = s->materials[m.material];
+        d.isOccluder = !(mat.type == HRC_MATERIAL_PBR && mat.alphaMask);                                       // Mesh.cpp:95-100
+        d.material = handles[m.material];
+        HrcMesh mh;
+        if ((rc = hrcCreateMesh(ctx, &d, &mh)) != HRC_OK) return fail(rc, "hrcCreateMesh");
+        ++res.meshCount;
+    }
+    if ((rc = hrcCommitScene(ctx)) != HRC_OK) return fail(rc, "hrcCommitScene");
+    std::vector<HrcDirLight> dl; std::vector<HrcPointLight> pl; std::vector<HrcSpotLight> sl;
+    for (const ImpLight& l : s->lights) {                                                                      // at most 5 per type (ShaderLightingDefines.h:18-20)
+        if (l.type == 0 && dl.size() < HRC_MAX_LIGHTS_PER_TYPE) { HrcDirLight o; hrhPackDirectionalLight(l.color, l.intensity, l.theta, l.phi, &o); dl.push_back(o); }
+        else if (l.type == 1 && pl.size() < HRC_MAX_LIGHTS_PER_TYPE) { HrcPointLight o; hrhPackPointLight(l.color, l.intensity, l.position, &o); pl.push_back(o); }
+        else if (l.type == 2 && sl.size() < HRC_MAX_LIGHTS_PER_TYPE) { HrcSpotLight o; hrhPackSpotLight(l.color, l.intensity, l.position, l.theta, l.phi, l.inner, l.outer, &o); sl.push_back(o); }
+    }
+    if ((rc = hrcSetDirectionalLights(ctx, (int32_t)dl.size(), dl.data())) != HRC_OK) return fail(rc, "hrcSetDirectionalLights");
+    if ((rc = hrcSetPointLights(ctx, (int32_t)pl.size(), pl.data())) != HRC_OK) return fail(rc, "hrcSetPointLights");
+    if ((rc = hrcSetSpotLights(ctx, (int32_t)sl.size(), sl.data())) != HRC_OK) return fail(rc, "hrcSetSpotLights");
+    res.dirLights = (int32_t)dl.size(); res.pointLights = (int32_t)pl.size(); res.spotLights = (int32_t)sl.size();
+    if (result) *result = res;
+    return HRC_OK;
+}

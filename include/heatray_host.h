@@ -178,6 +178,11 @@ HRC_API int  hrhSceneGetInfo(HrhScene scene, HrhSceneInfo* info);
 HRC_API int  hrhSceneGetMaterial(HrhScene scene, int32_t index, HrhSceneMaterial* out);
 HRC_API int  hrhSceneGetMesh(HrhScene scene, int32_t index, HrhSceneMesh* out);
 HRC_API int  hrhSceneGetLight(HrhScene scene, int32_t index, HrhSceneLight* out);
+/* Scene::loadFromDisk's second half (Scene.cpp:14-27, Mesh.cpp:55-155): loads the textures, builds the materials, creates one backend mesh
+ * per submesh, commits, replaces the punctual lights. multiscatterLUT: an existing LUT texture or HRC_NULL_TEXTURE to generate one. */
+typedef struct HrhSceneUploadResult { int32_t meshCount, materialCount, textureCount, texturesMissing; HrcTexture multiscatterLUT;
+                                      int32_t dirLights, pointLights, spotLights; } HrhSceneUploadResult;
+HRC_API int  hrhSceneUpload(HrhScene scene, HrcContext ctx, int32_t clearOldScene, HrcTexture multiscatterLUT, HrhSceneUploadResult* result);
 /* theta/phi of an imported directional or spot light from its node transform (ProcessLight :564-586, incl. its vec4(axis, 1) quirk). */
 HRC_API void hrhLightAnglesFromTransform(const float worldFromLight[16], float* theta, float* phi);
 HRC_API const char* hrhImportLastError(void);

@@ -276,3 +276,67 @@ def test_gpu_renders_imported_gltf_like_the_oracle(oracle_backend, gpu_backend, 
     assert np.array_equal(po[..., 3], pg[..., 3])
     assert np.isclose(pg[..., :3], po[..., :3], rtol=1e-3, atol=1e-4).all(-1).mean() >= 0.99
     assert po[..., :3].std() > 1e-3
+
+
+# ---- heatray_headless: load -> passes -> resolve -> screenshot as one native program ---------------------------------------
+def _headless():
+    from heatray_b200.build import APP, build_apps
+    if not APP.exists():
+        build_apps()
+    return APP
+
+
+def test_headless_program_fails_loudly_without_a_gpu(lib, tmp_path):
+    import subprocess
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    spec = scenes.cornell_box()
+    obj = scenes.write_obj(spec, tmp_path / "cornell.obj")
+    res = subprocess.run([str(_headless()), str(obj), "--size", "32", "32", "--passes", "1", "--out", str(tmp_path / "o.png")], capture_output=True, text=True)
+    assert res.returncode == 1 and "no CPU path" in res.stderr and not (tmp_path / "o.png").exists()
+    assert subprocess.run([str(_headless())], capture_output=True).returncode == 2
+
+
+@pytest.mark.gpu
+def test_headless_program_renders_assets_to_png_and_hdr(lib, gold_texture_dir, tmp_path):
+    """OBJ with an MTL texture and a glTF with lights through heatray_headless; the PNG is the display pipeline's output of the HDR means."""
+    import subprocess
+    spec = scenes.cornell_box()
+    obj = scenes.write_obj(spec, tmp_path / "cornell.obj")
+    with open(tmp_path / "cornell.mtl", "a") as f:
+        f.write("\n")
+    mtl = (tmp_path / "cornell.mtl").read_text().replace("newmtl m0\n", "newmtl m0\nmap_Kd albedo.png\n", 1)
+    (tmp_path / "cornell.mtl").write_text(mtl)
+    (tmp_path / "albedo.png").write_bytes(gold_texture_dir["file/png_mixed_RGB"].tobytes())
+    out, hdr = tmp_path / "c.png", tmp_path / "c.pfm"
+    res = subprocess.run([str(_headless()), str(obj), "--size", "96", "80", "--passes", "8", "--depth", "4", "--distance-scale", "0.45", "--env", "0.8", "0.8", "0.8",
+                          "--out", str(out), "--hdr", str(hdr), "--tonemap"], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    info = json.loads(res.stdout.strip().splitlines()[-1])
+    assert info["ok"] and info["passes"] == 8 and info["meshes"] == len(spec.meshes) and info["textures"] == 1 and info["textures_missing"] == 0
+    png = capi.load_image(out)
+    assert png.shape == (80, 96, 3) and png.std() > 10 and png.max() > 120
+    raw = hdr.read_bytes()
+    head = b"PF\n96 80\n-1.0\n"
+    mean = np.frombuffer(raw[len(head):], "<f4").reshape(80, 96, 3)            # bottom-up rows, rgb / alpha
+    assert np.isfinite(mean).all() and mean.max() > 0.2
+    # the PNG must be the colour pipeline applied to those means: re-run the pipeline through the C-ABI on a buffer holding them
+    b = capi.Backend(lib, "hrc", device=0)
+    b.resize(96, 80)
+    b.add_pixels(np.concatenate([mean, np.ones((80, 96, 1), np.float32)], -1))
+    ldr = b.resolve(capi.PostProcess(tonemappingEnabled=1), capi.RESOLVE_DISPLAY_RGB8)
+    b.close()
+    assert np.abs(np.flipud(ldr).astype(int) - png.astype(int)).max() <= 1
+    # glTF with punctual lights
+    res = subprocess.run([str(_headless()), str(_gltf(tmp_path, True)), "--size", "64", "48", "--passes", "4", "--out", str(tmp_path / "g.png")], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    info = json.loads(res.stdout.strip().splitlines()[-1])
+    assert info["ok"] and info["lights"] == [0, 1, 1] and info["meshes"] == 5 and info["textures_missing"] >= 1     # the glTF names a texture file that does not exist
+    assert capi.load_image(tmp_path / "g.png").std() > 5
+
+
+@pytest.fixture()
+def gold_texture_dir():
+    from pathlib import Path
+    return np.load(Path(__file__).parent / "golden" / "images_ref.npz")
