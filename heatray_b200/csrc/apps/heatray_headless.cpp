@@ -52,7 +52,7 @@ void loadSceneTask(void* user, HrcContext ctx) {                                
 
 void passComplete(void* user, int32_t, const float*, int32_t, int32_t, float passTime, uint64_t) {
     App& a = *static_cast<App*>(user);
-    a.passSeconds += passTime; a.passesDone++;
+    a.passSeconds = passTime; a.passesDone++;                                    // passTime counts from the start of the job
 }
 
 void screenshotTask(void* user, HrcContext ctx) {                                // saveScreenshot, HeatrayRenderer.cpp:1619-1662
@@ -135,10 +135,8 @@ int main(int argc, char** argv) {
     if (a.fstop > 0.0f) { o.fstop = a.fstop; o.apertureRadius = hrhApertureRadius(a.focalLength, a.fstop); }
 
     const auto t1 = std::chrono::steady_clock::now();
-    for (int p = 0; p < a.passes; ++p) {
-        o.resetInternalState = p == 0;
-        hrhPassGeneratorRenderPass(pg, &o, passComplete, &a);
-    }
+    o.resetInternalState = 1;
+    hrhPassGeneratorRenderPass(pg, &o, passComplete, &a);                       // offline mode: ONE job runs every pass up to maxRenderPasses (PassGenerator.cpp:366-399)
     hrhPassGeneratorWaitIdle(pg);
     const double renderS = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
     hrhPassGeneratorRunTask(pg, screenshotTask, &a);
