@@ -256,32 +256,39 @@ __device__ __forceinline__ void shadeMiss(const DScene& sc, const DFrame& fr, fl
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t byteOf(uint32_t x, int i) { return (x >> (i * 8)) & 0xffu; }
 
-// Möller–Trumbore with a FIXED operation order and no FMA contraction: the CPU oracle performs the very
-// same IEEE operations, so hit/miss decisions and (t,u,v) agree bit for bit (policy A-9).
-__device__ __forceinline__ float dotRn(float ax, float ay, float az, float bx, float by, float bz) {
-    return __fadd_rn(__fadd_rn(__fmul_rn(ax, bx), __fmul_rn(ay, by)), __fmul_rn(az, bz));
+// Möller–Trumbore as ONE fixed sequence of IEEE operations that the CPU oracle repeats (std::fmaf where an FMA stands here), so
+// hit/miss decisions and (t,u,v) agree bit for bit (policy A-9):
+//   cross(a,b).x = fma(a.y, b.z, -(a.z*b.y));  dot(a,b) = fma(a.z, b.z, fma(a.y, b.y, a.x*b.x));
+//   the barycentric tests run on the undivided numerators against |det| (sign of det folded in by XOR on the sign bit) and the one
+//   division 1/|det| is only reached by candidates that passed them — most leaf triangles are rejected before it.
+__device__ __forceinline__ float dotFma(float ax, float ay, float az, float bx, float by, float bz) {
+    return __fmaf_rn(az, bz, __fmaf_rn(ay, by, __fmul_rn(ax, bx)));
 }
 __device__ __forceinline__ bool triangleTest(float4 a, float4 b, float4 c, float3 o, float3 d, float tmin, float tmax,
                                              float& t, float& u, float& v, bool& back) {
     // pv = cross(d, e2)
-    float pvx = __fsub_rn(__fmul_rn(d.y, c.z), __fmul_rn(d.z, c.y));
-    float pvy = __fsub_rn(__fmul_rn(d.z, c.x), __fmul_rn(d.x, c.z));
-    float pvz = __fsub_rn(__fmul_rn(d.x, c.y), __fmul_rn(d.y, c.x));
-    float det = dotRn(b.x, b.y, b.z, pvx, pvy, pvz);
+    const float pvx = __fmaf_rn(d.y, c.z, -__fmul_rn(d.z, c.y));
+    const float pvy = __fmaf_rn(d.z, c.x, -__fmul_rn(d.x, c.z));
+    const float pvz = __fmaf_rn(d.x, c.y, -__fmul_rn(d.y, c.x));
+    const float det = dotFma(b.x, b.y, b.z, pvx, pvy, pvz);
     if (det == 0.0f) return false;
-    float inv = __fdiv_rn(1.0f, det);
-    float tvx = __fsub_rn(o.x, a.x), tvy = __fsub_rn(o.y, a.y), tvz = __fsub_rn(o.z, a.z);
-    u = __fmul_rn(dotRn(tvx, tvy, tvz, pvx, pvy, pvz), inv);
-    if (!(u >= 0.0f && u <= 1.0f)) return false;
+    const uint32_t sgn = __float_as_uint(det) & 0x80000000u;
+    const float adet = fabsf(det);
+    const float tvx = __fsub_rn(o.x, a.x), tvy = __fsub_rn(o.y, a.y), tvz = __fsub_rn(o.z, a.z);
+    const float U = __uint_as_float(__float_as_uint(dotFma(tvx, tvy, tvz, pvx, pvy, pvz)) ^ sgn);
+    if (!(U >= 0.0f && U <= adet)) return false;
     // qv = cross(tv, e1)
-    float qvx = __fsub_rn(__fmul_rn(tvy, b.z), __fmul_rn(tvz, b.y));
-    float qvy = __fsub_rn(__fmul_rn(tvz, b.x), __fmul_rn(tvx, b.z));
-    float qvz = __fsub_rn(__fmul_rn(tvx, b.y), __fmul_rn(tvy, b.x));
-    v = __fmul_rn(dotRn(d.x, d.y, d.z, qvx, qvy, qvz), inv);
-    if (!(v >= 0.0f && __fadd_rn(u, v) <= 1.0f)) return false;
-    t = __fmul_rn(dotRn(c.x, c.y, c.z, qvx, qvy, qvz), inv);
+    const float qvx = __fmaf_rn(tvy, b.z, -__fmul_rn(tvz, b.y));
+    const float qvy = __fmaf_rn(tvz, b.x, -__fmul_rn(tvx, b.z));
+    const float qvz = __fmaf_rn(tvx, b.y, -__fmul_rn(tvy, b.x));
+    const float V = __uint_as_float(__float_as_uint(dotFma(d.x, d.y, d.z, qvx, qvy, qvz)) ^ sgn);
+    if (!(V >= 0.0f && __fadd_rn(U, V) <= adet)) return false;
+    const float T = __uint_as_float(__float_as_uint(dotFma(c.x, c.y, c.z, qvx, qvy, qvz)) ^ sgn);
+    const float inv = __fdiv_rn(1.0f, adet);
+    t = __fmul_rn(T, inv);
     if (!(t > tmin && t < tmax)) return false;
-    back = det < 0.0f;
+    u = __fmul_rn(U, inv); v = __fmul_rn(V, inv);
+    back = sgn != 0u;
     return true;
 }
 
