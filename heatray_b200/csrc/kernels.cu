@@ -539,8 +539,11 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_co
 // gain), and "one node step or one triangle per trip".
 constexpr uint32_t kFull = 0xffffffffu;
 
+#ifndef HR_TRACE_MIN_BLOCKS
+#define HR_TRACE_MIN_BLOCKS 8
+#endif
 template <bool ANY, bool STATS, bool MASKED>
-__global__ void __launch_bounds__(128, 8) k_trace(const DScene sc, const __grid_constant__ DFrame fr, const PassBuffers pb, int iter, int kRefillIdle) {
+__global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene sc, const __grid_constant__ DFrame fr, const PassBuffers pb, int iter, int kRefillIdle) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t below = (1u << lane) - 1u;
     IterCtrl* ctrl = pb.ctrl + iter;
