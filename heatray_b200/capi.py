@@ -189,6 +189,35 @@ class RenderOptions(C.Structure):       # HrhRenderOptions ↔ PassGenerator::Re
                 ("debugPassRendering", i32), ("debugPassIndex", i32)]
 
 
+SESSION_STRING_SIZE = 512
+
+
+class HrhSession(C.Structure):          # one field per HEATRAY_SESSION_VARIABLES entry, in table order (Session.h:21-78)
+    _fields_ = [("interactiveMode", i32), ("maxRenderPasses", u32), ("maxChannelValue", f32), ("scene", C.c_char * SESSION_STRING_SIZE),
+                ("maxRayDepth", u32), ("sampleMode", u32), ("bokehShape", u32),
+                ("environmentMap", C.c_char * SESSION_STRING_SIZE), ("environmentBuiltIn", i32),
+                ("environmentExposureCompensation", f32), ("environmentThetaRotation", f32), ("environmentSolidColor", f32 * 3),
+                ("cameraAspectRatio", f32), ("cameraFocusDistance", f32), ("cameraFocalLength", f32), ("cameraApertureRadius", f32), ("cameraFStop", f32),
+                ("orbitDistance", f32), ("orbitPhi", f32), ("orbitTheta", f32), ("orbitTarget", f32 * 3), ("orbitMaxDistance", f32),
+                ("units", u32), ("aabbMin", f32 * 3), ("aabbMax", f32 * 3), ("distanceScale", f32),
+                ("rotationYaw", f32), ("rotationPitch", f32), ("rotationRoll", f32), ("scale", f32),
+                ("tonemapEnable", i32), ("exposure", f32), ("brightness", f32), ("contrast", f32), ("hue", f32), ("saturation", f32), ("vibrance", f32),
+                ("red", f32), ("green", f32), ("blue", f32), ("vignetteIntensity", f32), ("vignetteFalloff", f32)]
+
+    def flat(self):
+        """The 50 variables in table order: numbers as float, the two strings as str."""
+        out = []
+        for name, t in self._fields_:
+            v = getattr(self, name)
+            if isinstance(v, bytes):
+                out.append(v.decode())
+            elif hasattr(v, "__len__"):
+                out.extend(float(x) for x in v)
+            else:
+                out.append(float(v))
+        return out
+
+
 PASS_COMPLETE_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, i32, fp, i32, i32, f32, u64)
 CONTEXT_TASK = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p)
 
@@ -268,6 +297,18 @@ def _declare_host(lib):
     lib.hrhSceneGetLight.argtypes = [C.c_void_p, i32, C.POINTER(HrhSceneLight)]
     lib.hrhImportLastError.restype = C.c_char_p
     lib.hrhLightAnglesFromTransform.argtypes = [fp, fp, fp]
+    lib.hrhSceneTransformMatrix.argtypes = [f32, f32, f32, f32, fp]
+    lib.hrhSceneTransformMatrix.restype = None
+    lib.hrhSceneApplyTransform.argtypes = [C.c_void_p, fp]
+    lib.hrhSceneApplyTransform.restype = None
+    lib.hrhAABBCamera.argtypes = [fp, fp, fp, fp, fp]
+    lib.hrhSessionDefaults.argtypes = [C.POINTER(HrhSession)]
+    lib.hrhSessionDefaults.restype = None
+    lib.hrhSessionRead.argtypes = [C.c_char_p, C.POINTER(HrhSession), C.POINTER(i32)]
+    lib.hrhSessionWrite.argtypes = [C.c_char_p, C.POINTER(HrhSession)]
+    lib.hrhSessionApply.argtypes = [C.POINTER(HrhSession), C.POINTER(RenderOptions), C.POINTER(PostProcess)]
+    lib.hrhSessionApply.restype = None
+    lib.hrhSessionLastError.restype = C.c_char_p
     lib.hrhPlaneMesh.argtypes = [f32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.hrhSphereMesh.argtypes = [i32, i32, f32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(u32), C.POINTER(u32)]
 
@@ -529,6 +570,37 @@ def load_texture(path, generate_mips=True, convert_to_linear=False):
     lib.hrhExpandToRGBA8(C.byref(lt.image), _ptr(out))
     lib.hrhFreeImage(C.byref(lt.image))
     return out, fmt, ws, wt
+
+
+def session_defaults() -> HrhSession:
+    s = HrhSession()
+    load_library().hrhSessionDefaults(C.byref(s))
+    return s
+
+
+def read_session(path, into: HrhSession = None):
+    """Session::parseSessionFile (Session.cpp:88-150): returns (session, number of variables the file did not hold)."""
+    lib = load_library()
+    s = into if into is not None else session_defaults()
+    missing = i32()
+    rc = lib.hrhSessionRead(str(path).encode(), C.byref(s), C.byref(missing))
+    if rc != HRC_OK:
+        raise HrcError(rc, (lib.hrhSessionLastError() or b"").decode())
+    return s, missing.value
+
+
+def write_session(path, session: HrhSession):
+    lib = load_library()
+    rc = lib.hrhSessionWrite(str(path).encode(), C.byref(session))
+    if rc != HRC_OK:
+        raise HrcError(rc, (lib.hrhSessionLastError() or b"").decode())
+
+
+def apply_session(session: HrhSession):
+    """HeatrayRenderer::readSessionFile's mapping (HeatrayRenderer.cpp:503-600): returns (RenderOptions, PostProcess)."""
+    o, p = RenderOptions(), PostProcess()
+    load_library().hrhSessionApply(C.byref(session), C.byref(o), C.byref(p))
+    return o, p
 
 
 def write_png(path, pixels: np.ndarray, rows_bottom_up=True):

@@ -19,7 +19,8 @@
 namespace {
 
 struct App {
-    std::string scenePath, outPng = "heatray.png", outHdr, envMap;
+    std::string scenePath, outPng = "heatray.png", outHdr, envMap, sessionIn, sessionOut;
+    bool haveSession = false; HrhSession session{};                               // --session: HeatrayRenderer::readSessionFile (HeatrayRenderer.cpp:581-688)
     int width = 800, height = 800, passes = 32, depth = 10, device = 0;          // reference defaults: 800x800 render area (main.cpp:42-43), 32 passes, depth 10
     bool meters = false, envOff = false; float envColor[3] = {0.5f, 0.5f, 0.5f}, envEV = 0.0f;
     float phi = 0.0f, theta = 0.0f, distanceScale = 1.0f, fstop = 0.0f, focalLength = 50.0f;
@@ -35,6 +36,10 @@ void loadSceneTask(void* user, HrcContext ctx) {                                
     a.rc = hrhImportScene(a.scenePath.c_str(), a.meters ? 1 : 0, &scene);
     if (a.rc != HRC_OK) { a.error = hrhImportLastError(); return; }
     hrhSceneGetInfo(scene, &a.info);
+    if (a.haveSession) {                                                         // readSessionFile :671-683: the session's yaw/pitch/roll/scale goes onto every mesh
+        float xf[16]; hrhSceneTransformMatrix(a.session.rotationYaw, a.session.rotationPitch, a.session.rotationRoll, a.session.scale, xf);
+        hrhSceneApplyTransform(scene, xf);
+    }
     a.rc = hrhSceneUpload(scene, ctx, 1, HRC_NULL_TEXTURE, &a.upload);
     if (a.rc != HRC_OK) a.error = hrhImportLastError();
     hrhFreeScene(scene);
@@ -77,7 +82,9 @@ int usage() {
     std::fprintf(stderr,
         "usage: heatray_headless <scene.obj|.gltf|.glb> [--size W H] [--passes N] [--depth D] [--meters] [--device K]\n"
         "       [--env r g b | --env-map file.hdr | --no-env] [--ev EV] [--orbit PHI THETA] [--distance-scale S] [--focal MM] [--fstop F]\n"
-        "       [--out image.png] [--hdr image.hdr|image.pfm] [--tonemap] [--exposure EV]\n");
+        "       [--out image.png] [--hdr image.hdr|image.pfm] [--tonemap] [--exposure EV]\n"
+        "       [--session in.xml] [--save-session out.xml]     (a session supplies the scene, options, camera and post-processing;\n"
+        "                                                        flags given after --session override it)\n");
     return 2;
 }
 
@@ -103,6 +110,21 @@ int main(int argc, char** argv) {
         else if (k == "--fstop") { need(1); a.fstop = (float)std::atof(argv[++i]); }
         else if (k == "--out") { need(1); a.outPng = argv[++i]; }
         else if (k == "--hdr") { need(1); a.outHdr = argv[++i]; }
+        else if (k == "--save-session") { need(1); a.sessionOut = argv[++i]; }
+        else if (k == "--session") {
+            need(1); a.sessionIn = argv[++i];
+            hrhSessionDefaults(&a.session); int32_t missing = 0;
+            if (hrhSessionRead(a.sessionIn.c_str(), &a.session, &missing) != HRC_OK) { std::fprintf(stderr, "session: %s\n", hrhSessionLastError()); return 1; }
+            a.haveSession = true;
+            HrhRenderOptions so; hrhDefaultRenderOptions(&so);
+            hrhSessionApply(&a.session, &so, &a.post);
+            a.passes = (int)so.maxRenderPasses; a.depth = (int)so.maxRayDepth; a.meters = a.session.units == 1;        // SceneUnits::kCentimeters (HeatrayRenderer.h:302-305)
+            a.envOff = !so.envEnabled; a.envEV = so.envExposureCompensation; std::memcpy(a.envColor, so.envSolidColor, 12);
+            a.focalLength = so.focalLength; a.fstop = so.fstop; a.phi = a.session.orbitPhi; a.theta = a.session.orbitTheta;
+            if (a.scenePath.empty()) a.scenePath = a.session.scene;
+            if (so.envEnabled && !so.envUseSolidColor)                           // EnvironmentLight::changeImageSource (EnvironmentLight.cpp:30-46)
+                a.envMap = a.session.environmentBuiltIn ? std::string("Resources/Environments/") + a.session.environmentMap : std::string(a.session.environmentMap);
+        }
         else if (k == "--tonemap") a.post.tonemappingEnabled = 1;
         else if (k == "--exposure") { need(1); a.post.cameraExposure = std::pow(2.0f, (float)std::atof(argv[++i])); }
         else if (k[0] == '-') return usage();
@@ -122,17 +144,45 @@ int main(int argc, char** argv) {
     const double loadS = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 
     HrhRenderOptions o; hrhDefaultRenderOptions(&o);
-    o.enableInteractiveMode = 0; o.enableOfflineMode = 1;                        // no per-pass readback (PassGenerator.cpp:388-396)
+    if (a.haveSession) hrhSessionApply(&a.session, &o, nullptr);                // sample mode, bokeh shape, channel clamp, env rotation, aperture ... (:588-622)
+    o.enableInteractiveMode = 0; o.enableOfflineMode = 1;                        // no per-pass readback (PassGenerator.cpp:388-396); a headless run is always offline
     o.maxRenderPasses = (uint32_t)a.passes; o.maxRayDepth = (uint32_t)a.depth;
     o.envEnabled = a.envOff ? 0 : 1; o.envExposureCompensation = a.envEV;
-    if (!a.envMap.empty()) { o.envUseSolidColor = 0; o.envTexture = a.envTex; } else std::memcpy(o.envSolidColor, a.envColor, 12);
-    // camera framing, HeatrayRenderer.cpp:302-308 (AABB.h:34-44: radius() is the full diagonal)
-    float centre[3], diag = 0.0f;
-    for (int k = 0; k < 3; ++k) { centre[k] = 0.5f * (a.info.aabbMin[k] + a.info.aabbMax[k]); const float d = a.info.aabbMax[k] - a.info.aabbMin[k]; diag += d * d; }
-    const float distance = std::sqrt(diag) * 3.0f * a.distanceScale;
+    if (!a.envMap.empty()) { o.envUseSolidColor = 0; o.envTexture = a.envTex; } else { o.envUseSolidColor = 1; std::memcpy(o.envSolidColor, a.envColor, 12); }
+    // camera framing, HeatrayRenderer.cpp:300-310 (AABB.h:34-44: radius() is the full diagonal). With a session the stored AABB under the
+    // session's scene transform drives it when valid (:671-683); otherwise the stored orbit camera is used as is.
+    float centre[3], radius = 0.0f, distance = 0.0f, xf[16];
+    if (a.haveSession) {
+        hrhSceneTransformMatrix(a.session.rotationYaw, a.session.rotationPitch, a.session.rotationRoll, a.session.scale, xf);
+        if (hrhAABBCamera(a.session.aabbMin, a.session.aabbMax, xf, centre, &radius)) distance = radius * 3.0f;
+        else { std::memcpy(centre, a.session.orbitTarget, 12); distance = a.session.orbitDistance; o.focusDistance = a.session.cameraFocusDistance; }
+    } else {
+        hrhAABBCamera(a.info.aabbMin, a.info.aabbMax, nullptr, centre, &radius);
+        distance = radius * 3.0f;
+    }
+    distance *= a.distanceScale;
     hrhOrbitCameraViewMatrix(distance, a.phi, a.theta, centre, o.viewMatrix);
-    o.aspectRatio = (float)a.width / (float)a.height; o.focusDistance = distance; o.focalLength = a.focalLength;
+    o.aspectRatio = (float)a.width / (float)a.height; o.focalLength = a.focalLength;
+    if (radius > 0.0f) o.focusDistance = distance;                               // auto-focus on the scene centre (:308)
     if (a.fstop > 0.0f) { o.fstop = a.fstop; o.apertureRadius = hrhApertureRadius(a.focalLength, a.fstop); }
+    if (!a.sessionOut.empty()) {                                                 // writeSessionFile, HeatrayRenderer.cpp:503-579
+        HrhSession w; if (a.haveSession) w = a.session; else hrhSessionDefaults(&w);
+        w.interactiveMode = 0; w.maxRenderPasses = o.maxRenderPasses; w.maxRayDepth = o.maxRayDepth; w.maxChannelValue = o.maxChannelValue;
+        std::snprintf(w.scene, sizeof(w.scene), "%s", a.scenePath.c_str());
+        w.sampleMode = (uint32_t)o.sampleMode; w.bokehShape = (uint32_t)o.bokehShape;
+        if (!a.envMap.empty()) { if (!a.haveSession || a.envMap != std::string("Resources/Environments/") + a.session.environmentMap) { std::snprintf(w.environmentMap, sizeof(w.environmentMap), "%s", a.envMap.c_str()); w.environmentBuiltIn = 0; } }
+        else std::snprintf(w.environmentMap, sizeof(w.environmentMap), "%s", a.envOff ? "<none>" : "solid color");
+        w.environmentExposureCompensation = o.envExposureCompensation; w.environmentThetaRotation = o.envThetaRotation; std::memcpy(w.environmentSolidColor, o.envSolidColor, 12);
+        w.cameraAspectRatio = o.aspectRatio; w.cameraFocusDistance = o.focusDistance; w.cameraFocalLength = o.focalLength; w.cameraApertureRadius = o.apertureRadius; w.cameraFStop = o.fstop;
+        w.orbitDistance = distance; w.orbitPhi = a.phi; w.orbitTheta = a.theta; std::memcpy(w.orbitTarget, centre, 12); w.orbitMaxDistance = radius * 10.0f;
+        w.units = a.meters ? 1u : 0u;
+        if (!a.haveSession) { std::memcpy(w.aabbMin, a.info.aabbMin, 12); std::memcpy(w.aabbMax, a.info.aabbMax, 12); }
+        w.distanceScale = radius;
+        w.tonemapEnable = a.post.tonemappingEnabled; w.exposure = std::log2(a.post.cameraExposure); w.brightness = a.post.brightness; w.contrast = a.post.contrast;
+        w.hue = a.post.hue; w.saturation = a.post.saturation; w.vibrance = a.post.vibrance; w.red = a.post.red; w.green = a.post.green; w.blue = a.post.blue;
+        w.vignetteIntensity = a.post.vignetteIntensity; w.vignetteFalloff = a.post.vignetteFalloff;
+        if (hrhSessionWrite(a.sessionOut.c_str(), &w) != HRC_OK) std::fprintf(stderr, "warning: %s\n", hrhSessionLastError());
+    }
 
     const auto t1 = std::chrono::steady_clock::now();
     o.resetInternalState = 1;

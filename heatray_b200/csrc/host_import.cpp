@@ -143,6 +143,7 @@ struct HrhScene_t {
     std::vector<ImpMaterial> materials; std::vector<ImpMesh> meshes; std::vector<ImpLight> lights;
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0}; bool aabbValid = false;
     std::string dir;
+    float sceneXf[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};      // Scene::applyTransform (Scene.cpp:38-49)
 };
 
 namespace {
@@ -730,6 +731,37 @@ extern "C" {
 HRC_API const char* hrhImportLastError(void) { return g_importErr.c_str(); }
 HRC_API void hrhLightAnglesFromTransform(const float worldFromLight[16], float* theta, float* phi) { lightAngles(worldFromLight, *theta, *phi); }
 
+// ↔ HeatrayRenderer::SceneTransform::transform() (HeatrayRenderer.h:343-346): scale(scale) * yawPitchRoll(yaw, pitch, roll), column-major.
+HRC_API void hrhSceneTransformMatrix(float yaw, float pitch, float roll, float scale, float out16[16]) {
+    const float ch = std::cos(yaw), sh = std::sin(yaw), cp = std::cos(pitch), sp = std::sin(pitch), cb = std::cos(roll), sb = std::sin(roll);
+    const float R[16] = {ch * cb + sh * sp * sb, sb * cp, -sh * cb + ch * sp * sb, 0.0f,
+                         -ch * sb + sh * sp * cb, cb * cp, sb * sh + ch * sp * cb, 0.0f,
+                         sh * cp, -sp, ch * cp, 0.0f,
+                         0.0f, 0.0f, 0.0f, 1.0f};
+    float S[16]; matIdentity(S); S[0] = S[5] = S[10] = scale;
+    matMul(S, R, out16);
+}
+// ↔ util::AABB::center() / radius() / valid() (AABB.h:34-52). Quirks kept: only the two extreme corners go through the transform, radius() is the
+// full diagonal, and valid() is true when ANY axis has min < max.
+HRC_API int hrhAABBCamera(const float aabbMin[3], const float aabbMax[3], const float transform16[16], float center[3], float* radius) {
+    float I[16]; matIdentity(I);
+    const float* m = transform16 ? transform16 : I;
+    float a[3], b[3];
+    for (int r = 0; r < 3; ++r) {          // glm's mat4 * vec4: (m0 x + m1 y) + (m2 z + m3 w)
+        a[r] = (m[r] * aabbMin[0] + m[4 + r] * aabbMin[1]) + (m[8 + r] * aabbMin[2] + m[12 + r] * 1.0f);
+        b[r] = (m[r] * aabbMax[0] + m[4 + r] * aabbMax[1]) + (m[8 + r] * aabbMax[2] + m[12 + r] * 1.0f);
+    }
+    float d[3];
+    for (int r = 0; r < 3; ++r) { if (center) center[r] = (a[r] + b[r]) * 0.5f; d[r] = b[r] - a[r]; }
+    if (radius) *radius = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    return (aabbMin[0] < aabbMax[0] || aabbMin[1] < aabbMax[1] || aabbMin[2] < aabbMax[2]) ? 1 : 0;
+}
+// ↔ Scene::applyTransform (Scene.cpp:38-49): every mesh is uploaded with transform * its own worldFromEntity; winding stays the mesh's own (Mesh.cpp:86-91).
+HRC_API void hrhSceneApplyTransform(HrhScene scene, const float transform16[16]) {
+    if (!scene) return;
+    if (transform16) std::memcpy(scene->sceneXf, transform16, 64); else matIdentity(scene->sceneXf);
+}
+
 // ↔ AssimpMeshProvider::AssimpMeshProvider / LoadScene (AssimpMeshProvider.cpp:65-75, 662-723); Scene::loadFromDisk (Scene.cpp:14-27)
 HRC_API int hrhImportScene(const char* path, int32_t convertToMeters, HrhScene* out) {
     if (!path || !out) { g_importErr = "null argument"; return HRC_ERR_INVALID_VALUE; }
@@ -878,7 +910,7 @@ extern "C" HRC_API int hrhSceneUpload(HrhScene s, HrcContext ctx, int32_t clearO
         if (!m.tan.empty()) { d.tangents = m.tan.data(); d.tangentStride = 12; d.bitangents = m.bit.data(); d.bitangentStride = 12; }
         if (!m.col.empty()) { d.colors = m.col.data(); d.colorStride = 12; }
         d.vertexCount = (uint32_t)(m.pos.size() / 3); d.indices = m.idx.data(); d.elementCount = (uint32_t)m.idx.size(); d.drawMode = HRC_DRAW_TRIANGLES;
-        std::memcpy(d.worldFromEntity, m.xf, 64);
+        matMul(s->sceneXf, m.xf, d.worldFromEntity);                                                           // Scene.cpp:44: transform * submesh.transform
         d.frontFaceCW = det3(m.xf) < 0.0f;                                                                     // Mesh.cpp:86-91
         const ImpMaterial& mat = s->materials[m.material];
         d.isOccluder = !(mat.type == HRC_MATERIAL_PBR && mat.alphaMask);                                       // Mesh.cpp:95-100

@@ -142,6 +142,24 @@ HRC_API int  hrhWriteHDR(const char* path, const float* rgb, int32_t width, int3
 HRC_API int  hrhWritePFM(const char* path, const float* rgb, int32_t width, int32_t height, int32_t rowsBottomUp);
 HRC_API const char* hrhImageLastError(void);
 
+/* ---- session files (reference Session/Session.h:21-78, Session.cpp:88-214; HeatrayRenderer::read/writeSessionFile, HeatrayRenderer.cpp:503-690) ---- */
+#define HRH_SESSION_STRING_SIZE 512    /* Variable::Value::c, Session.cpp:41 */
+typedef struct HrhSession {            /* one field per HEATRAY_SESSION_VARIABLES entry, same order */
+    int32_t interactiveMode; uint32_t maxRenderPasses; float maxChannelValue; char scene[HRH_SESSION_STRING_SIZE];
+    uint32_t maxRayDepth, sampleMode, bokehShape;
+    char environmentMap[HRH_SESSION_STRING_SIZE]; int32_t environmentBuiltIn;
+    float environmentExposureCompensation, environmentThetaRotation, environmentSolidColor[3];
+    float cameraAspectRatio, cameraFocusDistance, cameraFocalLength, cameraApertureRadius, cameraFStop;
+    float orbitDistance, orbitPhi, orbitTheta, orbitTarget[3], orbitMaxDistance;
+    uint32_t units; float aabbMin[3], aabbMax[3], distanceScale, rotationYaw, rotationPitch, rotationRoll, scale;
+    int32_t tonemapEnable; float exposure, brightness, contrast, hue, saturation, vibrance, red, green, blue, vignetteIntensity, vignetteFalloff;
+} HrhSession;
+HRC_API void hrhSessionDefaults(HrhSession* session);                                 /* the table's defaults (Session.h:21-78) */
+HRC_API int  hrhSessionRead(const char* path, HrhSession* session, int32_t* missing); /* parseSessionFile; absent variables keep their value */
+HRC_API int  hrhSessionWrite(const char* path, const HrhSession* session);            /* writeSessionFile, tinyxml2 number formatting */
+HRC_API void hrhSessionApply(const HrhSession* session, HrhRenderOptions* options, HrcPostProcess* post);   /* readSessionFile's mapping */
+HRC_API const char* hrhSessionLastError(void);
+
 /* ---- scene import (reference Scene::loadFromDisk, Scene.cpp:14-27 -> AssimpMeshProvider, AssimpMeshProvider.cpp:65-723).
  * Own readers for Wavefront OBJ/MTL and glTF 2.0 (.gltf/.glb) that apply the reference's Assimp->Heatray mapping rules and hand
  * back what MeshProvider exposes (MeshProvider.h:50-81). Pointers stay valid until hrhFreeScene. ---- */
@@ -183,6 +201,11 @@ HRC_API int  hrhSceneGetLight(HrhScene scene, int32_t index, HrhSceneLight* out)
 typedef struct HrhSceneUploadResult { int32_t meshCount, materialCount, textureCount, texturesMissing; HrcTexture multiscatterLUT;
                                       int32_t dirLights, pointLights, spotLights; } HrhSceneUploadResult;
 HRC_API int  hrhSceneUpload(HrhScene scene, HrcContext ctx, int32_t clearOldScene, HrcTexture multiscatterLUT, HrhSceneUploadResult* result);
+/* Session scene transform: scale(scale) * yawPitchRoll (HeatrayRenderer.h:343-346); applied at upload as transform * mesh transform (Scene.cpp:38-49). */
+HRC_API void hrhSceneTransformMatrix(float yaw, float pitch, float roll, float scale, float out16[16]);
+HRC_API void hrhSceneApplyTransform(HrhScene scene, const float transform16[16]);
+/* util::AABB::center / radius / valid under a transform (AABB.h:34-52; NULL = identity): camera framing uses distance = 3 radius (HeatrayRenderer.cpp:300-310). Returns valid(). */
+HRC_API int  hrhAABBCamera(const float aabbMin[3], const float aabbMax[3], const float transform16[16], float center[3], float* radius);
 /* theta/phi of an imported directional or spot light from its node transform (ProcessLight :564-586, incl. its vec4(axis, 1) quirk). */
 HRC_API void hrhLightAnglesFromTransform(const float worldFromLight[16], float* theta, float* phi);
 HRC_API const char* hrhImportLastError(void);

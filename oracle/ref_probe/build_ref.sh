@@ -25,4 +25,6 @@ sed -e '/^#version/d' -e 's/^uniform sampler2D raytracedTexture;/struct sampler2
     "$REF/Resources/shaders/displayGL.frag" > /tmp/ref_display.inc
 g++ -std=gnu++20 -D_MSC_EXTENSIONS -O2 -fPIC -shared -fsingle-precision-constant -I$REF/3rdParty -I$REF/3rdParty/glm -w ref_display.cpp -o "$OUT/libref_display.so"
 g++ -std=c++17 -O2 -fPIC -shared -I$REF/3rdParty -w ref_stb.cpp -o "$OUT/libref_stb.so"
+# Session.h relies on MSVC pulling in <cstdint>: -include cstdint supplies it, nothing else changes
+g++ -std=c++20 -O1 -fPIC -shared -include cstdint -I$REF/Source -I$REF/3rdParty -w ref_session.cpp $REF/Source/HeatrayRenderer/Session/Session.cpp $REF/3rdParty/tinyxml2/tinyxml2.cpp -o "$OUT/libref_session.so"
 echo "oracle/_ref built"

@@ -100,7 +100,22 @@ def host():
         o = np.zeros(2, np.float32)
         lib.ref_light_angles(m.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p))
         la.append({"in": bits(m), "out": bits(o)})
-    (OUT / "host_glm_ref.json").write_text(json.dumps({"orbit_view": cams, "light_forward": lights, "light_angles": la}))
+    # SceneTransform::transform() (HeatrayRenderer.h:343-346) and util::AABB::center/radius/valid under that transform (AABB.h:34-52)
+    st, ab = [], []
+    for k in range(16):
+        y, p, r = (float(v) for v in rng.uniform(-3.2, 3.2, 3)) if k else (0.0, 0.0, 0.0)
+        sc = float(rng.uniform(0.01, 20.0)) if k else 1.0
+        o = np.zeros(16, np.float32)
+        lib.ref_scene_transform(f32(y), f32(p), f32(r), f32(sc), o.ctypes.data_as(C.c_void_p))
+        st.append({"in": bits([y, p, r, sc]), "out": bits(o)})
+        mn = rng.uniform(-5, 1, 3).astype(np.float32); mx = (mn + rng.uniform(-0.5, 6, 3)).astype(np.float32)
+        if k == 3:
+            mx = mn.copy()                                               # invalid box
+        o5 = np.zeros(5, np.float32)
+        lib.ref_aabb_camera(mn.ctypes.data_as(C.c_void_p), mx.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p), o5.ctypes.data_as(C.c_void_p))
+        ab.append({"min": bits(mn), "max": bits(mx), "transform": bits(o), "out": bits(o5)})
+    (OUT / "host_glm_ref.json").write_text(json.dumps({"orbit_view": cams, "light_forward": lights, "light_angles": la,
+                                                       "scene_transform": st, "aabb_camera": ab}))
 
 
 def display():
