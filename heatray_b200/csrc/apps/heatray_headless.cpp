@@ -23,7 +23,7 @@ struct App {
     bool haveSession = false; HrhSession session{};                               // --session: HeatrayRenderer::readSessionFile (HeatrayRenderer.cpp:581-688)
     int width = 800, height = 800, passes = 32, depth = 10, device = 0;          // reference defaults: 800x800 render area (main.cpp:42-43), 32 passes, depth 10
     bool meters = false, envOff = false; float envColor[3] = {0.5f, 0.5f, 0.5f}, envEV = 0.0f;
-    float phi = 0.0f, theta = 0.0f, distanceScale = 1.0f, fstop = 0.0f, focalLength = 50.0f;
+    float phi = 0.0f, theta = 0.0f, distanceScale = 1.0f, fstop = 0.0f, focalLength = 50.0f, exposureEV = 0.0f;
     HrcPostProcess post{0, 1.0f, 0.0f, 1.0f, 1.0f, 1.0f, 0.0f, 1.0f, 1.0f, 1.0f, 0.0f, 1.0f};
     // filled on the worker thread
     HrhSceneInfo info{}; HrhSceneUploadResult upload{}; HrcTexture envTex = HRC_NULL_TEXTURE; int rc = 0; std::string error;
@@ -118,6 +118,7 @@ int main(int argc, char** argv) {
             a.haveSession = true;
             HrhRenderOptions so; hrhDefaultRenderOptions(&so);
             hrhSessionApply(&a.session, &so, &a.post);
+            a.exposureEV = a.session.exposure;
             a.passes = (int)so.maxRenderPasses; a.depth = (int)so.maxRayDepth; a.meters = a.session.units == 1;        // SceneUnits::kCentimeters (HeatrayRenderer.h:302-305)
             a.envOff = !so.envEnabled; a.envEV = so.envExposureCompensation; std::memcpy(a.envColor, so.envSolidColor, 12);
             a.focalLength = so.focalLength; a.fstop = so.fstop; a.phi = a.session.orbitPhi; a.theta = a.session.orbitTheta;
@@ -126,7 +127,7 @@ int main(int argc, char** argv) {
                 a.envMap = a.session.environmentBuiltIn ? std::string("Resources/Environments/") + a.session.environmentMap : std::string(a.session.environmentMap);
         }
         else if (k == "--tonemap") a.post.tonemappingEnabled = 1;
-        else if (k == "--exposure") { need(1); a.post.cameraExposure = std::pow(2.0f, (float)std::atof(argv[++i])); }
+        else if (k == "--exposure") { need(1); a.exposureEV = (float)std::atof(argv[++i]); a.post.cameraExposure = std::pow(2.0f, a.exposureEV); }
         else if (k[0] == '-') return usage();
         else a.scenePath = k;
     }
@@ -178,7 +179,7 @@ int main(int argc, char** argv) {
         w.units = a.meters ? 1u : 0u;
         if (!a.haveSession) { std::memcpy(w.aabbMin, a.info.aabbMin, 12); std::memcpy(w.aabbMax, a.info.aabbMax, 12); }
         w.distanceScale = radius;
-        w.tonemapEnable = a.post.tonemappingEnabled; w.exposure = std::log2(a.post.cameraExposure); w.brightness = a.post.brightness; w.contrast = a.post.contrast;
+        w.tonemapEnable = a.post.tonemappingEnabled; w.exposure = a.exposureEV; w.brightness = a.post.brightness; w.contrast = a.post.contrast;
         w.hue = a.post.hue; w.saturation = a.post.saturation; w.vibrance = a.post.vibrance; w.red = a.post.red; w.green = a.post.green; w.blue = a.post.blue;
         w.vignetteIntensity = a.post.vignetteIntensity; w.vignetteFalloff = a.post.vignetteFalloff;
         if (hrhSessionWrite(a.sessionOut.c_str(), &w) != HRC_OK) std::fprintf(stderr, "warning: %s\n", hrhSessionLastError());
