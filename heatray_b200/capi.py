@@ -225,7 +225,7 @@ CONTEXT_TASK = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p)
 # names of every exported symbol of the backend C-ABI (checked by tests/test_abi.py against the header)
 BACKEND_SYMBOLS = [
     "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels", "Resolve",
-    "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "ClearScene", "CommitScene",
+    "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "SetMeshTransform", "ClearScene", "CommitScene",
     "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetInteractiveBlocks", "SetGlobals",
     "RenderPass", "EnqueuePass", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo",
 ]
@@ -451,6 +451,11 @@ class Backend:
 
     def destroy_mesh(self, mesh):
         self._call("DestroyMesh", i32(mesh))
+
+    def set_mesh_transform(self, mesh, transform):
+        """Scene::applyTransform for one mesh: `transform` is a mathematical 4x4 (row-major numpy); re-commit afterwards."""
+        M = np.asarray(transform, np.float32).reshape(4, 4)
+        self._call("SetMeshTransform", i32(mesh), (f32 * 16)(*M.T.reshape(-1)))
 
     def clear_scene(self):
         self._call("ClearScene")

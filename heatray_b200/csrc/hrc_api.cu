@@ -403,6 +403,10 @@ HRC_API int hrcDestroyMesh(HrcContext c, HrcMesh mesh) {
     if (!c || mesh < 0 || mesh >= (int)c->meshes.size() || !c->meshes[mesh].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad mesh handle");
     c->meshes[mesh] = MeshRec(); c->committed = false; return HRC_OK;
 }
+HRC_API int hrcSetMeshTransform(HrcContext c, HrcMesh mesh, const float* worldFromEntity) {
+    if (!c || mesh < 0 || mesh >= (int)c->meshes.size() || !c->meshes[mesh].alive || !worldFromEntity) return fail(c, HRC_ERR_INVALID_VALUE, "bad mesh handle");
+    std::memcpy(c->meshes[mesh].M, worldFromEntity, sizeof(c->meshes[mesh].M)); c->committed = false; return HRC_OK;
+}
 HRC_API int hrcClearScene(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     c->meshes.clear(); c->materials.clear(); c->committed = false; c->materialsDirty = true;

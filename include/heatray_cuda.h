@@ -178,6 +178,9 @@ typedef struct HrcMeshDesc {
 } HrcMeshDesc;
 HRC_API int hrcCreateMesh(HrcContext ctx, const HrcMeshDesc* desc, HrcMesh* out);
 HRC_API int hrcDestroyMesh(HrcContext ctx, HrcMesh mesh);
+/* Replaces a mesh's worldFromEntity ↔ Scene::applyTransform (Scene.cpp:38-49: the "worldFromEntity" uniform is rewritten with
+ * transform * submesh.transform; frontFaceCW stays what it was at creation). Takes effect at the next hrcCommitScene. */
+HRC_API int hrcSetMeshTransform(HrcContext ctx, HrcMesh mesh, const float worldFromEntity[16]);
 HRC_API int hrcClearScene(HrcContext ctx);  /* ↔ Scene::clearMeshesAndMaterials (PassGenerator.cpp:408) */
 /* Flattens all meshes to world space (vertex.rlsl:25-43), builds the SAH BVH on the host,
  * collapses it to 8-wide compressed nodes and uploads. Explicit where OpenRL is implicit. */

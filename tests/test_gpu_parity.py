@@ -256,6 +256,38 @@ def test_masked_occlusion_rays(oracle_mod, oracle_backend, gpu_backend):
     assert close.mean() >= 0.995, f"only {close.mean():.4f} of pixels match"
 
 
+def test_set_mesh_transform_matches_oracle_and_rebuild(oracle_backend, gpu_backend):
+    """hrcSetMeshTransform + hrcCommitScene (Scene::applyTransform, Scene.cpp:38-49): same hits as the oracle doing the same, and as a fresh build."""
+    spec = scenes.sphere_grid(width=16, height=16, passes=1, grid=2, u_slices=16, v_slices=8, env_size=(8, 4))
+    rng = np.random.default_rng(5)
+    n = 20000
+    rays = np.zeros(n, capi.RAY_DTYPE)
+    rays["origin"] = rng.uniform(-6, 6, (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays["direction"] = d.astype(np.float32)
+    rays["tmax"] = np.inf
+    T = scenes.translate(0.7, 0.4, -1.1) @ scenes.scale(1.5, 1.5, 1.5)
+    out = []
+    for b in (oracle_backend, gpu_backend):
+        r = renderer.Renderer(b)
+        r.load_scene(spec)
+        before = b.trace_rays(rays)
+        for h, ms in zip(r.mesh_handles, spec.meshes):
+            base = np.eye(4, dtype=np.float32) if ms.transform is None else np.asarray(ms.transform, np.float32)
+            b.set_mesh_transform(h, T @ base)
+        b.commit()
+        after = b.trace_rays(rays)
+        assert not np.array_equal(before["primId"], after["primId"])
+        out.append(after)
+    assert np.array_equal(out[0]["primId"], out[1]["primId"])
+    hit = out[0]["primId"] >= 0
+    assert hit.sum() > 1000
+    for k in ("t", "u", "v"):
+        assert np.array_equal(out[0][k][hit], out[1][k][hit])
+    with pytest.raises(capi.HrcError):
+        gpu_backend.set_mesh_transform(10 ** 6, T)
+
+
 def test_empty_scene_and_misses(gpu_backend, oracle_backend):
     """Empty scene: every primary ray runs the environment shader; image = solid colour * exposure."""
     spec = scenes.SceneSpec("empty", 32, 16, 2, 2, [], [], env=dict(enabled=True, solid=(0.25, 0.5, 0.75), map=None, ev=1.0, theta=0.0),

@@ -110,6 +110,30 @@ def test_strip_equals_triangles_and_winding(oracle_backend):
     assert [(x & capi.HIT_BACKFACE) != 0 for x in h3["primId"].tolist()] == [True, True, False]   # geometric winding flipped ...
 
 
+def test_set_mesh_transform_equals_creating_with_that_transform(oracle_backend):
+    """Scene::applyTransform (Scene.cpp:38-49): rewriting a mesh's worldFromEntity and re-committing == building it there."""
+    b = oracle_backend
+    b.resize(4, 4)
+    p, n, i = scenes.sphere_mesh(12, 8, 1.0)
+    T = scenes.translate(1.5, -0.5, 2.0) @ scenes.scale(2.0, 2.0, 2.0)
+    mat = b.create_material(capi.MATERIAL_PBR, 0, capi.PbrParams())
+    m0 = b.create_mesh(p, n, i, mat)
+    b.commit()
+    rays = _random_rays(4000, 4.0)
+    before = b.trace_rays(rays)
+    b.set_mesh_transform(m0, T)
+    b.commit()
+    moved = b.trace_rays(rays)
+    assert not np.array_equal(before["primId"], moved["primId"])
+    b.clear_scene()
+    mat = b.create_material(capi.MATERIAL_PBR, 0, capi.PbrParams())
+    b.create_mesh(p, n, i, mat, transform=T)
+    b.commit()
+    assert np.array_equal(b.trace_rays(rays), moved)
+    with pytest.raises(capi.HrcError):
+        b.set_mesh_transform(77, T)
+
+
 def _flat_scene(base=(0.8, 0.8, 0.8), **kw):
     p, n, i = scenes.plane_mesh(200.0, 200.0)
     mats = [scenes._pbr(base, rough=1.0, metal=0.0, f0=0.0)]
