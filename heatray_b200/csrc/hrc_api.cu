@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -663,6 +664,18 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
             cudaEventElapsedTime(&ms, c->evPool[1 + 3 * it], c->evPool[2 + 3 * it]); kernelMs[1] += ms;
             cudaEventElapsedTime(&ms, c->evPool[2 + 3 * it], c->evPool[3 + 3 * it]); kernelMs[2] += ms;
             cudaEventElapsedTime(&ms, c->evPool[3 + 3 * it], c->evPool[4 + 3 * it]); kernelMs[3] += ms;
+        }
+        if (std::getenv("HRC_DEBUG_ITERATIONS")) {          // per-iteration ray counts and kernel times of this pass, to stderr
+            std::vector<IterCtrl> hc(iterations);
+            cudaMemcpy(hc.data(), c->pb.ctrl, sizeof(IterCtrl) * iterations, cudaMemcpyDeviceToHost);
+            for (int it = 0; it < iterations; ++it) {
+                float a = 0, b = 0, d = 0;
+                cudaEventElapsedTime(&a, c->evPool[1 + 3 * it], c->evPool[2 + 3 * it]);
+                cudaEventElapsedTime(&b, c->evPool[2 + 3 * it], c->evPool[3 + 3 * it]);
+                cudaEventElapsedTime(&d, c->evPool[3 + 3 * it], c->evPool[4 + 3 * it]);
+                std::fprintf(stderr, "[hrc] iter %2d ext %8u (miss %8u pbr %8u glass %8u) closest %.3f ms | shade %.3f ms | occ %8u any %.3f ms\n", it, hc[it].extCount,
+                             hc[it].classCount[0], hc[it].classCount[1], hc[it].classCount[2], a, b, hc[it].shadowCount, d);
+            }
         }
     }
     return HRC_OK;
