@@ -372,13 +372,16 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms,
                 "higher_is_better": True, "scaling": "strong" if (shard == "bands" and world > 1) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": config_dict(spec, args.config, world, shard=shard, extra={"bvh_nodes": int(info.nodeCount), "bvh_build_s": float(info.buildSeconds),
-                                                                 "scene_bytes": int(info.nodeBytes + info.triangleBytes + info.shadingBytes)}),
+                                                                 "scene_bytes": int(info.nodeBytes + info.triangleBytes + info.shadingBytes),
+                                                                 "pass_pipelining": "value: the K passes are enqueued back to back (hrcEnqueuePass, the reference's offline mode) and rotate over %s sets of "
+                                                                                    "queues / accumulation buffers, so the latency-bound tail of a pass overlaps the head of the next; "
+                                                                                    "e2e: one synchronous pass + readback at a time" % os.environ.get("HRC_TUNE_PASS_LANES", "4")}),
                 "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K,
                 "clocks": clocks, "roofline": roof,
                 "e2e": {"value": rays_all / (e2e_ms / 1e3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms / K,
                         "h2d_bytes_per_step": C.sizeof(capi.FrameParams), "d2h_bytes_per_step": frame_bytes,
                         "api": "hrcRenderPass + hrcReadPixels/hrcReleasePixels (PassGenerator::renderPass + PixelPackBuffer map), pinned host buffer"},
-                "gpu_launches": launches}
+                "gpu_launches": launches + (0 if os.environ.get("HRC_TUNE_PASS_LANES") == "1" else 3)}       # + the lane joins (k_add_pixels) at the end of the timed region
         if world > 1:
             line["reduce_ms"] = reduce_ms
         if world == 1 and not args.no_cpu_baseline:

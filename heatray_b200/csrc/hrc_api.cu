@@ -39,7 +39,14 @@ struct HrcContext_t {
     std::vector<cudaEvent_t> evPool;
     std::string err;
     int smCount = 148;
-    int tuneRefillIdle = 10, tuneBlocksPerSM = 8;   // traversal scheduling knobs (HRC_TUNE_* environment overrides, for experiments)
+    int tuneRefillIdle = 10, tuneBlocksPerSM = 8;
+    // Extra lanes for hrcEnqueuePass: consecutive enqueued passes rotate over passLanes sets of queues / streams / accumulation buffers, so
+    // the latency-bound tail of one pass (a few thousand rays per kernel) runs next to the head of the following one. Every other entry
+    // point first joins the lanes (accum += the extra lanes' buffers), so callers see one buffer; the result is deterministic for a given call sequence.
+    struct Lane { PassBuffers pb{}; cudaStream_t s = nullptr, s2 = nullptr; std::vector<cudaEvent_t> evSync; float4* accum = nullptr;
+                  cudaEvent_t evDone = nullptr; bool active = false; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
+    int passLanes = 4, nextLane = 0;
+    cudaEvent_t evMerged = nullptr;   // traversal scheduling knobs (HRC_TUNE_* environment overrides, for experiments)
 
     int w = 0, h = 0;
     float4* accum = nullptr;
@@ -78,11 +85,60 @@ int failCuda(HrcContext c, cudaError_t e, const char* what) {
 
 template <class T> void freeDev(T*& p) { if (p) { cudaFree(p); p = nullptr; } }
 
-void freeQueues(HrcContext c) {
-    for (int k = 0; k < 2; ++k) { freeDev(c->pb.ext[k].od); freeDev(c->pb.ext[k].wm); }
-    for (int k = 0; k < 3; ++k) freeDev(c->pb.classIdx[k]);
-    freeDev(c->pb.shadow.o); freeDev(c->pb.shadow.d); freeDev(c->pb.shadow.w); freeDev(c->pb.hits);
-    c->pb.capacity = 0;
+void freeQueues(PassBuffers& pb) {
+    for (int k = 0; k < 2; ++k) { freeDev(pb.ext[k].od); freeDev(pb.ext[k].wm); }
+    for (int k = 0; k < 3; ++k) freeDev(pb.classIdx[k]);
+    freeDev(pb.shadow.o); freeDev(pb.shadow.d); freeDev(pb.shadow.w); freeDev(pb.hits);
+    pb.capacity = 0;
+}
+int allocQueues(HrcContext c, PassBuffers& pb, size_t n) {
+    for (int k = 0; k < 2; ++k) {
+        CU(c, cudaMalloc(&pb.ext[k].od, 2 * n * sizeof(float4))); CU(c, cudaMalloc(&pb.ext[k].wm, 2 * n * sizeof(float4)));
+    }
+    for (int k = 0; k < 3; ++k) CU(c, cudaMalloc(&pb.classIdx[k], n * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&pb.shadow.o, n * sizeof(float4))); CU(c, cudaMalloc(&pb.shadow.d, n * sizeof(float4)));
+    CU(c, cudaMalloc(&pb.shadow.w, n * sizeof(float4))); CU(c, cudaMalloc(&pb.hits, n * sizeof(float4)));
+    pb.capacity = (uint32_t)n;
+    return HRC_OK;
+}
+// Folds the extra lanes into the main one, in stream order on the main stream: after this, work on c->stream sees (and a synchronize
+// on it covers) everything that was enqueued on any lane.
+void joinLanes(HrcContext c) {
+    c->nextLane = 0;                       // a join between two enqueued passes keeps both on the main lane
+    const size_t n = (size_t)c->w * c->h;
+    bool any = false;
+    for (auto& L : c->extra) {
+        if (!L.active) continue;
+        cudaEventRecord(L.evDone, L.s);
+        cudaStreamWaitEvent(c->stream, L.evDone, 0);
+        launchAddPixels(c->accum, L.accum, n, c->stream);
+        cudaMemsetAsync(L.accum, 0, n * sizeof(float4), c->stream);
+        any = true;
+    }
+    if (!any) return;
+    cudaEventRecord(c->evMerged, c->stream);
+    for (auto& L : c->extra) if (L.active) { cudaStreamWaitEvent(L.s, c->evMerged, 0); L.active = false; }
+}
+void freeExtraLanes(HrcContext c) {         // buffers that depend on the frame size; streams and counters stay
+    for (auto& L : c->extra) { freeQueues(L.pb); freeDev(L.accum); L.active = false; }
+    c->nextLane = 0;
+}
+int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
+    if (L.accum) return HRC_OK;
+    const size_t n = (size_t)c->w * c->h;
+    if (!L.s) {
+        CU(c, cudaStreamCreateWithFlags(&L.s, cudaStreamNonBlocking)); CU(c, cudaStreamCreateWithFlags(&L.s2, cudaStreamNonBlocking));
+        for (int i = 0; i < 2 * kMaxIterations; ++i) { cudaEvent_t ev; CU(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); L.evSync.push_back(ev); }
+        CU(c, cudaEventCreateWithFlags(&L.evDone, cudaEventDisableTiming));
+        if (!c->evMerged) CU(c, cudaEventCreateWithFlags(&c->evMerged, cudaEventDisableTiming));
+        CU(c, cudaMalloc(&L.pb.ctrl, sizeof(IterCtrl) * kMaxIterations)); CU(c, cudaMalloc(&L.pb.stats, sizeof(DeviceStats)));
+        CU(c, cudaMemset(L.pb.stats, 0, sizeof(DeviceStats))); CU(c, cudaMemset(L.pb.ctrl, 0, sizeof(IterCtrl) * kMaxIterations));
+    }
+    CU(c, cudaMalloc(&L.accum, n * sizeof(float4)));
+    CU(c, cudaMemset(L.accum, 0, n * sizeof(float4)));
+    int r = allocQueues(c, L.pb, n); if (r) return r;
+    L.pb.accum = L.accum;
+    return HRC_OK;
 }
 
 DScene sceneOf(HrcContext c) {
@@ -192,6 +248,7 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
     for (int i = 0; i < 2 * kMaxIterations; ++i) { cudaEvent_t ev; cudaEventCreateWithFlags(&ev, cudaEventDisableTiming); c->evSync.push_back(ev); }
     if (const char* e2 = std::getenv("HRC_TUNE_OVERLAP")) c->overlap = std::atoi(e2) != 0;
+    if (const char* e2 = std::getenv("HRC_TUNE_PASS_LANES")) c->passLanes = std::max(1, std::min(kMaxLanes, std::atoi(e2)));   // 1: no overlap between passes
     cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop); cudaEventCreate(&c->evTimer0); cudaEventCreate(&c->evTimer1);
     cudaMalloc(&c->pb.ctrl, sizeof(IterCtrl) * kMaxIterations);
     cudaMalloc(&c->pb.stats, sizeof(DeviceStats));
@@ -210,8 +267,18 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
 HRC_API int hrcDestroyContext(HrcContext c) {
     if (!c) return HRC_OK;
     cudaSetDevice(c->device);
+    joinLanes(c);
     cudaStreamSynchronize(c->stream);
-    freeQueues(c);
+    freeQueues(c->pb); freeExtraLanes(c);
+    for (auto& L : c->extra) {
+        if (!L.s) continue;
+        cudaStreamSynchronize(L.s); cudaStreamSynchronize(L.s2);
+        for (auto ev : L.evSync) cudaEventDestroy(ev);
+        cudaEventDestroy(L.evDone);
+        freeDev(L.pb.ctrl); freeDev(L.pb.stats);
+        cudaStreamDestroy(L.s2); cudaStreamDestroy(L.s);
+    }
+    if (c->evMerged) cudaEventDestroy(c->evMerged);
     freeDev(c->accum); freeDev(c->staging); if (c->resolveDev) { cudaFree(c->resolveDev); c->resolveDev = nullptr; } if (c->pinned) cudaFreeHost(c->pinned);
     for (auto& t : c->textures) freeDev(t.dev);
     freeDev(c->dNodes); freeDev(c->dTris); freeDev(c->dShade); freeDev(c->dAttr); freeDev(c->dMaterials); freeDev(c->dTextures);
@@ -242,8 +309,9 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
     if ((uint64_t)w * (uint64_t)h > (1u << 24)) return fail(c, HRC_ERR_UNSUPPORTED, "framebuffers above 2^24 pixels are not supported (pixel index is packed in 24 bits)");
     if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "resize while pixels are mapped");
     cudaSetDevice(c->device);
+    joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
-    freeQueues(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
+    freeQueues(c->pb); freeExtraLanes(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
     if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
     c->pixelTables = false; c->offsetCount = 0;
     freeDev(c->dBlockCoords); freeDev(c->dBlockRand); c->blocksX = c->blocksY = 0;   // block tables depend on the frame size
@@ -251,13 +319,8 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
     CU(c, cudaMalloc(&c->accum, n * sizeof(float4)));
     CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));
     CU(c, cudaMallocHost(&c->pinned, n * sizeof(float4))); c->pinnedBytes = n * sizeof(float4);
-    for (int k = 0; k < 2; ++k) {
-        CU(c, cudaMalloc(&c->pb.ext[k].od, 2 * n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.ext[k].wm, 2 * n * sizeof(float4)));
-    }
-    for (int k = 0; k < 3; ++k) CU(c, cudaMalloc(&c->pb.classIdx[k], n * sizeof(uint32_t)));
-    CU(c, cudaMalloc(&c->pb.shadow.o, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.shadow.d, n * sizeof(float4)));
-    CU(c, cudaMalloc(&c->pb.shadow.w, n * sizeof(float4))); CU(c, cudaMalloc(&c->pb.hits, n * sizeof(float4)));
-    c->pb.capacity = (uint32_t)n; c->pb.accum = c->accum;
+    { int r = allocQueues(c, c->pb, n); if (r) return r; }
+    c->pb.accum = c->accum;
     c->w = w; c->h = h;
     CU(c, cudaStreamSynchronize(c->stream));
     return HRC_OK;
@@ -265,7 +328,7 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
 
 HRC_API int hrcClear(HrcContext c) {
     if (!c || !c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->w * c->h * sizeof(float4), c->stream));
     return HRC_OK;
 }
@@ -274,7 +337,7 @@ HRC_API int hrcReadPixels(HrcContext c, const float** rgba) {
     if (!c || !rgba) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "pixels already mapped");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemcpyAsync(c->pinned, c->accum, (size_t)c->w * c->h * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     c->mapped = true; *rgba = c->pinned;
@@ -288,7 +351,7 @@ HRC_API int hrcReleasePixels(HrcContext c) {
 HRC_API int hrcAddPixels(HrcContext c, const float* rgba) {
     if (!c || !rgba) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     const size_t n = (size_t)c->w * c->h;
     if (!c->staging) CU(c, cudaMalloc(&c->staging, n * sizeof(float4)));
     CU(c, cudaMemcpyAsync(c->staging, rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
@@ -299,7 +362,7 @@ HRC_API int hrcAddPixels(HrcContext c, const float* rgba) {
 HRC_API int hrcGetDevicePixels(HrcContext c, void** devPtr) {
     if (!c || !devPtr) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
     *devPtr = c->accum; return HRC_OK;
 }
@@ -309,7 +372,7 @@ HRC_API int hrcResolve(HrcContext c, const HrcPostProcess* post, int32_t format,
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     if (format < HRC_RESOLVE_DISPLAY_RGBA32F || format > HRC_RESOLVE_HDR_RGB32F) return fail(c, HRC_ERR_INVALID_VALUE, "unknown resolve format");
     if (!post && format != HRC_RESOLVE_HDR_RGB32F) return fail(c, HRC_ERR_INVALID_VALUE, "post-processing parameters are required for the display formats");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     const size_t n = (size_t)c->w * c->h;
     const size_t bytes = n * (format == HRC_RESOLVE_DISPLAY_RGBA32F ? 16 : format == HRC_RESOLVE_DISPLAY_RGB8 ? 3 : 12);
     const size_t padded = (bytes + 15) & ~(size_t)15;
@@ -329,7 +392,7 @@ HRC_API int hrcResolve(HrcContext c, const HrcPostProcess* post, int32_t format,
 
 HRC_API int hrcCreateTexture2D(HrcContext c, const HrcTextureDesc* d, const void* pixels, HrcTexture* out) {
     if (!c || !d || !pixels || !out || d->width <= 0 || d->height <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad texture descriptor");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     const size_t n = (size_t)d->width * d->height;
     std::vector<float4> host(n);
     const float* f = (const float*)pixels; const uint8_t* b = (const uint8_t*)pixels;
@@ -352,7 +415,7 @@ HRC_API int hrcCreateTexture2D(HrcContext c, const HrcTextureDesc* d, const void
 }
 HRC_API int hrcDestroyTexture(HrcContext c, HrcTexture tex) {
     if (!c || tex < 0 || tex >= (int)c->textures.size() || !c->textures[tex].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad texture handle");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->textures[tex].dev); c->textures[tex].alive = false; c->texturesDirty = true;
     return HRC_OK;
@@ -416,7 +479,7 @@ HRC_API int hrcClearScene(HrcContext c) {
 
 HRC_API int hrcCommitScene(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
     // 1. flatten to world space; primitive id = running triangle index in (mesh, element) order (policy A-9)
     std::vector<BuildTriangle> bt;
@@ -540,7 +603,7 @@ HRC_API int hrcSetSpotLights(HrcContext c, int32_t n, const HrcSpotLight* l) {
 
 HRC_API int hrcSetSequences(HrcContext c, int32_t ns, int32_t len, const float* xy, const float* ap) {
     if (!c || ns <= 0 || len <= 0 || !xy || !ap) return fail(c, HRC_ERR_INVALID_VALUE, "bad sequence tables");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->dSeq); freeDev(c->dAperture);
     const size_t bytes = (size_t)ns * len * sizeof(float2);
@@ -553,7 +616,7 @@ HRC_API int hrcSetSequences(HrcContext c, int32_t ns, int32_t len, const float* 
 HRC_API int hrcSetPixelTables(HrcContext c, const float* off, size_t count, const uint8_t* sid) {
     if (!c || !off || !sid || count == 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad pixel tables");
     if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "pixel tables need a framebuffer size first");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
     CU(c, cudaMalloc(&c->dSeqOffsetX, count * sizeof(float)));
@@ -567,7 +630,7 @@ HRC_API int hrcSetInteractiveBlocks(HrcContext c, int32_t bw, int32_t bh, const 
     if (!c || !coords || !rnd || bw <= 0 || bh <= 0 || bx <= 0 || by <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad interactive block tables");
     if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "interactive block tables need a framebuffer size first");
     if ((int64_t)bx * bw < c->w || (int64_t)by * bh < c->h) return fail(c, HRC_ERR_INVALID_VALUE, "block tables do not cover the frame");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->dBlockCoords); freeDev(c->dBlockRand);
     CU(c, cudaMalloc(&c->dBlockCoords, (size_t)bw * bh * 3 * sizeof(float)));
@@ -582,7 +645,7 @@ HRC_API int hrcSetGlobals(HrcContext c, const HrcGlobals* g) {
     c->globals = *g; return HRC_OK;
 }
 
-static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels, float* kernelMs /*[4]: raygen, closest, shade, any*/, int* launches /*[3]*/) {
+static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels, float* kernelMs /*[4]: raygen, closest, shade, any*/, int* launches /*[3]*/, int lane = 0) {
     if (!c || !fp) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->committed) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a committed scene");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
@@ -595,6 +658,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     const size_t maxIdx = (size_t)(int)(((float)(c->h - 1) + 0.5f) * (float)c->h + ((float)(c->w - 1) + 0.5f));
     if (maxIdx >= c->offsetCount) return fail(c, HRC_ERR_INVALID_VALUE, "sequence-offset table too short for the reference index formula");
     cudaSetDevice(c->device);
+    if (c->materialsDirty || c->texturesDirty) joinLanes(c);          // the uploads rewrite tables that passes in flight on the other lane read
     int r = uploadMaterials(c); if (r) return r;
     r = uploadTextures(c); if (r) return r;
 
@@ -619,40 +683,42 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     iterations = std::min(iterations, kMaxIterations);
     const DScene sc = sceneOf(c);
     const LaunchConfig lc = configOf(c);
-    cudaStream_t s = c->stream;
+    const PassBuffers& pb = lane ? c->extra[lane - 1].pb : c->pb;
+    const std::vector<cudaEvent_t>& evSync = lane ? c->extra[lane - 1].evSync : c->evSync;
+    cudaStream_t s = lane ? c->extra[lane - 1].s : c->stream;
 
     size_t evNeeded = timeKernels ? (size_t)(3 * iterations + 2) : 0;
     while (c->evPool.size() < evNeeded) { cudaEvent_t ev; CU(c, cudaEventCreate(&ev)); c->evPool.push_back(ev); }
     size_t ev = 0;
     auto mark = [&]() { if (timeKernels) cudaEventRecord(c->evPool[ev++], s); };
 
-    launchClearCtrl(c->pb, s);
+    launchClearCtrl(pb, s);
     mark();
-    launchRaygen(sc, fr, c->pb, s);
+    launchRaygen(sc, fr, pb, s);
     mark();
     if (timeKernels || !c->overlap || iterations < 2) {
         for (int it = 0; it < iterations; ++it) {
-            launchTraceClosest(sc, c->pb, it, lc, s); mark();
-            launchShade(sc, fr, c->pb, it, lc, s);    mark();
-            launchTraceAny(sc, fr, c->pb, it, lc, s); mark();
+            launchTraceClosest(sc, pb, it, lc, s); mark();
+            launchShade(sc, fr, pb, it, lc, s);    mark();
+            launchTraceAny(sc, fr, pb, it, lc, s); mark();
         }
     } else {
         // Occlusion rays of iteration i and extension rays of iteration i+1 are independent (both were emitted by shade(i)):
         // k_trace<any>(i) runs on the second stream next to k_trace<closest>(i+1) and fills the SMs its tail leaves idle.
         // shade(i+1) waits for both: it reuses the shadow queue and accumulates into the same pixels as the light shaders.
-        cudaStream_t s2 = c->stream2;
+        cudaStream_t s2 = lane ? c->extra[lane - 1].s2 : c->stream2;
         for (int it = 0; it < iterations; ++it) {
-            launchTraceClosest(sc, c->pb, it, lc, s);
-            if (it > 0) cudaStreamWaitEvent(s, c->evSync[2 * (it - 1) + 1], 0);
-            launchShade(sc, fr, c->pb, it, lc, s);
-            cudaEventRecord(c->evSync[2 * it], s);
-            cudaStreamWaitEvent(s2, c->evSync[2 * it], 0);
-            launchTraceAny(sc, fr, c->pb, it, lc, s2);
-            cudaEventRecord(c->evSync[2 * it + 1], s2);
+            launchTraceClosest(sc, pb, it, lc, s);
+            if (it > 0) cudaStreamWaitEvent(s, evSync[2 * (it - 1) + 1], 0);
+            launchShade(sc, fr, pb, it, lc, s);
+            cudaEventRecord(evSync[2 * it], s);
+            cudaStreamWaitEvent(s2, evSync[2 * it], 0);
+            launchTraceAny(sc, fr, pb, it, lc, s2);
+            cudaEventRecord(evSync[2 * it + 1], s2);
         }
-        cudaStreamWaitEvent(s, c->evSync[2 * (iterations - 1) + 1], 0);
+        cudaStreamWaitEvent(s, evSync[2 * (iterations - 1) + 1], 0);
     }
-    launchFinishPass(c->pb, iterations, s);
+    launchFinishPass(pb, iterations, s);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return failCuda(c, e, "kernel launch");
     if (launches) { launches[0] = iterations; launches[1] = iterations * ((int)lc.shadeMiss + (int)lc.shadePbr + (int)lc.shadeGlass); launches[2] = iterations; }
@@ -667,7 +733,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
         }
         if (std::getenv("HRC_DEBUG_ITERATIONS")) {          // per-iteration ray counts and kernel times of this pass, to stderr
             std::vector<IterCtrl> hc(iterations);
-            cudaMemcpy(hc.data(), c->pb.ctrl, sizeof(IterCtrl) * iterations, cudaMemcpyDeviceToHost);
+            cudaMemcpy(hc.data(), pb.ctrl, sizeof(IterCtrl) * iterations, cudaMemcpyDeviceToHost);
             for (int it = 0; it < iterations; ++it) {
                 float a = 0, b = 0, d = 0;
                 cudaEventElapsedTime(&a, c->evPool[1 + 3 * it], c->evPool[2 + 3 * it]);
@@ -681,15 +747,23 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     return HRC_OK;
 }
 
-static int readStats(HrcContext c, DeviceStats* out) {
+static int readStats(HrcContext c, DeviceStats* out) {     // callers have joined the lanes: the main stream is ordered after lane 1
+    DeviceStats x[kMaxLanes - 1] = {};
     CU(c, cudaMemcpyAsync(out, c->pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
+    for (int k = 0; k < kMaxLanes - 1; ++k)
+        if (c->extra[k].pb.stats) CU(c, cudaMemcpyAsync(&x[k], c->extra[k].pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
+    for (const DeviceStats& b : x) {
+    out->raysPrimary += b.raysPrimary; out->raysExtension += b.raysExtension; out->raysOcclusion += b.raysOcclusion;
+    out->nodesVisited += b.nodesVisited; out->trianglesTested += b.trianglesTested; out->nodesVisitedAny += b.nodesVisitedAny;
+    out->trianglesTestedAny += b.trianglesTestedAny; out->stackOverflows += b.stackOverflows;
+    }
     return HRC_OK;
 }
 
 HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* stats) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     float kms[4] = {0, 0, 0, 0}; int launches[3] = {0, 0, 0};
     DeviceStats before; int r = readStats(c, &before); if (r) return r;
     CU(c, cudaEventRecord(c->evStart, c->stream));
@@ -711,28 +785,41 @@ HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* 
     }
     return HRC_OK;
 }
-HRC_API int hrcEnqueuePass(HrcContext c, const HrcFrameParams* fp) { return enqueuePass(c, fp, false, nullptr, nullptr); }
+// Asynchronous pass. Consecutive calls rotate over the lanes (see HrcContext_t::extra); any other entry point joins them.
+HRC_API int hrcEnqueuePass(HrcContext c, const HrcFrameParams* fp) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    int lane = 0;
+    if (c->passLanes > 1 && c->accum && !c->kernelTiming) {
+        lane = c->nextLane;
+        if (lane > 0) { cudaSetDevice(c->device); int r = ensureLane(c, c->extra[lane - 1]); if (r) return r; }
+        c->nextLane = (c->nextLane + 1) % c->passLanes;
+    }
+    const int r = enqueuePass(c, fp, false, nullptr, nullptr, lane);
+    if (r == HRC_OK && lane > 0) c->extra[lane - 1].active = true;
+    return r;
+}
 HRC_API int hrcSynchronize(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
     return HRC_OK;
 }
 HRC_API int hrcResetStats(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemsetAsync(c->pb.stats, 0, sizeof(DeviceStats), c->stream));
+    for (auto& L : c->extra) if (L.pb.stats) CU(c, cudaMemsetAsync(L.pb.stats, 0, sizeof(DeviceStats), L.s));   // the lane's own stream already waits for the join
     return HRC_OK;
 }
 HRC_API int hrcTimerStart(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaEventRecord(c->evTimer0, c->stream));
     return HRC_OK;
 }
 HRC_API int hrcTimerStop(HrcContext c, float* ms) {
     if (!c || !ms) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaEventRecord(c->evTimer1, c->stream));
     CU(c, cudaEventSynchronize(c->evTimer1));
     CU(c, cudaEventElapsedTime(ms, c->evTimer0, c->evTimer1));
@@ -740,7 +827,7 @@ HRC_API int hrcTimerStop(HrcContext c, float* ms) {
 }
 HRC_API int hrcGetStats(HrcContext c, HrcPassStats* stats) {
     if (!c || !stats) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
-    cudaSetDevice(c->device);
+    cudaSetDevice(c->device); joinLanes(c);
     DeviceStats d; int r = readStats(c, &d); if (r) return r;
     std::memset(stats, 0, sizeof(*stats));
     stats->raysPrimary = d.raysPrimary; stats->raysExtension = d.raysExtension; stats->raysOcclusion = d.raysOcclusion;
