@@ -46,6 +46,7 @@ struct HrcContext_t {
     struct Lane { PassBuffers pb{}; cudaStream_t s = nullptr, s2 = nullptr; std::vector<cudaEvent_t> evSync; float4* accum = nullptr;
                   cudaEvent_t evDone = nullptr; bool active = false; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
     int passLanes = 4, nextLane = 0;
+    int tunePipelinedBlocksPerSM = 4;      // traversal CTAs per SM for pipelined passes: kernels of several lanes are resident together, so each takes fewer slots
     cudaEvent_t evMerged = nullptr;   // traversal scheduling knobs (HRC_TUNE_* environment overrides, for experiments)
 
     int w = 0, h = 0;
@@ -248,6 +249,7 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
     for (int i = 0; i < 2 * kMaxIterations; ++i) { cudaEvent_t ev; cudaEventCreateWithFlags(&ev, cudaEventDisableTiming); c->evSync.push_back(ev); }
     if (const char* e2 = std::getenv("HRC_TUNE_OVERLAP")) c->overlap = std::atoi(e2) != 0;
+    if (const char* e2 = std::getenv("HRC_TUNE_BLOCKS_PER_SM_PIPE")) c->tunePipelinedBlocksPerSM = std::max(1, std::min(16, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_PASS_LANES")) c->passLanes = std::max(1, std::min(kMaxLanes, std::atoi(e2)));   // 1: no overlap between passes
     cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop); cudaEventCreate(&c->evTimer0); cudaEventCreate(&c->evTimer1);
     cudaMalloc(&c->pb.ctrl, sizeof(IterCtrl) * kMaxIterations);
@@ -645,7 +647,7 @@ HRC_API int hrcSetGlobals(HrcContext c, const HrcGlobals* g) {
     c->globals = *g; return HRC_OK;
 }
 
-static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels, float* kernelMs /*[4]: raygen, closest, shade, any*/, int* launches /*[3]*/, int lane = 0) {
+static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels, float* kernelMs /*[4]: raygen, closest, shade, any*/, int* launches /*[3]*/, int lane = 0, bool pipelined = false) {
     if (!c || !fp) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->committed) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a committed scene");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
@@ -682,7 +684,8 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     int iterations = std::max(0, fr.g.maxRayDepth) + 1 + (c->anySingleSided ? 16 : 0);
     iterations = std::min(iterations, kMaxIterations);
     const DScene sc = sceneOf(c);
-    const LaunchConfig lc = configOf(c);
+    LaunchConfig lc = configOf(c);
+    if (pipelined) lc.traceBlocksPerSM = c->tunePipelinedBlocksPerSM;
     const PassBuffers& pb = lane ? c->extra[lane - 1].pb : c->pb;
     const std::vector<cudaEvent_t>& evSync = lane ? c->extra[lane - 1].evSync : c->evSync;
     cudaStream_t s = lane ? c->extra[lane - 1].s : c->stream;
@@ -789,12 +792,13 @@ HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* 
 HRC_API int hrcEnqueuePass(HrcContext c, const HrcFrameParams* fp) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     int lane = 0;
-    if (c->passLanes > 1 && c->accum && !c->kernelTiming) {
+    const bool pipelined = c->passLanes > 1 && c->accum && !c->kernelTiming;
+    if (pipelined) {
         lane = c->nextLane;
         if (lane > 0) { cudaSetDevice(c->device); int r = ensureLane(c, c->extra[lane - 1]); if (r) return r; }
         c->nextLane = (c->nextLane + 1) % c->passLanes;
     }
-    const int r = enqueuePass(c, fp, false, nullptr, nullptr, lane);
+    const int r = enqueuePass(c, fp, false, nullptr, nullptr, lane, pipelined);
     if (r == HRC_OK && lane > 0) c->extra[lane - 1].active = true;
     return r;
 }

@@ -10,7 +10,11 @@ python bench.py --config material_grid --no-cpu-baseline > $O/${T}_bench_materia
 python bench.py --config terrain --steps 8 --no-cpu-baseline > $O/${T}_bench_terrain.json 2>/dev/null
 python bench.py --config cornell --steps 64 --no-cpu-baseline > $O/${T}_bench_cornell.json 2>/dev/null
 python bench.py --impl reference --steps 16 --warmup 1 > $O/${T}_bench_reference.json 2>/dev/null
+# ncu serialises kernels; one lane keeps the launch list in plain pass order (3 warm-up passes, 2 counter passes with the STATS variants, 2 timed, 2 instrumented, 2 e2e)
+export HRC_TUNE_PASS_LANES=1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/${T}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_list.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_trace -s 60 -c 6 -o $O/${T}_trace_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_full.log 2>&1
+# one whole pass of traversal launches (9 closest + 9 any) from the timed region: skip 3 warm-up + 2 counter passes = 90 k_trace launches
+ncu --set full --clock-control none --import-source on -k regex:k_trace -s 90 -c 18 -o $O/${T}_trace_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_full.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_shade -s 40 -c 6 -o $O/${T}_shade_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${T}_ncu_full2.log 2>&1
+unset HRC_TUNE_PASS_LANES
 ls -la $O | tail -20
