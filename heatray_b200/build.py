@@ -21,7 +21,7 @@ LIB = PKG / "libheatray_cuda.so"
 
 NVCC = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden,-ffp-contract=off,-pthread"]
+COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden,-ffp-contract=off,-fwrapv,-pthread"]
 CU_FLAGS = ["--expt-relaxed-constexpr", "-Xptxas", "-v"]
 
 

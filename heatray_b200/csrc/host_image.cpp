@@ -13,6 +13,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <new>
+#include <stdexcept>
 #include <vector>
 
 namespace {
@@ -190,6 +192,8 @@ namespace {
 
 struct Decoded { int w = 0, h = 0, comp = 0; bool isFloat = false; std::vector<uint8_t> u8; std::vector<float> f32; };
 
+// Header sanity shared by the decoders (stb_image: STBI_MAX_DIMENSIONS = 1 << 24 per side): a corrupt header must not turn into a giant allocation.
+inline bool dimsOk(int64_t w, int64_t h) { return w > 0 && h > 0 && w <= (1 << 24) && h <= (1 << 24) && w * h <= (int64_t(1) << 28); }
 inline uint32_t be32(const uint8_t* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
 inline int paeth(int a, int b, int c) {
     const int p = a + b - c, pa = std::abs(p - a), pb = std::abs(p - b), pc = std::abs(p - c);
@@ -237,7 +241,7 @@ bool decodePNG(const uint8_t* p, size_t n, Decoded& img) {
         if (!std::memcmp(type, "IHDR", 4)) {
             if (len != 13) return false;
             w = (int)be32(data); h = (int)be32(data + 4); depth = data[8]; color = data[9]; interlace = data[12];
-            if (w <= 0 || h <= 0 || data[10] != 0 || data[11] != 0 || interlace > 1) return false;
+            if (!dimsOk(w, h) || data[10] != 0 || data[11] != 0 || interlace > 1) return false;
             if (depth != 1 && depth != 2 && depth != 4 && depth != 8 && depth != 16) return false;
             if (color != 0 && color != 2 && color != 3 && color != 4 && color != 6) return false;
             if (color == 3 && depth == 16) return false;
@@ -366,7 +370,7 @@ bool decodeHDR(const uint8_t* p, size_t n, Decoded& img) {
     if (!format) return false;
     hdrToken(p, n, pos, line);
     int w = 0, h = 0;
-    if (std::sscanf(line.c_str(), "-Y %d +X %d", &h, &w) != 2 || w <= 0 || h <= 0) return false;
+    if (std::sscanf(line.c_str(), "-Y %d +X %d", &h, &w) != 2 || !dimsOk(w, h)) return false;
     img.w = w; img.h = h; img.comp = 3; img.isFloat = true;
     img.f32.assign((size_t)w * h * 3, 0.0f);
     std::vector<uint8_t> scan((size_t)w * 4);
@@ -482,7 +486,7 @@ struct JDecoder {
     const uint8_t* p; size_t n, pos = 0;
     int w = 0, h = 0, ncomp = 0; bool progressive = false, jfif = false; int adobeTransform = -1;
     int hmax = 1, vmax = 1, mcuW = 0, mcuH = 0, mcuX = 0, mcuY = 0;
-    uint16_t quant[4][64]; bool quantPresent[4] = {false, false, false, false};
+    uint16_t quant[4][64] = {}; bool quantPresent[4] = {false, false, false, false};
     JHuff dc[4], ac[4];
     JComp comp[4];
     int restartInterval = 0;
@@ -491,10 +495,14 @@ struct JDecoder {
     JBits br;
 
     int decodeHuff(const JHuff& hf) {
+        if (!hf.present) return -1;                                  // the scan names a table no DHT segment defined
         int code = 0;
         for (int len = 1; len <= 16; ++len) {
             code = (code << 1) | br.bit();
-            if (hf.maxcode[len] >= 0 && code <= hf.maxcode[len] && code >= hf.mincode[len]) return hf.values[hf.valptr[len] + code - hf.mincode[len]];
+            if (hf.maxcode[len] >= 0 && code <= hf.maxcode[len] && code >= hf.mincode[len]) {
+                const int idx = hf.valptr[len] + code - hf.mincode[len];
+                return (idx >= 0 && idx < 256) ? hf.values[idx] : -1;   // over-subscribed length counts
+            }
         }
         return -1;
     }
@@ -772,7 +780,7 @@ bool decodeJPEG(const uint8_t* p, size_t n, Decoded& img) {
             if (gotFrame || dl < 6 || d[0] != 8) return false;
             j.progressive = m == 0xc2;
             j.h = be16(d + 1); j.w = be16(d + 3); j.ncomp = d[5];
-            if (j.w <= 0 || j.h <= 0 || (j.ncomp != 1 && j.ncomp != 3) || dl < 6 + 3 * j.ncomp) return false;
+            if (!dimsOk(j.w, j.h) || (j.ncomp != 1 && j.ncomp != 3) || dl < 6 + 3 * j.ncomp) return false;
             static const char rgb[3] = {'R', 'G', 'B'};
             for (int i = 0; i < j.ncomp; ++i) {
                 JComp& c = j.comp[i];
@@ -865,10 +873,13 @@ int decodeAny(const uint8_t* p, size_t n, int flip, HrhImage* out) {
     std::memset(out, 0, sizeof(*out));
     Decoded d;
     bool ok;
-    if (n >= 8 && p[0] == 137 && p[1] == 'P') ok = decodePNG(p, n, d);
-    else if (n >= 3 && p[0] == 0xff && p[1] == 0xd8) ok = decodeJPEG(p, n, d);
-    else if (isHDR(p, n)) ok = decodeHDR(p, n, d);
-    else return imgFail("unknown image type (PNG, JPEG and Radiance HDR are decoded here)");
+    try {                                                                    // no exception may cross the C boundary
+        if (n >= 8 && p[0] == 137 && p[1] == 'P') ok = decodePNG(p, n, d);
+        else if (n >= 3 && p[0] == 0xff && p[1] == 0xd8) ok = decodeJPEG(p, n, d);
+        else if (isHDR(p, n)) ok = decodeHDR(p, n, d);
+        else return imgFail("unknown image type (PNG, JPEG and Radiance HDR are decoded here)");
+    } catch (const std::bad_alloc&) { g_imgErr = "out of memory"; return HRC_ERR_OUT_OF_MEMORY; }
+      catch (const std::exception&) { return imgFail("corrupt or unsupported image data"); }
     if (!ok) return imgFail("corrupt or unsupported image data");
     const size_t elems = (size_t)d.w * d.h * d.comp, bytes = elems * (d.isFloat ? 4 : 1);
     void* mem = std::malloc(bytes ? bytes : 1);

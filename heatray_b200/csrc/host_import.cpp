@@ -17,6 +17,8 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -450,6 +452,15 @@ struct Gltf {
     Json doc; std::vector<std::vector<uint8_t>> buffers; std::string dir;
 
     // Reads accessor `index` as floats, `comps` per element (missing components 0, extra ones dropped); integers are normalised when flagged.
+    // Byte range of an accessor inside its buffer, validated: offsets and stride come from the file and may be negative, huge or NaN.
+    static bool span(const Json* bv, const Json* acc, int count, size_t elemBytes, size_t bufBytes, size_t& off, size_t& stride) {
+        const double o1 = jnum(bv, "byteOffset", 0), o2 = jnum(acc, "byteOffset", 0), st = jnum(bv, "byteStride", 0);
+        if (!(o1 >= 0.0) || !(o2 >= 0.0) || !(st >= 0.0) || o1 > (double)bufBytes || o2 > (double)bufBytes || st > 65536.0) return false;
+        off = (size_t)o1 + (size_t)o2; stride = (size_t)st; if (!stride) stride = elemBytes;
+        if (count <= 0) return count == 0;
+        if ((size_t)count > bufBytes) return false;                        // more elements than bytes: also keeps the product below in range
+        return off + stride * (size_t)(count - 1) + elemBytes <= bufBytes;
+    }
     bool readFloats(int index, int comps, std::vector<float>& out, int* fileComps = nullptr) const {
         const Json* acc = doc.get("accessors") ? doc.get("accessors")->at((size_t)index) : nullptr;
         if (!acc) return false;
@@ -467,10 +478,9 @@ struct Gltf {
         if (!bv) return false;
         const int buf = jint(bv, "buffer", -1);
         if (buf < 0 || buf >= (int)buffers.size()) return false;
-        const size_t off = (size_t)jnum(bv, "byteOffset", 0) + (size_t)jnum(acc, "byteOffset", 0);
-        size_t stride = (size_t)jnum(bv, "byteStride", 0); if (!stride) stride = (size_t)nc * csize;
         const std::vector<uint8_t>& b = buffers[buf];
-        if (count && off + stride * (size_t)(count - 1) + (size_t)nc * csize > b.size()) return false;
+        size_t off = 0, stride = 0;
+        if (!span(bv, acc, count, (size_t)nc * csize, b.size(), off, stride)) return false;
         for (int i = 0; i < count; ++i) for (int c = 0; c < std::min(nc, comps); ++c) {
             const uint8_t* p = b.data() + off + stride * i + (size_t)c * csize; float v;
             switch (ctype) {
@@ -494,9 +504,8 @@ struct Gltf {
         if (!bv) return false;
         const int buf = jint(bv, "buffer", -1), count = jint(acc, "count", 0);
         if (buf < 0 || buf >= (int)buffers.size()) return false;
-        const size_t off = (size_t)jnum(bv, "byteOffset", 0) + (size_t)jnum(acc, "byteOffset", 0);
-        size_t stride = (size_t)jnum(bv, "byteStride", 0); if (!stride) stride = 4;
-        if (count && off + stride * (size_t)(count - 1) + 4 > buffers[buf].size()) return false;
+        size_t off = 0, stride = 0;
+        if (count < 0 || !span(bv, acc, count, 4, buffers[buf].size(), off, stride)) return false;
         out.resize((size_t)count);
         for (int i = 0; i < count; ++i) std::memcpy(&out[i], buffers[buf].data() + off + stride * i, 4);
         return true;
@@ -770,9 +779,12 @@ HRC_API int hrhImportScene(const char* path, int32_t convertToMeters, HrhScene* 
     const std::string p = path; s->dir = dirOf(p);
     const float scale = convertToMeters ? 0.01f : 1.0f;                          // :693-695: the asset is assumed to be in centimetres
     bool ok;
-    if (endsWith(p, ".obj")) ok = importObj(p, scale, *s);
-    else if (endsWith(p, ".gltf") || endsWith(p, ".glb")) ok = importGltf(p, scale, *s);
-    else { g_importErr = "unsupported scene format (OBJ and glTF 2.0 are read here)"; return HRC_ERR_UNSUPPORTED; }
+    try {                                                                        // no exception may cross the C boundary
+        if (endsWith(p, ".obj")) ok = importObj(p, scale, *s);
+        else if (endsWith(p, ".gltf") || endsWith(p, ".glb")) ok = importGltf(p, scale, *s);
+        else { g_importErr = "unsupported scene format (OBJ and glTF 2.0 are read here)"; return HRC_ERR_UNSUPPORTED; }
+    } catch (const std::bad_alloc&) { g_importErr = "out of memory while importing the scene"; return HRC_ERR_OUT_OF_MEMORY; }
+      catch (const std::exception& e) { g_importErr = std::string("malformed scene file: ") + e.what(); return HRC_ERR_INVALID_VALUE; }
     if (!ok) return HRC_ERR_INVALID_VALUE;
     *out = s.release();
     return HRC_OK;

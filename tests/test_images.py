@@ -66,6 +66,62 @@ def test_corrupt_and_unknown_files_fail_loudly(lib, gold, tmp_path):
         capi.load_texture(tmp_path / "missing.png")
 
 
+def _mutate(rng, data, structural=b""):
+    b = bytearray(data)
+    for _ in range(int(rng.integers(1, 5))):
+        if len(b) <= 4:
+            break
+        pos = int(rng.integers(0, len(b)))
+        op = int(rng.integers(0, 5 if structural else 4))
+        if op == 0:
+            b[pos] = int(rng.integers(0, 256))
+        elif op == 1:
+            del b[pos:pos + int(rng.integers(1, 30))]
+        elif op == 2:
+            b[pos:pos] = bytes(rng.integers(0, 256, int(rng.integers(1, 8)), dtype=np.uint8))
+        elif op == 3:
+            del b[max(4, pos):]
+        else:
+            b[pos] = structural[int(rng.integers(0, len(structural)))]
+    return bytes(b)
+
+
+def test_malformed_images_are_rejected_not_crashed_on(lib, gold):
+    """Seeded mutations of every fixture (bit flips, cuts, insertions, truncation) plus three hand-made cases that used to crash or
+    over-allocate: the decoders must answer with an error code or an image, never take the process down."""
+    rng = np.random.default_rng(2024)
+    files = [k for k in gold.files if k.startswith("file/")]
+    decoded = rejected = 0
+    for t in range(1200):
+        data = _mutate(rng, gold[files[t % len(files)]].tobytes())
+        try:
+            im = capi.load_image(data)
+            assert im.size > 0
+            decoded += 1
+        except capi.HrcError:
+            rejected += 1
+    assert decoded > 50 and rejected > 50
+    # (a) a JPEG whose scan names Huffman tables that no DHT segment defined
+    jpg = bytearray(gold[[k for k in files if "jpeg" in k][0]].tobytes())
+    out, i = bytearray(jpg[:2]), 2
+    while i + 4 <= len(jpg) and jpg[i] == 0xFF and jpg[i + 1] != 0xDA:
+        seg = 2 + (jpg[i + 2] << 8 | jpg[i + 3])
+        if jpg[i + 1] != 0xC4:
+            out += jpg[i:i + seg]
+        i += seg
+    out += jpg[i:]
+    with pytest.raises(capi.HrcError):
+        capi.load_image(bytes(out))
+    # (b) a PNG header that claims 2^24 x 2^24 pixels
+    png = bytearray(gold[[k for k in files if "png" in k][0]].tobytes())
+    png[16:24] = (1 << 24).to_bytes(4, "big") * 2
+    with pytest.raises(capi.HrcError):
+        capi.load_image(bytes(png))
+    # (c) a Radiance header with an absurd resolution line
+    with pytest.raises(capi.HrcError):
+        capi.load_image(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 2000000000 +X 2000000000\n" + bytes(64))
+
+
 def test_load_texture_follows_the_reference_loader(lib, gold, tmp_path):
     """util::loadTextureInternal: vertical flip, sRGB -> linear requantisation with truncation and alpha left alone
     (TextureLoader.cpp:109-133), format from the channel count (:138-151), sampler state (:37-42)."""

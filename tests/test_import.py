@@ -278,6 +278,39 @@ def test_gpu_renders_imported_gltf_like_the_oracle(oracle_backend, gpu_backend, 
     assert po[..., :3].std() > 1e-3
 
 
+def test_malformed_scene_files_are_rejected_not_crashed_on(lib, tmp_path):
+    """Seeded mutations of a .gltf, a .glb, an .obj and its .mtl (bytes, digits, cuts, truncation) and a bufferView with a negative
+    offset: the importers must return an error or a scene, never crash or read outside a buffer."""
+    from test_images import _mutate
+    rng = np.random.default_rng(77)
+    glb, gltf = _gltf(tmp_path, True), _gltf(tmp_path, False)
+    obj = scenes.write_obj(scenes.cornell_box(), tmp_path / "cornell.obj")
+    bases = {p: p.read_bytes() for p in (glb, gltf, obj, tmp_path / "cornell.mtl")}
+    imported = rejected = 0
+    for t in range(800):
+        target = list(bases)[t % 4]
+        target.write_bytes(_mutate(rng, bases[target], structural=b"0123456789-e.{}[],:\""))
+        opened = obj if target.suffix == ".mtl" else target
+        try:
+            spec = scenes.import_scene(opened, load_textures=False)
+            assert spec is not None
+            imported += 1
+        except (capi.HrcError, ValueError):
+            rejected += 1
+        target.write_bytes(bases[target])
+    assert imported > 50 and rejected > 50
+    doc = json.loads(bases[gltf].decode())
+    doc["bufferViews"][0]["byteOffset"] = -4096
+    gltf.write_text(json.dumps(doc))
+    with pytest.raises(capi.HrcError):
+        scenes.import_scene(gltf, load_textures=False)
+    doc["bufferViews"][0]["byteOffset"] = 0
+    doc["accessors"][0]["count"] = 1 << 30
+    gltf.write_text(json.dumps(doc))
+    with pytest.raises(capi.HrcError):
+        scenes.import_scene(gltf, load_textures=False)
+
+
 # ---- heatray_headless: load -> passes -> resolve -> screenshot as one native program ---------------------------------------
 def _headless():
     from heatray_b200.build import APP, build_apps
