@@ -334,6 +334,136 @@ bool decodePNG(const uint8_t* p, size_t n, Decoded& img) {
 } // namespace
 
 // ---------------------------------------------------------------------------------------
+// TIFF (the FreeImage path of util::loadTexture, TextureLoader.cpp:44-87; the reference ships its multiscatter LUT as
+// Resources/multiscatter_lut.tiff: 128 x 128, one 32-bit float sample, LZW strips). Baseline subset: II / MM, strips, chunky planar
+// configuration, compression none / LZW / PackBits, predictor 1 / 2, 32-bit float with 1 or 3 samples (FIT_FLOAT / FIT_RGBF) and
+// 8-bit RGBA (FIT_BITMAP). Rows are returned top-down like the other decoders; the texture loader flips them (FreeImage bitmaps are
+// bottom-up). Quirk kept: FreeImage holds 8-bit pixels as B,G,R,A on little-endian hosts and the reference uploads those bytes as RL_RGBA.
+// ---------------------------------------------------------------------------------------
+namespace {
+
+struct TiffReader {
+    const uint8_t* p; size_t n; bool le;
+    bool ok(size_t off, size_t len) const { return off <= n && len <= n - off; }
+    uint32_t u16(size_t o) const { return le ? (uint32_t)(p[o] | (p[o + 1] << 8)) : (uint32_t)((p[o] << 8) | p[o + 1]); }
+    uint32_t u32(size_t o) const { return le ? ((uint32_t)p[o] | ((uint32_t)p[o + 1] << 8) | ((uint32_t)p[o + 2] << 16) | ((uint32_t)p[o + 3] << 24)) : be32(p + o); }
+    // value(s) of an IFD entry of type SHORT or LONG
+    bool values(size_t entry, std::vector<uint32_t>& out) const {
+        const uint32_t type = u16(entry + 2), count = u32(entry + 4);
+        const size_t sz = type == 3 ? 2 : type == 4 ? 4 : type == 1 ? 1 : 0;
+        if (!sz || count == 0 || count > (1u << 24)) return false;
+        size_t at = entry + 8;
+        if (sz * count > 4) { at = u32(entry + 8); if (!ok(at, sz * count)) return false; }
+        out.resize(count);
+        for (uint32_t i = 0; i < count; ++i) out[i] = sz == 2 ? u16(at + 2 * i) : sz == 4 ? u32(at + 4 * i) : p[at + i];
+        return true;
+    }
+};
+
+// TIFF flavour of LZW (TIFF 6.0 section 13): MSB-first codes of 9..12 bits, ClearCode 256, EoiCode 257, code width grows one code early.
+bool tiffLZW(const uint8_t* src, size_t n, std::vector<uint8_t>& out, size_t expected) {
+    std::vector<uint16_t> prefix(4096); std::vector<uint8_t> suffix(4096), first(4096); std::vector<uint16_t> length(4096);
+    for (int i = 0; i < 256; ++i) { prefix[i] = 0xffff; suffix[i] = first[i] = (uint8_t)i; length[i] = 1; }
+    int bits = 9, next = 258, old = -1; uint32_t acc = 0; int have = 0; size_t pos = 0;
+    out.clear(); out.reserve(expected);
+    auto emit = [&](int code) {
+        const size_t len = length[code], at = out.size();
+        out.resize(at + len);
+        for (size_t k = len; k-- > 0;) { out[at + k] = suffix[code]; code = prefix[code]; }
+    };
+    for (;;) {
+        while (have < bits) { if (pos >= n) return out.size() >= expected; acc = (acc << 8) | src[pos++]; have += 8; }
+        const int code = (int)((acc >> (have - bits)) & ((1u << bits) - 1)); have -= bits;
+        if (code == 257) break;
+        if (code == 256) { bits = 9; next = 258; old = -1; continue; }
+        if (old < 0) { if (code >= 256) return false; emit(code); old = code; continue; }
+        if (code < next) {
+            emit(code);
+            if (next < 4096) { prefix[next] = (uint16_t)old; suffix[next] = first[code]; first[next] = first[old]; length[next] = (uint16_t)(length[old] + 1); ++next; }
+        } else if (code == next && next < 4096) {
+            prefix[next] = (uint16_t)old; suffix[next] = first[old]; first[next] = first[old]; length[next] = (uint16_t)(length[old] + 1); ++next;
+            emit(code);
+        } else return false;
+        old = code;
+        if (next + 1 >= (1 << bits) && bits < 12) ++bits;
+        if (out.size() > expected + 4096) return false;
+    }
+    return out.size() >= expected;
+}
+
+bool tiffPackBits(const uint8_t* src, size_t n, std::vector<uint8_t>& out, size_t expected) {
+    out.clear(); size_t pos = 0;
+    while (pos < n && out.size() < expected) {
+        const int8_t c = (int8_t)src[pos++];
+        if (c >= 0) { const size_t len = (size_t)c + 1; if (pos + len > n) return false; out.insert(out.end(), src + pos, src + pos + len); pos += len; }
+        else if (c != -128) { if (pos >= n) return false; out.insert(out.end(), (size_t)(1 - c), src[pos++]); }
+    }
+    return out.size() >= expected;
+}
+
+bool isTIFF(const uint8_t* p, size_t n) { return n >= 8 && ((p[0] == 'I' && p[1] == 'I' && p[2] == 42 && p[3] == 0) || (p[0] == 'M' && p[1] == 'M' && p[2] == 0 && p[3] == 42)); }
+
+bool decodeTIFF(const uint8_t* p, size_t n, Decoded& img) {
+    if (!isTIFF(p, n)) return false;
+    TiffReader r{p, n, p[0] == 'I'};
+    const size_t ifd = r.u32(4);
+    if (!r.ok(ifd, 2)) return false;
+    const uint32_t entries = r.u16(ifd);
+    if (!r.ok(ifd + 2, (size_t)entries * 12)) return false;
+    uint32_t w = 0, h = 0, compression = 1, spp = 1, rowsPerStrip = 0xffffffffu, planar = 1, predictor = 1, photometric = 1;
+    std::vector<uint32_t> bitsPerSample{1}, sampleFormat{1}, offsets, counts, v;
+    for (uint32_t i = 0; i < entries; ++i) {
+        const size_t e = ifd + 2 + (size_t)i * 12;
+        const uint32_t tag = r.u16(e);
+        const bool known = tag == 256 || tag == 257 || tag == 258 || tag == 259 || tag == 262 || tag == 273 || tag == 277 || tag == 278 || tag == 279 || tag == 284 || tag == 317 || tag == 339;
+        if (!known) continue;
+        if (!r.values(e, v)) return false;
+        switch (tag) {
+        case 256: w = v[0]; break;            case 257: h = v[0]; break;
+        case 258: bitsPerSample = v; break;   case 259: compression = v[0]; break;
+        case 262: photometric = v[0]; break;  case 273: offsets = v; break;
+        case 277: spp = v[0]; break;          case 278: rowsPerStrip = v[0]; break;
+        case 279: counts = v; break;          case 284: planar = v[0]; break;
+        case 317: predictor = v[0]; break;    case 339: sampleFormat = v; break;
+        }
+    }
+    (void)photometric;
+    if (!dimsOk(w, h) || planar != 1 || spp < 1 || spp > 4 || offsets.empty() || offsets.size() != counts.size() || rowsPerStrip == 0) return false;
+    const uint32_t bps = bitsPerSample[0], fmt = sampleFormat[0];
+    for (uint32_t b : bitsPerSample) if (b != bps) return false;
+    const bool isFloat = bps == 32 && fmt == 3;
+    if (isFloat) { if (spp != 1 && spp != 3) return false; }                // FIT_FLOAT, FIT_RGBF; the reference asserts on anything else (:60-75)
+    else if (!(bps == 8 && fmt == 1 && spp == 4)) return false;             // FIT_BITMAP is uploaded as RL_RGBA (:65-68): only 32 bpp is consistent with that
+    if (compression != 1 && compression != 5 && compression != 32773) return false;
+    if (predictor != 1 && !(predictor == 2 && !isFloat)) return false;
+    const size_t bytesPerSample = bps / 8, rowBytes = (size_t)w * spp * bytesPerSample;
+    if (rowsPerStrip > h) rowsPerStrip = h;
+    const size_t strips = ((size_t)h + rowsPerStrip - 1) / rowsPerStrip;
+    if (offsets.size() < strips) return false;
+    std::vector<uint8_t> raw((size_t)h * rowBytes), strip;
+    for (size_t s = 0; s < strips; ++s) {
+        const size_t rows = std::min<size_t>(rowsPerStrip, h - s * rowsPerStrip), want = rows * rowBytes;
+        if (!r.ok(offsets[s], counts[s])) return false;
+        const uint8_t* src = p + offsets[s];
+        if (compression == 1) { if (counts[s] < want) return false; std::memcpy(raw.data() + s * rowsPerStrip * rowBytes, src, want); continue; }
+        if (!(compression == 5 ? tiffLZW(src, counts[s], strip, want) : tiffPackBits(src, counts[s], strip, want))) return false;
+        std::memcpy(raw.data() + s * rowsPerStrip * rowBytes, strip.data(), want);
+    }
+    if (predictor == 2) for (size_t y = 0; y < h; ++y) { uint8_t* row = raw.data() + y * rowBytes; for (size_t i = spp; i < rowBytes; ++i) row[i] = (uint8_t)(row[i] + row[i - spp]); }
+    img.w = (int)w; img.h = (int)h; img.comp = (int)spp; img.isFloat = isFloat;
+    if (isFloat) {
+        img.f32.resize((size_t)w * h * spp);
+        for (size_t i = 0; i < img.f32.size(); ++i) { const uint32_t bitsv = (r.le ? ((uint32_t)raw[4 * i] | ((uint32_t)raw[4 * i + 1] << 8) | ((uint32_t)raw[4 * i + 2] << 16) | ((uint32_t)raw[4 * i + 3] << 24)) : be32(raw.data() + 4 * i)); std::memcpy(&img.f32[i], &bitsv, 4); }
+    } else {
+        img.u8 = raw;
+        for (size_t i = 0; i + 3 < img.u8.size(); i += 4) std::swap(img.u8[i], img.u8[i + 2]);   // FreeImage's B,G,R,A byte order, handed to RL_RGBA as is
+    }
+    return true;
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------
 // Radiance .hdr (RGBE): header "#?RADIANCE" / "#?RGBE", FORMAT=32-bit_rle_rgbe, "-Y h +X w"; flat or new-style RLE scanlines.
 // Texel conversion as the reference's loader sees it (stbi_loadf, TextureLoader.cpp:95): mantissa * 2^(e - 136), no +0.5 bias,
 // exponent 0 -> black. Three channels.
@@ -877,7 +1007,8 @@ int decodeAny(const uint8_t* p, size_t n, int flip, HrhImage* out) {
         if (n >= 8 && p[0] == 137 && p[1] == 'P') ok = decodePNG(p, n, d);
         else if (n >= 3 && p[0] == 0xff && p[1] == 0xd8) ok = decodeJPEG(p, n, d);
         else if (isHDR(p, n)) ok = decodeHDR(p, n, d);
-        else return imgFail("unknown image type (PNG, JPEG and Radiance HDR are decoded here)");
+        else if (isTIFF(p, n)) ok = decodeTIFF(p, n, d);
+        else return imgFail("unknown image type (PNG, JPEG, Radiance HDR and baseline TIFF are decoded here)");
     } catch (const std::bad_alloc&) { g_imgErr = "out of memory"; return HRC_ERR_OUT_OF_MEMORY; }
       catch (const std::exception&) { return imgFail("corrupt or unsupported image data"); }
     if (!ok) return imgFail("corrupt or unsupported image data");

@@ -104,6 +104,19 @@ def test_camera_helpers(lib):
     assert np.isclose(lib.hrhApertureRadius(f32(50.0), f32(2.8)), 0.017857, rtol=1e-4)
 
 
+def test_multiscatter_lut_vs_the_lut_file_the_reference_ships(lib):
+    """Resources/multiscatter_lut.tiff is what the reference actually samples (MultiScatterUtil.cpp:141-150 loads it; :49-139 is the
+    generator that wrote it). Its texels (decoded by Pillow into tests/golden/tiff_ref.npz; FreeImage hands them over bottom-up) against
+    the table hrhGenerateMultiscatterLUT builds: the file was generated on another machine and libm, so the bar is 3e-7 absolute with
+    at least 99 % of the 16384 texels bit-equal."""
+    g = np.load(GOLD / "tiff_ref.npz")
+    shipped = g["ref/reference_multiscatter_lut"][::-1, :, 0]
+    lut = renderer.multiscatter_lut()
+    assert shipped.shape == lut.shape == (128, 128)
+    assert np.abs(shipped - lut).max() <= 3e-7
+    assert (_bits(shipped) == _bits(lut)).mean() >= 0.99
+
+
 def test_multiscatter_lut_vs_reference_generator(lib):
     g = json.loads((GOLD / "lut_ref.json").read_text())
     lut = renderer.multiscatter_lut()

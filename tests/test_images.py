@@ -66,6 +66,35 @@ def test_corrupt_and_unknown_files_fail_loudly(lib, gold, tmp_path):
         capi.load_texture(tmp_path / "missing.png")
 
 
+TIFF_GOLD = Path(__file__).resolve().parent / "golden" / "tiff_ref.npz"
+
+
+def test_tiff_fixtures_and_the_reference_lut_file(lib, tmp_path):
+    """Baseline TIFF (the FreeImage branch of util::loadTexture, TextureLoader.cpp:44-87). Expected texels come from Pillow, an independent
+    decoder (oracle/ref_probe/make_tiff_golden.py); one fixture is the reference's own Resources/multiscatter_lut.tiff."""
+    g = np.load(TIFF_GOLD)
+    names = sorted(k[5:] for k in g.files if k.startswith("file/"))
+    assert "reference_multiscatter_lut" in names and len(names) >= 11
+    for n in names:
+        got, want = capi.load_image(g["file/" + n].tobytes()), g["ref/" + n]
+        assert got.dtype == want.dtype and got.shape == want.shape, n
+        assert np.array_equal(got.view(np.uint8), want.view(np.uint8)), n
+    # the texture loader on a .tiff: FreeImage bitmaps are bottom-up, one float channel is RL_LUMINANCE (:69-72), default sampler clamps
+    path = tmp_path / "lut.tiff"
+    path.write_bytes(g["file/reference_multiscatter_lut"].tobytes())
+    px, fmt, ws, wt = capi.load_texture(path, generate_mips=False, convert_to_linear=False)
+    assert (fmt, ws, wt) == (capi.TEX_R32F, capi.WRAP_CLAMP, capi.WRAP_CLAMP)
+    assert np.array_equal(px[..., 0], g["ref/reference_multiscatter_lut"][::-1, :, 0])
+    # unsupported flavours are refused: 16-bit samples, 8-bit RGB (the reference would upload it as RGBA)
+    from PIL import Image
+    import io
+    for arr in (np.zeros((4, 4), np.uint16), np.zeros((4, 4, 3), np.uint8)):
+        b = io.BytesIO()
+        Image.fromarray(arr).save(b, format="TIFF")
+        with pytest.raises(capi.HrcError):
+            capi.load_image(b.getvalue())
+
+
 def _mutate(rng, data, structural=b""):
     b = bytearray(data)
     for _ in range(int(rng.integers(1, 5))):
@@ -91,9 +120,11 @@ def test_malformed_images_are_rejected_not_crashed_on(lib, gold):
     over-allocate: the decoders must answer with an error code or an image, never take the process down."""
     rng = np.random.default_rng(2024)
     files = [k for k in gold.files if k.startswith("file/")]
+    tg = np.load(TIFF_GOLD)
+    blobs = [gold[k].tobytes() for k in files] + [tg[k].tobytes() for k in tg.files if k.startswith("file/")]
     decoded = rejected = 0
-    for t in range(1200):
-        data = _mutate(rng, gold[files[t % len(files)]].tobytes())
+    for t in range(1500):
+        data = _mutate(rng, blobs[t % len(blobs)])
         try:
             im = capi.load_image(data)
             assert im.size > 0
