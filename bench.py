@@ -379,7 +379,8 @@ def main():
                 "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K,
                 "clocks": clocks, "roofline": roof,
                 "e2e": {"value": rays_all / (e2e_ms / 1e3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms / K,
-                        "h2d_bytes_per_step": C.sizeof(capi.FrameParams), "d2h_bytes_per_step": frame_bytes,
+                        "h2d_bytes_per_step": C.sizeof(capi.FrameParams),
+                        "d2h_bytes_per_step": frame_bytes if not (shard == "bands" and world > 1) else frame_bytes // world,   # band mode reads back only the rank's own rows
                         "api": "hrcRenderPass + hrcReadPixels/hrcReleasePixels (PassGenerator::renderPass + PixelPackBuffer map), pinned host buffer"},
                 "gpu_launches": launches + (0 if os.environ.get("HRC_TUNE_PASS_LANES") == "1" else 3)}       # + the lane joins (k_add_pixels) at the end of the timed region
         if world > 1:

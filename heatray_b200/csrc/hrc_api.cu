@@ -46,6 +46,10 @@ struct HrcContext_t {
     struct Lane { PassBuffers pb{}; cudaStream_t s = nullptr, s2 = nullptr; std::vector<cudaEvent_t> evSync; float4* accum = nullptr;
                   cudaEvent_t evDone = nullptr; bool active = false; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
     int passLanes = 4, nextLane = 0;
+    // Band bookkeeping for the readback: while every pass since the last clear rendered the same set of screen bands, pixels outside
+    // them are zero on the device and hrcReadPixels copies only the context's own rows.
+    int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
+    long long pinnedZeroKey = -1;          // which rows of the pinned frame may be non-zero: -1 any, 0 none (fresh), else the band set's key
     int tunePipelinedBlocksPerSM = 4;      // traversal CTAs per SM for pipelined passes: kernels of several lanes are resident together, so each takes fewer slots
     cudaEvent_t evMerged = nullptr;   // traversal scheduling knobs (HRC_TUNE_* environment overrides, for experiments)
 
@@ -321,9 +325,10 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
     CU(c, cudaMalloc(&c->accum, n * sizeof(float4)));
     CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));
     CU(c, cudaMallocHost(&c->pinned, n * sizeof(float4))); c->pinnedBytes = n * sizeof(float4);
+    std::memset(c->pinned, 0, n * sizeof(float4));
     { int r = allocQueues(c, c->pb, n); if (r) return r; }
     c->pb.accum = c->accum;
-    c->w = w; c->h = h;
+    c->w = w; c->h = h; c->accumOutsideBandsZero = true; c->rbBandCount = 0; c->pinnedZeroKey = 0;
     CU(c, cudaStreamSynchronize(c->stream));
     return HRC_OK;
 }
@@ -332,6 +337,7 @@ HRC_API int hrcClear(HrcContext c) {
     if (!c || !c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->w * c->h * sizeof(float4), c->stream));
+    c->accumOutsideBandsZero = true; c->rbBandCount = 0;
     return HRC_OK;
 }
 
@@ -340,7 +346,21 @@ HRC_API int hrcReadPixels(HrcContext c, const float** rgba) {
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "pixels already mapped");
     cudaSetDevice(c->device); joinLanes(c);
-    CU(c, cudaMemcpyAsync(c->pinned, c->accum, (size_t)c->w * c->h * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    if (c->accumOutsideBandsZero && c->rbBandCount > 1) {
+        // Screen-band sharding: this context only ever wrote its own interleaved bands since the last clear, so only those rows
+        // cross PCIe; the rest of the pinned frame is zero, as it is on the device.
+        const long long key = ((long long)c->rbBandHeight << 40) | ((long long)c->rbBandIndex << 20) | c->rbBandCount;
+        if (c->pinnedZeroKey != key && c->pinnedZeroKey != 0) std::memset(c->pinned, 0, (size_t)c->w * c->h * sizeof(float4));
+        c->pinnedZeroKey = key;
+        const size_t rowBytes = (size_t)c->w * sizeof(float4);
+        for (int y0 = c->rbBandIndex * c->rbBandHeight; y0 < c->h; y0 += c->rbBandHeight * c->rbBandCount) {
+            const int rows = std::min(c->rbBandHeight, c->h - y0);
+            CU(c, cudaMemcpyAsync((char*)c->pinned + (size_t)y0 * rowBytes, (const char*)c->accum + (size_t)y0 * rowBytes, (size_t)rows * rowBytes, cudaMemcpyDeviceToHost, c->stream));
+        }
+    } else {
+        CU(c, cudaMemcpyAsync(c->pinned, c->accum, (size_t)c->w * c->h * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+        c->pinnedZeroKey = -1;
+    }
     CU(c, cudaStreamSynchronize(c->stream));
     c->mapped = true; *rgba = c->pinned;
     return HRC_OK;
@@ -358,6 +378,7 @@ HRC_API int hrcAddPixels(HrcContext c, const float* rgba) {
     if (!c->staging) CU(c, cudaMalloc(&c->staging, n * sizeof(float4)));
     CU(c, cudaMemcpyAsync(c->staging, rgba, n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     launchAddPixels(c->accum, c->staging, n, c->stream);
+    c->accumOutsideBandsZero = false; c->rbBandCount = 0;
     CU(c, cudaStreamSynchronize(c->stream));
     return HRC_OK;
 }
@@ -366,6 +387,7 @@ HRC_API int hrcGetDevicePixels(HrcContext c, void** devPtr) {
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
+    c->accumOutsideBandsZero = false; c->rbBandCount = 0;      // the caller may write through the pointer (in-place NCCL reduce)
     *devPtr = c->accum; return HRC_OK;
 }
 
@@ -675,6 +697,9 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
         int rows = 0; for (int y = 0; y < c->h; ++y) if ((y / fr.bandHeight) % fr.bandCount == fr.bandIndex) rows++;
         fr.localRows = rows;
     } else fr.localRows = c->h;
+    if (fr.bandCount > 1 && c->accumOutsideBandsZero && (c->rbBandCount == 0 || (c->rbBandCount == fr.bandCount && c->rbBandIndex == fr.bandIndex && c->rbBandHeight == fr.bandHeight))) {
+        c->rbBandCount = fr.bandCount; c->rbBandIndex = fr.bandIndex; c->rbBandHeight = fr.bandHeight;
+    } else { c->accumOutsideBandsZero = false; c->rbBandCount = 0; }
     fr.numSequences = c->numSequences; fr.sequenceLength = c->sequenceLength; fr.offsetCount = (uint32_t)c->offsetCount;
     fr.interactiveMode = fp->interactiveMode ? 1 : 0; fr.blockW = c->blockW; fr.blockH = c->blockH;
     fr.blockSampleX = fp->currentBlockPixelSample[0]; fr.blockSampleY = fp->currentBlockPixelSample[1]; fr.blocksX = c->blocksX;

@@ -178,6 +178,55 @@ def test_band_sharding_matches_full_frame(gpu_backend):
     assert np.array_equal(total, full)
 
 
+def test_band_readback_copies_only_own_rows_and_stays_exact(gpu_backend):
+    """hrcReadPixels in band mode moves only the context's rows; the host frame must still equal the device frame in every situation
+    that can put data outside the bands (full-frame pass, hrcAddPixels, a changed band set, the device pointer handed out)."""
+    spec = SMALL["sphere_grid"]()
+    r = renderer.Renderer(gpu_backend)
+    r.load_scene(spec)
+    b = gpu_backend
+    h = spec.height
+
+    def device_frame():
+        # the resolve kernel reads the device buffer directly: HDR resolve = rgb / alpha, so compare coverage through alpha > 0
+        return b.resolve(None, capi.RESOLVE_HDR_RGB32F)
+
+    rows1 = (np.arange(h) // 8) % 3 == 1
+    r.set_band(8, 1, 3)
+    try:
+        r.render_pass(sample_index=0)
+        r.render_pass(sample_index=1)
+        px = r.pixels().copy()
+        assert (px[rows1][..., 3] == 2).all() and (px[~rows1] == 0).all()
+        # switch to another band set without clearing: the buffer now holds both, and the readback must show both
+        rows2 = (np.arange(h) // 8) % 3 == 2
+        r.set_band(8, 2, 3)
+        r.render_pass(sample_index=0)
+        px = r.pixels().copy()
+        assert (px[rows1][..., 3] == 2).all() and (px[rows2][..., 3] == 1).all() and (px[~(rows1 | rows2)] == 0).all()
+        # foreign pixels added by the host
+        b.clear()
+        r.set_band(8, 1, 3)
+        r.render_pass(sample_index=0)
+        extra = np.full((h, spec.width, 4), 0.25, np.float32)
+        b.add_pixels(extra)
+        px = r.pixels().copy()
+        assert np.allclose(px[~rows1], 0.25) and (px[rows1][..., 3] == 1.25).all()
+        # back to a clean band-only state, read twice (the pinned frame keeps zeros outside), then a full-frame pass
+        b.clear()
+        r.render_pass(sample_index=0)
+        a1 = r.pixels().copy(); a2 = r.pixels().copy()
+        assert np.array_equal(a1, a2) and (a1[~rows1] == 0).all() and (a1[rows1][..., 3] == 1).all()
+        r.set_band(1, 0, 1)
+        r.render_pass(sample_index=1)
+        full = r.pixels().copy()
+        assert (full[rows1][..., 3] == 2).all() and (full[~rows1][..., 3] == 1).all()
+        hdr = device_frame()
+        assert np.isfinite(hdr).all() and np.allclose(hdr, full[..., :3] / full[..., 3:4], rtol=1e-6, atol=1e-7)
+    finally:
+        r.set_band(1, 0, 1)
+
+
 def test_interactive_block_mode(oracle_backend, gpu_backend):
     """perspective.rlsl:42-57: each pass renders one pixel of every 3x3 block; the oracle and the kernels pick the same pixels
     (alpha planes equal after every pass), and nine passes add up to exactly one ordinary pass at the same sample index."""
