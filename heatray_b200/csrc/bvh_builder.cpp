@@ -34,7 +34,10 @@ struct Node2 {
     uint32_t first = 0, count = 0;  // prim range (leaf when count > 0)
 };
 
-constexpr int kBins = 16;
+constexpr int kMaxBins = 64;
+int g_bins = 32;                            // SAH bins per axis; 32 measured best on configs #2 / #3 (8: +1.7 / +2.4 %, 16: 0, 32: +1.2 / +4.0 %, 64: +1.0 / +3.4 %
+                                            // in whole-pass Mrays/s; exact sweep SAH below 64..4096 triangles changed nothing). HRC_TUNE_BINS overrides.
+#define kBins g_bins
 constexpr uint32_t kMaxLeafLimit = 3;      // a child slot encodes at most 3 triangles (unary count in 3 bits)
 // Leaf policy: at most g_maxLeaf triangles, made a leaf when n * area <= g_travCost * area + SAH(best split). Defaults measured on B200
 // (profiles/); HRC_TUNE_MAX_LEAF / HRC_TUNE_TRAV_COST override them for experiments.
@@ -62,14 +65,14 @@ struct Builder2 {
         for (int a = 0; a < 3; ++a) {
             const float cmin = cbounds.lo[a], cmax = cbounds.hi[a];
             if (!(cmax > cmin)) continue;
-            Box bb[kBins]; uint32_t bc[kBins];
+            Box bb[kMaxBins]; uint32_t bc[kMaxBins];
             for (int b = 0; b < kBins; ++b) { bb[b].reset(); bc[b] = 0; }
             const float scale = kBins / (cmax - cmin);
             for (uint32_t i = begin; i < end; ++i) {
                 int b = std::min(kBins - 1, std::max(0, (int)((prims[i].c[a] - cmin) * scale)));
                 bb[b].grow(prims[i].box); bc[b]++;
             }
-            float ra[kBins]; uint32_t rc[kBins];
+            float ra[kMaxBins]; uint32_t rc[kMaxBins];
             Box acc; acc.reset(); uint32_t cnt = 0;
             for (int b = kBins - 1; b > 0; --b) { acc.grow(bb[b]); cnt += bc[b]; ra[b] = cnt ? acc.halfArea() : 0.0f; rc[b] = cnt; }
             acc.reset(); cnt = 0;
@@ -137,6 +140,7 @@ void buildWideBVH(const BuildTriangle* tris, size_t count, int threads, WideBVH&
     }
     if (const char* e = std::getenv("HRC_TUNE_MAX_LEAF")) g_maxLeaf = (uint32_t)std::max(1, std::min((int)kMaxLeafLimit, std::atoi(e)));
     if (const char* e = std::getenv("HRC_TUNE_TRAV_COST")) g_travCost = (float)std::atof(e);
+    if (const char* e = std::getenv("HRC_TUNE_BINS")) g_bins = std::max(2, std::min(kMaxBins, std::atoi(e)));
     if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
     if (threads < 1) threads = 1;
     int spawnDepth = 0; while ((1 << spawnDepth) < threads) ++spawnDepth;
