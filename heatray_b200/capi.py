@@ -290,6 +290,7 @@ def _declare_host(lib):
     lib.hrhWritePFM.argtypes = [C.c_char_p, C.c_void_p, i32, i32, i32]
     lib.hrhImageLastError.restype = C.c_char_p
     lib.hrhImportScene.argtypes = [C.c_char_p, i32, C.POINTER(C.c_void_p)]
+    lib.hrhBuildPresetScene.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
     lib.hrhFreeScene.argtypes = [C.c_void_p]
     lib.hrhSceneGetInfo.argtypes = [C.c_void_p, C.POINTER(HrhSceneInfo)]
     lib.hrhSceneGetMaterial.argtypes = [C.c_void_p, i32, C.POINTER(HrhSceneMaterial)]

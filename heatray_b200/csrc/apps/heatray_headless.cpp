@@ -20,6 +20,7 @@ namespace {
 
 struct App {
     std::string scenePath, outPng = "heatray.png", outHdr, envMap, sessionIn, sessionOut;
+    bool preset = false;                                                          // a built-in scene: the reference keeps the camera where it is
     bool haveSession = false; HrhSession session{};                               // --session: HeatrayRenderer::readSessionFile (HeatrayRenderer.cpp:581-688)
     int width = 800, height = 800, passes = 32, depth = 10, device = 0;          // reference defaults: 800x800 render area (main.cpp:42-43), 32 passes, depth 10
     bool meters = false, envOff = false; float envColor[3] = {0.5f, 0.5f, 0.5f}, envEV = 0.0f;
@@ -33,7 +34,10 @@ struct App {
 void loadSceneTask(void* user, HrcContext ctx) {                                 // the LoadSceneCallback body (PassGenerator.cpp:124-136)
     App& a = *static_cast<App*>(user);
     HrhScene scene = nullptr;
-    a.rc = hrhImportScene(a.scenePath.c_str(), a.meters ? 1 : 0, &scene);
+    a.preset = false;
+    for (const char* p : {"Editable PBR Material", "Editable Glass Material", "Multi-Material", "Sphere Array"}) if (a.scenePath == p) a.preset = true;
+    a.rc = a.preset ? hrhBuildPresetScene(a.scenePath.c_str(), &scene)       // the built-in scenes of changeScene (HeatrayRenderer.cpp:123-286)
+                    : hrhImportScene(a.scenePath.c_str(), a.meters ? 1 : 0, &scene);
     if (a.rc != HRC_OK) { a.error = hrhImportLastError(); return; }
     hrhSceneGetInfo(scene, &a.info);
     if (a.haveSession) {                                                         // readSessionFile :671-683: the session's yaw/pitch/roll/scale goes onto every mesh
@@ -80,7 +84,7 @@ void screenshotTask(void* user, HrcContext ctx) {                               
 
 int usage() {
     std::fprintf(stderr,
-        "usage: heatray_headless <scene.obj|.gltf|.glb> [--size W H] [--passes N] [--depth D] [--meters] [--device K]\n"
+        "usage: heatray_headless <scene.obj|.gltf|.glb|built-in scene name> [--size W H] [--passes N] [--depth D] [--meters] [--device K]\n"
         "       [--env r g b | --env-map file.hdr | --no-env] [--ev EV] [--orbit PHI THETA] [--distance-scale S] [--focal MM] [--fstop F]\n"
         "       [--out image.png] [--hdr image.hdr|image.pfm] [--tonemap] [--exposure EV]\n"
         "       [--session in.xml] [--save-session out.xml]     (a session supplies the scene, options, camera and post-processing;\n"
@@ -157,6 +161,8 @@ int main(int argc, char** argv) {
         hrhSceneTransformMatrix(a.session.rotationYaw, a.session.rotationPitch, a.session.rotationRoll, a.session.scale, xf);
         if (hrhAABBCamera(a.session.aabbMin, a.session.aabbMax, xf, centre, &radius)) distance = radius * 3.0f;
         else { std::memcpy(centre, a.session.orbitTarget, 12); distance = a.session.orbitDistance; o.focusDistance = a.session.cameraFocusDistance; }
+    } else if (a.preset) {
+        centre[0] = centre[1] = centre[2] = 0.0f; distance = 19.0f; o.focusDistance = distance;       // OrbitCamera defaults (OrbitCamera.h:22-25), auto-focus on the centre
     } else {
         hrhAABBCamera(a.info.aabbMin, a.info.aabbMax, nullptr, centre, &radius);
         distance = radius * 3.0f;

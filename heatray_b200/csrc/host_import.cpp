@@ -771,6 +771,63 @@ HRC_API void hrhSceneApplyTransform(HrhScene scene, const float transform16[16])
     if (transform16) std::memcpy(scene->sceneXf, transform16, 64); else matIdentity(scene->sceneXf);
 }
 
+// ↔ the built-in scenes of HeatrayRenderer::changeScene (HeatrayRenderer.cpp:123-286): "Editable PBR Material", "Editable Glass Material",
+// "Multi-Material" (the default session's scene) and "Sphere Array", built from the same mesh providers (PlaneMeshProvider 15 x 15,
+// SphereMeshProvider 50 x 50) with the same material parameters and transforms. forceEnableAllTextures of the two editable scenes only
+// switches shader variants on for the material editor; with no texture bound the shading is the same, so it is not carried over.
+// The reference leaves the camera alone for these scenes (no AABB framing): HrhSceneInfo reports an empty AABB (min == max == 0).
+HRC_API int hrhBuildPresetScene(const char* name, HrhScene* out) {
+    if (!name || !out) { g_importErr = "null argument"; return HRC_ERR_INVALID_VALUE; }
+    *out = nullptr;
+    std::unique_ptr<HrhScene_t> s(new HrhScene_t());
+    auto sphere = [&](float radius, const char* meshName, int material, float tx, float ty, float tz) {
+        ImpMesh m; m.name = meshName; m.material = material;
+        uint32_t nv = 0, ni = 0;
+        hrhSphereMesh(50, 50, radius, nullptr, nullptr, nullptr, nullptr, &nv, &ni);
+        m.pos.resize(3 * (size_t)nv); m.nrm.resize(3 * (size_t)nv); m.uv.resize(2 * (size_t)nv); m.idx.resize(ni);
+        hrhSphereMesh(50, 50, radius, m.pos.data(), m.nrm.data(), m.uv.data(), m.idx.data(), &nv, &ni);
+        m.xf[12] = tx; m.xf[13] = ty; m.xf[14] = tz;                     // glm::translate(mat4(1), t)
+        s->meshes.push_back(std::move(m));
+    };
+    auto pbr = [&](const char* matName, float metallic, float roughness, float base, float f0) {
+        ImpMaterial m; m.name = matName; m.type = HRC_MATERIAL_PBR; m.metallic = metallic; m.roughness = roughness;
+        m.baseColor[0] = m.baseColor[1] = m.baseColor[2] = base; m.specularF0 = f0;       // the other parameters keep PhysicallyBasedMaterial::Parameters' defaults
+        s->materials.push_back(m); return (int)s->materials.size() - 1;
+    };
+    auto glass = [&](const char* matName, float r, float g, float b, float ior, float roughness, float density) {
+        ImpMaterial m; m.name = matName; m.type = HRC_MATERIAL_GLASS; m.baseColor[0] = r; m.baseColor[1] = g; m.baseColor[2] = b;
+        m.ior = ior; m.roughness = roughness; m.density = density;
+        s->materials.push_back(m); return (int)s->materials.size() - 1;
+    };
+    const std::string n = name;
+    if (n == "Editable PBR Material") sphere(1.0f, "PBR Sphere", pbr("PBR", 0.0f, 1.0f, 0.8f, 0.0f), 0, 0, 0);               // :123-138
+    else if (n == "Editable Glass Material") sphere(1.0f, "Glass Sphere", glass("Glass", 0.8f, 0.8f, 0.8f, 1.33f, 0.0f, 0.8f), 0, 0, 0);   // :139-152
+    else if (n == "Multi-Material") {                                                                                          // :153-240
+        ImpMesh plane; plane.name = "Plane"; plane.material = pbr("Ground", 0.0f, 1.0f, 0.9f, 0.0f);
+        plane.pos.resize(12); plane.nrm.resize(12); plane.uv.resize(8);
+        uint32_t strip[4];
+        hrhPlaneMesh(15.0f, 15.0f, plane.pos.data(), plane.nrm.data(), plane.uv.data(), strip);
+        plane.idx = {strip[0], strip[1], strip[2], strip[2], strip[1], strip[3]};          // the provider's 4-index strip as a triangle list (odd triangle swapped)
+        plane.xf[13] = -1.5f;
+        s->meshes.push_back(std::move(plane));
+        sphere(1.0f, "Sphere", pbr("PBR", 1.0f, 0.1f, 0.4f, 0.3f), -0.9f, -0.5f, -0.8f);
+        sphere(1.0f, "Sphere", glass("Glass", 0.9f, 0.6f, 0.6f, 1.57f, 0.1f, 0.5f), 1.2f, -0.5f, 0.8f);
+    } else if (n == "Sphere Array") {                                                                                          // :241-285
+        const float radius = 0.5f, padding = radius * 0.2f;
+        for (int row = 0; row < 2; ++row) {
+            float roughness = 0.0f;                                                          // accumulated in fp32 exactly like the reference's loop
+            float startX = (-5.0f * (radius * 2.0f + padding)) + ((radius * 2.0f + padding) * 0.5f);
+            for (int i = 0; i < 10; ++i) {
+                char label[96]; std::snprintf(label, sizeof(label), row ? "Sphere conductor roughness %f" : "Sphere dialectric roughness %f", roughness);
+                sphere(radius, "Sphere", pbr(label, row ? 1.0f : 0.0f, roughness, 1.0f, 0.0f), startX, row ? 1.5f : 0.0f, 0.0f);
+                roughness += 0.1f; startX += radius * 2.0f + padding;
+            }
+        }
+    } else { g_importErr = "unknown built-in scene (Editable PBR Material, Editable Glass Material, Multi-Material, Sphere Array)"; return HRC_ERR_INVALID_VALUE; }
+    *out = s.release();
+    return HRC_OK;
+}
+
 // ↔ AssimpMeshProvider::AssimpMeshProvider / LoadScene (AssimpMeshProvider.cpp:65-75, 662-723); Scene::loadFromDisk (Scene.cpp:14-27)
 HRC_API int hrhImportScene(const char* path, int32_t convertToMeters, HrhScene* out) {
     if (!path || !out) { g_importErr = "null argument"; return HRC_ERR_INVALID_VALUE; }

@@ -419,6 +419,29 @@ def import_scene(path, convert_to_meters=False, width=512, height=512, passes=16
     rc = lib.hrhImportScene(str(path).encode(), int(convert_to_meters), C.byref(h))
     if rc != capi.HRC_OK:
         raise capi.HrcError(rc, (lib.hrhImportLastError() or b"").decode())
+    return _spec_from_scene_handle(lib, h, Path(str(path)).stem, width, height, passes, max_depth, env, camera, load_textures)
+
+
+PRESET_SCENES = ("Editable PBR Material", "Editable Glass Material", "Multi-Material", "Sphere Array")
+
+
+def preset_scene(name, width=512, height=512, passes=16, max_depth=5, env=None, camera=None) -> SceneSpec:
+    """One of the reference's built-in scenes (HeatrayRenderer::changeScene, HeatrayRenderer.cpp:123-286) through hrhBuildPresetScene.
+    The reference does not re-frame the camera for them: the default OrbitCamera applies (distance 19, OrbitCamera.h:22-25), focus on it."""
+    import ctypes as C
+    lib = capi.load_library()
+    h = C.c_void_p()
+    rc = lib.hrhBuildPresetScene(str(name).encode(), C.byref(h))
+    if rc != capi.HRC_OK:
+        raise capi.HrcError(rc, (lib.hrhImportLastError() or b"").decode())
+    cam = dict(distance=19.0, phi=0.0, theta=0.0, target=(0.0, 0.0, 0.0), focal_length=50.0, fstop=None, focus_distance=19.0)
+    cam.update(camera or {})
+    return _spec_from_scene_handle(lib, h, str(name), width, height, passes, max_depth, env, cam, False)
+
+
+def _spec_from_scene_handle(lib, h, name, width, height, passes, max_depth, env, camera, load_textures) -> SceneSpec:
+    """HrhScene -> SceneSpec; frees the handle."""
+    import ctypes as C
     try:
         info = capi.HrhSceneInfo()
         lib.hrhSceneGetInfo(h, C.byref(info))
@@ -485,7 +508,7 @@ def import_scene(path, convert_to_meters=False, width=512, height=512, passes=16
         centre, radius = (lo + hi) * 0.5, float(np.linalg.norm(hi - lo))                   # AABB.h:34-44 (radius() is the full diagonal)
         cam = dict(distance=radius * 3.0, phi=0.0, theta=0.0, target=tuple(float(v) for v in centre), focal_length=50.0, fstop=None, focus_distance=radius * 3.0)
         cam.update(camera or {})
-        return SceneSpec(Path(str(path)).stem, width, height, passes, max_depth, meshes, materials,
+        return SceneSpec(name, width, height, passes, max_depth, meshes, materials,
                          env=env or dict(enabled=True, solid=(0.5, 0.5, 0.5), map=None, ev=0.0, theta=0.0),
                          dir_lights=dl[:5], point_lights=pl[:5], spot_lights=sl[:5], camera=cam)
     finally:

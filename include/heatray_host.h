@@ -201,6 +201,9 @@ HRC_API int  hrhSceneGetLight(HrhScene scene, int32_t index, HrhSceneLight* out)
 typedef struct HrhSceneUploadResult { int32_t meshCount, materialCount, textureCount, texturesMissing; HrcTexture multiscatterLUT;
                                       int32_t dirLights, pointLights, spotLights; } HrhSceneUploadResult;
 HRC_API int  hrhSceneUpload(HrhScene scene, HrcContext ctx, int32_t clearOldScene, HrcTexture multiscatterLUT, HrhSceneUploadResult* result);
+/* The reference's built-in scenes (HeatrayRenderer::changeScene, HeatrayRenderer.cpp:123-286): "Editable PBR Material", "Editable Glass Material",
+ * "Multi-Material", "Sphere Array". The scene AABB is reported empty: the reference does not re-frame the camera for them. */
+HRC_API int  hrhBuildPresetScene(const char* name, HrhScene* out);
 /* Session scene transform: scale(scale) * yawPitchRoll (HeatrayRenderer.h:343-346); applied at upload as transform * mesh transform (Scene.cpp:38-49). */
 HRC_API void hrhSceneTransformMatrix(float yaw, float pitch, float roll, float scale, float out16[16]);
 HRC_API void hrhSceneApplyTransform(HrhScene scene, const float transform16[16]);

@@ -106,6 +106,21 @@ def test_image_parity_equal_spp(name, oracle_backend, gpu_backend):
     assert sg.nodesVisited > 0 and sg.trianglesTested > 0
 
 
+@pytest.mark.parametrize("name", list(scenes.PRESET_SCENES))
+def test_builtin_scenes_image_parity(name, oracle_backend, gpu_backend):
+    """The reference's built-in scenes (HeatrayRenderer::changeScene) through hrhBuildPresetScene, at equal spp on both sides."""
+    spec = scenes.preset_scene(name, width=128, height=96, passes=3, max_depth=5)
+    ro, rg = _pair(oracle_backend, gpu_backend, spec)
+    for _ in range(spec.passes):
+        so, sg = ro.render_pass(), rg.render_pass()
+    po, pg = ro.pixels(), rg.pixels()
+    assert np.array_equal(po[..., 3], pg[..., 3]) and (po[..., 3] == spec.passes).all()
+    close = np.isclose(pg[..., :3], po[..., :3], rtol=1e-3, atol=1e-4).all(-1)
+    assert close.mean() >= 0.99, f"only {close.mean():.4f} of pixels match"
+    assert _psnr(renderer.resolve(po), renderer.resolve(pg), spec.max_channel_value) >= 40.0
+    assert abs(int(sg.rays) - int(so.rays)) <= 0.002 * so.rays and pg[..., :3].std() > 0.01
+
+
 def test_config1_cornell_converged_image(oracle_backend, gpu_backend):
     """BASELINE.json configs[0] at full size: Cornell box 512x512, 64 progressive 1-spp passes, 4 bounces, same QMC tables.
     Stated tolerance for the converged (resolved) images: RMSE <= 2e-3 of the clamp value (pi), PSNR >= 54 dB; sample counts exact."""

@@ -278,6 +278,44 @@ def test_gpu_renders_imported_gltf_like_the_oracle(oracle_backend, gpu_backend, 
     assert po[..., :3].std() > 1e-3
 
 
+def test_builtin_scenes_follow_change_scene(lib, oracle_backend):
+    """hrhBuildPresetScene vs HeatrayRenderer::changeScene (HeatrayRenderer.cpp:123-286): meshes, transforms and material parameters."""
+    assert scenes.PRESET_SCENES == ("Editable PBR Material", "Editable Glass Material", "Multi-Material", "Sphere Array")
+    sp = scenes.preset_scene("Multi-Material")
+    assert [len(m.indices) // 3 for m in sp.meshes] == [2, 5000, 5000]                  # PlaneMeshProvider(15, 15), SphereMeshProvider(50, 50, 1)
+    plane, s1, s2 = sp.meshes
+    assert np.allclose(plane.transform[:3, 3], (0.0, -1.5, 0.0)) and np.abs(plane.positions).max() == 7.5
+    assert np.allclose(s1.transform[:3, 3], (-0.9, -0.5, -0.8)) and np.allclose(s2.transform[:3, 3], (1.2, -0.5, 0.8))
+    assert np.allclose(np.linalg.norm(s1.positions, axis=1), 1.0, atol=1e-6)
+    g, m1, m2 = (sp.materials[m.material] for m in sp.meshes)
+    assert g.kind == "pbr" and np.allclose(g.params["baseColor"], 0.9) and g.params["roughness"] == 1.0 and g.params["specularF0"] == 0.0
+    assert m1.params["metallic"] == 1.0 and m1.params["roughness"] == np.float32(0.1) and np.allclose(m1.params["baseColor"], 0.4) and m1.params["specularF0"] == np.float32(0.3)
+    assert m2.kind == "glass" and np.allclose(m2.params["baseColor"], (0.9, 0.6, 0.6)) and m2.params["ior"] == np.float32(1.57)
+    assert m2.params["roughness"] == np.float32(0.1) and m2.params["density"] == 0.5
+    arr = scenes.preset_scene("Sphere Array")
+    assert len(arr.meshes) == 20 and len(arr.materials) == 20
+    rough, x = np.float32(0.0), np.float32(-5.0 * 1.1 + 0.55)
+    for i in range(10):
+        for row, metal, y in ((0, 0.0, 0.0), (1, 1.0, 1.5)):
+            mesh = arr.meshes[row * 10 + i]
+            p = arr.materials[mesh.material].params
+            assert p["metallic"] == metal and p["roughness"] == rough and np.allclose(p["baseColor"], 1.0) and p["specularF0"] == 0.0
+            assert np.allclose(mesh.transform[:3, 3], (x, y, 0.0), atol=1e-6)
+            assert np.allclose(np.linalg.norm(mesh.positions, axis=1), 0.5, atol=1e-6)
+        rough = np.float32(rough + np.float32(0.1)); x = np.float32(x + np.float32(1.1))      # the reference accumulates both in fp32
+    for name, kind in (("Editable PBR Material", "pbr"), ("Editable Glass Material", "glass")):
+        e = scenes.preset_scene(name)
+        assert len(e.meshes) == 1 and e.materials[0].kind == kind and np.allclose(e.materials[0].params["baseColor"], 0.8)
+    with pytest.raises(capi.HrcError):
+        scenes.preset_scene("Cornell")
+    # and it renders: the default camera (OrbitCamera.h:22-25) looks at the two spheres on the ground plane
+    r = renderer.Renderer(oracle_backend)
+    r.load_scene(scenes.preset_scene("Multi-Material", width=48, height=32, passes=2, max_depth=3))
+    r.render_pass(); r.render_pass()
+    px = r.pixels()
+    assert np.isfinite(px).all() and (px[..., 3] == 2).all() and px[..., :3].std() > 0.01
+
+
 def test_malformed_scene_files_are_rejected_not_crashed_on(lib, tmp_path):
     """Seeded mutations of a .gltf, a .glb, an .obj and its .mtl (bytes, digits, cuts, truncation) and a bufferView with a negative
     offset: the importers must return an error or a scene, never crash or read outside a buffer."""

@@ -217,3 +217,30 @@ def test_headless_session_round_trip_reproduces_the_image(tmp_path):
     moved = np.abs(ic.astype(int) - ia.astype(int)).mean()
     print("scene transform: mean abs diff", moved)
     assert ic.std() > 5 and moved > 4 * max(same.mean(), 0.25)
+
+
+@pytest.mark.gpu
+def test_headless_renders_the_default_session_scene(tmp_path):
+    """The default session names the built-in "Multi-Material" scene (Session.h:25): heatray_headless builds it like changeScene does."""
+    import subprocess
+    s = capi.session_defaults()
+    assert s.scene == b"Multi-Material"
+    s.maxRenderPasses, s.maxRayDepth = 4, 4
+    s.environmentMap = b"solid color"
+    s.environmentSolidColor[:] = [0.6, 0.6, 0.7]
+    s.orbitDistance, s.orbitPhi, s.orbitTheta = 19.0, 0.0, 0.0                 # OrbitCamera defaults (the table's own defaults are placeholders)
+    s.orbitTarget[:] = [0.0, 0.0, 0.0]
+    s.cameraFocusDistance = 19.0
+    # post-processing: the table's defaults are all zero (a black picture); the viewer always writes its own PostProcessingParams
+    s.contrast = s.hue = s.saturation = s.red = s.green = s.blue = s.vignetteFalloff = 1.0
+    sess, out = tmp_path / "default.xml", tmp_path / "mm.png"
+    capi.write_session(sess, s)
+    res = subprocess.run([str(_headless()), "--session", str(sess), "--size", "96", "64", "--out", str(out)], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    info = json.loads(res.stdout.strip().splitlines()[-1])
+    assert info["ok"] and info["meshes"] == 3 and info["materials"] == 3 and info["passes"] == 4
+    img = capi.load_image(out)
+    assert img.shape == (64, 96, 3) and img.std() > 1 and len(np.unique(img)) > 16      # a bright ground under a uniform sky: low contrast, not flat
+    # and by name on the command line
+    res = subprocess.run([str(_headless()), "Sphere Array", "--size", "96", "64", "--passes", "2", "--out", str(tmp_path / "sa.png")], capture_output=True, text=True)
+    assert res.returncode == 0 and json.loads(res.stdout.strip().splitlines()[-1])["meshes"] == 20
