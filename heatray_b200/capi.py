@@ -303,6 +303,9 @@ def _declare_host(lib):
     lib.hrhSceneApplyTransform.argtypes = [C.c_void_p, fp]
     lib.hrhSceneApplyTransform.restype = None
     lib.hrhAABBCamera.argtypes = [fp, fp, fp, fp, fp]
+    lib.hrhAABBBottom.argtypes = [fp, fp, fp]
+    lib.hrhAABBBottom.restype = f32
+    lib.hrhSceneAddGroundPlane.argtypes = [C.c_void_p, fp, fp, fp]
     lib.hrhSessionDefaults.argtypes = [C.POINTER(HrhSession)]
     lib.hrhSessionDefaults.restype = None
     lib.hrhSessionRead.argtypes = [C.c_char_p, C.POINTER(HrhSession), C.POINTER(i32)]

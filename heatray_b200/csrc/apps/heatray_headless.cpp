@@ -20,6 +20,7 @@ namespace {
 
 struct App {
     std::string scenePath, outPng = "heatray.png", outHdr, envMap, sessionIn, sessionOut;
+    bool groundPlane = false;                                                     // --ground-plane: the viewer's "Add Ground Plane" button
     bool preset = false;                                                          // a built-in scene: the reference keeps the camera where it is
     bool haveSession = false; HrhSession session{};                               // --session: HeatrayRenderer::readSessionFile (HeatrayRenderer.cpp:581-688)
     int width = 800, height = 800, passes = 32, depth = 10, device = 0;          // reference defaults: 800x800 render area (main.cpp:42-43), 32 passes, depth 10
@@ -43,6 +44,11 @@ void loadSceneTask(void* user, HrcContext ctx) {                                
     if (a.haveSession) {                                                         // readSessionFile :671-683: the session's yaw/pitch/roll/scale goes onto every mesh
         float xf[16]; hrhSceneTransformMatrix(a.session.rotationYaw, a.session.rotationPitch, a.session.rotationRoll, a.session.scale, xf);
         hrhSceneApplyTransform(scene, xf);
+    }
+    if (a.groundPlane) {
+        float xf[16]; hrhSceneTransformMatrix(a.session.rotationYaw, a.session.rotationPitch, a.session.rotationRoll, a.session.scale, xf);
+        const bool useSessionBox = a.haveSession && hrhAABBCamera(a.session.aabbMin, a.session.aabbMax, nullptr, nullptr, nullptr);
+        hrhSceneAddGroundPlane(scene, useSessionBox ? a.session.aabbMin : a.info.aabbMin, useSessionBox ? a.session.aabbMax : a.info.aabbMax, a.haveSession ? xf : nullptr);
     }
     a.rc = hrhSceneUpload(scene, ctx, 1, HRC_NULL_TEXTURE, &a.upload);
     if (a.rc != HRC_OK) a.error = hrhImportLastError();
@@ -87,6 +93,7 @@ int usage() {
         "usage: heatray_headless <scene.obj|.gltf|.glb|built-in scene name> [--size W H] [--passes N] [--depth D] [--meters] [--device K]\n"
         "       [--env r g b | --env-map file.hdr | --no-env] [--ev EV] [--orbit PHI THETA] [--distance-scale S] [--focal MM] [--fstop F]\n"
         "       [--out image.png] [--hdr image.hdr|image.pfm] [--tonemap] [--exposure EV]\n"
+        "       [--ground-plane]\n"
         "       [--session in.xml] [--save-session out.xml]     (a session supplies the scene, options, camera and post-processing;\n"
         "                                                        flags given after --session override it)\n");
     return 2;
@@ -114,6 +121,7 @@ int main(int argc, char** argv) {
         else if (k == "--fstop") { need(1); a.fstop = (float)std::atof(argv[++i]); }
         else if (k == "--out") { need(1); a.outPng = argv[++i]; }
         else if (k == "--hdr") { need(1); a.outHdr = argv[++i]; }
+        else if (k == "--ground-plane") a.groundPlane = true;
         else if (k == "--save-session") { need(1); a.sessionOut = argv[++i]; }
         else if (k == "--session") {
             need(1); a.sessionIn = argv[++i];

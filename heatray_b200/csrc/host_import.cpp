@@ -765,6 +765,33 @@ HRC_API int hrhAABBCamera(const float aabbMin[3], const float aabbMax[3], const 
     if (radius) *radius = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
     return (aabbMin[0] < aabbMax[0] || aabbMin[1] < aabbMax[1] || aabbMin[2] < aabbMax[2]) ? 1 : 0;
 }
+// ↔ util::AABB::bottom() (AABB.h:46-51): center().y - |transformedMax.y - transformedMin.y| / 2.
+HRC_API float hrhAABBBottom(const float aabbMin[3], const float aabbMax[3], const float transform16[16]) {
+    float I[16]; matIdentity(I);
+    const float* m = transform16 ? transform16 : I;
+    const float ay = (m[1] * aabbMin[0] + m[5] * aabbMin[1]) + (m[9] * aabbMin[2] + m[13] * 1.0f);
+    const float by = (m[1] * aabbMax[0] + m[5] * aabbMax[1]) + (m[9] * aabbMax[2] + m[13] * 1.0f);
+    return (ay + by) * 0.5f - std::fabs(by - ay) * 0.5f;
+}
+// ↔ the viewer's "Add Ground Plane" (HeatrayRenderer.cpp:1167-1193): a square plane of side max(1, size_t(radius)) * 5 at the bottom of the
+// scene AABB, PBR metallic 0 / roughness 0.9 / base colour 0.9 / specularF0 0.2. Returns the new mesh's index, or -1.
+HRC_API int hrhSceneAddGroundPlane(HrhScene scene, const float aabbMin[3], const float aabbMax[3], const float transform16[16]) {
+    if (!scene || !aabbMin || !aabbMax) return -1;
+    float radius = 0.0f;
+    hrhAABBCamera(aabbMin, aabbMax, transform16, nullptr, &radius);
+    const size_t side = std::max<size_t>(1, (size_t)radius) * 5;               // the reference truncates the radius to an integer first
+    ImpMaterial mat; mat.name = "Ground Plane"; mat.type = HRC_MATERIAL_PBR; mat.metallic = 0.0f; mat.roughness = 0.9f; mat.specularF0 = 0.2f;
+    mat.baseColor[0] = mat.baseColor[1] = mat.baseColor[2] = 0.9f;
+    scene->materials.push_back(mat);
+    ImpMesh plane; plane.name = "Ground Plane"; plane.material = (int)scene->materials.size() - 1;
+    plane.pos.resize(12); plane.nrm.resize(12); plane.uv.resize(8);
+    uint32_t strip[4];
+    hrhPlaneMesh((float)side, (float)side, plane.pos.data(), plane.nrm.data(), plane.uv.data(), strip);
+    plane.idx = {strip[0], strip[1], strip[2], strip[2], strip[1], strip[3]};
+    plane.xf[13] = hrhAABBBottom(aabbMin, aabbMax, transform16);
+    scene->meshes.push_back(std::move(plane));
+    return (int)scene->meshes.size() - 1;
+}
 // ↔ Scene::applyTransform (Scene.cpp:38-49): every mesh is uploaded with transform * its own worldFromEntity; winding stays the mesh's own (Mesh.cpp:86-91).
 HRC_API void hrhSceneApplyTransform(HrhScene scene, const float transform16[16]) {
     if (!scene) return;

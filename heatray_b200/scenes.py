@@ -410,7 +410,7 @@ _SLOT_FIELDS = ["baseColorTexture", "metallicRoughnessTexture", "emissiveTexture
 _SLOT_LINEAR = [True, False, True, False, False, False, False]     # convertToLinear per slot (AssimpMeshProvider.cpp:448-505)
 
 
-def import_scene(path, convert_to_meters=False, width=512, height=512, passes=16, max_depth=5, env=None, camera=None, load_textures=True) -> SceneSpec:
+def import_scene(path, convert_to_meters=False, width=512, height=512, passes=16, max_depth=5, env=None, camera=None, load_textures=True, ground_plane=False) -> SceneSpec:
     """OBJ / glTF asset -> SceneSpec through the C++ importer (host_import.cpp) and texture loader (host_image.cpp).
     Camera framing follows HeatrayRenderer.cpp:302-308: target = AABB centre, distance = 3 x AABB diagonal, focus on the target."""
     import ctypes as C
@@ -419,6 +419,10 @@ def import_scene(path, convert_to_meters=False, width=512, height=512, passes=16
     rc = lib.hrhImportScene(str(path).encode(), int(convert_to_meters), C.byref(h))
     if rc != capi.HRC_OK:
         raise capi.HrcError(rc, (lib.hrhImportLastError() or b"").decode())
+    if ground_plane:                                                   # the viewer's "Add Ground Plane" (HeatrayRenderer.cpp:1167-1193)
+        info = capi.HrhSceneInfo()
+        lib.hrhSceneGetInfo(h, C.byref(info))
+        lib.hrhSceneAddGroundPlane(h, info.aabbMin, info.aabbMax, None)
     return _spec_from_scene_handle(lib, h, Path(str(path)).stem, width, height, passes, max_depth, env, camera, load_textures)
 
 

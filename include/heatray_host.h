@@ -209,6 +209,9 @@ HRC_API void hrhSceneTransformMatrix(float yaw, float pitch, float roll, float s
 HRC_API void hrhSceneApplyTransform(HrhScene scene, const float transform16[16]);
 /* util::AABB::center / radius / valid under a transform (AABB.h:34-52; NULL = identity): camera framing uses distance = 3 radius (HeatrayRenderer.cpp:300-310). Returns valid(). */
 HRC_API int  hrhAABBCamera(const float aabbMin[3], const float aabbMax[3], const float transform16[16], float center[3], float* radius);
+HRC_API float hrhAABBBottom(const float aabbMin[3], const float aabbMax[3], const float transform16[16]);   /* util::AABB::bottom(), AABB.h:46-51 */
+/* The viewer's "Add Ground Plane" (HeatrayRenderer.cpp:1167-1193): side max(1, size_t(radius)) * 5 at the AABB's bottom. Returns the mesh index or -1. */
+HRC_API int  hrhSceneAddGroundPlane(HrhScene scene, const float aabbMin[3], const float aabbMax[3], const float transform16[16]);
 /* theta/phi of an imported directional or spot light from its node transform (ProcessLight :564-586, incl. its vec4(axis, 1) quirk). */
 HRC_API void hrhLightAnglesFromTransform(const float worldFromLight[16], float* theta, float* phi);
 HRC_API const char* hrhImportLastError(void);

@@ -111,7 +111,7 @@ def host():
         mn = rng.uniform(-5, 1, 3).astype(np.float32); mx = (mn + rng.uniform(-0.5, 6, 3)).astype(np.float32)
         if k == 3:
             mx = mn.copy()                                               # invalid box
-        o5 = np.zeros(5, np.float32)
+        o5 = np.zeros(6, np.float32)
         lib.ref_aabb_camera(mn.ctypes.data_as(C.c_void_p), mx.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p), o5.ctypes.data_as(C.c_void_p))
         ab.append({"min": bits(mn), "max": bits(mx), "transform": bits(o), "out": bits(o5)})
     (OUT / "host_glm_ref.json").write_text(json.dumps({"orbit_view": cams, "light_forward": lights, "light_angles": la,

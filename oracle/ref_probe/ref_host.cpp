@@ -16,11 +16,11 @@ void ref_scene_transform(float yaw, float pitch, float roll, float scale, float*
     glm::mat4 m = glm::scale(glm::mat4(1.0f), glm::vec3(scale)) * glm::yawPitchRoll(yaw, pitch, roll);
     for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out16[4 * i + j] = m[i][j];
 }
-// util::AABB (unmodified header): center(), radius(), valid() with a transform set -> out = cx, cy, cz, radius, valid.
+// util::AABB (unmodified header): center(), radius(), valid(), bottom() with a transform set -> out = cx, cy, cz, radius, valid, bottom.
 void ref_aabb_camera(const float* mn, const float* mx, const float* in16, float* out5) {
     util::AABB b; b.min = glm::vec3(mn[0], mn[1], mn[2]); b.max = glm::vec3(mx[0], mx[1], mx[2]);
     for (int c = 0; c < 4; ++c) for (int r = 0; r < 4; ++r) b.transform[c][r] = in16[4 * c + r];
-    glm::vec3 c = b.center(); out5[0] = c.x; out5[1] = c.y; out5[2] = c.z; out5[3] = b.radius(); out5[4] = b.valid() ? 1.0f : 0.0f;
+    glm::vec3 c = b.center(); out5[0] = c.x; out5[1] = c.y; out5[2] = c.z; out5[3] = b.radius(); out5[4] = b.valid() ? 1.0f : 0.0f; out5[5] = b.bottom();
 }
 void ref_orbit_view(float distance, float phi, float theta, const float* target, float* out16) {
     OrbitCamera c; c.distance = distance; c.phi = phi; c.theta = theta; c.target = glm::vec3(target[0], target[1], target[2]);

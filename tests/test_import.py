@@ -316,6 +316,22 @@ def test_builtin_scenes_follow_change_scene(lib, oracle_backend):
     assert np.isfinite(px).all() and (px[..., 3] == 2).all() and px[..., :3].std() > 0.01
 
 
+def test_ground_plane_like_the_viewers_button(lib, tmp_path):
+    """HeatrayRenderer.cpp:1167-1193: side = max(1, size_t(AABB diagonal)) * 5, at the AABB's bottom, PBR 0 / 0.9 / 0.9 / 0.2."""
+    obj = scenes.write_obj(scenes.cornell_box(), tmp_path / "cornell.obj")
+    plain = scenes.import_scene(obj, load_textures=False)
+    sp = scenes.import_scene(obj, load_textures=False, ground_plane=True)
+    assert len(sp.meshes) == len(plain.meshes) + 1 and len(sp.materials) == len(plain.materials) + 1
+    world = np.concatenate([m.positions @ np.asarray(m.transform)[:3, :3].T + np.asarray(m.transform)[:3, 3] for m in plain.meshes])
+    lo, hi = world.min(0), world.max(0)
+    side = max(1, int(np.float32(np.linalg.norm((hi - lo).astype(np.float32))))) * 5
+    gp = sp.meshes[-1]
+    assert len(gp.indices) == 6 and np.abs(gp.positions[:, [0, 2]]).max() == side / 2 and (gp.positions[:, 1] == 0).all()
+    assert np.isclose(np.asarray(gp.transform)[1, 3], lo[1], atol=1e-6) and np.allclose(np.asarray(gp.transform)[[0, 2], 3], 0.0)
+    p = sp.materials[gp.material].params
+    assert (p["metallic"], p["roughness"], p["specularF0"]) == (0.0, np.float32(0.9), np.float32(0.2)) and np.allclose(p["baseColor"], 0.9)
+
+
 def test_malformed_scene_files_are_rejected_not_crashed_on(lib, tmp_path):
     """Seeded mutations of a .gltf, a .glb, an .obj and its .mtl (bytes, digits, cuts, truncation) and a bufferView with a negative
     offset: the importers must return an error or a scene, never crash or read outside a buffer."""

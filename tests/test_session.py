@@ -163,7 +163,8 @@ def test_scene_transform_and_aabb_camera_match_the_reference_glm():
         mn, mx, t = (_unbits(c[k]) for k in ("min", "max", "transform"))
         cen, rad = (capi.f32 * 3)(), capi.f32()
         v = lib.hrhAABBCamera((capi.f32 * 3)(*mn), (capi.f32 * 3)(*mx), (capi.f32 * 16)(*t), cen, C.byref(rad))
-        got = np.array([*cen, rad.value, v], np.float32)
+        bottom = lib.hrhAABBBottom((capi.f32 * 3)(*mn), (capi.f32 * 3)(*mx), (capi.f32 * 16)(*t))
+        got = np.array([*cen, rad.value, v, bottom], np.float32)
         assert np.array_equal(got.view(np.uint32), np.array(c["out"], np.uint32))
         valid += v
     assert 0 < valid < len(g["aabb_camera"])                                   # the set holds an invalid box too
