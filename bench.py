@@ -328,13 +328,42 @@ def main():
     if world > 1:
         reduce_timed()
     barrier()
+    e2e_serial_ms = (time.perf_counter() - t0) * 1e3
+
+    # The same K steps the way hr::PassGenerator runs them when the caller keeps its next renderPass job queued (host_pass_generator.cpp:
+    # look-ahead): pass i+1 is started into the backend's deferred buffer before pass i is read back, so the host copy of every pass
+    # (still one full readback per step, each holding exactly i+1 samples) overlaps the rendering of the next one.
+    def pipelined_steps(n):
+        total = 0.0
+        r.frame.sampleIndex = sidx(0)
+        b.enqueue_pass(r.frame)
+        for i in range(n):
+            if i + 1 < n:
+                r.frame.sampleIndex = sidx(i + 1)
+                b.enqueue_pass_deferred(r.frame)
+            px = b.map_pixels()
+            total += float(px[0, 0, 3])
+            b.unmap_pixels()
+            if i + 1 < n:
+                b.commit_deferred()
+        return total
+
+    pipelined_steps(max(3, W))                    # untimed warm-up: the deferred buffers are allocated on first use
+    b.clear()
+    barrier()
+    t0 = time.perf_counter()
+    alpha_sum = pipelined_steps(K)
+    if world > 1:
+        reduce_timed()
+    barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
+    assert alpha_sum == checksum, "the pipelined steps did not each deliver exactly their own pass count"
 
     # ---- gather over ranks (max time, summed rays) -------------------------------------------------
     if world > 1:
-        t = torch.tensor([dev_ms, wall_ms, e2e_ms], device="cuda", dtype=torch.float64)
+        t = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e_serial_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, wall_ms, e2e_ms = t.tolist()
+        dev_ms, wall_ms, e2e_ms, e2e_serial_ms = t.tolist()
         rt = torch.tensor([float(rays_total)], device="cuda", dtype=torch.float64)
         dist.all_reduce(rt, op=dist.ReduceOp.SUM)
         rays_all = rt.item()
@@ -375,13 +404,16 @@ def main():
                                                                  "scene_bytes": int(info.nodeBytes + info.triangleBytes + info.shadingBytes),
                                                                  "pass_pipelining": "value: the K passes are enqueued back to back (hrcEnqueuePass, the reference's offline mode) and rotate over %s sets of "
                                                                                     "queues / accumulation buffers, so the latency-bound tail of a pass overlaps the head of the next; "
-                                                                                    "e2e: one synchronous pass + readback at a time" % os.environ.get("HRC_TUNE_PASS_LANES", "4")}),
+                                                                                    "e2e: pass i+1 renders into the deferred buffer while pass i is read back (e2e.serial: one step at a time)" % os.environ.get("HRC_TUNE_PASS_LANES", "4")}),
                 "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K,
                 "clocks": clocks, "roofline": roof,
                 "e2e": {"value": rays_all / (e2e_ms / 1e3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms / K,
                         "h2d_bytes_per_step": C.sizeof(capi.FrameParams),
                         "d2h_bytes_per_step": frame_bytes if not (shard == "bands" and world > 1) else frame_bytes // world,   # band mode reads back only the rank's own rows
-                        "api": "hrcRenderPass + hrcReadPixels/hrcReleasePixels (PassGenerator::renderPass + PixelPackBuffer map), pinned host buffer"},
+                        "api": "per step: hrcEnqueuePassDeferred (the next pass) + hrcReadPixels/hrcReleasePixels (this pass, pinned host buffer) + hrcCommitDeferred - what "
+                               "hr::PassGenerator::renderPass does when the caller keeps its next job queued; every step delivers its own full frame to the host",
+                        "serial": {"value": rays_all / (e2e_serial_ms / 1e3) / 1e6, "ms_per_step": e2e_serial_ms / K,
+                                   "api": "hrcRenderPass + hrcReadPixels/hrcReleasePixels, one step at a time (the reference viewer's loop, HeatrayRenderer.cpp:366-408)"}},
                 "gpu_launches": launches + (0 if os.environ.get("HRC_TUNE_PASS_LANES") == "1" else 3)}       # + the lane joins (k_add_pixels) at the end of the timed region
         if world > 1:
             line["reduce_ms"] = reduce_ms

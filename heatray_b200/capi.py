@@ -227,7 +227,7 @@ BACKEND_SYMBOLS = [
     "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels", "Resolve",
     "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "SetMeshTransform", "ClearScene", "CommitScene",
     "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetInteractiveBlocks", "SetGlobals",
-    "RenderPass", "EnqueuePass", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo",
+    "RenderPass", "EnqueuePass", "EnqueuePassDeferred", "CommitDeferred", "DiscardDeferred", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo",
 ]
 
 _lib = None
@@ -515,6 +515,15 @@ class Backend:
 
     def enqueue_pass(self, frame: FrameParams):
         self._call("EnqueuePass", C.byref(frame))
+
+    def enqueue_pass_deferred(self, frame: FrameParams):
+        self._call("EnqueuePassDeferred", C.byref(frame))
+
+    def commit_deferred(self):
+        self._call("CommitDeferred")
+
+    def discard_deferred(self):
+        self._call("DiscardDeferred")
 
     def synchronize(self):
         self._call("Synchronize")

@@ -65,7 +65,7 @@ public:
 
     void renderPass(const HrhRenderOptions& opts, HrhPassCompleteCallback cb, void* user) {   // :115-122
         HrhRenderOptions copy = opts;
-        enqueue([this, copy, cb, user]() { runRenderFrameJob(copy, cb, user); });
+        enqueue([this, copy, cb, user]() { runRenderFrameJob(copy, cb, user); }, &copy);
     }
 
     void runTask(HrhContextTask task, void* user) { enqueue([this, task, user]() { task(user, m_ctx); }); }   // loadScene / changeLighting / modifyScene / runOpenRLTask
@@ -78,19 +78,30 @@ public:
     const char* lastError() const { return m_error.c_str(); }
 
 private:
-    void enqueue(std::function<void()> job) {
-        { std::lock_guard<std::mutex> g(m_mutex); m_jobs.push_back(std::move(job)); }
+    struct Job { std::function<void()> fn; bool isRender = false; HrhRenderOptions options{}; };
+    void enqueue(std::function<void()> job, const HrhRenderOptions* renderOptions = nullptr) {
+        Job j; j.fn = std::move(job);
+        if (renderOptions) { j.isRender = true; j.options = *renderOptions; }
+        { std::lock_guard<std::mutex> g(m_mutex); m_jobs.push_back(std::move(j)); }
         m_cv.notify_one();
+    }
+    // Look-ahead for runRenderFrameJob: is the job right behind the running one another pass of the same progressive render (no reset)?
+    bool nextJobContinuesTheRender() {
+        std::lock_guard<std::mutex> g(m_mutex);
+        if (m_jobs.empty() || !m_jobs.front().isRender) return false;
+        const HrhRenderOptions& n = m_jobs.front().options;
+        return !n.resetInternalState && n.enableInteractiveMode == m_options.enableInteractiveMode && n.enableOfflineMode == m_options.enableOfflineMode;
     }
     void workerLoop() {
         for (;;) {
-            std::function<void()> job;
+            std::function<void()> job; bool isRender = false;
             {
                 std::unique_lock<std::mutex> g(m_mutex);
                 m_cv.wait(g, [this]() { return m_quit || !m_jobs.empty(); });
                 if (m_jobs.empty()) { if (m_quit) return; continue; }
-                job = std::move(m_jobs.front()); m_jobs.pop_front(); m_busy = true;
+                job = std::move(m_jobs.front().fn); isRender = m_jobs.front().isRender; m_jobs.pop_front(); m_busy = true;
             }
+            if (!isRender) dropPrefetchedPass();                          // anything else (scene, size, lights ...) invalidates a pass rendered ahead
             job();
             { std::lock_guard<std::mutex> g(m_mutex); m_busy = false; }
             m_idle.notify_all();
@@ -164,7 +175,10 @@ private:
         check(hrcSetEnvironment(m_ctx, &env));
     }
 
+    void dropPrefetchedPass() { if (m_prefetched && m_ctx) { hrcDiscardDeferred(m_ctx); m_prefetched = false; } }
+
     void resetRenderingState(const HrhRenderOptions& n) {                // PassGenerator.cpp:435-577
+        dropPrefetchedPass();
         m_currentSampleIndex = 0;
         m_currentBlockPixelSample[0] = m_currentBlockPixelSample[1] = 0;
         check(hrcClear(m_ctx));
@@ -213,9 +227,20 @@ private:
                     if (++m_currentBlockPixelSample[1] == 3) { m_currentBlockPixelSample[0] = m_currentBlockPixelSample[1] = 0; ++m_currentSampleIndex; }
                 }
             } else ++m_currentSampleIndex;
-            int rc = hrcEnqueuePass(m_ctx, &f);                            // rlRenderFrame(), :386
+            int rc;
+            if (m_prefetched && std::memcmp(&m_prefetchedFrame, &f, sizeof(f)) == 0) { rc = hrcCommitDeferred(m_ctx); m_prefetched = false; }   // this pass was rendered ahead
+            else { dropPrefetchedPass(); rc = hrcEnqueuePass(m_ctx, &f); }  // rlRenderFrame(), :386
             check(rc);
             jobCompleted = rc != HRC_OK || !(m_options.enableOfflineMode && m_currentSampleIndex < m_options.maxRenderPasses);   // :390
+            // Look-ahead: when the caller has already queued the next pass of this progressive render, start it now, into a deferred
+            // buffer, so that it renders while this pass is copied to the host and handed to the callback. The frame constants of that
+            // pass are fully determined here (no reset: the queued job's own options are not consulted, :334-339).
+            if (jobCompleted && rc == HRC_OK && !m_options.enableOfflineMode && !m_options.enableInteractiveMode && !m_options.debugPassRendering &&
+                m_currentSampleIndex < m_options.maxRenderPasses && nextJobContinuesTheRender()) {
+                HrcFrameParams ahead = f;
+                ahead.sampleIndex = (int)m_currentSampleIndex;
+                if (hrcEnqueuePassDeferred(m_ctx, &ahead) == HRC_OK) { m_prefetchedFrame = ahead; m_prefetched = true; }
+            }
             const float* pixels = nullptr;
             if (jobCompleted && rc == HRC_OK) {                            // setPixelData + map, :392-394 and HeatrayRenderer.cpp:391-395
                 rc = hrcReadPixels(m_ctx, &pixels); check(rc);
@@ -229,7 +254,7 @@ private:
     std::thread m_worker;
     std::mutex m_mutex;
     std::condition_variable m_cv, m_idle;
-    std::deque<std::function<void()>> m_jobs;
+    std::deque<Job> m_jobs;
     bool m_quit = false, m_busy = false, m_initialised = false;
 
     HrcContext m_ctx = nullptr;
@@ -237,6 +262,7 @@ private:
     HrhRenderOptions m_options{};
     HrcGlobals m_globals{};
     bool m_envApplied = false, m_globalsApplied = false, m_mapped = false;
+    bool m_prefetched = false; HrcFrameParams m_prefetchedFrame{};     // a pass rendered ahead into the backend's deferred buffer
     HrcTexture m_solidTex = HRC_NULL_TEXTURE;
     uint32_t m_currentSampleIndex = 0;
     uint32_t m_blockShuffleSeed = 0x5eed;   // the reference seeds this shuffle from std::random_device (quirk B-Q6)

@@ -46,6 +46,9 @@ struct HrcContext_t {
     struct Lane { PassBuffers pb{}; cudaStream_t s = nullptr, s2 = nullptr; std::vector<cudaEvent_t> evSync; float4* accum = nullptr;
                   cudaEvent_t evDone = nullptr; bool active = false; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
     int passLanes = 4, nextLane = 0;
+    // Deferred passes (hrcEnqueuePassDeferred): rendered into one of two side lanes that joins ignore until hrcCommitDeferred, so a
+    // caller can already render pass i+1 while pass i is being read back (hr::PassGenerator does that when its next job is queued).
+    Lane deferred[2]; int deferredNext = 0, deferredPending = -1;
     // Band bookkeeping for the readback: while every pass since the last clear rendered the same set of screen bands, pixels outside
     // them are zero on the device and hrcReadPixels copies only the context's own rows.
     int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
@@ -112,21 +115,30 @@ void joinLanes(HrcContext c) {
     c->nextLane = 0;                       // a join between two enqueued passes keeps both on the main lane
     const size_t n = (size_t)c->w * c->h;
     bool any = false;
-    for (auto& L : c->extra) {
-        if (!L.active) continue;
+    auto fold = [&](HrcContext_t::Lane& L) {
+        if (!L.active) return;
         cudaEventRecord(L.evDone, L.s);
         cudaStreamWaitEvent(c->stream, L.evDone, 0);
         launchAddPixels(c->accum, L.accum, n, c->stream);
         cudaMemsetAsync(L.accum, 0, n * sizeof(float4), c->stream);
         any = true;
-    }
+    };
+    for (auto& L : c->extra) fold(L);
+    for (auto& L : c->deferred) fold(L);          // committed deferred passes only: a pending one keeps running, invisible
     if (!any) return;
     cudaEventRecord(c->evMerged, c->stream);
-    for (auto& L : c->extra) if (L.active) { cudaStreamWaitEvent(L.s, c->evMerged, 0); L.active = false; }
+    auto release = [&](HrcContext_t::Lane& L) { if (L.active) { cudaStreamWaitEvent(L.s, c->evMerged, 0); L.active = false; } };
+    for (auto& L : c->extra) release(L);
+    for (auto& L : c->deferred) release(L);
+}
+// For calls that free or rewrite what a pending deferred pass still reads (resize, scene / table uploads): wait for it.
+void waitPendingDeferred(HrcContext c) {
+    if (c->deferredPending >= 0 && c->deferred[c->deferredPending].s) cudaStreamSynchronize(c->deferred[c->deferredPending].s);
 }
 void freeExtraLanes(HrcContext c) {         // buffers that depend on the frame size; streams and counters stay
     for (auto& L : c->extra) { freeQueues(L.pb); freeDev(L.accum); L.active = false; }
-    c->nextLane = 0;
+    for (auto& L : c->deferred) { freeQueues(L.pb); freeDev(L.accum); L.active = false; }
+    c->nextLane = 0; c->deferredPending = -1;
 }
 int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
     if (L.accum) return HRC_OK;
@@ -273,10 +285,11 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
 HRC_API int hrcDestroyContext(HrcContext c) {
     if (!c) return HRC_OK;
     cudaSetDevice(c->device);
-    joinLanes(c);
+    joinLanes(c); waitPendingDeferred(c);
     cudaStreamSynchronize(c->stream);
     freeQueues(c->pb); freeExtraLanes(c);
-    for (auto& L : c->extra) {
+    for (HrcContext_t::Lane* Lp : {&c->extra[0], &c->extra[1], &c->extra[2], &c->deferred[0], &c->deferred[1]}) {
+        HrcContext_t::Lane& L = *Lp;
         if (!L.s) continue;
         cudaStreamSynchronize(L.s); cudaStreamSynchronize(L.s2);
         for (auto ev : L.evSync) cudaEventDestroy(ev);
@@ -315,7 +328,7 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
     if ((uint64_t)w * (uint64_t)h > (1u << 24)) return fail(c, HRC_ERR_UNSUPPORTED, "framebuffers above 2^24 pixels are not supported (pixel index is packed in 24 bits)");
     if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "resize while pixels are mapped");
     cudaSetDevice(c->device);
-    joinLanes(c);
+    joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeQueues(c->pb); freeExtraLanes(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
     if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
@@ -439,7 +452,7 @@ HRC_API int hrcCreateTexture2D(HrcContext c, const HrcTextureDesc* d, const void
 }
 HRC_API int hrcDestroyTexture(HrcContext c, HrcTexture tex) {
     if (!c || tex < 0 || tex >= (int)c->textures.size() || !c->textures[tex].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad texture handle");
-    cudaSetDevice(c->device); joinLanes(c);
+    cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->textures[tex].dev); c->textures[tex].alive = false; c->texturesDirty = true;
     return HRC_OK;
@@ -503,7 +516,7 @@ HRC_API int hrcClearScene(HrcContext c) {
 
 HRC_API int hrcCommitScene(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    cudaSetDevice(c->device); joinLanes(c);
+    cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
     // 1. flatten to world space; primitive id = running triangle index in (mesh, element) order (policy A-9)
     std::vector<BuildTriangle> bt;
@@ -627,7 +640,7 @@ HRC_API int hrcSetSpotLights(HrcContext c, int32_t n, const HrcSpotLight* l) {
 
 HRC_API int hrcSetSequences(HrcContext c, int32_t ns, int32_t len, const float* xy, const float* ap) {
     if (!c || ns <= 0 || len <= 0 || !xy || !ap) return fail(c, HRC_ERR_INVALID_VALUE, "bad sequence tables");
-    cudaSetDevice(c->device); joinLanes(c);
+    cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->dSeq); freeDev(c->dAperture);
     const size_t bytes = (size_t)ns * len * sizeof(float2);
@@ -640,7 +653,7 @@ HRC_API int hrcSetSequences(HrcContext c, int32_t ns, int32_t len, const float* 
 HRC_API int hrcSetPixelTables(HrcContext c, const float* off, size_t count, const uint8_t* sid) {
     if (!c || !off || !sid || count == 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad pixel tables");
     if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "pixel tables need a framebuffer size first");
-    cudaSetDevice(c->device); joinLanes(c);
+    cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
     CU(c, cudaMalloc(&c->dSeqOffsetX, count * sizeof(float)));
@@ -654,7 +667,7 @@ HRC_API int hrcSetInteractiveBlocks(HrcContext c, int32_t bw, int32_t bh, const 
     if (!c || !coords || !rnd || bw <= 0 || bh <= 0 || bx <= 0 || by <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad interactive block tables");
     if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "interactive block tables need a framebuffer size first");
     if ((int64_t)bx * bw < c->w || (int64_t)by * bh < c->h) return fail(c, HRC_ERR_INVALID_VALUE, "block tables do not cover the frame");
-    cudaSetDevice(c->device); joinLanes(c);
+    cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
     freeDev(c->dBlockCoords); freeDev(c->dBlockRand);
     CU(c, cudaMalloc(&c->dBlockCoords, (size_t)bw * bh * 3 * sizeof(float)));
@@ -682,7 +695,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     const size_t maxIdx = (size_t)(int)(((float)(c->h - 1) + 0.5f) * (float)c->h + ((float)(c->w - 1) + 0.5f));
     if (maxIdx >= c->offsetCount) return fail(c, HRC_ERR_INVALID_VALUE, "sequence-offset table too short for the reference index formula");
     cudaSetDevice(c->device);
-    if (c->materialsDirty || c->texturesDirty) joinLanes(c);          // the uploads rewrite tables that passes in flight on the other lane read
+    if (c->materialsDirty || c->texturesDirty) { joinLanes(c); waitPendingDeferred(c); }   // the uploads rewrite tables that passes in flight on other lanes read
     int r = uploadMaterials(c); if (r) return r;
     r = uploadTextures(c); if (r) return r;
 
@@ -711,9 +724,10 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     const DScene sc = sceneOf(c);
     LaunchConfig lc = configOf(c);
     if (pipelined) lc.traceBlocksPerSM = c->tunePipelinedBlocksPerSM;
-    const PassBuffers& pb = lane ? c->extra[lane - 1].pb : c->pb;
-    const std::vector<cudaEvent_t>& evSync = lane ? c->extra[lane - 1].evSync : c->evSync;
-    cudaStream_t s = lane ? c->extra[lane - 1].s : c->stream;
+    HrcContext_t::Lane* L = lane > 0 ? &c->extra[lane - 1] : lane < 0 ? &c->deferred[-lane - 1] : nullptr;      // lane < 0: deferred lane -lane-1
+    const PassBuffers& pb = L ? L->pb : c->pb;
+    const std::vector<cudaEvent_t>& evSync = L ? L->evSync : c->evSync;
+    cudaStream_t s = L ? L->s : c->stream;
 
     size_t evNeeded = timeKernels ? (size_t)(3 * iterations + 2) : 0;
     while (c->evPool.size() < evNeeded) { cudaEvent_t ev; CU(c, cudaEventCreate(&ev)); c->evPool.push_back(ev); }
@@ -734,7 +748,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
         // Occlusion rays of iteration i and extension rays of iteration i+1 are independent (both were emitted by shade(i)):
         // k_trace<any>(i) runs on the second stream next to k_trace<closest>(i+1) and fills the SMs its tail leaves idle.
         // shade(i+1) waits for both: it reuses the shadow queue and accumulates into the same pixels as the light shaders.
-        cudaStream_t s2 = lane ? c->extra[lane - 1].s2 : c->stream2;
+        cudaStream_t s2 = L ? L->s2 : c->stream2;
         for (int it = 0; it < iterations; ++it) {
             launchTraceClosest(sc, pb, it, lc, s);
             if (it > 0) cudaStreamWaitEvent(s, evSync[2 * (it - 1) + 1], 0);
@@ -776,10 +790,12 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
 }
 
 static int readStats(HrcContext c, DeviceStats* out) {     // callers have joined the lanes: the main stream is ordered after lane 1
-    DeviceStats x[kMaxLanes - 1] = {};
+    DeviceStats x[kMaxLanes - 1 + 2] = {};
     CU(c, cudaMemcpyAsync(out, c->pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
     for (int k = 0; k < kMaxLanes - 1; ++k)
         if (c->extra[k].pb.stats) CU(c, cudaMemcpyAsync(&x[k], c->extra[k].pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
+    for (int k = 0; k < 2; ++k)            // deferred lanes: counters of passes that finished (a pending pass adds its own when it ends)
+        if (c->deferred[k].pb.stats) CU(c, cudaMemcpyAsync(&x[kMaxLanes - 1 + k], c->deferred[k].pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     for (const DeviceStats& b : x) {
     out->raysPrimary += b.raysPrimary; out->raysExtension += b.raysExtension; out->raysOcclusion += b.raysOcclusion;
@@ -827,9 +843,40 @@ HRC_API int hrcEnqueuePass(HrcContext c, const HrcFrameParams* fp) {
     if (r == HRC_OK && lane > 0) c->extra[lane - 1].active = true;
     return r;
 }
+// Deferred pass: rendered like hrcEnqueuePass, but into a side buffer that no other call sees until hrcCommitDeferred. One at a time.
+// Lets a caller that already knows its next pass start it before it reads the current result back (hr::PassGenerator look-ahead).
+HRC_API int hrcEnqueuePassDeferred(HrcContext c, const HrcFrameParams* fp) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (c->deferredPending >= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "a deferred pass is already pending (commit or discard it first)");
+    if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
+    cudaSetDevice(c->device);
+    const int d = c->deferredNext;
+    if (c->deferred[d].active) joinLanes(c);                      // its previous pass was committed but not folded in yet
+    int r = ensureLane(c, c->deferred[d]); if (r) return r;
+    r = enqueuePass(c, fp, false, nullptr, nullptr, -(d + 1), false);
+    if (r == HRC_OK) { c->deferredPending = d; c->deferredNext = d ^ 1; }
+    return r;
+}
+HRC_API int hrcCommitDeferred(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (c->deferredPending < 0) return fail(c, HRC_ERR_INVALID_OPERATION, "no deferred pass is pending");
+    c->deferred[c->deferredPending].active = true;                // the next join folds it in (and waits for it, in stream order)
+    c->deferredPending = -1;
+    return HRC_OK;
+}
+HRC_API int hrcDiscardDeferred(HrcContext c) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (c->deferredPending < 0) return HRC_OK;
+    cudaSetDevice(c->device);
+    HrcContext_t::Lane& L = c->deferred[c->deferredPending];
+    CU(c, cudaMemsetAsync(L.accum, 0, (size_t)c->w * c->h * sizeof(float4), L.s));      // after its kernels, in stream order
+    CU(c, cudaStreamSynchronize(L.s));                          // rare (reset, scene change): whatever follows may free what the pass was reading
+    c->deferredPending = -1;
+    return HRC_OK;
+}
 HRC_API int hrcSynchronize(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    cudaSetDevice(c->device); joinLanes(c);
+    cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
     return HRC_OK;
 }
@@ -838,6 +885,7 @@ HRC_API int hrcResetStats(HrcContext c) {
     cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemsetAsync(c->pb.stats, 0, sizeof(DeviceStats), c->stream));
     for (auto& L : c->extra) if (L.pb.stats) CU(c, cudaMemsetAsync(L.pb.stats, 0, sizeof(DeviceStats), L.s));   // the lane's own stream already waits for the join
+    for (auto& L : c->deferred) if (L.pb.stats) CU(c, cudaMemsetAsync(L.pb.stats, 0, sizeof(DeviceStats), L.s));
     return HRC_OK;
 }
 HRC_API int hrcTimerStart(HrcContext c) {

@@ -260,6 +260,12 @@ HRC_API int hrcRenderPass(HrcContext ctx, const HrcFrameParams* frame, HrcPassSt
  * a sum, accumulator.rlsl:27). Every other entry point folds those buffers into the one the caller sees first, so this is not
  * observable except through fp32 addition order; the result is deterministic for a given sequence of calls. */
 HRC_API int hrcEnqueuePass(HrcContext ctx, const HrcFrameParams* frame);
+/* A deferred pass renders like hrcEnqueuePass but into a side buffer that no other call sees until hrcCommitDeferred (then the next
+ * read / resolve / pass folds it in); hrcDiscardDeferred drops it. One at a time. It lets a caller that already knows its next pass
+ * start it before reading the current result back: the host copy of pass i then overlaps the rendering of pass i+1. */
+HRC_API int hrcEnqueuePassDeferred(HrcContext ctx, const HrcFrameParams* frame);
+HRC_API int hrcCommitDeferred(HrcContext ctx);
+HRC_API int hrcDiscardDeferred(HrcContext ctx);
 HRC_API int hrcSynchronize(HrcContext ctx);
 HRC_API int hrcResetStats(HrcContext ctx);
 /* CUDA-event stopwatch on the context's stream: Start records, Stop records + waits and returns the device time between them. */

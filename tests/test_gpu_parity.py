@@ -193,6 +193,44 @@ def test_band_sharding_matches_full_frame(gpu_backend):
     assert np.array_equal(total, full)
 
 
+def test_deferred_pass_is_invisible_until_committed(gpu_backend, oracle_backend):
+    """hrcEnqueuePassDeferred / hrcCommitDeferred / hrcDiscardDeferred, mirrored by the oracle: the side pass shows up in no read, resolve
+    or further pass until it is committed; discarding it leaves no trace; one at a time."""
+    spec = SMALL["cornell"]()
+    out = []
+    for b in (oracle_backend, gpu_backend):
+        r = renderer.Renderer(b)
+        r.load_scene(spec)
+        r.render_pass(sample_index=0)
+        p0 = r.pixels().copy()
+        r.frame.sampleIndex = 1
+        b.enqueue_pass_deferred(r.frame)
+        assert np.array_equal(r.pixels(), p0)                                  # not visible
+        with pytest.raises(capi.HrcError):
+            b.enqueue_pass_deferred(r.frame)                                   # one at a time
+        r.render_pass(sample_index=2)                                          # other passes go on without it
+        p02 = r.pixels().copy()
+        assert (p02[..., 3] == 2).all()
+        b.commit_deferred()
+        p012 = r.pixels().copy()
+        assert (p012[..., 3] == 3).all()
+        with pytest.raises(capi.HrcError):
+            b.commit_deferred()                                                # nothing pending any more
+        r.frame.sampleIndex = 3
+        b.enqueue_pass_deferred(r.frame)
+        b.discard_deferred()
+        b.discard_deferred()                                                   # idempotent
+        assert np.array_equal(r.pixels(), p012)
+        b.clear()
+        for i in range(3):
+            r.render_pass(sample_index=i)
+        serial = r.pixels().copy()
+        assert np.allclose(p012, serial, rtol=1e-5, atol=1e-6) and np.array_equal(p012[..., 3], serial[..., 3])
+        out.append(p012)
+    close = np.isclose(out[1][..., :3], out[0][..., :3], rtol=1e-3, atol=1e-4).all(-1)
+    assert close.mean() >= 0.99
+
+
 def test_band_readback_copies_only_own_rows_and_stays_exact(gpu_backend):
     """hrcReadPixels in band mode moves only the context's rows; the host frame must still equal the device frame in every situation
     that can put data outside the bands (full-frame pass, hrcAddPixels, a changed band set, the device pointer handed out)."""

@@ -58,8 +58,33 @@ def test_pass_generator_matches_direct_backend(lib, gpu_backend):
         lib.hrhPassGeneratorWaitIdle(pg)
         assert lib.hrhPassGeneratorLastError(pg) == b""
         assert [g[0] for g in got] == [1, 1, 1] and [g[1] for g in got] == [1, 2, 3]
-        assert np.array_equal(got[-1][2], want)
-        assert (got[0][2][..., 3] == 1).all()
+        # the three jobs were queued together, so passes 2 and 3 were rendered ahead into the deferred buffer while the previous result
+        # was read back: same samples, folded in as one addition per pass (fp32 rounding of the sum order)
+        assert np.array_equal(got[-1][2][..., 3], want[..., 3]) and np.allclose(got[-1][2], want, rtol=1e-5, atol=1e-6)
+        assert (got[0][2][..., 3] == 1).all() and (got[1][2][..., 3] == 2).all()      # every callback sees exactly its own pass count
+        # submitted one at a time there is nothing to look ahead to: bit-identical to the direct path
+        got.clear()
+        for i in range(3):
+            o.resetInternalState = 1 if i == 0 else 0
+            lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+            lib.hrhPassGeneratorWaitIdle(pg)
+        assert [g[1] for g in got] == [1, 2, 3] and np.array_equal(got[-1][2], want)
+        # a reset queued right behind a pass drops the pass rendered ahead
+        got.clear()
+        o.resetInternalState = 1
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        o.resetInternalState = 0
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        o.resetInternalState = 1
+        lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        o.resetInternalState = 0
+        for i in range(2):
+            lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert lib.hrhPassGeneratorLastError(pg) == b""
+        assert [g[1] for g in got] == [1, 2, 1, 2, 3]
+        assert np.array_equal(got[-1][2][..., 3], want[..., 3]) and np.allclose(got[-1][2], want, rtol=1e-5, atol=1e-6)
+        assert np.allclose(got[1][2], got[3][2], rtol=1e-5, atol=1e-6)
 
         # offline mode: all passes inside one job, pixels only at the end (PassGenerator.cpp:346-400)
         got.clear()
