@@ -303,6 +303,26 @@ __device__ __forceinline__ float byteToUnitFloat(uint32_t q) {
     return __uint_as_float(__byte_perm(q, 0x3F800000u, 0x7604u + (J << 4)));
 }
 
+// Traversal stack of a lane. With HR_SMEM_STACK = N > 0 the N entries nearest the root of the stack live in shared memory
+// ([entry][thread], conflict-free: a lane always hits its own bank pair) and only deeper entries go to thread-local memory.
+#ifndef HR_SMEM_STACK
+#define HR_SMEM_STACK 0
+#endif
+struct TraceStack {
+    uint2 deep[kTraceStack - HR_SMEM_STACK];
+#if HR_SMEM_STACK > 0
+    uint2* sh;
+    __device__ __forceinline__ void bind(uint2* blockShared) { sh = blockShared + threadIdx.x; }
+    __device__ __forceinline__ void put(int i, uint2 v) { if (i < HR_SMEM_STACK) sh[i * 128] = v; else deep[i - HR_SMEM_STACK] = v; }
+    __device__ __forceinline__ uint2 get(int i) const { return i < HR_SMEM_STACK ? sh[i * 128] : deep[i - HR_SMEM_STACK]; }
+#define HR_DECLARE_TRACE_STACK(NAME) __shared__ uint2 NAME##_sh[HR_SMEM_STACK * 128]; TraceStack NAME; NAME.bind(NAME##_sh)
+#else
+    __device__ __forceinline__ void put(int i, uint2 v) { deep[i] = v; }
+    __device__ __forceinline__ uint2 get(int i) const { return deep[i]; }
+#define HR_DECLARE_TRACE_STACK(NAME) TraceStack NAME
+#endif
+};
+
 // Per-lane traversal state. A lane keeps it across the warp-synchronous phases of k_trace (node step, triangle rounds,
 // refill), so a warp tops itself up with fresh rays while slow rays are still in flight.
 struct Traversal {
@@ -336,12 +356,12 @@ struct Traversal {
     // Pops the nearest pending child of `group`, tests its 8 children, leaves the hit internal children in `group` and
     // files the hit leaf triangles as a pending triangle group.
     template <bool STATS, bool ANY>
-    __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, uint2* stack, TraceCounters& tc) {
+    __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, TraceStack& stack, TraceCounters& tc) {
         const uint32_t hits = group.y;
         const uint32_t bit = 31u - __clz(hits);                  // highest set bit = nearest remaining child
         group.y &= ~(1u << bit);
         if (group.y & 0xff000000u) {
-            if (sp < kTraceStack) stack[sp++] = group; else if (STATS) tc.overflow++;
+            if (sp < kTraceStack) stack.put(sp++, group); else if (STATS) tc.overflow++;
         }
         const uint32_t slot = (bit - 24u) ^ (octInv & 7u);
         const uint32_t rel = __popc(hits & ~(0xffffffffu << slot));   // internal children stored before this slot
@@ -412,8 +432,8 @@ struct Traversal {
     }
 
     // Takes the next node group from the stack when the current one is used up.
-    __device__ __forceinline__ void popIfEmpty(const uint2* stack) {
-        if (!hasNodeWork() && sp > 0) group = stack[--sp];
+    __device__ __forceinline__ void popIfEmpty(const TraceStack& stack) {
+        if (!hasNodeWork() && sp > 0) group = stack.get(--sp);
     }
 
     // Tests ONE pending triangle. Returns true when an any-hit ray is finished.
@@ -441,7 +461,7 @@ struct Traversal {
 // Plain per-thread traversal (the hrcTraceRays parity hook): same steps, no warp scheduling.
 template <bool ANY>
 __device__ __forceinline__ void traverseSimple(const float4* __restrict__ nodes, const float4* __restrict__ tris, Traversal& tr) {
-    uint2 stack[kTraceStack];
+    HR_DECLARE_TRACE_STACK(stack);
     TraceCounters tc{0u, 0u, 0u};
     for (;;) {
         if (tr.hasNodeWork()) tr.nodeStep<false, ANY>(nodes, stack, tc);
@@ -554,7 +574,7 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
     const float4* __restrict__ tris = sc.tris;
     TraceCounters tc{0u, 0u, 0u};
     Traversal tr;
-    uint2 stack[kTraceStack];
+    HR_DECLARE_TRACE_STACK(stack);
     bool active = false, exhausted = false;
     uint32_t rayIdx = 0, doneIdx = 0;
     int doneClass = -1;                      // closest-hit only: class of a finished ray not yet appended to its list
