@@ -1074,6 +1074,10 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
 #ifndef HR_SHADE_MIN_BLOCKS
 #define HR_SHADE_MIN_BLOCKS 4
 #endif
+#ifndef HR_SHADE_PREFETCH
+#define HR_SHADE_PREFETCH 0
+#endif
+__device__ __forceinline__ void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 template <int CLS>
 __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -1087,13 +1091,38 @@ __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene
     const int hardCap = fr.g.maxRayDepth + 16;                                // policy A-14
     const bool lastIter = (iter + 1 >= kMaxIterations);
 
+#if HR_SHADE_PREFETCH
+    // The list entries of the next two trips are loaded ahead; the ray and hit records of the next trip are pulled into L2
+    // while this trip shades (they are streamed from DRAM otherwise: three dependent misses before the first FMA).
+    const uint32_t stride = warpsTotal * 32u;
+    uint32_t iNext = 0xffffffffu, iNext2 = 0xffffffffu;
+    if (CLS != 0) {
+        const uint32_t k0 = warpId * 32u + lane;
+        if (k0 < count) iNext = list[k0];
+        if (k0 + stride < count) iNext2 = list[k0 + stride];
+    }
+#endif
     for (uint32_t base = warpId * 32u; base < count; base += warpsTotal * 32u) {
         const uint32_t k = base + lane;
         Emit e; e.hasOcc = false; e.hasExt = false;
         InRay in; in.depth = 0; in.pixel = 0; in.sequenceID = 0; in.sequenceIndexOffset = 0;
         uint32_t inMissKind = 0;
+#if HR_SHADE_PREFETCH
+        const uint32_t iCur = iNext;
+        if (CLS != 0) {
+            iNext = iNext2;
+            iNext2 = (k + 2u * stride < count) ? list[k + 2u * stride] : 0xffffffffu;
+            if (iNext != 0xffffffffu) {
+                prefetchL2(rq.od + 2 * (size_t)iNext); prefetchL2(rq.wm + 2 * (size_t)iNext); prefetchL2(pb.hits + iNext);
+            }
+        }
+#endif
         if (k < count) {
+#if HR_SHADE_PREFETCH
+            const size_t i = CLS != 0 ? iCur : list[k];
+#else
             const size_t i = list[k];
+#endif
             const float4 rd = __ldcs(rq.od + 2 * i + 1), rw = __ldcs(rq.wm + 2 * i), rm = __ldcs(rq.wm + 2 * i + 1);
             const uint32_t mx = __float_as_uint(rm.x);
             in.d = xyz(rd); in.weight = xyz(rw);
