@@ -385,7 +385,11 @@ struct Traversal {
         const float Bnx = Bx - ex_, Bny = By - ey_, Bnz = Bz - ez_;
         const float Bfx = Bx + ex_, Bfy = By + ey_, Bfz = Bz + ez_;
         const bool negX = !(octInv & 4u), negY = !(octInv & 2u), negZ = !(octInv & 1u);
+#if HR_TFAR_PRESCALE
+        const float tfar = (ANY ? tmaxRay : bestT) * 1.000001f;   // experiment: the tie guard once per node step instead of once per child
+#else
         const float tfar = ANY ? tmaxRay : bestT;   // occlusion rays cull against maxT only: bestT then tracks the nearest alpha-masked hit, which must not hide occluders
+#endif
         const uint32_t octInv4 = octInv * 0x01010101u;
 
         uint32_t hitMask = 0;
@@ -402,6 +406,11 @@ struct Traversal {
             const uint32_t nx = negX ? qhix : qlox, fx = negX ? qlox : qhix;
             const uint32_t ny = negY ? qhiy : qloy, fy = negY ? qloy : qhiy;
             const uint32_t nz = negZ ? qhiz : qloz, fz = negZ ? qloz : qhiz;
+#if HR_TFAR_PRESCALE
+#define HR_TIE_GUARD(X) (X)
+#else
+#define HR_TIE_GUARD(X) ((X) * 1.000001f)
+#endif
 #define HR_PLANES(Q, SEL, A, B, LO, HI)                                                                                \
             { const uint32_t h_ = __byte_perm(Q, 0x64646464u, SEL);   /* two fp16 magic numbers 1024 + q in one PRMT */  \
               const __half2 hv_ = *reinterpret_cast<const __half2*>(&h_);                                               \
@@ -410,7 +419,7 @@ struct Traversal {
             {                                                                                                          \
                 const float tn = fmaxf(fmaxf(TNX, TNY), fmaxf(TNZ, tmin));                                              \
                 const float tf = fminf(fminf(TFX, TFY), fminf(TFZ, tfar));                                              \
-                if (tn <= tf * 1.000001f) /* conservative: rounding must never cull an exact tie */                     \
+                if (tn <= HR_TIE_GUARD(tf)) /* conservative: rounding must never cull an exact tie */                   \
                     hitMask |= byteOf(childBits4, J) << byteOf(bitIndex4, J);                                           \
             }
 #define HR_PAIR(J0, J1, SEL)                                                                                           \
@@ -424,6 +433,7 @@ struct Traversal {
 #undef HR_PAIR
 #undef HR_HIT
 #undef HR_PLANES
+#undef HR_TIE_GUARD
         }
         group.x = __float_as_uint(n1.x);
         group.y = (hitMask & 0xff000000u) | (eimask >> 24);
@@ -558,6 +568,10 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_co
 // them in warp-wide rounds (triangle-test lane utilisation doubled, node-step utilisation and scheduling overhead ate the
 // gain), and "one node step or one triangle per trip".
 constexpr uint32_t kFull = 0xffffffffu;
+__device__ __forceinline__ void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+#ifndef HR_RAY_PREFETCH_AHEAD
+#define HR_RAY_PREFETCH_AHEAD 0
+#endif
 
 #ifndef HR_TRACE_MIN_BLOCKS
 #define HR_TRACE_MIN_BLOCKS 8
@@ -607,6 +621,13 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                     const uint32_t i = base + __popc(idle & below);
                     if (i < count) {
                         const float4 ro = __ldcs(ANY ? pb.shadow.o + i : qod + 2 * (size_t)i), rd = __ldcs(ANY ? pb.shadow.d + i : qod + 2 * (size_t)i + 1);   // streamed: keep the BVH in L2
+#if HR_RAY_PREFETCH_AHEAD > 0
+                        // the queue is consumed in index order by all warps together: pull the ray HR_RAY_PREFETCH_AHEAD places further on into L2
+                        if (i + HR_RAY_PREFETCH_AHEAD < count) {
+                            if (ANY) { prefetchL2(pb.shadow.o + i + HR_RAY_PREFETCH_AHEAD); prefetchL2(pb.shadow.d + i + HR_RAY_PREFETCH_AHEAD); }
+                            else prefetchL2(qod + 2 * (size_t)(i + HR_RAY_PREFETCH_AHEAD));
+                        }
+#endif
                         rayIdx = i;
                         tr.begin(xyz(ro), xyz(rd), 0.0f, ro.w);
                         if (MASKED) { extraT = rd.w; maskedPasses = 0; }
@@ -1077,7 +1098,6 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
 #ifndef HR_SHADE_PREFETCH
 #define HR_SHADE_PREFETCH 0
 #endif
-__device__ __forceinline__ void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 template <int CLS>
 __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
     const uint32_t lane = threadIdx.x & 31u;
