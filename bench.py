@@ -333,22 +333,26 @@ def main():
     # The same K steps the way hr::PassGenerator runs them when the caller keeps its next renderPass job queued (host_pass_generator.cpp:
     # look-ahead): pass i+1 is started into the backend's deferred buffer before pass i is read back, so the host copy of every pass
     # (still one full readback per step, each holding exactly i+1 samples) overlaps the rendering of the next one.
+    lookahead = max(1, min(3, int(os.environ.get("HR_BENCH_LOOKAHEAD", "3"))))      # HRC_MAX_DEFERRED_PASSES = 3
+
     def pipelined_steps(n):
         total = 0.0
         r.frame.sampleIndex = sidx(0)
         b.enqueue_pass(r.frame)
+        nxt = 1
         for i in range(n):
-            if i + 1 < n:
-                r.frame.sampleIndex = sidx(i + 1)
+            while nxt < n and nxt - i <= lookahead:          # passes i+1 .. i+lookahead render while pass i is copied to the host
+                r.frame.sampleIndex = sidx(nxt)
                 b.enqueue_pass_deferred(r.frame)
+                nxt += 1
             px = b.map_pixels()
             total += float(px[0, 0, 3])
             b.unmap_pixels()
             if i + 1 < n:
-                b.commit_deferred()
+                b.commit_deferred()                          # the oldest pending pass: i+1
         return total
 
-    pipelined_steps(max(3, W))                    # untimed warm-up: the deferred buffers are allocated on first use
+    pipelined_steps(max(8, W))                    # untimed warm-up: the deferred buffers (a ring of 4) are allocated on first use
     b.clear()
     barrier()
     t0 = time.perf_counter()
@@ -404,14 +408,15 @@ def main():
                                                                  "scene_bytes": int(info.nodeBytes + info.triangleBytes + info.shadingBytes),
                                                                  "pass_pipelining": "value: the K passes are enqueued back to back (hrcEnqueuePass, the reference's offline mode) and rotate over %s sets of "
                                                                                     "queues / accumulation buffers, so the latency-bound tail of a pass overlaps the head of the next; "
-                                                                                    "e2e: pass i+1 renders into the deferred buffer while pass i is read back (e2e.serial: one step at a time)" % os.environ.get("HRC_TUNE_PASS_LANES", "4")}),
+                                                                                    "e2e: passes i+1 .. i+%d render into deferred buffers while pass i is read back (e2e.serial: one step at a time)" % (os.environ.get("HRC_TUNE_PASS_LANES", "4"), lookahead)}),
                 "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K,
                 "clocks": clocks, "roofline": roof,
                 "e2e": {"value": rays_all / (e2e_ms / 1e3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms / K,
                         "h2d_bytes_per_step": C.sizeof(capi.FrameParams),
                         "d2h_bytes_per_step": frame_bytes if not (shard == "bands" and world > 1) else frame_bytes // world,   # band mode reads back only the rank's own rows
-                        "api": "per step: hrcEnqueuePassDeferred (the next pass) + hrcReadPixels/hrcReleasePixels (this pass, pinned host buffer) + hrcCommitDeferred - what "
-                               "hr::PassGenerator::renderPass does when the caller keeps its next job queued; every step delivers its own full frame to the host",
+                        "api": "per step: hrcEnqueuePassDeferred (keeps %d passes ahead) + hrcReadPixels/hrcReleasePixels (this pass, pinned host buffer) + hrcCommitDeferred (the next pass) - "
+                               "hr::PassGenerator::renderPass's look-ahead for a caller that keeps its next jobs queued; every step delivers its own full frame to the host" % lookahead,
+                        "lookahead": lookahead,
                         "serial": {"value": rays_all / (e2e_serial_ms / 1e3) / 1e6, "ms_per_step": e2e_serial_ms / K,
                                    "api": "hrcRenderPass + hrcReadPixels/hrcReleasePixels, one step at a time (the reference viewer's loop, HeatrayRenderer.cpp:366-408)"}},
                 "gpu_launches": launches + (0 if os.environ.get("HRC_TUNE_PASS_LANES") == "1" else 3)}       # + the lane joins (k_add_pixels) at the end of the timed region

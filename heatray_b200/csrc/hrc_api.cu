@@ -46,9 +46,12 @@ struct HrcContext_t {
     struct Lane { PassBuffers pb{}; cudaStream_t s = nullptr, s2 = nullptr; std::vector<cudaEvent_t> evSync; float4* accum = nullptr;
                   cudaEvent_t evDone = nullptr; bool active = false; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
     int passLanes = 4, nextLane = 0;
-    // Deferred passes (hrcEnqueuePassDeferred): rendered into one of two side lanes that joins ignore until hrcCommitDeferred, so a
-    // caller can already render pass i+1 while pass i is being read back (hr::PassGenerator does that when its next job is queued).
-    Lane deferred[2]; int deferredNext = 0, deferredPending = -1;
+    // Deferred passes (hrcEnqueuePassDeferred): rendered into side lanes that joins ignore until hrcCommitDeferred, so a caller can
+    // already render passes i+1 .. i+3 while pass i is being read back (hr::PassGenerator does that when its next job is queued).
+    // A ring: the deferredCount lanes before deferredNext are pending, oldest first; one lane more than may be pending, so the lane
+    // a new pass takes is either free or holds a committed pass that the next join folds in.
+    Lane deferred[kDeferredLanes]; int deferredNext = 0, deferredCount = 0;
+    int oldestDeferred() const { return (deferredNext - deferredCount + kDeferredLanes) % kDeferredLanes; }
     // Band bookkeeping for the readback: while every pass since the last clear rendered the same set of screen bands, pixels outside
     // them are zero on the device and hrcReadPixels copies only the context's own rows.
     int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
@@ -124,7 +127,7 @@ void joinLanes(HrcContext c) {
         any = true;
     };
     for (auto& L : c->extra) fold(L);
-    for (auto& L : c->deferred) fold(L);          // committed deferred passes only: a pending one keeps running, invisible
+    for (int k = 0; k < kDeferredLanes; ++k) fold(c->deferred[(c->deferredNext + k) % kDeferredLanes]);   // committed deferred passes only, in commit order (ring order from the next free lane); pending ones keep running, invisible
     if (!any) return;
     cudaEventRecord(c->evMerged, c->stream);
     auto release = [&](HrcContext_t::Lane& L) { if (L.active) { cudaStreamWaitEvent(L.s, c->evMerged, 0); L.active = false; } };
@@ -133,12 +136,13 @@ void joinLanes(HrcContext c) {
 }
 // For calls that free or rewrite what a pending deferred pass still reads (resize, scene / table uploads): wait for it.
 void waitPendingDeferred(HrcContext c) {
-    if (c->deferredPending >= 0 && c->deferred[c->deferredPending].s) cudaStreamSynchronize(c->deferred[c->deferredPending].s);
+    for (int k = 0, d = c->oldestDeferred(); k < c->deferredCount; ++k, d = (d + 1) % kDeferredLanes)
+        if (c->deferred[d].s) cudaStreamSynchronize(c->deferred[d].s);
 }
 void freeExtraLanes(HrcContext c) {         // buffers that depend on the frame size; streams and counters stay
     for (auto& L : c->extra) { freeQueues(L.pb); freeDev(L.accum); L.active = false; }
     for (auto& L : c->deferred) { freeQueues(L.pb); freeDev(L.accum); L.active = false; }
-    c->nextLane = 0; c->deferredPending = -1;
+    c->nextLane = 0; c->deferredCount = 0;
 }
 int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
     if (L.accum) return HRC_OK;
@@ -288,7 +292,10 @@ HRC_API int hrcDestroyContext(HrcContext c) {
     joinLanes(c); waitPendingDeferred(c);
     cudaStreamSynchronize(c->stream);
     freeQueues(c->pb); freeExtraLanes(c);
-    for (HrcContext_t::Lane* Lp : {&c->extra[0], &c->extra[1], &c->extra[2], &c->deferred[0], &c->deferred[1]}) {
+    std::vector<HrcContext_t::Lane*> lanes;
+    for (auto& L : c->extra) lanes.push_back(&L);
+    for (auto& L : c->deferred) lanes.push_back(&L);
+    for (HrcContext_t::Lane* Lp : lanes) {
         HrcContext_t::Lane& L = *Lp;
         if (!L.s) continue;
         cudaStreamSynchronize(L.s); cudaStreamSynchronize(L.s2);
@@ -790,11 +797,11 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
 }
 
 static int readStats(HrcContext c, DeviceStats* out) {     // callers have joined the lanes: the main stream is ordered after lane 1
-    DeviceStats x[kMaxLanes - 1 + 2] = {};
+    DeviceStats x[kMaxLanes - 1 + kDeferredLanes] = {};
     CU(c, cudaMemcpyAsync(out, c->pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
     for (int k = 0; k < kMaxLanes - 1; ++k)
         if (c->extra[k].pb.stats) CU(c, cudaMemcpyAsync(&x[k], c->extra[k].pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
-    for (int k = 0; k < 2; ++k)            // deferred lanes: counters of passes that finished (a pending pass adds its own when it ends)
+    for (int k = 0; k < kDeferredLanes; ++k)            // deferred lanes: counters of passes that finished (a pending pass adds its own when it ends)
         if (c->deferred[k].pb.stats) CU(c, cudaMemcpyAsync(&x[kMaxLanes - 1 + k], c->deferred[k].pb.stats, sizeof(DeviceStats), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     for (const DeviceStats& b : x) {
@@ -843,35 +850,37 @@ HRC_API int hrcEnqueuePass(HrcContext c, const HrcFrameParams* fp) {
     if (r == HRC_OK && lane > 0) c->extra[lane - 1].active = true;
     return r;
 }
-// Deferred pass: rendered like hrcEnqueuePass, but into a side buffer that no other call sees until hrcCommitDeferred. One at a time.
-// Lets a caller that already knows its next pass start it before it reads the current result back (hr::PassGenerator look-ahead).
+// Deferred pass: rendered like hrcEnqueuePass, but into a side buffer that no other call sees until hrcCommitDeferred. Up to
+// kDeferredLanes - 1 may be pending; they are committed oldest first. Lets a caller that already knows its next passes start them
+// before it reads the current result back (hr::PassGenerator look-ahead).
 HRC_API int hrcEnqueuePassDeferred(HrcContext c, const HrcFrameParams* fp) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    if (c->deferredPending >= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "a deferred pass is already pending (commit or discard it first)");
+    if (c->deferredCount >= kDeferredLanes - 1) return fail(c, HRC_ERR_INVALID_OPERATION, "too many deferred passes are pending (commit or discard first)");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
     cudaSetDevice(c->device);
     const int d = c->deferredNext;
     if (c->deferred[d].active) joinLanes(c);                      // its previous pass was committed but not folded in yet
     int r = ensureLane(c, c->deferred[d]); if (r) return r;
-    r = enqueuePass(c, fp, false, nullptr, nullptr, -(d + 1), false);
-    if (r == HRC_OK) { c->deferredPending = d; c->deferredNext = d ^ 1; }
+    r = enqueuePass(c, fp, false, nullptr, nullptr, -(d + 1), c->deferredCount >= 1);     // several in flight: the pipelined launch shape (fewer traversal CTAs per SM each)
+    if (r == HRC_OK) { c->deferredNext = (d + 1) % kDeferredLanes; c->deferredCount++; }
     return r;
 }
 HRC_API int hrcCommitDeferred(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    if (c->deferredPending < 0) return fail(c, HRC_ERR_INVALID_OPERATION, "no deferred pass is pending");
-    c->deferred[c->deferredPending].active = true;                // the next join folds it in (and waits for it, in stream order)
-    c->deferredPending = -1;
+    if (c->deferredCount <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "no deferred pass is pending");
+    c->deferred[c->oldestDeferred()].active = true;               // the next join folds it in (and waits for it, in stream order)
+    c->deferredCount--;
     return HRC_OK;
 }
 HRC_API int hrcDiscardDeferred(HrcContext c) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
-    if (c->deferredPending < 0) return HRC_OK;
+    if (c->deferredCount <= 0) return HRC_OK;
     cudaSetDevice(c->device);
-    HrcContext_t::Lane& L = c->deferred[c->deferredPending];
-    CU(c, cudaMemsetAsync(L.accum, 0, (size_t)c->w * c->h * sizeof(float4), L.s));      // after its kernels, in stream order
-    CU(c, cudaStreamSynchronize(L.s));                          // rare (reset, scene change): whatever follows may free what the pass was reading
-    c->deferredPending = -1;
+    for (int d = c->oldestDeferred(); c->deferredCount > 0; d = (d + 1) % kDeferredLanes, c->deferredCount--) {      // all pending passes
+        HrcContext_t::Lane& L = c->deferred[d];
+        CU(c, cudaMemsetAsync(L.accum, 0, (size_t)c->w * c->h * sizeof(float4), L.s));      // after its kernels, in stream order
+        CU(c, cudaStreamSynchronize(L.s));                      // rare (reset, scene change): whatever follows may free what the pass was reading
+    }
     return HRC_OK;
 }
 HRC_API int hrcSynchronize(HrcContext c) {

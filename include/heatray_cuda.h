@@ -261,8 +261,10 @@ HRC_API int hrcRenderPass(HrcContext ctx, const HrcFrameParams* frame, HrcPassSt
  * observable except through fp32 addition order; the result is deterministic for a given sequence of calls. */
 HRC_API int hrcEnqueuePass(HrcContext ctx, const HrcFrameParams* frame);
 /* A deferred pass renders like hrcEnqueuePass but into a side buffer that no other call sees until hrcCommitDeferred (then the next
- * read / resolve / pass folds it in); hrcDiscardDeferred drops it. One at a time. It lets a caller that already knows its next pass
- * start it before reading the current result back: the host copy of pass i then overlaps the rendering of pass i+1. */
+ * read / resolve / pass folds it in). Up to HRC_MAX_DEFERRED_PASSES may be pending; hrcCommitDeferred commits the oldest one,
+ * hrcDiscardDeferred drops all that are pending. It lets a caller that already knows its next passes start them before reading the
+ * current result back: the host copy of pass i then overlaps the rendering of passes i+1 .. i+3. */
+#define HRC_MAX_DEFERRED_PASSES 3
 HRC_API int hrcEnqueuePassDeferred(HrcContext ctx, const HrcFrameParams* frame);
 HRC_API int hrcCommitDeferred(HrcContext ctx);
 HRC_API int hrcDiscardDeferred(HrcContext ctx);

@@ -195,7 +195,7 @@ def test_band_sharding_matches_full_frame(gpu_backend):
 
 def test_deferred_pass_is_invisible_until_committed(gpu_backend, oracle_backend):
     """hrcEnqueuePassDeferred / hrcCommitDeferred / hrcDiscardDeferred, mirrored by the oracle: the side pass shows up in no read, resolve
-    or further pass until it is committed; discarding it leaves no trace; one at a time."""
+    or further pass until it is committed; discarding it leaves no trace."""
     spec = SMALL["cornell"]()
     out = []
     for b in (oracle_backend, gpu_backend):
@@ -206,8 +206,6 @@ def test_deferred_pass_is_invisible_until_committed(gpu_backend, oracle_backend)
         r.frame.sampleIndex = 1
         b.enqueue_pass_deferred(r.frame)
         assert np.array_equal(r.pixels(), p0)                                  # not visible
-        with pytest.raises(capi.HrcError):
-            b.enqueue_pass_deferred(r.frame)                                   # one at a time
         r.render_pass(sample_index=2)                                          # other passes go on without it
         p02 = r.pixels().copy()
         assert (p02[..., 3] == 2).all()
@@ -227,6 +225,55 @@ def test_deferred_pass_is_invisible_until_committed(gpu_backend, oracle_backend)
         serial = r.pixels().copy()
         assert np.allclose(p012, serial, rtol=1e-5, atol=1e-6) and np.array_equal(p012[..., 3], serial[..., 3])
         out.append(p012)
+    close = np.isclose(out[1][..., :3], out[0][..., :3], rtol=1e-3, atol=1e-4).all(-1)
+    assert close.mean() >= 0.99
+
+
+def test_up_to_three_deferred_passes_commit_oldest_first(gpu_backend, oracle_backend):
+    """Three passes may be pending at once (a fourth is refused); each commit makes exactly the oldest one visible, a discard drops
+    all that are still pending, and the sum equals the same passes rendered one after the other."""
+    spec = SMALL["cornell"]()
+    out = []
+    for b in (oracle_backend, gpu_backend):
+        r = renderer.Renderer(b)
+        r.load_scene(spec)
+        singles = []
+        for i in range(4):
+            b.clear()
+            r.render_pass(sample_index=i)
+            singles.append(r.pixels().copy())
+        b.clear()
+        r.render_pass(sample_index=0)
+        for i in (1, 2, 3):
+            r.frame.sampleIndex = i
+            b.enqueue_pass_deferred(r.frame)
+        with pytest.raises(capi.HrcError):
+            b.enqueue_pass_deferred(r.frame)                                   # a fourth pending pass
+        assert np.array_equal(r.pixels(), singles[0])
+        want = singles[0].copy()
+        for i in (1, 2):
+            b.commit_deferred()
+            want = want + singles[i]
+            got = r.pixels().copy()
+            assert (got[..., 3] == i + 1).all()
+            assert np.allclose(got, want, rtol=1e-5, atol=1e-6)
+        r.frame.sampleIndex = 1
+        b.enqueue_pass_deferred(r.frame)                                       # the ring wraps: pass 3 and this one are pending
+        b.discard_deferred()                                                   # drops both
+        with pytest.raises(capi.HrcError):
+            b.commit_deferred()
+        assert np.allclose(r.pixels(), want, rtol=1e-5, atol=1e-6)
+        for k in range(6):                                                     # steady state of a look-ahead of two, around the ring
+            r.frame.sampleIndex = k % 4
+            b.enqueue_pass_deferred(r.frame)
+            if k >= 1:
+                b.commit_deferred()
+                want = want + singles[(k - 1) % 4]
+                got = r.pixels().copy()
+                assert (got[..., 3] == 3 + k).all()
+                assert np.allclose(got, want, rtol=1e-5, atol=1e-5)
+        b.discard_deferred()
+        out.append(got)
     close = np.isclose(out[1][..., :3], out[0][..., :3], rtol=1e-3, atol=1e-4).all(-1)
     assert close.mean() >= 0.99
 
