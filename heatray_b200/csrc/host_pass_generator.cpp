@@ -86,11 +86,17 @@ private:
         m_cv.notify_one();
     }
     // Look-ahead for runRenderFrameJob: is the job right behind the running one another pass of the same progressive render (no reset)?
-    bool nextJobContinuesTheRender() {
+    // How many of the jobs queued right behind the running one (up to HRC_MAX_DEFERRED_PASSES) continue the same progressive render.
+    int queuedContinuations() {
         std::lock_guard<std::mutex> g(m_mutex);
-        if (m_jobs.empty() || !m_jobs.front().isRender) return false;
-        const HrhRenderOptions& n = m_jobs.front().options;
-        return !n.resetInternalState && n.enableInteractiveMode == m_options.enableInteractiveMode && n.enableOfflineMode == m_options.enableOfflineMode;
+        int k = 0;
+        for (const auto& j : m_jobs) {
+            if (k >= HRC_MAX_DEFERRED_PASSES || !j.isRender) break;
+            const HrhRenderOptions& n = j.options;
+            if (n.resetInternalState || n.enableInteractiveMode != m_options.enableInteractiveMode || n.enableOfflineMode != m_options.enableOfflineMode) break;
+            ++k;
+        }
+        return k;
     }
     void workerLoop() {
         for (;;) {
@@ -175,7 +181,7 @@ private:
         check(hrcSetEnvironment(m_ctx, &env));
     }
 
-    void dropPrefetchedPass() { if (m_prefetched && m_ctx) { hrcDiscardDeferred(m_ctx); m_prefetched = false; } }
+    void dropPrefetchedPass() { if (!m_prefetched.empty() && m_ctx) hrcDiscardDeferred(m_ctx); m_prefetched.clear(); }
 
     void resetRenderingState(const HrhRenderOptions& n) {                // PassGenerator.cpp:435-577
         dropPrefetchedPass();
@@ -228,18 +234,21 @@ private:
                 }
             } else ++m_currentSampleIndex;
             int rc;
-            if (m_prefetched && std::memcmp(&m_prefetchedFrame, &f, sizeof(f)) == 0) { rc = hrcCommitDeferred(m_ctx); m_prefetched = false; }   // this pass was rendered ahead
+            if (!m_prefetched.empty() && std::memcmp(&m_prefetched.front(), &f, sizeof(f)) == 0) { rc = hrcCommitDeferred(m_ctx); m_prefetched.pop_front(); }   // this pass was rendered ahead
             else { dropPrefetchedPass(); rc = hrcEnqueuePass(m_ctx, &f); }  // rlRenderFrame(), :386
             check(rc);
             jobCompleted = rc != HRC_OK || !(m_options.enableOfflineMode && m_currentSampleIndex < m_options.maxRenderPasses);   // :390
-            // Look-ahead: when the caller has already queued the next pass of this progressive render, start it now, into a deferred
-            // buffer, so that it renders while this pass is copied to the host and handed to the callback. The frame constants of that
-            // pass are fully determined here (no reset: the queued job's own options are not consulted, :334-339).
-            if (jobCompleted && rc == HRC_OK && !m_options.enableOfflineMode && !m_options.enableInteractiveMode && !m_options.debugPassRendering &&
-                m_currentSampleIndex < m_options.maxRenderPasses && nextJobContinuesTheRender()) {
-                HrcFrameParams ahead = f;
-                ahead.sampleIndex = (int)m_currentSampleIndex;
-                if (hrcEnqueuePassDeferred(m_ctx, &ahead) == HRC_OK) { m_prefetchedFrame = ahead; m_prefetched = true; }
+            // Look-ahead: when the caller has already queued the next passes of this progressive render (up to three), start them now,
+            // into deferred buffers, so that they render while this pass is copied to the host and handed to the callback. The frame
+            // constants of those passes are fully determined here (no reset: the queued jobs' own options are not consulted, :334-339).
+            if (jobCompleted && rc == HRC_OK && !m_options.enableOfflineMode && !m_options.enableInteractiveMode && !m_options.debugPassRendering) {
+                const int want = queuedContinuations();
+                while ((int)m_prefetched.size() < want && m_currentSampleIndex + m_prefetched.size() < (size_t)m_options.maxRenderPasses) {
+                    HrcFrameParams ahead = f;
+                    ahead.sampleIndex = (int)(m_currentSampleIndex + m_prefetched.size());
+                    if (hrcEnqueuePassDeferred(m_ctx, &ahead) != HRC_OK) break;
+                    m_prefetched.push_back(ahead);
+                }
             }
             const float* pixels = nullptr;
             if (jobCompleted && rc == HRC_OK) {                            // setPixelData + map, :392-394 and HeatrayRenderer.cpp:391-395
@@ -262,7 +271,7 @@ private:
     HrhRenderOptions m_options{};
     HrcGlobals m_globals{};
     bool m_envApplied = false, m_globalsApplied = false, m_mapped = false;
-    bool m_prefetched = false; HrcFrameParams m_prefetchedFrame{};     // a pass rendered ahead into the backend's deferred buffer
+    std::deque<HrcFrameParams> m_prefetched;                           // passes rendered ahead into the backend's deferred buffers, oldest first
     HrcTexture m_solidTex = HRC_NULL_TEXTURE;
     uint32_t m_currentSampleIndex = 0;
     uint32_t m_blockShuffleSeed = 0x5eed;   // the reference seeds this shuffle from std::random_device (quirk B-Q6)

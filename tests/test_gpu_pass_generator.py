@@ -133,3 +133,51 @@ def test_pass_generator_matches_direct_backend(lib, gpu_backend):
         assert np.array_equal(got[0][2], inter)
     finally:
         lib.hrhPassGeneratorDestroy(pg)
+
+
+def test_pass_generator_keeps_three_passes_ahead(lib, gpu_backend):
+    """Six jobs queued together: the generator renders up to three passes (HRC_MAX_DEFERRED_PASSES) ahead of the readback; every callback
+    still sees exactly its own pass count and the sum equals the same passes rendered one after the other."""
+    spec = scenes.cornell_box(width=64, height=48, passes=8)
+    w, h = spec.width, spec.height
+    rg = renderer.Renderer(gpu_backend)
+    rg.load_scene(spec)
+    for _ in range(6):
+        rg.render_pass()
+    want = rg.pixels().copy()
+
+    pg = C.c_void_p()
+    assert lib.hrhPassGeneratorCreate(0, w, h, C.byref(pg)) == 0, lib.hrhPassGeneratorLastError(pg)
+    try:
+        def load(user, ctx):
+            b = capi.Backend(lib, "hrc", borrowed_ctx=ctx)
+            b.width, b.height = w, h
+            renderer.Renderer(b).upload_scene(spec, set_environment=False)
+        task = capi.CONTEXT_TASK(load)
+        lib.hrhPassGeneratorRunTask(pg, task, None)
+        got = []
+
+        def done(user, available, pixels, pw, ph, seconds, index):
+            got.append((available, index, np.ctypeslib.as_array(pixels, shape=(ph, pw, 4)).copy() if available else None))
+        cb = capi.PASS_COMPLETE_CALLBACK(done)
+        o = _options(lib, spec, w, h)
+        for i in range(6):
+            o.resetInternalState = 1 if i == 0 else 0
+            lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert lib.hrhPassGeneratorLastError(pg) == b""
+        assert [g[1] for g in got] == [1, 2, 3, 4, 5, 6]
+        for k, g in enumerate(got):
+            assert g[0] == 1 and (g[2][..., 3] == k + 1).all()
+        assert np.allclose(got[-1][2], want, rtol=1e-5, atol=1e-6)
+        # a reset in the queue bounds the look-ahead: nothing is rendered ahead across it
+        got.clear()
+        for i, reset in enumerate([1, 0, 0, 1, 0]):
+            o.resetInternalState = reset
+            lib.hrhPassGeneratorRenderPass(pg, C.byref(o), cb, None)
+        lib.hrhPassGeneratorWaitIdle(pg)
+        assert lib.hrhPassGeneratorLastError(pg) == b""
+        assert [g[1] for g in got] == [1, 2, 3, 1, 2]
+        assert (got[-1][2][..., 3] == 2).all()
+    finally:
+        lib.hrhPassGeneratorDestroy(pg)
