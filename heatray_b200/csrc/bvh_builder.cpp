@@ -42,6 +42,7 @@ constexpr uint32_t kMaxLeafLimit = 3;      // a child slot encodes at most 3 tri
 // Leaf policy: at most g_maxLeaf triangles, made a leaf when n * area <= g_travCost * area + SAH(best split). Defaults measured on B200
 // (profiles/); HRC_TUNE_MAX_LEAF / HRC_TUNE_TRAV_COST override them for experiments.
 uint32_t g_maxLeaf = 3; float g_travCost = 0.5f;
+bool g_splitLeaves = true;                // HRC_TUNE_SPLIT_LEAVES=0: keep multi-triangle leaves together even when the wide node has free slots
 #define kMaxLeaf g_maxLeaf
 
 struct Builder2 {
@@ -140,6 +141,7 @@ void buildWideBVH(const BuildTriangle* tris, size_t count, int threads, WideBVH&
     }
     if (const char* e = std::getenv("HRC_TUNE_MAX_LEAF")) g_maxLeaf = (uint32_t)std::max(1, std::min((int)kMaxLeafLimit, std::atoi(e)));
     if (const char* e = std::getenv("HRC_TUNE_TRAV_COST")) g_travCost = (float)std::atof(e);
+    if (const char* e = std::getenv("HRC_TUNE_SPLIT_LEAVES")) g_splitLeaves = std::atoi(e) != 0;
     if (const char* e = std::getenv("HRC_TUNE_BINS")) g_bins = std::max(2, std::min(kMaxBins, std::atoi(e)));
     if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
     if (threads < 1) threads = 1;
@@ -185,12 +187,33 @@ void buildWideBVH(const BuildTriangle* tris, size_t count, int threads, WideBVH&
             const Node2& c = nodes2[kids[best]];
             kids[best] = c.left; kids[nk++] = c.right;
         }
+        // Child records: inner kids keep their binary node; leaf kids carry (first, count, box) so that a leaf can be split further here.
+        struct Kid { uint32_t n2, first, count; Box box; };
+        Kid kid[8];
+        for (int k = 0; k < nk; ++k) { const Node2& c = nodes2[kids[k]]; kid[k] = Kid{kids[k], c.first, c.count, c.box}; }
+        // Free slots cost nothing in the node step (all 8 are evaluated): while some are left, peel triangles off multi-triangle leaves
+        // into children of their own, largest expected saving in triangle tests first (area(leaf) * n - area(tri) - area(rest) * (n - 1)).
+        if (g_splitLeaves) {
+            auto boxOf = [&](uint32_t first, uint32_t n) { Box b; b.reset(); for (uint32_t i = 0; i < n; ++i) { b.grow(prims[first + i].box.lo); b.grow(prims[first + i].box.hi); } return b; };
+            while (nk < 8) {
+                int best = -1; float bestGain = 0.0f; Box bestHead, bestRest;
+                for (int k = 0; k < nk; ++k) {
+                    if (kid[k].count < 2) continue;
+                    const Box head = boxOf(kid[k].first, 1), rest = boxOf(kid[k].first + 1, kid[k].count - 1);
+                    const float gain = kid[k].box.halfArea() * (float)kid[k].count - head.halfArea() - rest.halfArea() * (float)(kid[k].count - 1);
+                    if (gain > bestGain) { bestGain = gain; best = k; bestHead = head; bestRest = rest; }
+                }
+                if (best < 0) break;
+                kid[nk++] = Kid{0u, kid[best].first + 1, kid[best].count - 1, bestRest};
+                kid[best].count = 1; kid[best].box = bestHead;
+            }
+        }
         // octant-ordered slot assignment: greedily give each slot the child lying furthest along its sign vector
         int slotOf[8]; bool slotUsed[8] = {false}; bool kidDone[8] = {false};
         float pc[3]; for (int a = 0; a < 3; ++a) pc[a] = 0.5f * (src.box.lo[a] + src.box.hi[a]);
         float aff[8][8];
         for (int k = 0; k < nk; ++k) {
-            const Box& cb = nodes2[kids[k]].box;
+            const Box& cb = kid[k].box;
             float d[3]; for (int a = 0; a < 3; ++a) d[a] = 0.5f * (cb.lo[a] + cb.hi[a]) - pc[a];
             for (int s = 0; s < 8; ++s) aff[k][s] = slotAffinity(d, s);
         }
@@ -214,8 +237,7 @@ void buildWideBVH(const BuildTriangle* tris, size_t count, int threads, WideBVH&
         uint32_t triOffset = 0, innerCount = 0;
         for (int s = 0; s < 8; ++s) {
             if (kidAt[s] < 0) continue;
-            const uint32_t kid = kids[kidAt[s]];
-            const Node2& c = nodes2[kid];
+            const Kid& c = kid[kidAt[s]];
             for (int a = 0; a < 3; ++a) {
                 double cell = w.exp[a] ? std::ldexp(1.0, (int)w.exp[a] - 127) : 0.0;
                 int lo = 0, hi = 0;
@@ -229,7 +251,7 @@ void buildWideBVH(const BuildTriangle* tris, size_t count, int threads, WideBVH&
             if (c.count == 0) {
                 w.imask |= (uint8_t)(1u << s);
                 w.meta[s] = (uint8_t)(0x20 | (24 + s));
-                queue.push_back(Pending{kid, w.childBase + innerCount, cur.depth + 1});
+                queue.push_back(Pending{c.n2, w.childBase + innerCount, cur.depth + 1});
                 innerCount++;
             } else {
                 const uint32_t unary = (1u << c.count) - 1u;   // 1 -> 001, 2 -> 011, 3 -> 111

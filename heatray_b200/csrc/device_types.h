@@ -105,7 +105,7 @@ struct PassBuffers {
     uint32_t capacity;        // rays per queue
 };
 
-struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle; };
+struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle, refillIdleAny; };
 
 void launchClearCtrl(const PassBuffers& pb, cudaStream_t s);
 void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s);

@@ -39,7 +39,7 @@ struct HrcContext_t {
     std::vector<cudaEvent_t> evPool;
     std::string err;
     int smCount = 148;
-    int tuneRefillIdle = 10, tuneBlocksPerSM = 8;
+    int tuneRefillIdle = 10, tuneRefillIdleAny = 10, tuneBlocksPerSM = 8;
     // Extra lanes for hrcEnqueuePass: consecutive enqueued passes rotate over passLanes sets of queues / streams / accumulation buffers, so
     // the latency-bound tail of one pass (a few thousand rays per kernel) runs next to the head of the following one. Every other entry
     // point first joins the lanes (accum += the extra lanes' buffers), so callers see one buffer; the result is deterministic for a given call sequence.
@@ -169,7 +169,7 @@ DScene sceneOf(HrcContext c) {
 }
 LaunchConfig configOf(HrcContext c) {
     LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters;
-    lc.refillIdle = c->tuneRefillIdle; lc.traceBlocksPerSM = c->tuneBlocksPerSM;
+    lc.refillIdle = c->tuneRefillIdle; lc.refillIdleAny = c->tuneRefillIdleAny; lc.traceBlocksPerSM = c->tuneBlocksPerSM;
     lc.masked = c->anyMasked;
     lc.shadeMiss = c->lights.envEnabled != 0; lc.shadePbr = c->anyPbr; lc.shadeGlass = c->anyGlass;
     return lc;
@@ -280,7 +280,8 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     std::memset(&c->globals, 0, sizeof(c->globals));
     c->globals.maxRayDepth = 5; c->globals.maxChannelValue = 3.14159265358979f;   // GlobalData defaults, PassGenerator.h:270-272
     c->lights.envTex = -1;
-    if (const char* e = std::getenv("HRC_TUNE_REFILL_IDLE")) c->tuneRefillIdle = std::max(1, std::min(32, std::atoi(e)));
+    if (const char* e = std::getenv("HRC_TUNE_REFILL_IDLE")) c->tuneRefillIdle = c->tuneRefillIdleAny = std::max(1, std::min(32, std::atoi(e)));
+    if (const char* e = std::getenv("HRC_TUNE_REFILL_IDLE_ANY")) c->tuneRefillIdleAny = std::max(1, std::min(32, std::atoi(e)));      // occlusion traversal only
     if (const char* e = std::getenv("HRC_TUNE_BLOCKS_PER_SM")) c->tuneBlocksPerSM = std::max(1, std::min(16, std::atoi(e)));
     *out = c;
     return HRC_OK;

@@ -1259,11 +1259,11 @@ void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const
 void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     const int grid = lc.smCount * lc.traceBlocksPerSM;
     if (lc.masked) {
-        if (lc.collectStats) k_trace<true, true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
-        else                 k_trace<true, false, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+        if (lc.collectStats) k_trace<true, true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
+        else                 k_trace<true, false, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
     } else {
-        if (lc.collectStats) k_trace<true, true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
-        else                 k_trace<true, false, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdle);
+        if (lc.collectStats) k_trace<true, true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
+        else                 k_trace<true, false, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
     }
 }
 
