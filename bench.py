@@ -70,13 +70,19 @@ class ClockSampler(threading.Thread):
                 break
             parts = [x.strip() for x in line.split(",")]
             if len(parts) >= 6:
-                self.samples.append(parts)
+                self.samples.append(parts + [time.perf_counter()])
         try:
             proc.kill()
         except Exception:
             pass
 
-    def finish(self):
+    def wait_ready(self, timeout=5.0):
+        """nvidia-smi takes a few hundred ms to print its first line: wait for it so that a short timed region is not missed."""
+        t = time.perf_counter()
+        while not self.samples and time.perf_counter() - t < timeout:
+            time.sleep(0.02)
+
+    def finish(self, window=None):
         self.stop_flag = True
         try:
             self.proc.kill()
@@ -91,7 +97,11 @@ class ClockSampler(threading.Thread):
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[2:6]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+        out = {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+        if window:
+            out["samples_in_timed_region"] = sum(1 for x in self.samples if window[0] <= x[-1] <= window[1])
+            out["window"] = "100 ms samples from the start of the timed region to the end of the instrumented replay of the same passes (same kernels, same load)"
+        return out
 
 
 def build_spec(name, small=False):
@@ -196,7 +206,7 @@ def cpu_baseline_sample(spec, budget_s=12.0):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--steps", type=int, default=128)    # 128 passes of config #2 = 0.4 s timed: several 100 ms clock samples fall inside it
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--config", default="sphere_grid", choices=list(WORKLOAD_NAMES))
@@ -290,8 +300,9 @@ def main():
     #      with CUDA events on that stream (no host synchronisation inside), then the reduce ------------------------------
     sampler = ClockSampler(local_rank)
     sampler.start()
-    time.sleep(0.3)
+    sampler.wait_ready()
     barrier()
+    sampler.samples.clear()                      # idle samples from before the region do not count
     t0 = time.perf_counter()
     b.timer_start()
     for i in range(K):
@@ -300,8 +311,8 @@ def main():
     reduce_ms = reduce_timed()
     dev_ms = pass_ms + reduce_ms
     barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    clocks = sampler.finish()
+    t1 = time.perf_counter()
+    wall_ms = (t1 - t0) * 1e3
 
     # ---- instrumented replay of the same K passes: CUDA events between the kernels give each kernel's launch durations
     #      (their sum is within ~2 % of the clean region above; the shares and the roofline use these) ---------------------
@@ -314,6 +325,7 @@ def main():
         ms_closest += st.msClosest; ms_any += st.msAny; ms_shade += st.msShade; ms_raygen += st.msRaygen; inst_ms += st.gpuMs
         launches += int(st.closestLaunches + st.anyLaunches + st.shadeLaunches) + 3     # + clear, raygen, finish
     b.set_option(capi.OPT_KERNEL_TIMING, 0)
+    clocks = sampler.finish(window=(t0, t1))
 
     # ---- end-to-end region: the reference-facing call sequence with HOST buffers (pass + PixelPackBuffer readback) ----
     b.clear()
