@@ -56,9 +56,11 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, device):
         super().__init__(daemon=True)
-        self.device, self.samples, self.stop_flag = device, [], False
+        self.device, self.samples, self.stop_flag, self.proc, self.source = device, [], False, None, "nvidia-smi -lms 100"
 
     def run(self):
+        if self._run_nvml():
+            return
         try:
             proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                                     stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -75,6 +77,29 @@ class ClockSampler(threading.Thread):
             proc.kill()
         except Exception:
             pass
+
+    def _run_nvml(self):
+        """NVML in-process (nvidia_ml_py): one sample every 10 ms, so even a 50 ms timed region is covered. False -> fall back to nvidia-smi."""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(int(self.device))
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            bits = (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                    ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap))
+            nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM); nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+        except Exception:
+            return False
+        self.source = "nvml, 10 ms"
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+            except Exception:
+                break
+            self.samples.append([str(sm), str(mx)] + ["Active" if r & bit else "Not Active" for _, bit in bits] + [time.perf_counter()])
+            time.sleep(0.01)
+        return True
 
     def wait_ready(self, timeout=5.0):
         """nvidia-smi takes a few hundred ms to print its first line: wait for it so that a short timed region is not missed."""
@@ -100,7 +125,8 @@ class ClockSampler(threading.Thread):
         out = {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
         if window:
             out["samples_in_timed_region"] = sum(1 for x in self.samples if window[0] <= x[-1] <= window[1])
-            out["window"] = "100 ms samples from the start of the timed region to the end of the instrumented replay of the same passes (same kernels, same load)"
+            out["source"] = self.source
+            out["window"] = "samples from the start of the timed region to the end of the instrumented replay of the same passes (same kernels, same load)"
         return out
 
 
