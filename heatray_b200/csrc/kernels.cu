@@ -170,6 +170,28 @@ __device__ __forceinline__ void loadVaryings(const DScene& sc, int prim, float u
 // ---------------------------------------------------------------------------------------
 // accumulator.rlsl:12-28. One thread owns a pixel inside any one kernel, so plain RMW is exclusive.
 // ---------------------------------------------------------------------------------------
+// accumulator.rlsl:27 (the built-in accumulate): pixel += value. Within one kernel launch a pixel receives contributions from one thread
+// only (one path per pixel per pass), and launches that touch the same buffer are ordered by streams and events, so a plain
+// read-modify-write is safe. RED = true issues it as one 128-bit reduction at L2 instead (red.global.add.v4.f32, sm_90+): same sum, but
+// the thread does not wait for the old value. Experiment switch HR_ACCUM_RED (light shaders inside k_trace<any> only), off: the occlusion
+// kernel alone gains 2-3 %, the whole pass loses (profiles/r01_v9_notes.md); in k_shade the reductions are slower than the read-modify-write.
+#ifndef HR_ACCUM_RED
+#define HR_ACCUM_RED 0
+#endif
+#ifndef HR_ACCUM_SKIP_ZERO
+#define HR_ACCUM_SKIP_ZERO 1
+#endif
+template <bool RED>
+__device__ __forceinline__ void addToPixel(float4* accum, uint32_t pixel, float x, float y, float z, float w) {
+    if (RED) {
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(accum + pixel), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+    } else {
+        float4 p = accum[pixel];
+        p.x += x; p.y += y; p.z += z; p.w += w;
+        accum[pixel] = p;
+    }
+}
+template <bool RED = false>
 __device__ __forceinline__ void performAccumulate(const HrcGlobals& g, float4* accum, uint32_t pixel, float3 color) {
     float3 value = f3(0.0f);
     if (g.enableAccumulatorVisualizer == 1) {
@@ -183,14 +205,13 @@ __device__ __forceinline__ void performAccumulate(const HrcGlobals& g, float4* a
     } else {
         value = f3(fminf(g.maxChannelValue, color.x), fminf(g.maxChannelValue, color.y), fminf(g.maxChannelValue, color.z));
     }
-    float4 p = accum[pixel];
-    p.x += value.x; p.y += value.y; p.z += value.z;
-    accum[pixel] = p;
+#if HR_ACCUM_SKIP_ZERO
+    if (value.x == 0.0f && value.y == 0.0f && value.z == 0.0f) return;      // adding +0 to a non-negative sum changes nothing: skip the memory round trip
+#endif
+    addToPixel<RED>(accum, pixel, value.x, value.y, value.z, 0.0f);
 }
 __device__ __forceinline__ void accumulate4(float4* accum, uint32_t pixel, float3 rgb, float a) {
-    float4 p = accum[pixel];
-    p.x += rgb.x; p.y += rgb.y; p.z += rgb.z; p.w += a;
-    accum[pixel] = p;
+    addToPixel<false>(accum, pixel, rgb.x, rgb.y, rgb.z, a);
 }
 
 // sequence.rlsl:18-28
@@ -215,6 +236,7 @@ struct SeqCursor {
 // ---------------------------------------------------------------------------------------
 // Light ("miss") shaders
 // ---------------------------------------------------------------------------------------
+template <bool RED = false>
 __device__ __forceinline__ void shadeMiss(const DScene& sc, const DFrame& fr, float4* accum, uint32_t pixel,
                                           uint32_t missKind, uint32_t missIndex, float3 dir, float3 weight, float tmax, float extraT) {
     const DLights& L = fr.lights;
@@ -229,14 +251,14 @@ __device__ __forceinline__ void shadeMiss(const DScene& sc, const DFrame& fr, fl
         float3 sample = f3(0.0f);
         if (L.envTex >= 0) sample = xyz(texFetch(sc.textures[L.envTex], u, 1.0f - v));
         sample = sample * L.envExposure;
-        performAccumulate(fr.g, accum, pixel, weight * sample);
+        performAccumulate<RED>(fr.g, accum, pixel, weight * sample);
         break; }
     case kMissDir:                                                      // directionalLight.rlsl:20-26
-        performAccumulate(fr.g, accum, pixel, weight * f3(L.dirColor[missIndex]));
+        performAccumulate<RED>(fr.g, accum, pixel, weight * f3(L.dirColor[missIndex]));
         break;
     case kMissPoint: {                                                  // pointLight.rlsl:20-29 (rl_IntersectionT = maxT, policy A-7)
         float attenuation = 1.0f / square(tmax + extraT);
-        performAccumulate(fr.g, accum, pixel, weight * f3(L.pointColor[missIndex]) * attenuation);
+        performAccumulate<RED>(fr.g, accum, pixel, weight * f3(L.pointColor[missIndex]) * attenuation);
         break; }
     case kMissSpot: {                                                   // spotLight.rlsl:20-36
         float rayAngle = dot(-dir, f3(L.spotDirection[missIndex]));
@@ -244,7 +266,7 @@ __device__ __forceinline__ void shadeMiss(const DScene& sc, const DFrame& fr, fl
             float attenuation = 1.0f / square(tmax + extraT);
             float3 result = weight * f3(L.spotColor[missIndex]) * attenuation;
             result = result * (1.0f - glslSmoothstep(L.spotAngles[missIndex][0], L.spotAngles[missIndex][1], rayAngle));
-            performAccumulate(fr.g, accum, pixel, result);
+            performAccumulate<RED>(fr.g, accum, pixel, result);
         }
         break; }
     default: break;
@@ -672,7 +694,7 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                 if (ANY) {             // the ray reached its light: run the light shader (policy A-5/A-6)
                     const float4 w = __ldcs(pb.shadow.w + rayIdx);
                     const uint32_t bits = __float_as_uint(w.w);
-                    shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, MASKED ? extraT : pb.shadow.d[rayIdx].w);
+                    shadeMiss<HR_ACCUM_RED != 0>(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, MASKED ? extraT : pb.shadow.d[rayIdx].w);
                 } else {
                     __stcs(pb.hits + rayIdx, tr.found ? make_float4(tr.bestT, tr.bestU, tr.bestV, __int_as_float(tr.bestPrim))
                                                       : make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));
