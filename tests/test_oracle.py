@@ -282,3 +282,31 @@ def test_interactive_block_mode_covers_each_pixel_once(oracle_backend):
     r.reset()
     r.render_pass()
     assert np.array_equal(r.pixels(), inter)
+
+
+def test_deferred_passes_commit_oldest_first(oracle_backend):
+    """The oracle's mirror of hrcEnqueuePassDeferred / Commit / Discard (the contract the CUDA library is tested against on the GPU): up to
+    three pending, invisible until committed, committed oldest first, a discard drops all pending."""
+    spec = scenes.cornell_box(width=32, height=32, passes=4)
+    b = oracle_backend
+    r = renderer.Renderer(b)
+    r.load_scene(spec)
+    singles = []
+    for i in range(4):
+        b.clear()
+        r.render_pass(sample_index=i)
+        singles.append(r.pixels().copy())
+    b.clear()
+    r.render_pass(sample_index=0)
+    for i in (1, 2, 3):
+        r.frame.sampleIndex = i
+        b.enqueue_pass_deferred(r.frame)
+    with pytest.raises(capi.HrcError):
+        b.enqueue_pass_deferred(r.frame)
+    assert np.array_equal(r.pixels(), singles[0])
+    b.commit_deferred()
+    assert np.array_equal(r.pixels(), singles[0] + singles[1])
+    b.discard_deferred()
+    with pytest.raises(capi.HrcError):
+        b.commit_deferred()
+    assert np.array_equal(r.pixels(), singles[0] + singles[1])
