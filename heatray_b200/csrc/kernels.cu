@@ -191,19 +191,21 @@ __device__ __forceinline__ void addToPixel(float4* accum, uint32_t pixel, float 
         accum[pixel] = p;
     }
 }
+// GLSL min(x, y): "returns y if y < x, otherwise x" (a NaN in x comes back as NaN, a NaN in y is dropped); fminf would drop both.
+__device__ __forceinline__ float glslMin(float x, float y) { return (y < x) ? y : x; }
 template <bool RED = false>
 __device__ __forceinline__ void performAccumulate(const HrcGlobals& g, float4* accum, uint32_t pixel, float3 color) {
     float3 value = f3(0.0f);
     if (g.enableAccumulatorVisualizer == 1) {
         if (g.showNANs == 1) {
             bool any = isnan(color.x) || isnan(color.y) || isnan(color.z);
-            value = any ? f3(100.0f) : f3(fminf(color.x, 1.0f), fminf(color.y, 1.0f), fminf(color.z, 1.0f)) * 0.1f;
+            value = any ? f3(100.0f) : f3(glslMin(color.x, 1.0f), glslMin(color.y, 1.0f), glslMin(color.z, 1.0f)) * 0.1f;
         } else if (g.showInf == 1) {
             bool any = isinf(color.x) || isinf(color.y) || isinf(color.z);
-            value = any ? f3(100.0f) : f3(fminf(color.x, 1.0f), fminf(color.y, 1.0f), fminf(color.z, 1.0f)) * 0.1f;
+            value = any ? f3(100.0f) : f3(glslMin(color.x, 1.0f), glslMin(color.y, 1.0f), glslMin(color.z, 1.0f)) * 0.1f;
         }
     } else {
-        value = f3(fminf(g.maxChannelValue, color.x), fminf(g.maxChannelValue, color.y), fminf(g.maxChannelValue, color.z));
+        value = f3(glslMin(g.maxChannelValue, color.x), glslMin(g.maxChannelValue, color.y), glslMin(g.maxChannelValue, color.z));
     }
 #if HR_ACCUM_SKIP_ZERO
     if (value.x == 0.0f && value.y == 0.0f && value.z == 0.0f) return;      // adding +0 to a non-negative sum changes nothing: skip the memory round trip
@@ -999,8 +1001,8 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
     if (!frontFacing) {                                                       // :161-167
         N = -N; nIn = m.ior; nOut = 1.0f;
         const float3 absorption = f3(1.0f) - baseColor;                       // beersLaw :131-136
-        const float k = m.density * -s.T;
-        weight = in.weight * f3(expf(absorption.x * k), expf(absorption.y * k), expf(absorption.z * k));
+        const float3 k = (absorption * m.density) * -s.T;                    // exp(absorption * Material.density * -rayLength): left to right, as the shader text associates it
+        weight = in.weight * f3(expf(k.x), expf(k.y), expf(k.z));
     }
     float roughness = m.roughness, roughnessAlpha = m.roughnessAlpha;
     if (flags & HRC_MAT_HAS_METALLIC_ROUGHNESS_TEXTURE) {                     // :171-176 (.g; metallic ignored)

@@ -27,4 +27,8 @@ g++ -std=gnu++20 -D_MSC_EXTENSIONS -O2 -fPIC -shared -fsingle-precision-constant
 g++ -std=c++17 -O2 -fPIC -shared -I$REF/3rdParty -w ref_stb.cpp -o "$OUT/libref_stb.so"
 # Session.h relies on MSVC pulling in <cstdint>: -include cstdint supplies it, nothing else changes
 g++ -std=c++20 -O1 -fPIC -shared -include cstdint -I$REF/Source -I$REF/3rdParty -w ref_session.cpp $REF/Source/HeatrayRenderer/Session/Session.cpp $REF/3rdParty/tinyxml2/tinyxml2.cpp -o "$OUT/libref_session.so"
+# The shader programs themselves (frame shader, PBR / glass per #define set, the four light shaders) as C++: rlsl_to_cpp.py resolves the
+# #include lines like ShaderCodeLoader.cpp and rewrites the RLSL-only declarations (listed in its header) into /tmp; rlsl_shim.h supplies the built-ins.
+python3 rlsl_to_cpp.py /tmp/hr_ref_shaders
+g++ -std=gnu++20 -D_MSC_EXTENSIONS -O2 -ffp-contract=off -fPIC -shared -fsingle-precision-constant -I/tmp/hr_ref_shaders -I. -I$REF/3rdParty -I$REF/3rdParty/glm -w ref_shaders.cpp -o "$OUT/libref_shaders.so"
 echo "oracle/_ref built"
