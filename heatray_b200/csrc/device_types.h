@@ -73,6 +73,14 @@ struct ShadowQueue {
 // Per-iteration control words, zeroed at the start of every pass.
 struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; uint32_t classCount[3]; uint32_t maskedContinuations; };   // class 0: miss, 1: PBR, 2: glass
 
+// Coherence sort of the extension rays between wavefront iterations (HRC_TUNE_SORT_BITS > 0): k_shade files every emitted ray under
+// key = octant << 3b | morton(cell of its origin in a 2^b-per-axis grid over the scene box), k_sort_scan turns the histogram into bin
+// offsets, k_sort_scatter writes the ray indices bin by bin into `order`, and k_trace<closest> pulls rays through `order`, so the 32 rays
+// a warp refills with start in the same part of the scene heading the same way. Ray records stay where k_shade wrote them.
+constexpr int kSortMaxBits = 5;                          // cells per axis = 2^bits; bins = 8 octants * 2^(3 bits)
+constexpr uint32_t kSortMinRays = 32768;                 // below this the iteration is latency-bound: not sorted
+struct SortCtrl { uint32_t sorted; uint32_t pad[3]; };   // per iteration: 1 when `order` is valid for its extension rays
+
 struct DeviceStats {                       // accumulated by k_finish_pass
     unsigned long long raysPrimary, raysExtension, raysOcclusion, nodesVisited, trianglesTested, nodesVisitedAny, trianglesTestedAny, stackOverflows;
 };
@@ -91,6 +99,7 @@ struct DScene {
     const uint8_t* sequenceId;
     const float* blockCoords; // interactive mode: blockW*blockH RGB texels of shuffled (row, col, 0)
     const float2* blockRand;  // interactive mode: per block (random(blockIndex), random(blockIndex.yx))
+    float sortMin[3], sortScale[3];   // coherence sort grid: cell = (origin - sortMin) * sortScale, clamped to [0, 2^bits)
 };
 
 // Launch wrappers implemented in kernels.cu
@@ -103,15 +112,22 @@ struct PassBuffers {
     DeviceStats* stats;
     float4* accum;
     uint32_t capacity;        // rays per queue
+    // coherence sort (nullptr when off)
+    uint32_t* sortKeys;       // key of extension ray j of the NEXT iteration
+    uint32_t* sortOrder;      // sorted position -> ray index
+    uint32_t* sortHist;       // bins counters (zeroed by k_sort_scan after use)
+    uint32_t* sortOffs;       // bins running offsets
+    SortCtrl* sortCtrl;       // kMaxIterations entries
 };
 
-struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle, refillIdleAny; };
+struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle, refillIdleAny; int sortBits; };
 
 void launchClearCtrl(const PassBuffers& pb, cudaStream_t s);
 void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s);
 void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
 void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
 void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);   // orders the extension rays of iteration `iter` (emitted by shade(iter - 1))
 void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s);
 void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig& lc, cudaStream_t s);
 void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s);

@@ -56,6 +56,8 @@ struct HrcContext_t {
     // them are zero on the device and hrcReadPixels copies only the context's own rows.
     int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
     long long pinnedZeroKey = -1;          // which rows of the pinned frame may be non-zero: -1 any, 0 none (fresh), else the band set's key
+    int tuneSortBits = 0;                  // HRC_TUNE_SORT_BITS: cells per axis (2^bits) of the coherence sort grid, 0 = off
+    float sceneMin[3] = {0, 0, 0}, sceneMax[3] = {1, 1, 1};
     int tunePipelinedBlocksPerSM = 4;      // traversal CTAs per SM for pipelined passes: kernels of several lanes are resident together, so each takes fewer slots
     cudaEvent_t evMerged = nullptr;   // traversal scheduling knobs (HRC_TUNE_* environment overrides, for experiments)
 
@@ -100,6 +102,7 @@ void freeQueues(PassBuffers& pb) {
     for (int k = 0; k < 2; ++k) { freeDev(pb.ext[k].od); freeDev(pb.ext[k].wm); }
     for (int k = 0; k < 3; ++k) freeDev(pb.classIdx[k]);
     freeDev(pb.shadow.o); freeDev(pb.shadow.d); freeDev(pb.shadow.w); freeDev(pb.hits);
+    freeDev(pb.sortKeys); freeDev(pb.sortOrder); freeDev(pb.sortHist); freeDev(pb.sortOffs); freeDev(pb.sortCtrl);
     pb.capacity = 0;
 }
 int allocQueues(HrcContext c, PassBuffers& pb, size_t n) {
@@ -109,6 +112,13 @@ int allocQueues(HrcContext c, PassBuffers& pb, size_t n) {
     for (int k = 0; k < 3; ++k) CU(c, cudaMalloc(&pb.classIdx[k], n * sizeof(uint32_t)));
     CU(c, cudaMalloc(&pb.shadow.o, n * sizeof(float4))); CU(c, cudaMalloc(&pb.shadow.d, n * sizeof(float4)));
     CU(c, cudaMalloc(&pb.shadow.w, n * sizeof(float4))); CU(c, cudaMalloc(&pb.hits, n * sizeof(float4)));
+    if (c->tuneSortBits > 0) {                       // coherence sort of the extension rays (device_types.h)
+        const size_t bins = std::max<size_t>(1024, (size_t)8 << (3 * c->tuneSortBits));
+        CU(c, cudaMalloc(&pb.sortKeys, n * sizeof(uint32_t))); CU(c, cudaMalloc(&pb.sortOrder, n * sizeof(uint32_t)));
+        CU(c, cudaMalloc(&pb.sortHist, bins * sizeof(uint32_t))); CU(c, cudaMalloc(&pb.sortOffs, bins * sizeof(uint32_t)));
+        CU(c, cudaMalloc(&pb.sortCtrl, kMaxIterations * sizeof(SortCtrl)));
+        CU(c, cudaMemset(pb.sortHist, 0, bins * sizeof(uint32_t))); CU(c, cudaMemset(pb.sortCtrl, 0, kMaxIterations * sizeof(SortCtrl)));
+    }
     pb.capacity = (uint32_t)n;
     return HRC_OK;
 }
@@ -165,12 +175,16 @@ int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
 DScene sceneOf(HrcContext c) {
     DScene s; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.attr = c->dAttr; s.materials = c->dMaterials; s.textures = c->dTextures;
     s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId; s.blockCoords = c->dBlockCoords; s.blockRand = c->dBlockRand;
+    for (int k = 0; k < 3; ++k) {
+        const float extent = c->sceneMax[k] - c->sceneMin[k];
+        s.sortMin[k] = c->sceneMin[k]; s.sortScale[k] = extent > 0.0f ? (float)(1 << c->tuneSortBits) / extent : 0.0f;
+    }
     return s;
 }
 LaunchConfig configOf(HrcContext c) {
     LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters;
     lc.refillIdle = c->tuneRefillIdle; lc.refillIdleAny = c->tuneRefillIdleAny; lc.traceBlocksPerSM = c->tuneBlocksPerSM;
-    lc.masked = c->anyMasked;
+    lc.masked = c->anyMasked; lc.sortBits = c->tuneSortBits;
     lc.shadeMiss = c->lights.envEnabled != 0; lc.shadePbr = c->anyPbr; lc.shadeGlass = c->anyGlass;
     return lc;
 }
@@ -269,6 +283,7 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
     for (int i = 0; i < 2 * kMaxIterations; ++i) { cudaEvent_t ev; cudaEventCreateWithFlags(&ev, cudaEventDisableTiming); c->evSync.push_back(ev); }
     if (const char* e2 = std::getenv("HRC_TUNE_OVERLAP")) c->overlap = std::atoi(e2) != 0;
+    if (const char* e2 = std::getenv("HRC_TUNE_SORT_BITS")) c->tuneSortBits = std::max(0, std::min(kSortMaxBits, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_BLOCKS_PER_SM_PIPE")) c->tunePipelinedBlocksPerSM = std::max(1, std::min(16, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_PASS_LANES")) c->passLanes = std::max(1, std::min(kMaxLanes, std::atoi(e2)));   // 1: no overlap between passes
     cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop); cudaEventCreate(&c->evTimer0); cudaEventCreate(&c->evTimer1);
@@ -610,6 +625,7 @@ HRC_API int hrcCommitScene(HrcContext c) {
     CU(c, cudaMemcpyAsync(c->dTris, tris.data(), tris.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaMemcpyAsync(c->dShade, shade.data(), shade.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < 3; ++k) { c->sceneMin[k] = bvh.sceneMin[k]; c->sceneMax[k] = bvh.sceneMax[k]; }
     c->info.triangleCount = bt.size(); c->info.nodeCount = bvh.nodes.size();
     c->info.nodeBytes = bvh.nodes.size() * sizeof(WideNode); c->info.triangleBytes = bt.size() * 48; c->info.shadingBytes = bt.size() * 64 + attr.size() * sizeof(float4);
     c->info.buildSeconds = (float)bvh.buildSeconds;
@@ -749,7 +765,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     if (timeKernels || !c->overlap || iterations < 2) {
         for (int it = 0; it < iterations; ++it) {
             launchTraceClosest(sc, pb, it, lc, s); mark();
-            launchShade(sc, fr, pb, it, lc, s);    mark();
+            launchShade(sc, fr, pb, it, lc, s);    if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s); mark();
             launchTraceAny(sc, fr, pb, it, lc, s); mark();
         }
     } else {
@@ -762,6 +778,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
             if (it > 0) cudaStreamWaitEvent(s, evSync[2 * (it - 1) + 1], 0);
             launchShade(sc, fr, pb, it, lc, s);
             cudaEventRecord(evSync[2 * it], s);
+            if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
             cudaStreamWaitEvent(s2, evSync[2 * it], 0);
             launchTraceAny(sc, fr, pb, it, lc, s2);
             cudaEventRecord(evSync[2 * it + 1], s2);

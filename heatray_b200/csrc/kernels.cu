@@ -610,6 +610,8 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
     const float4* __restrict__ qod = (iter & 1) ? pb.ext[1].od : pb.ext[0].od;   // no dynamic indexing of kernel parameters (it forces a local copy)
     const float4* __restrict__ nodes = sc.nodes;
     const float4* __restrict__ tris = sc.tris;
+    // coherence sort: sorted position -> ray index (extension rays of iterations >= 1 only; see device_types.h)
+    const uint32_t* __restrict__ order = (!ANY && pb.sortCtrl && pb.sortCtrl[iter].sorted) ? pb.sortOrder : nullptr;
     TraceCounters tc{0u, 0u, 0u};
     Traversal tr;
     HR_DECLARE_TRACE_STACK(stack);
@@ -642,8 +644,9 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                 if ((int)lane == leader) base = atomicAdd(head, n);
                 base = __shfl_sync(kFull, base, leader);
                 if (!active) {
-                    const uint32_t i = base + __popc(idle & below);
+                    uint32_t i = base + __popc(idle & below);
                     if (i < count) {
+                        if (!ANY && order) i = __ldcs(order + i);
                         const float4 ro = __ldcs(ANY ? pb.shadow.o + i : qod + 2 * (size_t)i), rd = __ldcs(ANY ? pb.shadow.d + i : qod + 2 * (size_t)i + 1);   // streamed: keep the BVH in L2
 #if HR_RAY_PREFETCH_AHEAD > 0
                         // the queue is consumed in index order by all warps together: pull the ray HR_RAY_PREFETCH_AHEAD places further on into L2
@@ -1122,8 +1125,24 @@ __device__ void shadeGlass(const DScene& sc, const DFrame& fr, float4* accum, co
 #ifndef HR_SHADE_PREFETCH
 #define HR_SHADE_PREFETCH 0
 #endif
+// Sort key of an extension ray: octant of its direction above the Morton code of its origin's cell (device_types.h).
+__device__ __forceinline__ uint32_t spreadBits3(uint32_t v) {          // 5 low bits -> every third bit
+    v = (v | (v << 8)) & 0x0000100fu;
+    v = (v | (v << 4)) & 0x000010c3u;
+    v = (v | (v << 2)) & 0x00001249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t raySortKey(const DScene& sc, float3 o, float3 d, int bits) {
+    const int top = (1 << bits) - 1;
+    const uint32_t ix = (uint32_t)min(max((int)((o.x - sc.sortMin[0]) * sc.sortScale[0]), 0), top);
+    const uint32_t iy = (uint32_t)min(max((int)((o.y - sc.sortMin[1]) * sc.sortScale[1]), 0), top);
+    const uint32_t iz = (uint32_t)min(max((int)((o.z - sc.sortMin[2]) * sc.sortScale[2]), 0), top);
+    const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    return (oct << (3 * bits)) | spreadBits3(ix) | (spreadBits3(iy) << 1) | (spreadBits3(iz) << 2);
+}
+
 template <int CLS>
-__global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter) {
+__global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter, int sortBits) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = (gridDim.x * blockDim.x) >> 5;
     const uint32_t warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -1225,7 +1244,51 @@ __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene
             __stcs(nq.od + 2 * j + 1, make_float4(e.extD.x, e.extD.y, e.extD.z, 0.0f));
             __stcs(nq.wm + 2 * j, make_float4(e.extW.x, e.extW.y, e.extW.z, __uint_as_float(in.pixel)));
             __stcs(nq.wm + 2 * j + 1, make_float4(__uint_as_float((in.depth + 1u) | (mk << 8) | (in.sequenceID << 16)), __int_as_float(in.sequenceIndexOffset), 0.0f, 0.0f));
+            if (sortBits > 0) {
+                const uint32_t key = raySortKey(sc, e.extO, e.extD, sortBits);
+                __stcs(pb.sortKeys + j, key);
+                atomicAdd(pb.sortHist + key, 1u);
+            }
         }
+    }
+}
+
+// Histogram -> exclusive bin offsets for the extension rays of iteration `iter`, one CTA of 1024 threads (bins is a multiple of 1024);
+// re-arms the histogram for the next iteration. Iterations with few rays are latency-bound anyway and stay unsorted.
+__global__ void __launch_bounds__(1024) k_sort_scan(PassBuffers pb, int iter, uint32_t bins) {
+    __shared__ uint32_t warpSums[32];
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+    const uint32_t per = bins >> 10;
+    const bool sorted = pb.ctrl[iter].extCount >= kSortMinRays;
+    if (t == 0) pb.sortCtrl[iter].sorted = sorted ? 1u : 0u;
+    uint32_t* hist = pb.sortHist + (size_t)t * per;
+    uint32_t* offs = pb.sortOffs + (size_t)t * per;
+    uint32_t sum = 0;
+    if (sorted) for (uint32_t k = 0; k < per; ++k) sum += hist[k];
+    uint32_t incl = sum;
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= (uint32_t)d) incl += v; }
+    if (lane == 31) warpSums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = warpSums[lane];
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, w, d); if (lane >= (uint32_t)d) w += v; }
+        warpSums[lane] = w;
+    }
+    __syncthreads();
+    uint32_t run = incl - sum + (warp ? warpSums[warp - 1] : 0u);
+    for (uint32_t k = 0; k < per; ++k) {
+        const uint32_t h = hist[k];
+        if (sorted) offs[k] = run;
+        run += h;
+        hist[k] = 0u;
+    }
+}
+__global__ void __launch_bounds__(256) k_sort_scatter(PassBuffers pb, int iter) {
+    if (!pb.sortCtrl[iter].sorted) return;
+    const uint32_t count = pb.ctrl[iter].extCount;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
+        const uint32_t key = __ldcs(pb.sortKeys + j);
+        pb.sortOrder[atomicAdd(pb.sortOffs + key, 1u)] = j;
     }
 }
 
@@ -1293,9 +1356,17 @@ void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, i
 
 void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     const int grid = lc.smCount * 8;
-    if (lc.shadeMiss)  k_shade<0><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
-    if (lc.shadePbr)   k_shade<1><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
-    if (lc.shadeGlass) k_shade<2><<<grid, 128, 0, s>>>(sc, fr, pb, iter);
+    const int sortBits = pb.sortKeys ? lc.sortBits : 0;
+    if (lc.shadeMiss)  k_shade<0><<<grid, 128, 0, s>>>(sc, fr, pb, iter, 0);
+    if (lc.shadePbr)   k_shade<1><<<grid, 128, 0, s>>>(sc, fr, pb, iter, sortBits);
+    if (lc.shadeGlass) k_shade<2><<<grid, 128, 0, s>>>(sc, fr, pb, iter, sortBits);
+}
+
+void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+    if (!pb.sortKeys || lc.sortBits <= 0) return;
+    const uint32_t bins = 8u << (3 * lc.sortBits);
+    k_sort_scan<<<1, 1024, 0, s>>>(pb, iter, bins < 1024u ? 1024u : bins);
+    k_sort_scatter<<<lc.smCount * 4, 256, 0, s>>>(pb, iter);
 }
 
 void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s) { k_finish_pass<<<1, 32, 0, s>>>(pb, iterations); }
