@@ -38,6 +38,7 @@ constexpr int kMaxBins = 64;
 int g_bins = 32;                            // SAH bins per axis; 32 measured best on configs #2 / #3 (8: +1.7 / +2.4 %, 16: 0, 32: +1.2 / +4.0 %, 64: +1.0 / +3.4 %
                                             // in whole-pass Mrays/s; exact sweep SAH below 64..4096 triangles changed nothing). HRC_TUNE_BINS overrides.
 #define kBins g_bins
+constexpr int kMaxBinaryDepth = 30;        // < kTraceStack (device_types.h); hrcCommitScene keeps its depth check as an assertion
 constexpr uint32_t kMaxLeafLimit = 3;      // a child slot encodes at most 3 triangles (unary count in 3 bits)
 // Leaf policy: at most g_maxLeaf triangles, made a leaf when n * area <= g_travCost * area + SAH(best split). Defaults measured on B200
 // (profiles/); HRC_TUNE_MAX_LEAF / HRC_TUNE_TRAV_COST override them for experiments.
@@ -85,10 +86,20 @@ struct Builder2 {
             }
         }
 
+        // Depth guard: the traversal stack holds kTraceStack entries (one per wide level, and a wide level spans at least one binary
+        // level). A branch that is unusually deep for the primitives it still holds (SAH peeling one triangle per level off a skewed
+        // distribution) finishes with median splits, which need ceil(log2 n) more levels, so the tree can never outgrow the stack.
+        int log2n = 0; while ((1u << log2n) < n) ++log2n;
+        if (depth + log2n >= kMaxBinaryDepth) bestAxis = -1;
+
         uint32_t mid;
-        if (bestAxis < 0) {                       // all centroids coincide
+        if (bestAxis < 0) {                       // all centroids coincide (or the depth guard fired): median split
             if (n <= kMaxLeaf) { node.first = begin; node.count = n; return; }
             mid = begin + n / 2;
+            int wide = 0;
+            for (int a = 1; a < 3; ++a) if (cbounds.hi[a] - cbounds.lo[a] > cbounds.hi[wide] - cbounds.lo[wide]) wide = a;
+            if (cbounds.hi[wide] > cbounds.lo[wide])
+                std::nth_element(prims.begin() + begin, prims.begin() + mid, prims.begin() + end, [wide](const Prim& x, const Prim& y) { return x.c[wide] < y.c[wide]; });
         } else {
             const float area = bounds.halfArea();
             if (n <= kMaxLeaf && (float)n * area <= g_travCost * area + bestCost) { node.first = begin; node.count = n; return; }

@@ -43,7 +43,7 @@ struct DLights {
     int32_t envTex; float envExposure, envTheta; int32_t pad;
 };
 
-// Per-pass constants, passed to kernels BY VALUE (constant bank).
+// Per-pass constants: uploaded into a constant-memory slot per lane (kernels.cu g_frames), kernels are passed the slot number.
 struct DFrame {
     HrcGlobals g;
     float fovTan, aspectRatio, focusDistance, apertureRadius;
@@ -122,13 +122,15 @@ struct PassBuffers {
 
 struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle, refillIdleAny; int sortBits; };
 
+constexpr int kFrameSlots = 1 + (kMaxLanes - 1) + kDeferredLanes;     // one constant-memory DFrame per lane: main, extra lanes, deferred lanes
+void uploadFrame(const DFrame* pinnedFrame, int slot, cudaStream_t s);  // stream-ordered copy into the lane's slot; the source must stay valid until it ran
 void launchClearCtrl(const PassBuffers& pb, cudaStream_t s);
-void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s);
-void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
-void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
-void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchRaygen(const DScene& sc, int slot, uint32_t total, const PassBuffers& pb, cudaStream_t s);
+void launchTraceClosest(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchShade(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchTraceAny(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
 void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);   // orders the extension rays of iteration `iter` (emitted by shade(iter - 1))
-void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s);
+void launchFinishPass(const PassBuffers& pb, int iterations, bool rearm, cudaStream_t s);   // rearm: also zero the control words for the next pass
 void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig& lc, cudaStream_t s);
 void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s);
 void launchResolve(const float4* accum, const HrcPostProcess& post, int format, int w, int h, void* out, cudaStream_t s);   // resolve.cu

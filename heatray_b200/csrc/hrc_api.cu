@@ -15,6 +15,12 @@ using namespace hr;
 
 namespace {
 
+// One captured pass: every kernel argument of a pass is fixed by these values (the per-pass constants travel through a constant-memory
+// slot), so a pass whose key matches replays the instantiated graph: one upload + one graph launch instead of ~40 launches + ~36 event calls.
+struct GraphKey { DScene sc; PassBuffers pb; LaunchConfig lc; int32_t iterations; uint32_t total; int32_t slot; int32_t overlap; };
+struct GraphEntry { GraphKey key; cudaGraphExec_t exec = nullptr; uint64_t lastUse = 0; };
+constexpr int kFrameRing = 32;            // pinned staging entries for the per-pass constants: the host runs at most this many passes ahead of the device
+
 struct TextureRec { float4* dev = nullptr; int w = 0, h = 0, wrapS = 0, wrapT = 0; bool alive = false; };
 struct MaterialRec { DMaterial d; int type; uint32_t flags; };
 struct MeshRec {
@@ -44,7 +50,10 @@ struct HrcContext_t {
     // the latency-bound tail of one pass (a few thousand rays per kernel) runs next to the head of the following one. Every other entry
     // point first joins the lanes (accum += the extra lanes' buffers), so callers see one buffer; the result is deterministic for a given call sequence.
     struct Lane { PassBuffers pb{}; cudaStream_t s = nullptr, s2 = nullptr; std::vector<cudaEvent_t> evSync; float4* accum = nullptr;
-                  cudaEvent_t evDone = nullptr; bool active = false; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
+                  cudaEvent_t evDone = nullptr; bool active = false; std::vector<GraphEntry> graphs; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
+    std::vector<GraphEntry> graphs;        // captured passes of the main lane
+    bool useGraphs = true; uint64_t graphClock = 0;
+    DFrame* frameRing = nullptr; cudaEvent_t frameEv[kFrameRing] = {}; bool frameUsed[kFrameRing] = {}; int frameNext = 0;
     int passLanes = 4, nextLane = 0;
     // Deferred passes (hrcEnqueuePassDeferred): rendered into side lanes that joins ignore until hrcCommitDeferred, so a caller can
     // already render passes i+1 .. i+3 while pass i is being read back (hr::PassGenerator does that when its next job is queued).
@@ -55,6 +64,7 @@ struct HrcContext_t {
     // Band bookkeeping for the readback: while every pass since the last clear rendered the same set of screen bands, pixels outside
     // them are zero on the device and hrcReadPixels copies only the context's own rows.
     int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
+    bool devicePixelsExported = false;     // hrcGetDevicePixels handed the buffer out: the caller may write any row at any time (in-place NCCL reduce), so reads copy whole frames until hrcResize
     long long pinnedZeroKey = -1;          // which rows of the pinned frame may be non-zero: -1 any, 0 none (fresh), else the band set's key
     int tuneSortBits = 0;                  // HRC_TUNE_SORT_BITS: cells per axis (2^bits) of the coherence sort grid, 0 = off
     float sceneMin[3] = {0, 0, 0}, sceneMax[3] = {1, 1, 1};
@@ -97,6 +107,13 @@ int failCuda(HrcContext c, cudaError_t e, const char* what) {
 #define CU(c, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return failCuda(c, e_, #call); } while (0)
 
 template <class T> void freeDev(T*& p) { if (p) { cudaFree(p); p = nullptr; } }
+
+void destroyGraphList(std::vector<GraphEntry>& v) { for (auto& g : v) if (g.exec) cudaGraphExecDestroy(g.exec); v.clear(); }
+void destroyGraphs(HrcContext c) {
+    destroyGraphList(c->graphs);
+    for (auto& L : c->extra) destroyGraphList(L.graphs);
+    for (auto& L : c->deferred) destroyGraphList(L.graphs);
+}
 
 void freeQueues(PassBuffers& pb) {
     for (int k = 0; k < 2; ++k) { freeDev(pb.ext[k].od); freeDev(pb.ext[k].wm); }
@@ -150,8 +167,8 @@ void waitPendingDeferred(HrcContext c) {
         if (c->deferred[d].s) cudaStreamSynchronize(c->deferred[d].s);
 }
 void freeExtraLanes(HrcContext c) {         // buffers that depend on the frame size; streams and counters stay
-    for (auto& L : c->extra) { freeQueues(L.pb); freeDev(L.accum); L.active = false; }
-    for (auto& L : c->deferred) { freeQueues(L.pb); freeDev(L.accum); L.active = false; }
+    for (auto& L : c->extra) { freeQueues(L.pb); freeDev(L.accum); L.active = false; destroyGraphList(L.graphs); }
+    for (auto& L : c->deferred) { freeQueues(L.pb); freeDev(L.accum); L.active = false; destroyGraphList(L.graphs); }
     c->nextLane = 0; c->deferredCount = 0;
 }
 int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
@@ -165,15 +182,18 @@ int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
         CU(c, cudaMalloc(&L.pb.ctrl, sizeof(IterCtrl) * kMaxIterations)); CU(c, cudaMalloc(&L.pb.stats, sizeof(DeviceStats)));
         CU(c, cudaMemset(L.pb.stats, 0, sizeof(DeviceStats))); CU(c, cudaMemset(L.pb.ctrl, 0, sizeof(IterCtrl) * kMaxIterations));
     }
-    CU(c, cudaMalloc(&L.accum, n * sizeof(float4)));
-    CU(c, cudaMemset(L.accum, 0, n * sizeof(float4)));
-    int r = allocQueues(c, L.pb, n); if (r) return r;
+    auto allocate = [&]() -> int {
+        CU(c, cudaMalloc(&L.accum, n * sizeof(float4)));
+        CU(c, cudaMemset(L.accum, 0, n * sizeof(float4)));
+        return allocQueues(c, L.pb, n);
+    };
+    if (int r = allocate()) { freeQueues(L.pb); freeDev(L.accum); return r; }      // a retry starts from scratch instead of finding a lane without queues
     L.pb.accum = L.accum;
     return HRC_OK;
 }
 
 DScene sceneOf(HrcContext c) {
-    DScene s; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.attr = c->dAttr; s.materials = c->dMaterials; s.textures = c->dTextures;
+    DScene s{}; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.attr = c->dAttr; s.materials = c->dMaterials; s.textures = c->dTextures;
     s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId; s.blockCoords = c->dBlockCoords; s.blockRand = c->dBlockRand;
     for (int k = 0; k < 3; ++k) {
         const float extent = c->sceneMax[k] - c->sceneMin[k];
@@ -182,7 +202,7 @@ DScene sceneOf(HrcContext c) {
     return s;
 }
 LaunchConfig configOf(HrcContext c) {
-    LaunchConfig lc; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters;
+    LaunchConfig lc{}; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters;
     lc.refillIdle = c->tuneRefillIdle; lc.refillIdleAny = c->tuneRefillIdleAny; lc.traceBlocksPerSM = c->tuneBlocksPerSM;
     lc.masked = c->anyMasked; lc.sortBits = c->tuneSortBits;
     lc.shadeMiss = c->lights.envEnabled != 0; lc.shadePbr = c->anyPbr; lc.shadeGlass = c->anyGlass;
@@ -283,6 +303,9 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
     for (int i = 0; i < 2 * kMaxIterations; ++i) { cudaEvent_t ev; cudaEventCreateWithFlags(&ev, cudaEventDisableTiming); c->evSync.push_back(ev); }
     if (const char* e2 = std::getenv("HRC_TUNE_OVERLAP")) c->overlap = std::atoi(e2) != 0;
+    if (const char* e2 = std::getenv("HRC_TUNE_GRAPHS")) c->useGraphs = std::atoi(e2) != 0;      // 0: launch every kernel of a pass individually (experiments)
+    if (cudaMallocHost(&c->frameRing, sizeof(DFrame) * kFrameRing) != cudaSuccess) { int r = fail(nullptr, HRC_ERR_OUT_OF_MEMORY, "pinned frame ring"); delete c; return r; }
+    for (auto& ev : c->frameEv) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
     if (const char* e2 = std::getenv("HRC_TUNE_SORT_BITS")) c->tuneSortBits = std::max(0, std::min(kSortMaxBits, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_BLOCKS_PER_SM_PIPE")) c->tunePipelinedBlocksPerSM = std::max(1, std::min(16, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_PASS_LANES")) c->passLanes = std::max(1, std::min(kMaxLanes, std::atoi(e2)));   // 1: no overlap between passes
@@ -307,6 +330,9 @@ HRC_API int hrcDestroyContext(HrcContext c) {
     cudaSetDevice(c->device);
     joinLanes(c); waitPendingDeferred(c);
     cudaStreamSynchronize(c->stream);
+    destroyGraphs(c);
+    for (auto ev : c->frameEv) if (ev) cudaEventDestroy(ev);
+    if (c->frameRing) cudaFreeHost(c->frameRing);
     freeQueues(c->pb); freeExtraLanes(c);
     std::vector<HrcContext_t::Lane*> lanes;
     for (auto& L : c->extra) lanes.push_back(&L);
@@ -353,19 +379,28 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
     cudaSetDevice(c->device);
     joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
-    freeQueues(c->pb); freeExtraLanes(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
-    if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
-    c->pixelTables = false; c->offsetCount = 0;
-    freeDev(c->dBlockCoords); freeDev(c->dBlockRand); c->blocksX = c->blocksY = 0;   // block tables depend on the frame size
+    auto dropFrame = [&]() {      // the context has no framebuffer from here until every allocation below has succeeded
+        freeQueues(c->pb); freeExtraLanes(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
+        if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
+        c->pinnedBytes = 0; c->pb.accum = nullptr; c->w = c->h = 0;
+        c->pixelTables = false; c->offsetCount = 0;
+        freeDev(c->dBlockCoords); freeDev(c->dBlockRand); c->blocksX = c->blocksY = 0;   // block tables depend on the frame size
+        destroyGraphs(c);
+    };
+    dropFrame();
     const size_t n = (size_t)w * h;
-    CU(c, cudaMalloc(&c->accum, n * sizeof(float4)));
-    CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));
-    CU(c, cudaMallocHost(&c->pinned, n * sizeof(float4))); c->pinnedBytes = n * sizeof(float4);
-    std::memset(c->pinned, 0, n * sizeof(float4));
-    { int r = allocQueues(c, c->pb, n); if (r) return r; }
+    auto allocate = [&]() -> int {
+        CU(c, cudaMalloc(&c->accum, n * sizeof(float4)));
+        CU(c, cudaMemsetAsync(c->accum, 0, n * sizeof(float4), c->stream));
+        CU(c, cudaMallocHost(&c->pinned, n * sizeof(float4))); c->pinnedBytes = n * sizeof(float4);
+        std::memset(c->pinned, 0, n * sizeof(float4));
+        { int r = allocQueues(c, c->pb, n); if (r) return r; }
+        CU(c, cudaStreamSynchronize(c->stream));
+        return HRC_OK;
+    };
+    if (int r = allocate()) { const std::string why = c->err; dropFrame(); c->err = why; return r; }
     c->pb.accum = c->accum;
-    c->w = w; c->h = h; c->accumOutsideBandsZero = true; c->rbBandCount = 0; c->pinnedZeroKey = 0;
-    CU(c, cudaStreamSynchronize(c->stream));
+    c->w = w; c->h = h; c->accumOutsideBandsZero = true; c->devicePixelsExported = false; c->rbBandCount = 0; c->pinnedZeroKey = 0;
     return HRC_OK;
 }
 
@@ -373,7 +408,7 @@ HRC_API int hrcClear(HrcContext c) {
     if (!c || !c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->w * c->h * sizeof(float4), c->stream));
-    c->accumOutsideBandsZero = true; c->rbBandCount = 0;
+    c->accumOutsideBandsZero = !c->devicePixelsExported; c->rbBandCount = 0;
     return HRC_OK;
 }
 
@@ -423,7 +458,7 @@ HRC_API int hrcGetDevicePixels(HrcContext c, void** devPtr) {
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaStreamSynchronize(c->stream));
-    c->accumOutsideBandsZero = false; c->rbBandCount = 0;      // the caller may write through the pointer (in-place NCCL reduce)
+    c->accumOutsideBandsZero = false; c->rbBandCount = 0; c->devicePixelsExported = true;      // the caller may write through the pointer (in-place NCCL reduce), now and after any later hrcClear
     *devPtr = c->accum; return HRC_OK;
 }
 
@@ -706,7 +741,37 @@ HRC_API int hrcSetGlobals(HrcContext c, const HrcGlobals* g) {
     c->globals = *g; return HRC_OK;
 }
 
-static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels, float* kernelMs /*[4]: raygen, closest, shade, any*/, int* launches /*[3]*/, int lane = 0, bool pipelined = false) {
+// The kernels of one pass, in launch order, on the lane's two streams. Called either directly or under stream capture.
+static void issuePass(const DScene& sc, int slot, uint32_t total, const PassBuffers& pb, const LaunchConfig& lc, int iterations, bool overlap,
+                      cudaStream_t s, cudaStream_t s2, const std::vector<cudaEvent_t>& evSync) {
+    launchRaygen(sc, slot, total, pb, s);
+    if (!overlap || iterations < 2) {
+        for (int it = 0; it < iterations; ++it) {
+            launchTraceClosest(sc, slot, pb, it, lc, s);
+            launchShade(sc, slot, pb, it, lc, s);
+            if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
+            launchTraceAny(sc, slot, pb, it, lc, s);
+        }
+    } else {
+        // Occlusion rays of iteration i and extension rays of iteration i+1 are independent (both were emitted by shade(i)):
+        // k_trace<any>(i) runs on the second stream next to k_trace<closest>(i+1) and fills the SMs its tail leaves idle.
+        // shade(i+1) waits for both: it reuses the shadow queue and accumulates into the same pixels as the light shaders.
+        for (int it = 0; it < iterations; ++it) {
+            launchTraceClosest(sc, slot, pb, it, lc, s);
+            if (it > 0) cudaStreamWaitEvent(s, evSync[2 * (it - 1) + 1], 0);
+            launchShade(sc, slot, pb, it, lc, s);
+            cudaEventRecord(evSync[2 * it], s);
+            if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
+            cudaStreamWaitEvent(s2, evSync[2 * it], 0);
+            launchTraceAny(sc, slot, pb, it, lc, s2);
+            cudaEventRecord(evSync[2 * it + 1], s2);
+        }
+        cudaStreamWaitEvent(s, evSync[2 * (iterations - 1) + 1], 0);
+    }
+    launchFinishPass(pb, iterations, true, s);          // also re-arms the control words: a lane's IterCtrl is all zero whenever no pass is in flight on it
+}
+
+static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels, float* kernelMs /*[5]: raygen, closest, shade, any, closest of iteration 0*/, int* launches /*[3]*/, int lane = 0, bool pipelined = false) {
     if (!c || !fp) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->committed) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a committed scene");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
@@ -716,12 +781,15 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
         if (fp->blockSize[0] != c->blockW || fp->blockSize[1] != c->blockH) return fail(c, HRC_ERR_INVALID_VALUE, "blockSize differs from the uploaded block tables");
     }
     if (c->mapped) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass while pixels are mapped");
+    if (fp->sampleIndex < 0) return fail(c, HRC_ERR_INVALID_VALUE, "negative sampleIndex");
     const size_t maxIdx = (size_t)(int)(((float)(c->h - 1) + 0.5f) * (float)c->h + ((float)(c->w - 1) + 0.5f));
     if (maxIdx >= c->offsetCount) return fail(c, HRC_ERR_INVALID_VALUE, "sequence-offset table too short for the reference index formula");
     cudaSetDevice(c->device);
     if (c->materialsDirty || c->texturesDirty) { joinLanes(c); waitPendingDeferred(c); }   // the uploads rewrite tables that passes in flight on other lanes read
     int r = uploadMaterials(c); if (r) return r;
     r = uploadTextures(c); if (r) return r;
+    if (c->globals.maxRayDepth < 0 || c->globals.maxRayDepth + 1 + (c->anySingleSided ? 16 : 0) > kMaxIterations)
+        return fail(c, HRC_ERR_INVALID_VALUE, "maxRayDepth out of range (a pass runs at most 64 wavefront iterations: maxRayDepth + 1, + 16 pass-through segments with single-sided materials)");
 
     DFrame fr; std::memset(&fr, 0, sizeof(fr));
     fr.g = c->globals; fr.g.sampleIndex = fp->sampleIndex;
@@ -743,60 +811,51 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     fr.lights = c->lights;
     if (fr.lights.envEnabled && fr.lights.envTex >= 0 && !c->textures[fr.lights.envTex].alive) return fail(c, HRC_ERR_INVALID_OPERATION, "environment texture was destroyed");
 
-    int iterations = std::max(0, fr.g.maxRayDepth) + 1 + (c->anySingleSided ? 16 : 0);
-    iterations = std::min(iterations, kMaxIterations);
+    const int iterations = fr.g.maxRayDepth + 1 + (c->anySingleSided ? 16 : 0);
     const DScene sc = sceneOf(c);
     LaunchConfig lc = configOf(c);
     if (pipelined) lc.traceBlocksPerSM = c->tunePipelinedBlocksPerSM;
     HrcContext_t::Lane* L = lane > 0 ? &c->extra[lane - 1] : lane < 0 ? &c->deferred[-lane - 1] : nullptr;      // lane < 0: deferred lane -lane-1
+    const int slot = lane > 0 ? lane : lane < 0 ? kMaxLanes + (-lane - 1) : 0;
     const PassBuffers& pb = L ? L->pb : c->pb;
     const std::vector<cudaEvent_t>& evSync = L ? L->evSync : c->evSync;
-    cudaStream_t s = L ? L->s : c->stream;
+    cudaStream_t s = L ? L->s : c->stream, s2 = L ? L->s2 : c->stream2;
+    const uint32_t total = (uint32_t)fr.w * (uint32_t)fr.localRows;
 
-    size_t evNeeded = timeKernels ? (size_t)(3 * iterations + 2) : 0;
-    while (c->evPool.size() < evNeeded) { cudaEvent_t ev; CU(c, cudaEventCreate(&ev)); c->evPool.push_back(ev); }
-    size_t ev = 0;
-    auto mark = [&]() { if (timeKernels) cudaEventRecord(c->evPool[ev++], s); };
+    // per-pass constants: pinned ring entry -> the lane's constant-memory slot, in stream order
+    const int k = c->frameNext; c->frameNext = (k + 1) % kFrameRing;
+    if (c->frameUsed[k]) CU(c, cudaEventSynchronize(c->frameEv[k]));
+    c->frameRing[k] = fr; c->frameUsed[k] = true;
+    uploadFrame(&c->frameRing[k], slot, s);
+    CU(c, cudaEventRecord(c->frameEv[k], s));
 
-    launchClearCtrl(pb, s);
-    mark();
-    launchRaygen(sc, fr, pb, s);
-    mark();
-    if (timeKernels || !c->overlap || iterations < 2) {
-        for (int it = 0; it < iterations; ++it) {
-            launchTraceClosest(sc, pb, it, lc, s); mark();
-            launchShade(sc, fr, pb, it, lc, s);    if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s); mark();
-            launchTraceAny(sc, fr, pb, it, lc, s); mark();
-        }
-    } else {
-        // Occlusion rays of iteration i and extension rays of iteration i+1 are independent (both were emitted by shade(i)):
-        // k_trace<any>(i) runs on the second stream next to k_trace<closest>(i+1) and fills the SMs its tail leaves idle.
-        // shade(i+1) waits for both: it reuses the shadow queue and accumulates into the same pixels as the light shaders.
-        cudaStream_t s2 = L ? L->s2 : c->stream2;
-        for (int it = 0; it < iterations; ++it) {
-            launchTraceClosest(sc, pb, it, lc, s);
-            if (it > 0) cudaStreamWaitEvent(s, evSync[2 * (it - 1) + 1], 0);
-            launchShade(sc, fr, pb, it, lc, s);
-            cudaEventRecord(evSync[2 * it], s);
-            if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
-            cudaStreamWaitEvent(s2, evSync[2 * it], 0);
-            launchTraceAny(sc, fr, pb, it, lc, s2);
-            cudaEventRecord(evSync[2 * it + 1], s2);
-        }
-        cudaStreamWaitEvent(s, evSync[2 * (iterations - 1) + 1], 0);
-    }
-    launchFinishPass(pb, iterations, s);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return failCuda(c, e, "kernel launch");
     if (launches) { launches[0] = iterations; launches[1] = iterations * ((int)lc.shadeMiss + (int)lc.shadePbr + (int)lc.shadeGlass); launches[2] = iterations; }
-    if (timeKernels && kernelMs) {
-        CU(c, cudaStreamSynchronize(s));
-        float ms = 0; kernelMs[0] = kernelMs[1] = kernelMs[2] = kernelMs[3] = 0;
-        cudaEventElapsedTime(&ms, c->evPool[0], c->evPool[1]); kernelMs[0] = ms;
+    if (timeKernels) {
+        // instrumented pass: CUDA events between the kernels, nothing overlapped
+        const size_t evNeeded = (size_t)(3 * iterations + 2);
+        while (c->evPool.size() < evNeeded) { cudaEvent_t ev; CU(c, cudaEventCreate(&ev)); c->evPool.push_back(ev); }
+        size_t ev = 0;
+        auto mark = [&]() { cudaEventRecord(c->evPool[ev++], s); };
+        mark();
+        launchRaygen(sc, slot, total, pb, s);
+        mark();
         for (int it = 0; it < iterations; ++it) {
-            cudaEventElapsedTime(&ms, c->evPool[1 + 3 * it], c->evPool[2 + 3 * it]); kernelMs[1] += ms;
-            cudaEventElapsedTime(&ms, c->evPool[2 + 3 * it], c->evPool[3 + 3 * it]); kernelMs[2] += ms;
-            cudaEventElapsedTime(&ms, c->evPool[3 + 3 * it], c->evPool[4 + 3 * it]); kernelMs[3] += ms;
+            launchTraceClosest(sc, slot, pb, it, lc, s); mark();
+            launchShade(sc, slot, pb, it, lc, s);    if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s); mark();
+            launchTraceAny(sc, slot, pb, it, lc, s); mark();
+        }
+        launchFinishPass(pb, iterations, false, s);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return failCuda(c, e, "kernel launch");
+        CU(c, cudaStreamSynchronize(s));
+        if (kernelMs) {
+            float ms = 0; for (int q = 0; q < 5; ++q) kernelMs[q] = 0;
+            cudaEventElapsedTime(&ms, c->evPool[0], c->evPool[1]); kernelMs[0] = ms;
+            for (int it = 0; it < iterations; ++it) {
+                cudaEventElapsedTime(&ms, c->evPool[1 + 3 * it], c->evPool[2 + 3 * it]); kernelMs[1] += ms; if (it == 0) kernelMs[4] = ms;
+                cudaEventElapsedTime(&ms, c->evPool[2 + 3 * it], c->evPool[3 + 3 * it]); kernelMs[2] += ms;
+                cudaEventElapsedTime(&ms, c->evPool[3 + 3 * it], c->evPool[4 + 3 * it]); kernelMs[3] += ms;
+            }
         }
         if (std::getenv("HRC_DEBUG_ITERATIONS")) {          // per-iteration ray counts and kernel times of this pass, to stderr
             std::vector<IterCtrl> hc(iterations);
@@ -810,7 +869,39 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
                              hc[it].classCount[0], hc[it].classCount[1], hc[it].classCount[2], a, b, hc[it].shadowCount, d);
             }
         }
+        launchClearCtrl(pb, s);                             // the invariant every other pass relies on: control words are zero between passes
+        return HRC_OK;
     }
+
+    if (c->useGraphs) {
+        GraphKey key; std::memset(&key, 0, sizeof(key));
+        key.sc = sc; key.pb = pb; key.lc = lc; key.iterations = iterations; key.total = total; key.slot = slot; key.overlap = c->overlap ? 1 : 0;
+        std::vector<GraphEntry>& cache = L ? L->graphs : c->graphs;
+        GraphEntry* g = nullptr;
+        for (auto& e : cache) if (std::memcmp(&e.key, &key, sizeof(key)) == 0) { g = &e; break; }
+        if (!g) {
+            cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr;
+            cudaError_t e = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+            if (e == cudaSuccess) {
+                issuePass(sc, slot, total, pb, lc, iterations, c->overlap, s, s2, evSync);
+                e = cudaStreamEndCapture(s, &graph);
+            }
+            if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+            if (graph) cudaGraphDestroy(graph);
+            if (e != cudaSuccess) { cudaGetLastError(); return failCuda(c, e, "capturing the pass as a CUDA graph (HRC_TUNE_GRAPHS=0 launches the kernels one by one)"); }
+            if (cache.size() >= 4) {                        // a lane sees few distinct shapes (band set, depth, counters on / off): drop the least recently used
+                size_t lru = 0; for (size_t i = 1; i < cache.size(); ++i) if (cache[i].lastUse < cache[lru].lastUse) lru = i;
+                cudaGraphExecDestroy(cache[lru].exec); cache.erase(cache.begin() + lru);
+            }
+            GraphEntry ne; ne.key = key; ne.exec = exec; cache.push_back(ne); g = &cache.back();
+        }
+        g->lastUse = ++c->graphClock;
+        CU(c, cudaGraphLaunch(g->exec, s));
+        return HRC_OK;
+    }
+    issuePass(sc, slot, total, pb, lc, iterations, c->overlap, s, s2, evSync);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return failCuda(c, e, "kernel launch");
     return HRC_OK;
 }
 
@@ -833,7 +924,7 @@ static int readStats(HrcContext c, DeviceStats* out) {     // callers have joine
 HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* stats) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     cudaSetDevice(c->device); joinLanes(c);
-    float kms[4] = {0, 0, 0, 0}; int launches[3] = {0, 0, 0};
+    float kms[5] = {0, 0, 0, 0, 0}; int launches[3] = {0, 0, 0};
     DeviceStats before; int r = readStats(c, &before); if (r) return r;
     CU(c, cudaEventRecord(c->evStart, c->stream));
     r = enqueuePass(c, fp, c->kernelTiming && stats, kms, launches); if (r) return r;

@@ -19,6 +19,11 @@
 namespace hr {
 namespace {
 
+// Per-pass constants (DFrame) live in constant memory, one slot per lane of passes in flight: a pass uploads its DFrame into its lane's
+// slot in stream order (uploadFrame) and every kernel of the pass is told the slot number. The kernel arguments of a pass are then the
+// same from pass to pass, which is what lets hrc_api.cu capture the whole pass once as a CUDA graph and replay it.
+__constant__ DFrame g_frames[kFrameSlots];
+
 // ---------------------------------------------------------------------------------------
 // float3 helpers
 // ---------------------------------------------------------------------------------------
@@ -514,7 +519,9 @@ __global__ void k_clear_ctrl(IterCtrl* ctrl) {
 }
 
 // perspective.rlsl:39-93 — one thread per pixel of this context's screen bands.
-__global__ void __launch_bounds__(256) k_raygen(const DScene sc, const __grid_constant__ DFrame fr, RayQueue q, float4* accum, IterCtrl* ctrl, uint32_t total) {
+__global__ void __launch_bounds__(256) k_raygen(const DScene sc, const int slot, RayQueue q, float4* accum, IterCtrl* ctrl) {
+    const DFrame& fr = g_frames[slot];
+    const uint32_t total = (uint32_t)fr.w * (uint32_t)fr.localRows;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t == 0 && !fr.interactiveMode) ctrl[0].extCount = total;
     const int W = fr.w, H = fr.h;
@@ -601,7 +608,8 @@ __device__ __forceinline__ void prefetchL2(const void* p) { asm volatile("prefet
 #define HR_TRACE_MIN_BLOCKS 8
 #endif
 template <bool ANY, bool STATS, bool MASKED>
-__global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene sc, const __grid_constant__ DFrame fr, const PassBuffers pb, int iter, int kRefillIdle) {
+__global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene sc, const int slot, const PassBuffers pb, int iter, int kRefillIdle) {
+    const DFrame& fr = g_frames[slot];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t below = (1u << lane) - 1u;
     IterCtrl* ctrl = pb.ctrl + iter;
@@ -1142,7 +1150,8 @@ __device__ __forceinline__ uint32_t raySortKey(const DScene& sc, float3 o, float
 }
 
 template <int CLS>
-__global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const __grid_constant__ DFrame fr, PassBuffers pb, int iter, int sortBits) {
+__global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const int slot, PassBuffers pb, int iter, int sortBits) {
+    const DFrame& fr = g_frames[slot];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = (gridDim.x * blockDim.x) >> 5;
     const uint32_t warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -1292,7 +1301,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(PassBuffers pb, int iter) 
     }
 }
 
-__global__ void k_finish_pass(PassBuffers pb, int iterations) {
+__global__ void k_finish_pass(PassBuffers pb, int iterations, int rearm) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     unsigned long long ext = 0, occ = 0;
     for (int i = 1; i < iterations; ++i) ext += pb.ctrl[i].extCount;
@@ -1300,6 +1309,7 @@ __global__ void k_finish_pass(PassBuffers pb, int iterations) {
     pb.stats->raysPrimary += pb.ctrl[0].extCount;
     pb.stats->raysExtension += ext;
     pb.stats->raysOcclusion += occ;
+    if (rearm) for (int i = 0; i < kMaxIterations; ++i) pb.ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};   // the next pass on these buffers starts without a clear kernel
 }
 
 // hrcTraceRays: the fixed-ray-set parity hook. Same node / triangle steps as the pass kernels.
@@ -1330,36 +1340,38 @@ __global__ void k_add_pixels(float4* accum, const float4* src, size_t n) {
 // ---------------------------------------------------------------------------------------
 void launchClearCtrl(const PassBuffers& pb, cudaStream_t s) { k_clear_ctrl<<<1, kMaxIterations, 0, s>>>(pb.ctrl); }
 
-void launchRaygen(const DScene& sc, const DFrame& fr, const PassBuffers& pb, cudaStream_t s) {
-    const uint32_t total = (uint32_t)fr.w * (uint32_t)fr.localRows;
+void uploadFrame(const DFrame* pinnedFrame, int slot, cudaStream_t s) {
+    cudaMemcpyToSymbolAsync(g_frames, pinnedFrame, sizeof(DFrame), (size_t)slot * sizeof(DFrame), cudaMemcpyHostToDevice, s);
+}
+
+void launchRaygen(const DScene& sc, int slot, uint32_t total, const PassBuffers& pb, cudaStream_t s) {
     if (total == 0) return;
-    k_raygen<<<(total + 255) / 256, 256, 0, s>>>(sc, fr, pb.ext[0], pb.accum, pb.ctrl, total);
+    k_raygen<<<(total + 255) / 256, 256, 0, s>>>(sc, slot, pb.ext[0], pb.accum, pb.ctrl);
 }
 
-void launchTraceClosest(const DScene& sc, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
-    DFrame dummy{};   // closest-hit traversal does not read the frame constants
+void launchTraceClosest(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     const int grid = lc.smCount * lc.traceBlocksPerSM;
-    if (lc.collectStats) k_trace<false, true, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
-    else                 k_trace<false, false, false><<<grid, 128, 0, s>>>(sc, dummy, pb, iter, lc.refillIdle);
+    if (lc.collectStats) k_trace<false, true, false><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdle);
+    else                 k_trace<false, false, false><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdle);
 }
 
-void launchTraceAny(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+void launchTraceAny(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     const int grid = lc.smCount * lc.traceBlocksPerSM;
     if (lc.masked) {
-        if (lc.collectStats) k_trace<true, true, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
-        else                 k_trace<true, false, true><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
+        if (lc.collectStats) k_trace<true, true, true><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdleAny);
+        else                 k_trace<true, false, true><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdleAny);
     } else {
-        if (lc.collectStats) k_trace<true, true, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
-        else                 k_trace<true, false, false><<<grid, 128, 0, s>>>(sc, fr, pb, iter, lc.refillIdleAny);
+        if (lc.collectStats) k_trace<true, true, false><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdleAny);
+        else                 k_trace<true, false, false><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdleAny);
     }
 }
 
-void launchShade(const DScene& sc, const DFrame& fr, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+void launchShade(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
     const int grid = lc.smCount * 8;
     const int sortBits = pb.sortKeys ? lc.sortBits : 0;
-    if (lc.shadeMiss)  k_shade<0><<<grid, 128, 0, s>>>(sc, fr, pb, iter, 0);
-    if (lc.shadePbr)   k_shade<1><<<grid, 128, 0, s>>>(sc, fr, pb, iter, sortBits);
-    if (lc.shadeGlass) k_shade<2><<<grid, 128, 0, s>>>(sc, fr, pb, iter, sortBits);
+    if (lc.shadeMiss)  k_shade<0><<<grid, 128, 0, s>>>(sc, slot, pb, iter, 0);
+    if (lc.shadePbr)   k_shade<1><<<grid, 128, 0, s>>>(sc, slot, pb, iter, sortBits);
+    if (lc.shadeGlass) k_shade<2><<<grid, 128, 0, s>>>(sc, slot, pb, iter, sortBits);
 }
 
 void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
@@ -1369,7 +1381,7 @@ void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cud
     k_sort_scatter<<<lc.smCount * 4, 256, 0, s>>>(pb, iter);
 }
 
-void launchFinishPass(const PassBuffers& pb, int iterations, cudaStream_t s) { k_finish_pass<<<1, 32, 0, s>>>(pb, iterations); }
+void launchFinishPass(const PassBuffers& pb, int iterations, bool rearm, cudaStream_t s) { k_finish_pass<<<1, 32, 0, s>>>(pb, iterations, rearm ? 1 : 0); }
 
 void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig&, cudaStream_t s) {
     if (n <= 0) return;
