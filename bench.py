@@ -324,6 +324,9 @@ def main():
 
     # ---- timed region: exactly K passes, inputs resident in HBM, enqueued back to back on the context's stream and timed
     #      with CUDA events on that stream (no host synchronisation inside), then the reduce ------------------------------
+    for i in range(2 * 4):                       # untimed: every lane captures its pass graph for this launch shape (counters off) before the clock starts
+        r.enqueue_pass(sample_index=sidx(i))
+    b.clear()
     sampler = ClockSampler(local_rank)
     sampler.start()
     sampler.wait_ready()

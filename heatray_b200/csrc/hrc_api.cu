@@ -894,6 +894,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
                 cudaGraphExecDestroy(cache[lru].exec); cache.erase(cache.begin() + lru);
             }
             GraphEntry ne; ne.key = key; ne.exec = exec; cache.push_back(ne); g = &cache.back();
+            if (std::getenv("HRC_DEBUG_GRAPHS")) std::fprintf(stderr, "[hrc] captured a pass graph: lane slot %d, %d iterations, %u pixels (%zu cached on this lane)\n", slot, iterations, total, cache.size());
         }
         g->lastUse = ++c->graphClock;
         CU(c, cudaGraphLaunch(g->exec, s));
