@@ -23,7 +23,7 @@ TEX_R32F, TEX_RGB32F, TEX_RGBA32F, TEX_RGBA8 = 0, 1, 2, 3
 WRAP_CLAMP, WRAP_REPEAT = 0, 1
 DRAW_TRIANGLES, DRAW_TRIANGLE_STRIP = 0, 1
 HIT_BACKFACE = 0x40000000
-OPT_TRAVERSAL_COUNTERS, OPT_KERNEL_TIMING = 0, 1
+OPT_TRAVERSAL_COUNTERS, OPT_KERNEL_TIMING, OPT_SPECULATIVE_PASSES = 0, 1, 2
 SAMPLE_RANDOM, SAMPLE_HALTON, SAMPLE_HAMMERSLEY, SAMPLE_BLUE_NOISE, SAMPLE_SOBOL = range(5)
 BOKEH_CIRCULAR, BOKEH_PENTAGON, BOKEH_HEXAGON, BOKEH_OCTAGON = range(4)
 
@@ -121,7 +121,8 @@ class FrameParams(C.Structure):
 class PassStats(C.Structure):
     _fields_ = [("gpuMs", f32), ("raysPrimary", u64), ("raysExtension", u64), ("raysOcclusion", u64), ("nodesVisited", u64),
                 ("trianglesTested", u64), ("nodesVisitedAny", u64), ("trianglesTestedAny", u64), ("closestLaunches", u64), ("anyLaunches", u64), ("shadeLaunches", u64),
-                ("msClosest", f32), ("msAny", f32), ("msShade", f32), ("msRaygen", f32)]
+                ("msClosest", f32), ("msAny", f32), ("msShade", f32), ("msRaygen", f32),
+                ("msClosestPrimary", f32), ("reserved0", f32), ("nodesVisitedPrimary", u64), ("trianglesTestedPrimary", u64)]
 
     @property
     def rays(self):

@@ -83,6 +83,7 @@ struct SortCtrl { uint32_t sorted; uint32_t pad[3]; };   // per iteration: 1 whe
 
 struct DeviceStats {                       // accumulated by k_finish_pass
     unsigned long long raysPrimary, raysExtension, raysOcclusion, nodesVisited, trianglesTested, nodesVisitedAny, trianglesTestedAny, stackOverflows;
+    unsigned long long nodesVisitedPrimary, trianglesTestedPrimary;      // iteration 0 of the closest-hit kernel (included in nodesVisited / trianglesTested)
 };
 
 struct DScene {

@@ -51,6 +51,13 @@ struct HrcContext_t {
     // point first joins the lanes (accum += the extra lanes' buffers), so callers see one buffer; the result is deterministic for a given call sequence.
     struct Lane { PassBuffers pb{}; cudaStream_t s = nullptr, s2 = nullptr; std::vector<cudaEvent_t> evSync; float4* accum = nullptr;
                   cudaEvent_t evDone = nullptr; bool active = false; std::vector<GraphEntry> graphs; } extra[kMaxLanes - 1];      // lanes 1 .. passLanes-1; lane 0 is the main set above
+    // Speculative look-ahead (HRC_OPT_SPECULATIVE_PASSES = n > 0): hrcRenderPass(i) also starts passes i+1 .. i+n of the same progressive
+    // render in the deferred lanes. If the caller's next hrcRenderPass asks for exactly what was predicted (same frame parameters, next
+    // sample index, no state change in between) the pass is already rendered or under way and is simply committed; anything else discards
+    // the predictions. A caller that renders and reads back one pass at a time (the reference viewer's loop) then gets its readback
+    // overlapped with the next passes without queueing anything itself.
+    int specDepth = 0; uint64_t stateVersion = 0;
+    HrcFrameParams deferredParams[kDeferredLanes] = {}; uint64_t deferredVersion[kDeferredLanes] = {};
     std::vector<GraphEntry> graphs;        // captured passes of the main lane
     bool useGraphs = true; uint64_t graphClock = 0;
     DFrame* frameRing = nullptr; cudaEvent_t frameEv[kFrameRing] = {}; bool frameUsed[kFrameRing] = {}; int frameNext = 0;
@@ -365,6 +372,11 @@ HRC_API int hrcSetOption(HrcContext c, int32_t option, int32_t value) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     if (option == HRC_OPT_TRAVERSAL_COUNTERS) c->counters = value != 0;
     else if (option == HRC_OPT_KERNEL_TIMING) c->kernelTiming = value != 0;
+    else if (option == HRC_OPT_SPECULATIVE_PASSES) {
+        if (value < 0 || value > HRC_MAX_DEFERRED_PASSES) return fail(c, HRC_ERR_INVALID_VALUE, "0..3 speculative passes");
+        if (c->deferredCount > 0) { int r = hrcDiscardDeferred(c); if (r) return r; }
+        c->specDepth = value;
+    }
     else return fail(c, HRC_ERR_INVALID_VALUE, "unknown option");
     return HRC_OK;
 }
@@ -372,6 +384,7 @@ HRC_API int hrcSetOption(HrcContext c, int32_t option, int32_t value) {
 HRC_API const char* hrcGetLastError(HrcContext c) { return c ? c->err.c_str() : g_err.c_str(); }
 
 HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
+    if (c) c->stateVersion++;
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     if (w <= 0 || h <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "non-positive framebuffer size");
     if ((uint64_t)w * (uint64_t)h > (1u << 24)) return fail(c, HRC_ERR_UNSUPPORTED, "framebuffers above 2^24 pixels are not supported (pixel index is packed in 24 bits)");
@@ -405,6 +418,7 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
 }
 
 HRC_API int hrcClear(HrcContext c) {
+    if (c) c->stateVersion++;
     if (!c || !c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->w * c->h * sizeof(float4), c->stream));
@@ -442,6 +456,7 @@ HRC_API int hrcReleasePixels(HrcContext c) {
     c->mapped = false; return HRC_OK;
 }
 HRC_API int hrcAddPixels(HrcContext c, const float* rgba) {
+    if (c) c->stateVersion++;
     if (!c || !rgba) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
@@ -454,6 +469,7 @@ HRC_API int hrcAddPixels(HrcContext c, const float* rgba) {
     return HRC_OK;
 }
 HRC_API int hrcGetDevicePixels(HrcContext c, void** devPtr) {
+    if (c) c->stateVersion++;
     if (!c || !devPtr) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
@@ -486,6 +502,7 @@ HRC_API int hrcResolve(HrcContext c, const HrcPostProcess* post, int32_t format,
 }
 
 HRC_API int hrcCreateTexture2D(HrcContext c, const HrcTextureDesc* d, const void* pixels, HrcTexture* out) {
+    if (c) c->stateVersion++;
     if (!c || !d || !pixels || !out || d->width <= 0 || d->height <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad texture descriptor");
     cudaSetDevice(c->device); joinLanes(c);
     const size_t n = (size_t)d->width * d->height;
@@ -509,6 +526,7 @@ HRC_API int hrcCreateTexture2D(HrcContext c, const HrcTextureDesc* d, const void
     return HRC_OK;
 }
 HRC_API int hrcDestroyTexture(HrcContext c, HrcTexture tex) {
+    if (c) c->stateVersion++;
     if (!c || tex < 0 || tex >= (int)c->textures.size() || !c->textures[tex].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad texture handle");
     cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
@@ -517,6 +535,7 @@ HRC_API int hrcDestroyTexture(HrcContext c, HrcTexture tex) {
 }
 
 HRC_API int hrcCreateMaterial(HrcContext c, int32_t type, uint32_t flags, const void* params, size_t bytes, HrcMaterial* out) {
+    if (c) c->stateVersion++;
     if (!c || !params || !out) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (flags >> 10) return fail(c, HRC_ERR_INVALID_VALUE, "unknown material feature flags");
     MaterialRec m; m.flags = flags;
@@ -526,12 +545,14 @@ HRC_API int hrcCreateMaterial(HrcContext c, int32_t type, uint32_t flags, const 
     return HRC_OK;
 }
 HRC_API int hrcUpdateMaterial(HrcContext c, HrcMaterial mat, const void* params, size_t bytes) {
+    if (c) c->stateVersion++;
     if (!c || mat < 0 || mat >= (int)c->materials.size() || !params) return fail(c, HRC_ERR_INVALID_VALUE, "bad material handle");
     int r = packMaterial(c, c->materials[mat], c->materials[mat].type, params, bytes); if (r) return r;
     c->materialsDirty = true; return HRC_OK;
 }
 
 HRC_API int hrcCreateMesh(HrcContext c, const HrcMeshDesc* d, HrcMesh* out) {
+    if (c) c->stateVersion++;
     if (!c || !d || !out || !d->positions || !d->normals || !d->indices) return fail(c, HRC_ERR_INVALID_VALUE, "mesh needs positions, normals and indices");
     if (d->material < 0 || d->material >= (int)c->materials.size()) return fail(c, HRC_ERR_INVALID_VALUE, "bad material handle");
     if (d->drawMode != HRC_DRAW_TRIANGLES && d->drawMode != HRC_DRAW_TRIANGLE_STRIP) return fail(c, HRC_ERR_INVALID_VALUE, "bad draw mode");
@@ -559,20 +580,24 @@ HRC_API int hrcCreateMesh(HrcContext c, const HrcMeshDesc* d, HrcMesh* out) {
     return HRC_OK;
 }
 HRC_API int hrcDestroyMesh(HrcContext c, HrcMesh mesh) {
+    if (c) c->stateVersion++;
     if (!c || mesh < 0 || mesh >= (int)c->meshes.size() || !c->meshes[mesh].alive) return fail(c, HRC_ERR_INVALID_VALUE, "bad mesh handle");
     c->meshes[mesh] = MeshRec(); c->committed = false; return HRC_OK;
 }
 HRC_API int hrcSetMeshTransform(HrcContext c, HrcMesh mesh, const float* worldFromEntity) {
+    if (c) c->stateVersion++;
     if (!c || mesh < 0 || mesh >= (int)c->meshes.size() || !c->meshes[mesh].alive || !worldFromEntity) return fail(c, HRC_ERR_INVALID_VALUE, "bad mesh handle");
     std::memcpy(c->meshes[mesh].M, worldFromEntity, sizeof(c->meshes[mesh].M)); c->committed = false; return HRC_OK;
 }
 HRC_API int hrcClearScene(HrcContext c) {
+    if (c) c->stateVersion++;
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     c->meshes.clear(); c->materials.clear(); c->committed = false; c->materialsDirty = true;
     return HRC_OK;
 }
 
 HRC_API int hrcCommitScene(HrcContext c) {
+    if (c) c->stateVersion++;
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
@@ -669,6 +694,7 @@ HRC_API int hrcCommitScene(HrcContext c) {
 }
 
 HRC_API int hrcSetEnvironment(HrcContext c, const HrcEnvLight* env) {
+    if (c) c->stateVersion++;
     if (!c || !env) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     if (env->enabled && env->texture >= 0 && (env->texture >= (int)c->textures.size() || !c->textures[env->texture].alive))
         return fail(c, HRC_ERR_INVALID_VALUE, "bad environment texture handle");
@@ -676,18 +702,21 @@ HRC_API int hrcSetEnvironment(HrcContext c, const HrcEnvLight* env) {
     return HRC_OK;
 }
 HRC_API int hrcSetDirectionalLights(HrcContext c, int32_t n, const HrcDirLight* l) {
+    if (c) c->stateVersion++;
     if (!c || n < 0 || n > HRC_MAX_LIGHTS_PER_TYPE || (n && !l)) return fail(c, HRC_ERR_INVALID_VALUE, "0..5 directional lights");
     c->lights.nDir = n;
     for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) { c->lights.dirDirection[i][k] = l[i].direction[k]; c->lights.dirColor[i][k] = l[i].color[k]; }
     return HRC_OK;
 }
 HRC_API int hrcSetPointLights(HrcContext c, int32_t n, const HrcPointLight* l) {
+    if (c) c->stateVersion++;
     if (!c || n < 0 || n > HRC_MAX_LIGHTS_PER_TYPE || (n && !l)) return fail(c, HRC_ERR_INVALID_VALUE, "0..5 point lights");
     c->lights.nPoint = n;
     for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) { c->lights.pointPosition[i][k] = l[i].position[k]; c->lights.pointColor[i][k] = l[i].color[k]; }
     return HRC_OK;
 }
 HRC_API int hrcSetSpotLights(HrcContext c, int32_t n, const HrcSpotLight* l) {
+    if (c) c->stateVersion++;
     if (!c || n < 0 || n > HRC_MAX_LIGHTS_PER_TYPE || (n && !l)) return fail(c, HRC_ERR_INVALID_VALUE, "0..5 spot lights");
     c->lights.nSpot = n;
     for (int i = 0; i < n; ++i) {
@@ -698,6 +727,7 @@ HRC_API int hrcSetSpotLights(HrcContext c, int32_t n, const HrcSpotLight* l) {
 }
 
 HRC_API int hrcSetSequences(HrcContext c, int32_t ns, int32_t len, const float* xy, const float* ap) {
+    if (c) c->stateVersion++;
     if (!c || ns <= 0 || len <= 0 || !xy || !ap) return fail(c, HRC_ERR_INVALID_VALUE, "bad sequence tables");
     cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
     CU(c, cudaStreamSynchronize(c->stream));
@@ -710,6 +740,7 @@ HRC_API int hrcSetSequences(HrcContext c, int32_t ns, int32_t len, const float* 
     return HRC_OK;
 }
 HRC_API int hrcSetPixelTables(HrcContext c, const float* off, size_t count, const uint8_t* sid) {
+    if (c) c->stateVersion++;
     if (!c || !off || !sid || count == 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad pixel tables");
     if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "pixel tables need a framebuffer size first");
     cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
@@ -723,6 +754,7 @@ HRC_API int hrcSetPixelTables(HrcContext c, const float* off, size_t count, cons
     return HRC_OK;
 }
 HRC_API int hrcSetInteractiveBlocks(HrcContext c, int32_t bw, int32_t bh, const float* coords, int32_t bx, int32_t by, const float* rnd) {
+    if (c) c->stateVersion++;
     if (!c || !coords || !rnd || bw <= 0 || bh <= 0 || bx <= 0 || by <= 0) return fail(c, HRC_ERR_INVALID_VALUE, "bad interactive block tables");
     if (c->w <= 0) return fail(c, HRC_ERR_INVALID_OPERATION, "interactive block tables need a framebuffer size first");
     if ((int64_t)bx * bw < c->w || (int64_t)by * bh < c->h) return fail(c, HRC_ERR_INVALID_VALUE, "block tables do not cover the frame");
@@ -737,6 +769,7 @@ HRC_API int hrcSetInteractiveBlocks(HrcContext c, int32_t bw, int32_t bh, const 
     return HRC_OK;
 }
 HRC_API int hrcSetGlobals(HrcContext c, const HrcGlobals* g) {
+    if (c) c->stateVersion++;
     if (!c || !g) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
     c->globals = *g; return HRC_OK;
 }
@@ -918,6 +951,34 @@ static int readStats(HrcContext c, DeviceStats* out) {     // callers have joine
     out->raysPrimary += b.raysPrimary; out->raysExtension += b.raysExtension; out->raysOcclusion += b.raysOcclusion;
     out->nodesVisited += b.nodesVisited; out->trianglesTested += b.trianglesTested; out->nodesVisitedAny += b.nodesVisitedAny;
     out->trianglesTestedAny += b.trianglesTestedAny; out->stackOverflows += b.stackOverflows;
+    out->nodesVisitedPrimary += b.nodesVisitedPrimary; out->trianglesTestedPrimary += b.trianglesTestedPrimary;
+    }
+    return HRC_OK;
+}
+
+// hrcRenderPass under HRC_OPT_SPECULATIVE_PASSES: commit the predicted pass if the prediction holds, else render it now; then keep
+// specDepth passes of the same progressive render running ahead in the deferred lanes.
+static int renderOrCommitPredicted(HrcContext c, const HrcFrameParams* fp, int* launches) {
+    if (!fp) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    int r = HRC_OK;
+    const int oldest = c->oldestDeferred();
+    const bool hit = c->deferredCount > 0 && c->deferredVersion[oldest] == c->stateVersion && std::memcmp(&c->deferredParams[oldest], fp, sizeof(*fp)) == 0;
+    if (hit) { c->deferred[oldest].active = true; c->deferredCount--; }            // the next join folds it in (and waits for it, in stream order)
+    else {
+        if (c->deferredCount > 0) { r = hrcDiscardDeferred(c); if (r) return r; }
+        r = enqueuePass(c, fp, false, nullptr, launches); if (r) return r;
+    }
+    if (fp->interactiveMode) return HRC_OK;                                         // block passes change their parameters every pass: not predicted
+    HrcFrameParams nx = *fp;
+    for (int ahead = c->deferredCount + 1; ahead <= c->specDepth; ++ahead) {
+        nx.sampleIndex = fp->sampleIndex + ahead;
+        if ((float)nx.sampleIndex >= fp->maxSampleIndex) break;                      // the progressive render ends at maxRenderPasses (PassGenerator.cpp:368)
+        const int d = c->deferredNext;
+        if (c->deferred[d].active) joinLanes(c);                                    // its previous pass was committed but not folded in yet
+        r = ensureLane(c, c->deferred[d]); if (r) return r;
+        r = enqueuePass(c, &nx, false, nullptr, nullptr, -(d + 1), true); if (r) return r;
+        c->deferredParams[d] = nx; c->deferredVersion[d] = c->stateVersion;
+        c->deferredNext = (d + 1) % kDeferredLanes; c->deferredCount++;
     }
     return HRC_OK;
 }
@@ -928,7 +989,9 @@ HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* 
     float kms[5] = {0, 0, 0, 0, 0}; int launches[3] = {0, 0, 0};
     DeviceStats before; int r = readStats(c, &before); if (r) return r;
     CU(c, cudaEventRecord(c->evStart, c->stream));
-    r = enqueuePass(c, fp, c->kernelTiming && stats, kms, launches); if (r) return r;
+    if (c->specDepth > 0 && !(c->kernelTiming && stats)) { r = renderOrCommitPredicted(c, fp, launches); if (r) return r; joinLanes(c); }
+    else { if (c->deferredCount > 0 && c->specDepth > 0) { r = hrcDiscardDeferred(c); if (r) return r; }
+    r = enqueuePass(c, fp, c->kernelTiming && stats, kms, launches); if (r) return r; }
     CU(c, cudaEventRecord(c->evStop, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return failCuda(c, e, "render pass");
@@ -941,7 +1004,8 @@ HRC_API int hrcRenderPass(HrcContext c, const HrcFrameParams* fp, HrcPassStats* 
         stats->nodesVisited = after.nodesVisited - before.nodesVisited; stats->trianglesTested = after.trianglesTested - before.trianglesTested;
         stats->nodesVisitedAny = after.nodesVisitedAny - before.nodesVisitedAny; stats->trianglesTestedAny = after.trianglesTestedAny - before.trianglesTestedAny;
         stats->closestLaunches = launches[0]; stats->shadeLaunches = launches[1]; stats->anyLaunches = launches[2];
-        stats->msRaygen = kms[0]; stats->msClosest = kms[1]; stats->msShade = kms[2]; stats->msAny = kms[3];
+        stats->msRaygen = kms[0]; stats->msClosest = kms[1]; stats->msShade = kms[2]; stats->msAny = kms[3]; stats->msClosestPrimary = kms[4];
+        stats->nodesVisitedPrimary = after.nodesVisitedPrimary - before.nodesVisitedPrimary; stats->trianglesTestedPrimary = after.trianglesTestedPrimary - before.trianglesTestedPrimary;
         if (after.stackOverflows != before.stackOverflows) return fail(c, HRC_ERR_INVALID_OPERATION, "traversal stack overflow");
     }
     return HRC_OK;
@@ -965,6 +1029,7 @@ HRC_API int hrcEnqueuePass(HrcContext c, const HrcFrameParams* fp) {
 // before it reads the current result back (hr::PassGenerator look-ahead).
 HRC_API int hrcEnqueuePassDeferred(HrcContext c, const HrcFrameParams* fp) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (c->specDepth > 0) return fail(c, HRC_ERR_INVALID_OPERATION, "the deferred lanes are in use by HRC_OPT_SPECULATIVE_PASSES");
     if (c->deferredCount >= kDeferredLanes - 1) return fail(c, HRC_ERR_INVALID_OPERATION, "too many deferred passes are pending (commit or discard first)");
     if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "render pass without a framebuffer");
     cudaSetDevice(c->device);
@@ -1029,6 +1094,7 @@ HRC_API int hrcGetStats(HrcContext c, HrcPassStats* stats) {
     stats->raysPrimary = d.raysPrimary; stats->raysExtension = d.raysExtension; stats->raysOcclusion = d.raysOcclusion;
     stats->nodesVisited = d.nodesVisited; stats->trianglesTested = d.trianglesTested;
     stats->nodesVisitedAny = d.nodesVisitedAny; stats->trianglesTestedAny = d.trianglesTestedAny;
+    stats->nodesVisitedPrimary = d.nodesVisitedPrimary; stats->trianglesTestedPrimary = d.trianglesTestedPrimary;
     return HRC_OK;
 }
 

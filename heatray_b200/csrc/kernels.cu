@@ -726,6 +726,7 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
             atomicAdd(ANY ? &pb.stats->nodesVisitedAny : &pb.stats->nodesVisited, (unsigned long long)n);
             atomicAdd(ANY ? &pb.stats->trianglesTestedAny : &pb.stats->trianglesTested, (unsigned long long)t);
             if (ov) atomicAdd(&pb.stats->stackOverflows, (unsigned long long)ov);
+            if (!ANY && iter == 0) { atomicAdd(&pb.stats->nodesVisitedPrimary, (unsigned long long)n); atomicAdd(&pb.stats->trianglesTestedPrimary, (unsigned long long)t); }
         }
     }
 }

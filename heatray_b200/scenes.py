@@ -260,7 +260,7 @@ def cornell_box(width=512, height=512, passes=64, max_depth=4):
                      camera=dict(distance=5.4, phi=0.0, theta=0.0, target=(0.0, 1.0, 0.0), focal_length=50.0, fstop=None, focus_distance=5.4))
 
 
-def sphere_grid(width=1920, height=1080, passes=32, max_depth=8, grid=8, u_slices=64, v_slices=32, seed=2, env_size=(2048, 1024)):
+def sphere_grid(width=1920, height=1080, passes=32, max_depth=8, grid=8, u_slices=64, v_slices=32, seed=2, env_size=(2048, 1024), distance=None, name="sphere_grid"):
     """Config #2 ("Sponza-scale"): grid x grid lat-long spheres (2*u*v tris each) + floor + 2 walls (6 tris)."""
     rng = SplitMix64(seed)
     mats = [_pbr((0.6, 0.6, 0.6), rough=0.9, f0=0.5)]
@@ -281,9 +281,16 @@ def sphere_grid(width=1920, height=1080, passes=32, max_depth=8, grid=8, u_slice
             x = (gx - (grid - 1) / 2) * 1.9
             z = (gz - (grid - 1) / 2) * 1.9
             meshes.append(MeshSpec(sp, sn, si, len(mats) - 1, translate(x, 0.0, z)))
-    return SceneSpec("sphere_grid", width, height, passes, max_depth, meshes, mats,
+    distance = 19.0 * grid / 8 if distance is None else distance            # OrbitCamera.h:22 default distance for the 8 x 8 grid, scaled with the grid
+    return SceneSpec(name, width, height, passes, max_depth, meshes, mats,
                      env=dict(enabled=True, solid=None, map=studio_environment(*env_size), ev=0.0, theta=0.0),
-                     camera=dict(distance=19.0, phi=0.0, theta=0.6, target=(0.0, 0.0, 0.0), focal_length=50.0, fstop=None, focus_distance=19.0))
+                     camera=dict(distance=distance, phi=0.0, theta=0.6, target=(0.0, 0.0, 0.0), focal_length=50.0, fstop=None, focus_distance=distance))
+
+
+def sphere_grid_1m(width=1920, height=1080, passes=32, max_depth=8):
+    """The workload BASELINE.json's target is quoted on: ~1 M triangles at 1080p, 8 bounces — a 16 x 16 grid of the reference's own
+    64 x 32 lat-long spheres (SphereMeshProvider.h:45-131, 4096 triangles each) = 1,048,576 + floor / walls (6) = 1,048,582 triangles."""
+    return sphere_grid(width, height, passes, max_depth, grid=16, seed=6, name="sphere_grid_1m")
 
 
 def material_grid(width=1920, height=1080, passes=32, max_depth=8, grid=11, u_slices=64, v_slices=32, seed=3):

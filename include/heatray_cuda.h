@@ -65,7 +65,14 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out);
 /* Runtime switches (no reference equivalent; OpenRL exposes RL_PROFILE-style enums it never uses, rl.h:346-355). */
 enum {
     HRC_OPT_TRAVERSAL_COUNTERS = 0,  /* count nodes visited / triangles tested (slightly slower kernels) */
-    HRC_OPT_KERNEL_TIMING = 1        /* CUDA events between kernels: HrcPassStats.ms* are filled by hrcRenderPass */
+    HRC_OPT_KERNEL_TIMING = 1,       /* CUDA events between kernels: HrcPassStats.ms* are filled by hrcRenderPass */
+    HRC_OPT_SPECULATIVE_PASSES = 2   /* n = 0..3 (default 0): hrcRenderPass(i) also starts passes i+1..i+n of the same progressive render (same frame
+                                      * parameters, consecutive sample indices below maxSampleIndex) into side buffers nothing else sees. When the next
+                                      * hrcRenderPass asks for exactly the predicted pass and no state changed in between, it is committed instead of
+                                      * rendered; any other request discards the predictions. For callers that render and read back one pass at a
+                                      * time (the reference viewer's loop, HeatrayRenderer.cpp:366-408): the readback then overlaps the next passes.
+                                      * The picture differs from the unspeculated one by fp32 addition order only. With n > 0 HrcPassStats counts the
+                                      * work that finished during the call (one pass in steady state), and hrcEnqueuePassDeferred is unavailable. */
 };
 HRC_API int hrcSetOption(HrcContext ctx, int32_t option, int32_t value);
 HRC_API int hrcDestroyContext(HrcContext ctx);
@@ -250,6 +257,10 @@ typedef struct HrcPassStats {
     uint64_t nodesVisitedAny, trianglesTestedAny;         /* occlusion kernel; only with HRC_OPT_TRAVERSAL_COUNTERS */
     uint64_t closestLaunches, anyLaunches, shadeLaunches; /* kernels launched by this pass */
     float    msClosest, msAny, msShade, msRaygen;         /* only with HRC_OPT_KERNEL_TIMING (per-kernel events, summed over the pass) */
+    /* the primary-ray share of the closest-hit figures above (wavefront iteration 0), so that callers can report secondary
+     * (extension) rays on their own: secondary = total - primary */
+    float    msClosestPrimary; float reserved0;
+    uint64_t nodesVisitedPrimary, trianglesTestedPrimary;
 } HrcPassStats;
 /* Enqueues and completes one pass; stats may be NULL. */
 HRC_API int hrcRenderPass(HrcContext ctx, const HrcFrameParams* frame, HrcPassStats* stats);
