@@ -133,6 +133,8 @@ class ClockSampler(threading.Thread):
 def build_spec(name, small=False):
     if name == "sphere_grid":
         return scenes.sphere_grid() if not small else scenes.sphere_grid(width=480, height=270, grid=4, u_slices=32, v_slices=16, env_size=(512, 256))
+    if name == "sphere_grid_1m":
+        return scenes.sphere_grid_1m() if not small else scenes.sphere_grid(width=480, height=270, grid=6, u_slices=32, v_slices=16, env_size=(512, 256), name="sphere_grid_1m")
     if name == "material_grid":
         return scenes.material_grid() if not small else scenes.material_grid(width=480, height=270, grid=5, u_slices=32, v_slices=16)
     if name == "terrain":
@@ -146,21 +148,23 @@ def build_spec(name, small=False):
 
 WORKLOAD_NAMES = {
     "sphere_grid": "configs[1]: procedural Sponza-scale 8x8 sphere grid, PBR roughness/metallic + env light + NEE",
+    "sphere_grid_1m": "north_star target workload: ~1M-triangle scene (16x16 grid of the reference's 64x32 lat-long spheres), 1080p, 8 bounces, PBR + env light + NEE",
     "material_grid": "configs[2]: 11x11 glass + clearcoat material grid, f/2.8 hexagonal bokeh, spot + directional",
     "terrain": "configs[3]: displaced terrain + flattened foliage",
     "cornell": "configs[0]: Cornell box, 1 point light",
     "convergence": "configs[4]: convergence run 3840x2160, 1024 spp sharded by sample index, NCCL reduce of the fp32 accumulation buffer",
 }
+BAND_ROWS = int(os.environ.get("HR_BENCH_BAND_ROWS", "16"))
 
 
 def config_dict(spec, name, n_gpus, extra=None, shard="sample"):
-    par = "single GPU" if n_gpus <= 1 else (f"sample-index sharding x{n_gpus}, one NCCL fp32 sum-reduce of the accumulation buffer" if shard == "sample"
-                                            else f"screen-band sharding x{n_gpus} (interleaved 16-row bands), one NCCL fp32 sum-reduce of the disjoint bands")
+    par = "single GPU" if n_gpus <= 1 else (f"sample-index sharding x{n_gpus}, one NCCL fp32 sum of the accumulation buffers" if shard == "sample"
+                                            else f"screen-band sharding x{n_gpus} (interleaved {BAND_ROWS}-row bands), one NCCL gather of each rank's own rows")
     d = {"workload": WORKLOAD_NAMES[name], "scene": spec.name, "triangles": spec.triangle_count, "resolution": f"{spec.width}x{spec.height}",
          "max_ray_depth": spec.max_depth, "spp_per_step": 1, "qmc": "owen-scrambled sobol (16 sequences)",
          "parallelism": par,
          "l2_policy": "inputs larger than L2: every pass streams its ray / hit queues (%d MB at this resolution) through the 126 MB L2; the BVH + triangles are %s" % (
-             spec.width * spec.height * 204 // 1000000, "L2-resident by design (< 126 MB)" if spec.triangle_count < 1000000 else "larger than L2 as well")}
+             spec.width * spec.height * 204 // 1000000, "L2-resident by design (< 126 MB)" if spec.triangle_count < 1000000 else "not guaranteed to stay in L2 beside them")}
     if extra:
         d.update(extra)
     return d
@@ -176,7 +180,7 @@ def algorithmic_bytes(st, closest=True):
 
 
 def run_reference(args, rank, world):
-    """CPU arm: the oracle (a restatement of the reference's shaders; OpenRL itself cannot run here), all host threads."""
+    """CPU arm: the oracle (a restatement of the reference's shaders, pinned to the shader text; OpenRL itself cannot run here), all host threads."""
     if rank != 0:
         return
     from oracle import loader
@@ -203,7 +207,7 @@ def run_reference(args, rank, world):
             "ms_per_step": statistics.mean(step_ms), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "reference", "config": config_dict(spec, args.config, 1, {"step": sample}),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                             "note": "CPU restatement of reference shaders + own BVH; OpenRL itself unavailable on this box"},
+                             "note": "CPU restatement of reference shaders (pinned bit for bit to the shader text, tests/test_shader_pinning.py) + own BVH; OpenRL itself unavailable on this box"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -229,15 +233,130 @@ def cpu_baseline_sample(spec, budget_s=12.0):
             "note": "CPU restatement of reference shaders + own BVH (oracle/, -O3 x86-64-v3 build); OpenRL itself unavailable on this box"}
 
 
+class Rig:
+    """One rank's backend + renderer + the torch view of its accumulation buffer and the exchange step of its sharding mode."""
+
+    def __init__(self, lib, spec, shard, rank, world, local_rank, steps):
+        import torch
+        self.torch, self.spec, self.shard, self.rank, self.world, self.local_rank = torch, spec, shard, rank, world, local_rank
+        self.bands = shard == "bands" and world > 1
+        self.b = capi.Backend(lib, "hrc", device=local_rank, collect_stats=False)
+        self.r = renderer.Renderer(self.b)
+        self.r.load_scene(spec)
+        self.info = self.b.scene_info()
+        # sample-index sharding: rank r renders sample indices r, r + world, ... (wrapped into the QMC table length);
+        # screen-band sharding: every rank renders every sample index for its interleaved bands (strong scaling)
+        self.passes_total = max(spec.passes, steps if self.bands else steps * world)
+        if self.bands:
+            self.r.set_band(BAND_ROWS, rank, world)
+        self.r.reset(passes=self.passes_total)
+        if self.bands:
+            self.r.set_band(BAND_ROWS, rank, world)
+        self.acc = None
+        if world > 1:
+            ptr = self.b.device_pixels()
+
+            class _Arr:
+                __cuda_array_interface__ = {"shape": (spec.height, spec.width, 4), "typestr": "<f4", "data": (ptr, False), "version": 2}
+            self.acc = torch.as_tensor(_Arr(), device=f"cuda:{local_rank}")
+            self.red = torch.empty_like(self.acc)                 # the exchange step of the e2e region works on a copy: the local sum keeps growing
+            self.host = torch.empty(self.acc.shape, dtype=self.acc.dtype, pin_memory=True) if rank == 0 else None
+        self.ev0, self.ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def sidx(self, step):
+        return step % self.passes_total if self.bands else (self.rank + step * self.world) % self.passes_total
+
+    def exchange(self, buf=None):
+        """The one collective of the path, timed with CUDA events on torch's current stream (the pass streams were synchronised before).
+        Sample mode: fp32 sum of the accumulation buffers (HR_BENCH_COLLECTIVE = all_reduce (default, in-switch reduction where NCCL has NVLS) | reduce).
+        Band mode: gather of each rank's own rows onto rank 0 (disjoint pixels, frame / world bytes per rank)."""
+        if self.world <= 1:
+            return 0.0
+        import torch.distributed as dist
+        from heatray_b200 import sharding
+        buf = self.acc if buf is None else buf
+        self.ev0.record()
+        if self.bands:
+            sharding.gather_bands(buf, BAND_ROWS, self.rank, self.world, dst=0)
+        elif os.environ.get("HR_BENCH_COLLECTIVE", "all_reduce") == "reduce":
+            dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
+        else:
+            dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+        self.ev1.record()
+        self.ev1.synchronize()
+        return self.ev0.elapsed_time(self.ev1)
+
+    def close(self):
+        self.b.close()
+
+
+def measure_value(rig, K, barrier, sampler=None):
+    """Exactly K passes, inputs resident in HBM, enqueued back to back (hrcEnqueuePass) and timed with CUDA events on the launching stream, then the exchange step."""
+    b, r = rig.b, rig.r
+    for i in range(2 * 4):                       # untimed: every lane captures its pass graph for this launch shape before the clock starts
+        r.enqueue_pass(sample_index=rig.sidx(i))
+    b.clear()
+    b.reset_stats()                              # ray totals read after the region count its K passes only
+    barrier()
+    if sampler:
+        sampler.samples.clear()                  # idle samples from before the region do not count
+    t0 = time.perf_counter()
+    b.timer_start()
+    for i in range(K):
+        r.enqueue_pass(sample_index=rig.sidx(i))
+    pass_ms = b.timer_stop()
+    ex_ms = rig.exchange()
+    barrier()
+    t1 = time.perf_counter()
+    return pass_ms, ex_ms, t0, t1
+
+
+def exchange_check(rig, barrier, passes_per_rank=4):
+    """Multi-GPU correctness on the hardware: the exchanged frame of `passes_per_rank` passes per rank against rank 0's own single-GPU render of the
+    same sample indices (sample mode: alpha exact, rgb up to fp32 summation order; band mode: bit-identical)."""
+    import torch
+    b, r, world = rig.b, rig.r, rig.world
+    b.clear()
+    for i in range(passes_per_rank):
+        r.render_pass(want_stats=False, sample_index=rig.sidx(i))
+    b.synchronize()
+    barrier()
+    rig.exchange()
+    out = None
+    if rig.rank == 0:
+        multi = rig.acc.clone()
+        b.clear()
+        if rig.bands:
+            r.set_band(0, 0, 1)
+            indices = [rig.sidx(i) for i in range(passes_per_rank)]
+        else:
+            indices = [(q + i * world) % rig.passes_total for i in range(passes_per_rank) for q in range(world)]
+        for s in indices:
+            r.render_pass(want_stats=False, sample_index=s)
+        b.synchronize()
+        single = rig.acc
+        alpha_exact = bool(torch.equal(multi[..., 3], single[..., 3])) and bool((single[..., 3] == len(indices)).all())
+        denom = torch.clamp(single[..., :3].abs(), min=1e-3)
+        max_rel = float(((multi[..., :3] - single[..., :3]).abs() / denom).max())
+        out = {"alpha_exact": alpha_exact, "max_rel": max_rel, "bit_identical": bool(torch.equal(multi, single)),
+               "passes": len(indices), "what": "exchanged N-rank frame vs rank 0's single-GPU render of the same sample indices"}
+        if rig.bands:
+            r.set_band(BAND_ROWS, rig.rank, world)
+    b.clear()
+    barrier()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=128)    # 128 passes of config #2 = 0.4 s timed: several 100 ms clock samples fall inside it
+    ap.add_argument("--steps", type=int, default=128)    # 128 passes of config #2 = 0.4 s timed: several clock samples fall inside it
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--config", default="sphere_grid", choices=list(WORKLOAD_NAMES))
     ap.add_argument("--small", action="store_true", help="reduced-size scene (debug only; not a valid bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="multi-GPU runs: skip the extra strong-scaling measurement of configs[3] (terrain, screen bands)")
     ap.add_argument("--shard", default=None, choices=["sample", "bands"],
                     help="multi-GPU partition (SURVEY 8e): sample-index (default; weak scaling) or interleaved screen bands (default for terrain; strong scaling)")
     args = ap.parse_args()
@@ -268,48 +387,15 @@ def main():
     lib = capi.load_library()
     spec = build_spec(args.config, args.small)
     shard = args.shard or ("bands" if args.config == "terrain" else "sample")
-    b = capi.Backend(lib, "hrc", device=local_rank, collect_stats=False)
-    r = renderer.Renderer(b)
-    r.load_scene(spec)
-    info = b.scene_info()
     K, W = args.steps, args.warmup
-    if shard == "bands" and world > 1:
-        # screen-band sharding: every rank renders every sample index for its interleaved 16-row bands (strong scaling)
-        passes_total = max(spec.passes, K)
-        r.set_band(16, rank, world)
-    else:
-        # sample-index sharding: rank r renders sample indices r, r + world, ... (wrapped into the QMC table length)
-        passes_total = max(spec.passes, K * world)
-    r.reset(passes=passes_total)
-    if shard == "bands" and world > 1:
-        r.set_band(16, rank, world)
-
-    def sidx(step):
-        return step % passes_total if (shard == "bands" and world > 1) else (rank + step * world) % passes_total
-
-    acc = None
-    if world > 1:   # the exchange step: one fp32 sum-reduce of the accumulation buffer, in place on the device pointer
-        ptr = b.device_pixels()
-
-        class _Arr:
-            __cuda_array_interface__ = {"shape": (spec.height, spec.width, 4), "typestr": "<f4", "data": (ptr, False), "version": 2}
-        acc = torch.as_tensor(_Arr(), device=f"cuda:{local_rank}")
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-
-    def reduce_timed():
-        """NCCL reduce timed with CUDA events on torch's current stream (the pass stream has been synchronised before)."""
-        if world <= 1:
-            return 0.0
-        ev0.record()
-        dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
-        ev1.record()
-        ev1.synchronize()
-        return ev0.elapsed_time(ev1)
+    rig = Rig(lib, spec, shard, rank, world, local_rank, K)
+    b, r, info, sidx = rig.b, rig.r, rig.info, rig.sidx
+    bands = rig.bands
 
     # ---- warm-up -----------------------------------------------------------------------------
     for i in range(W):
         r.render_pass(want_stats=False, sample_index=sidx(i))
-    reduce_timed()
+    rig.exchange()
     b.clear()
 
     # ---- traversal counters for the roofline numerator (same sample indices as the timed region; not timed) ----
@@ -322,93 +408,111 @@ def main():
     b.clear()
     rays_total = counters.rays
 
-    # ---- timed region: exactly K passes, inputs resident in HBM, enqueued back to back on the context's stream and timed
-    #      with CUDA events on that stream (no host synchronisation inside), then the reduce ------------------------------
-    for i in range(2 * 4):                       # untimed: every lane captures its pass graph for this launch shape (counters off) before the clock starts
-        r.enqueue_pass(sample_index=sidx(i))
-    b.clear()
+    # ---- timed region ------------------------------------------------------------------------------
     sampler = ClockSampler(local_rank)
     sampler.start()
     sampler.wait_ready()
-    barrier()
-    sampler.samples.clear()                      # idle samples from before the region do not count
-    t0 = time.perf_counter()
-    b.timer_start()
-    for i in range(K):
-        r.enqueue_pass(sample_index=sidx(i))
-    pass_ms = b.timer_stop()
-    reduce_ms = reduce_timed()
+    pass_ms, reduce_ms, t0, t1 = measure_value(rig, K, barrier, sampler)
     dev_ms = pass_ms + reduce_ms
-    barrier()
-    t1 = time.perf_counter()
     wall_ms = (t1 - t0) * 1e3
 
     # ---- instrumented replay of the same K passes: CUDA events between the kernels give each kernel's launch durations
-    #      (their sum is within ~2 % of the clean region above; the shares and the roofline use these) ---------------------
+    #      (the shares and the roofline use these) ----------------------------------------------------------------------
     b.clear()
     b.set_option(capi.OPT_KERNEL_TIMING, 1)
-    ms_closest = ms_any = ms_shade = ms_raygen = inst_ms = 0.0
+    ms_closest = ms_any = ms_shade = ms_raygen = ms_primary = inst_ms = 0.0
     launches = 0
     for i in range(K):
         st = r.render_pass(want_stats=True, sample_index=sidx(i))
-        ms_closest += st.msClosest; ms_any += st.msAny; ms_shade += st.msShade; ms_raygen += st.msRaygen; inst_ms += st.gpuMs
-        launches += int(st.closestLaunches + st.anyLaunches + st.shadeLaunches) + 3     # + clear, raygen, finish
+        ms_closest += st.msClosest; ms_any += st.msAny; ms_shade += st.msShade; ms_raygen += st.msRaygen; ms_primary += st.msClosestPrimary; inst_ms += st.gpuMs
+        launches += int(st.closestLaunches + st.anyLaunches + st.shadeLaunches) + 2     # + raygen, finish
     b.set_option(capi.OPT_KERNEL_TIMING, 0)
     clocks = sampler.finish(window=(t0, t1))
 
-    # ---- end-to-end region: the reference-facing call sequence with HOST buffers (pass + PixelPackBuffer readback) ----
-    b.clear()
-    barrier()
-    t0 = time.perf_counter()
-    checksum = 0.0
-    for i in range(K):
-        r.render_pass(want_stats=False, sample_index=sidx(i))
-        px = b.map_pixels()                       # D2H of the RGBA32F accumulation buffer into pinned memory, every pass
-        checksum += float(px[0, 0, 3])
-        b.unmap_pixels()
-    if world > 1:
-        reduce_timed()
-    barrier()
-    e2e_serial_ms = (time.perf_counter() - t0) * 1e3
-
-    # The same K steps the way hr::PassGenerator runs them when the caller keeps its next renderPass job queued (host_pass_generator.cpp:
-    # look-ahead): pass i+1 is started into the backend's deferred buffer before pass i is read back, so the host copy of every pass
-    # (still one full readback per step, each holding exactly i+1 samples) overlaps the rendering of the next one.
-    lookahead = max(1, min(3, int(os.environ.get("HR_BENCH_LOOKAHEAD", "3"))))      # HRC_MAX_DEFERRED_PASSES = 3
-
-    def pipelined_steps(n):
+    # ---- end-to-end regions: the reference-facing call sequence with HOST buffers ---------------------------------------
+    # The caller is the reference viewer's loop (HeatrayRenderer.cpp:366-408): hrcRenderPass, then map the pixel pack buffer, one pass at a
+    # time. N > 1: every step ends with the exchange step on a copy of the accumulation buffers and rank 0 alone copies the combined frame
+    # to its host (the other ranks have nothing to show).
+    def caller_loop(n):
         total = 0.0
-        r.frame.sampleIndex = sidx(0)
-        b.enqueue_pass(r.frame)
-        nxt = 1
         for i in range(n):
-            while nxt < n and nxt - i <= lookahead:          # passes i+1 .. i+lookahead render while pass i is copied to the host
-                r.frame.sampleIndex = sidx(nxt)
-                b.enqueue_pass_deferred(r.frame)
-                nxt += 1
-            px = b.map_pixels()
-            total += float(px[0, 0, 3])
-            b.unmap_pixels()
-            if i + 1 < n:
-                b.commit_deferred()                          # the oldest pending pass: i+1
+            r.render_pass(want_stats=False, sample_index=sidx(i))
+            if world > 1:
+                rig.red.copy_(rig.acc)
+                rig.exchange(rig.red)
+                if rank == 0:
+                    rig.host.copy_(rig.red, non_blocking=True)
+                    torch.cuda.synchronize()
+                    total += float(rig.host[0, 0, 3])
+            else:
+                px = b.map_pixels()               # D2H of the RGBA32F accumulation buffer into pinned memory, every pass
+                total += float(px[0, 0, 3])
+                b.unmap_pixels()
         return total
 
-    pipelined_steps(max(8, W))                    # untimed warm-up: the deferred buffers (a ring of 4) are allocated on first use
-    b.clear()
-    barrier()
-    t0 = time.perf_counter()
-    alpha_sum = pipelined_steps(K)
-    if world > 1:
-        reduce_timed()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
-    assert alpha_sum == checksum, "the pipelined steps did not each deliver exactly their own pass count"
+    def timed_caller_loop(spec_depth):
+        b.set_option(capi.OPT_SPECULATIVE_PASSES, spec_depth)
+        b.clear()
+        caller_loop(max(8, W))                    # untimed: side buffers and their pass graphs exist before the clock starts
+        b.clear()
+        barrier()
+        t = time.perf_counter()
+        chk = caller_loop(K)
+        barrier()
+        ms = (time.perf_counter() - t) * 1e3
+        b.set_option(capi.OPT_SPECULATIVE_PASSES, 0)
+        return ms, chk
+
+    e2e_plain_ms, chk_plain = timed_caller_loop(0)
+    e2e_ms, chk_spec = timed_caller_loop(3)
+    assert chk_plain == chk_spec, "speculated passes leaked into a frame the caller read"
+
+    # The same K steps with the caller queueing ahead explicitly (hr::PassGenerator's look-ahead when renderPass jobs are queued behind the
+    # running one): passes i+1 .. i+3 render into deferred buffers while pass i is read back.
+    e2e_look_ms = None
+    if world == 1:
+        lookahead = 3
+
+        def pipelined_steps(n):
+            total = 0.0
+            r.frame.sampleIndex = sidx(0)
+            b.enqueue_pass(r.frame)
+            nxt = 1
+            for i in range(n):
+                while nxt < n and nxt - i <= lookahead:
+                    r.frame.sampleIndex = sidx(nxt)
+                    b.enqueue_pass_deferred(r.frame)
+                    nxt += 1
+                px = b.map_pixels()
+                total += float(px[0, 0, 3])
+                b.unmap_pixels()
+                if i + 1 < n:
+                    b.commit_deferred()
+            return total
+
+        b.clear()
+        pipelined_steps(max(8, W))
+        b.clear()
+        barrier()
+        t = time.perf_counter()
+        chk_look = pipelined_steps(K)
+        barrier()
+        e2e_look_ms = (time.perf_counter() - t) * 1e3
+        assert chk_look == chk_plain
+
+    # ---- multi-GPU: correctness of the exchange on the hardware, and the strong-scaling case BASELINE.json names (configs[3] by bands) ----
+    reduce_check = exchange_check(rig, barrier) if world > 1 else None
+    strong = None
+    if world > 1 and not args.no_strong and args.config != "terrain" and not args.small:
+        rig.close()
+        rig = None
+        strong = strong_terrain(lib, rank, world, local_rank, barrier)
 
     # ---- gather over ranks (max time, summed rays) -------------------------------------------------
     if world > 1:
-        t = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e_serial_ms], device="cuda", dtype=torch.float64)
+        t = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, wall_ms, e2e_ms, e2e_serial_ms = t.tolist()
+        dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms = t.tolist()
         rt = torch.tensor([float(rays_total)], device="cuda", dtype=torch.float64)
         dist.all_reduce(rt, op=dist.ReduceOp.SUM)
         rays_all = rt.item()
@@ -423,17 +527,36 @@ def main():
         bytes_any = algorithmic_bytes(counters, False)
         dominant_closest = ms_closest >= ms_any
         dom_bytes, dom_ms = (bytes_closest, ms_closest) if dominant_closest else (bytes_any, ms_any)
+        dom_name = "k_trace<closest>" if dominant_closest else "k_trace<any>"
         n_launch = K * int(st.closestLaunches)
         achieved = dom_bytes / (dom_ms / 1e3) / 1e9
         rays_c = counters.raysPrimary + counters.raysExtension
-        roof = {"bound": "hbm", "kernel": "k_trace<closest>" if dominant_closest else "k_trace<any>",
+        # secondary (extension) rays only: iterations >= 1 of the closest-hit kernel — the "incoherent secondary-ray throughput" of north_star
+        sec_rays = counters.raysExtension
+        sec_nodes = counters.nodesVisited - counters.nodesVisitedPrimary
+        sec_tris = counters.trianglesTested - counters.trianglesTestedPrimary
+        sec_ms = ms_closest - ms_primary
+        sec_bytes = 48 * sec_rays + 80 * sec_nodes + 48 * sec_tris
+        traffic = load_traffic(args.config, dom_name)
+        avg_launch_ms = dom_ms / n_launch
+        roof = {"bound": "hbm", "kernel": dom_name,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": load_traffic(args.config, "k_trace<closest>" if dominant_closest else "k_trace<any>"),
+                "traffic": traffic,
                 "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": dom_bytes / n_launch, "avg_launch_ms": dom_ms / n_launch, "launches": n_launch,
+                "algorithmic_GBps": achieved,
+                "dram_GBps_measured": (traffic / (avg_launch_ms / 1e3) / 1e9) if traffic else None,
+                "dram_frac_measured": (traffic / (avg_launch_ms / 1e3) / 1e9 / peak) if traffic else None,
+                "limiter": "issue slots, not DRAM: `frac` is the algorithmic node + triangle bytes per second against the HBM copy peak as the metric defines it; the BVH of this config is served "
+                           "from L1 / L2 (ncu: issue-active 62-78 %, 14-21 of 32 lanes per instruction, DRAM 2-6 % of peak; profiles/*_ncu_trace_full_summary.txt), "
+                           "dram_frac_measured is the kernel's real share of HBM bandwidth",
+                "algorithmic_bytes_per_launch": dom_bytes / n_launch, "avg_launch_ms": avg_launch_ms, "launches": n_launch,
                 "per_ray": {"closest": {"rays": int(rays_c), "nodes": counters.nodesVisited / max(1, rays_c), "tris": counters.trianglesTested / max(1, rays_c),
                                         "bytes": bytes_closest / max(1, rays_c), "ms": ms_closest, "GBps": bytes_closest / (ms_closest / 1e3) / 1e9,
                                         "Mrays_per_s": rays_c / (ms_closest / 1e3) / 1e6},
+                            "secondary": {"rays": int(sec_rays), "nodes": sec_nodes / max(1, sec_rays), "tris": sec_tris / max(1, sec_rays),
+                                          "bytes": sec_bytes / max(1, sec_rays), "ms": sec_ms, "GBps": sec_bytes / (max(sec_ms, 1e-9) / 1e3) / 1e9,
+                                          "Mrays_per_s": sec_rays / (max(sec_ms, 1e-9) / 1e3) / 1e6,
+                                          "what": "extension rays only: wavefront iterations >= 1 of k_trace<closest> (per GPU), launch durations from the instrumented replay"},
                             "any": {"rays": int(counters.raysOcclusion), "nodes": counters.nodesVisitedAny / max(1, counters.raysOcclusion),
                                     "tris": counters.trianglesTestedAny / max(1, counters.raysOcclusion),
                                     "bytes": bytes_any / max(1, counters.raysOcclusion), "ms": ms_any, "GBps": bytes_any / (max(ms_any, 1e-9) / 1e3) / 1e9,
@@ -441,34 +564,88 @@ def main():
                 "kernel_share_of_step": {"closest": ms_closest / inst_ms, "any": ms_any / inst_ms, "shade": ms_shade / inst_ms, "raygen": ms_raygen / inst_ms},
                 "instrumented_ms_per_step": inst_ms / K,
                 "timing": "value: K passes enqueued back to back, CUDA events on the launching stream; kernel durations: CUDA events between the kernels in a replay of the same K passes",
-                "note": "scene BVH fits L2 for this config, so DRAM traffic is dominated by queue streams; see DESIGN.md"}
+                "note": "scene BVH fits L2 for this config, so DRAM traffic is dominated by queue streams; see DESIGN.md" if spec.triangle_count < 1000000 else "see DESIGN.md"}
         frame_bytes = spec.width * spec.height * 16
+        e2e = {"value": rays_all / (e2e_ms / 1e3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms / K,
+               "h2d_bytes_per_step": C.sizeof(capi.FrameParams),
+               "d2h_bytes_per_step": frame_bytes,
+               "api": ("per step: hrcRenderPass, then hrcReadPixels / hrcReleasePixels (pinned host buffer), one pass at a time - the reference viewer's loop (HeatrayRenderer.cpp:366-408) - "
+                       "with HRC_OPT_SPECULATIVE_PASSES = 3: the backend keeps the next three passes of the progressive render running while the caller reads this one back; "
+                       "every step delivers its own full frame (exactly i + 1 samples) to the host") if world == 1 else
+                      ("per step and rank: hrcRenderPass (HRC_OPT_SPECULATIVE_PASSES = 3), device copy of the accumulation buffer, the exchange step on the copy, "
+                       "rank 0 copies the combined frame to its pinned host buffer; the other ranks read nothing back"),
+               "speculative_passes": 3,
+               "serial": {"value": rays_all / (e2e_plain_ms / 1e3) / 1e6, "ms_per_step": e2e_plain_ms / K,
+                          "api": "the same caller loop with HRC_OPT_SPECULATIVE_PASSES = 0: one pass in flight, readback not overlapped"}}
+        if e2e_look_ms:
+            e2e["lookahead3"] = {"value": rays_all / (e2e_look_ms / 1e3) / 1e6, "ms_per_step": e2e_look_ms / K,
+                                 "api": "caller queues ahead itself: hrcEnqueuePassDeferred keeps 3 passes ahead, hrcReadPixels, hrcCommitDeferred (hr::PassGenerator with renderPass jobs queued)"}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms,
-                "higher_is_better": True, "scaling": "strong" if (shard == "bands" and world > 1) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "higher_is_better": True, "scaling": "strong" if bands else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": config_dict(spec, args.config, world, shard=shard, extra={"bvh_nodes": int(info.nodeCount), "bvh_build_s": float(info.buildSeconds),
                                                                  "scene_bytes": int(info.nodeBytes + info.triangleBytes + info.shadingBytes),
                                                                  "pass_pipelining": "value: the K passes are enqueued back to back (hrcEnqueuePass, the reference's offline mode) and rotate over %s sets of "
-                                                                                    "queues / accumulation buffers, so the latency-bound tail of a pass overlaps the head of the next; "
-                                                                                    "e2e: passes i+1 .. i+%d render into deferred buffers while pass i is read back (e2e.serial: one step at a time)" % (os.environ.get("HRC_TUNE_PASS_LANES", "4"), lookahead)}),
-                "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K,
-                "clocks": clocks, "roofline": roof,
-                "e2e": {"value": rays_all / (e2e_ms / 1e3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms / K,
-                        "h2d_bytes_per_step": C.sizeof(capi.FrameParams),
-                        "d2h_bytes_per_step": frame_bytes if not (shard == "bands" and world > 1) else frame_bytes // world,   # band mode reads back only the rank's own rows
-                        "api": "per step: hrcEnqueuePassDeferred (keeps %d passes ahead) + hrcReadPixels/hrcReleasePixels (this pass, pinned host buffer) + hrcCommitDeferred (the next pass) - "
-                               "hr::PassGenerator::renderPass's look-ahead for a caller that keeps its next jobs queued; every step delivers its own full frame to the host" % lookahead,
-                        "lookahead": lookahead,
-                        "serial": {"value": rays_all / (e2e_serial_ms / 1e3) / 1e6, "ms_per_step": e2e_serial_ms / K,
-                                   "api": "hrcRenderPass + hrcReadPixels/hrcReleasePixels, one step at a time (the reference viewer's loop, HeatrayRenderer.cpp:366-408)"}},
-                "gpu_launches": launches + (0 if os.environ.get("HRC_TUNE_PASS_LANES") == "1" else 3)}       # + the lane joins (k_add_pixels) at the end of the timed region
+                                                                                    "queues / accumulation buffers, so the latency-bound tail of a pass overlaps the head of the next; each lane replays its pass as one captured CUDA graph" % os.environ.get("HRC_TUNE_PASS_LANES", "4")}),
+                "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K, "timed_region_ms": dev_ms,
+                "clocks": clocks, "roofline": roof, "e2e": e2e,
+                "gpu_launches": launches + 3}       # + the lane joins (k_add_pixels) at the end of the timed region
         if world > 1:
             line["reduce_ms"] = reduce_ms
+            line["exchange"] = "gather of own rows" if bands else os.environ.get("HR_BENCH_COLLECTIVE", "all_reduce")
+            line["reduce_check"] = reduce_check
+            if strong:
+                line["strong"] = strong
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_sample(spec)
         print(json.dumps(line), flush=True)
-    b.close()
+    if rig:
+        rig.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def strong_terrain(lib, rank, world, local_rank, barrier, steps=16):
+    """configs[3] (terrain, 10 M triangles, 4K) by interleaved screen bands on all ranks: strong scaling. Also times the same passes on rank 0
+    alone over the full frame (the other ranks wait), so that the line carries its own single-GPU figure."""
+    import torch
+    import torch.distributed as dist
+    spec = build_spec("terrain")
+    rig = Rig(lib, spec, "bands", rank, world, local_rank, steps)
+    b, r = rig.b, rig.r
+    for i in range(3):
+        r.render_pass(want_stats=False, sample_index=rig.sidx(i))
+    b.clear()
+    b.reset_stats()
+    pass_ms, ex_ms, _, _ = measure_value(rig, steps, barrier)
+    rays = float(b.get_stats().rays)
+    check = exchange_check(rig, barrier, passes_per_rank=2)
+    t = torch.tensor([pass_ms + ex_ms, ex_ms], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    rt = torch.tensor([rays], device="cuda", dtype=torch.float64)
+    dist.all_reduce(rt, op=dist.ReduceOp.SUM)
+    out = None
+    n1_ms = n1_rays = 0.0
+    if rank == 0:                                  # the single-GPU figure: full frame, same passes, the other ranks idle
+        r.set_band(0, 0, 1)
+        b.clear(); b.reset_stats()
+        for i in range(8):
+            r.enqueue_pass(sample_index=i)
+        b.clear(); b.reset_stats()
+        b.timer_start()
+        for i in range(steps):
+            r.enqueue_pass(sample_index=i)
+        n1_ms = b.timer_stop()
+        n1_rays = float(b.get_stats().rays)
+    barrier()
+    if rank == 0:
+        value = rt.item() / (t[0].item() / 1e3) / 1e6
+        n1_value = n1_rays / (n1_ms / 1e3) / 1e6
+        out = {"config": f"configs[3] terrain ({spec.triangle_count} triangles, {spec.width}x{spec.height}), interleaved {BAND_ROWS}-row screen bands, gather of own rows",
+               "value": value, "unit": UNIT, "ms_per_step": t[0].item() / steps, "steps": steps, "exchange_ms": t[1].item(),
+               "n1_value": n1_value, "n1_ms_per_step": n1_ms / steps, "speedup": value / n1_value, "efficiency": value / n1_value / world,
+               "reduce_check": check}
+    rig.close()
+    return out
 
 
 if __name__ == "__main__":

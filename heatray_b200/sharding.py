@@ -23,3 +23,26 @@ def reduce_accumulation(tensor, dst: int = 0):
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.reduce(tensor, dst=dst, op=dist.ReduceOp.SUM)
     return tensor
+
+
+def gather_bands(acc, band_height: int, rank: int, world: int, dst: int = 0):
+    """Screen-band exchange step: every rank sends ONLY the rows it rendered (frame / world bytes) and rank `dst` puts them in
+    place; the other ranks' buffers are left as they are. `acc` is the (H, W, 4) fp32 accumulation buffer of this rank (pixels
+    outside its bands are zero). Bands are disjoint, so the result is bit-identical to a single-rank render
+    ("ncclGather of disjoint bands" instead of a sum of zero-padded frames)."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_initialized() and world > 1):
+        return acc
+    height = acc.shape[0]
+    rows = [torch.from_numpy(np.flatnonzero(band_rows(height, band_height, r, world))).to(acc.device) for r in range(world)]
+    most = max(len(x) for x in rows)
+    mine = torch.zeros((most,) + tuple(acc.shape[1:]), dtype=acc.dtype, device=acc.device)      # equal-sized pieces for the collective
+    mine[:len(rows[rank])] = acc[rows[rank]]
+    pieces = [torch.empty_like(mine) for _ in range(world)] if rank == dst else None
+    dist.gather(mine, pieces, dst=dst)
+    if rank == dst:
+        for r in range(world):
+            if r != dst:
+                acc[rows[r]] = pieces[r][:len(rows[r])]
+    return acc

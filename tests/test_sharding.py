@@ -48,15 +48,18 @@ def _worker(rank, world, port, mode, out_path):
         r.set_band(4, rank, world)
         for s in range(spec.passes):
             r.render_pass(sample_index=s)
-    acc = torch.from_numpy(r.pixels())
-    sharding.reduce_accumulation(acc, dst=0)
+    acc = torch.from_numpy(r.pixels().copy())
+    if mode == "bands_gather":
+        sharding.gather_bands(acc, 4, rank, world, dst=0)
+    else:
+        sharding.reduce_accumulation(acc, dst=0)
     if rank == 0:
         np.save(out_path, acc.numpy())
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode", ["samples", "bands"])
+@pytest.mark.parametrize("mode", ["samples", "bands", "bands_gather"])
 def test_two_rank_gloo_equals_single_rank(tmp_path, mode, oracle_mod):
     from heatray_b200 import renderer, scenes
     spec = scenes.cornell_box(width=32, height=32, passes=4)
@@ -72,7 +75,7 @@ def test_two_rank_gloo_equals_single_rank(tmp_path, mode, oracle_mod):
     mp.spawn(_worker, args=(2, port, mode, str(out)), nprocs=2, join=True)
     multi = np.load(out)
     assert np.array_equal(multi[..., 3], single[..., 3])
-    if mode == "bands":
+    if mode.startswith("bands"):
         assert np.array_equal(multi, single)                       # disjoint pixels: bit-identical
     else:
         assert np.allclose(multi, single, rtol=1e-6, atol=1e-7)    # same samples, different fp32 summation order
