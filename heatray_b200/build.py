@@ -22,7 +22,10 @@ LIB = PKG / "libheatray_cuda.so"
 NVCC = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden,-ffp-contract=off,-fwrapv,-pthread"]
-CU_FLAGS = ["--expt-relaxed-constexpr", "-Xptxas", "-v"]
+# -fmad=false: the shading arithmetic is evaluated operation by operation as the shader text (and the oracle, -ffp-contract=off) states it; FMAs
+# appear only where the source writes fmaf / __fmaf_rn (traversal). Contraction was THE source of GPU-vs-oracle pixel differences: at 1080p pixels
+# within 1e-4 of the oracle go from 99.0 % to 99.96 %, for 1.8 - 2.8 % of whole-pass throughput (profiles/r02_notes.md).
+CU_FLAGS = ["--expt-relaxed-constexpr", "-fmad=false", "-Xptxas", "-v"]
 
 
 def _sources():

@@ -23,7 +23,7 @@ TEX_R32F, TEX_RGB32F, TEX_RGBA32F, TEX_RGBA8 = 0, 1, 2, 3
 WRAP_CLAMP, WRAP_REPEAT = 0, 1
 DRAW_TRIANGLES, DRAW_TRIANGLE_STRIP = 0, 1
 HIT_BACKFACE = 0x40000000
-OPT_TRAVERSAL_COUNTERS, OPT_KERNEL_TIMING, OPT_SPECULATIVE_PASSES = 0, 1, 2
+OPT_TRAVERSAL_COUNTERS, OPT_KERNEL_TIMING, OPT_SPECULATIVE_PASSES, OPT_PIXEL_RAY_COUNTS = 0, 1, 2, 3
 SAMPLE_RANDOM, SAMPLE_HALTON, SAMPLE_HAMMERSLEY, SAMPLE_BLUE_NOISE, SAMPLE_SOBOL = range(5)
 BOKEH_CIRCULAR, BOKEH_PENTAGON, BOKEH_HEXAGON, BOKEH_OCTAGON = range(4)
 
@@ -228,7 +228,7 @@ BACKEND_SYMBOLS = [
     "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels", "Resolve",
     "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "SetMeshTransform", "ClearScene", "CommitScene",
     "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetInteractiveBlocks", "SetGlobals",
-    "RenderPass", "EnqueuePass", "EnqueuePassDeferred", "CommitDeferred", "DiscardDeferred", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo",
+    "RenderPass", "EnqueuePass", "EnqueuePassDeferred", "CommitDeferred", "DiscardDeferred", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo", "ReadRayCounts",
 ]
 
 _lib = None
@@ -544,6 +544,12 @@ class Backend:
         st = PassStats()
         self._call("GetStats", C.byref(st))
         return st
+
+    def ray_counts(self) -> np.ndarray:
+        """Rays per pixel since the last clear (OPT_PIXEL_RAY_COUNTS), (h, w) uint32, row 0 = bottom."""
+        out = np.zeros((self.height, self.width), np.uint32)
+        self._call("ReadRayCounts", _ptr(out))
+        return out
 
     def trace_rays(self, rays: np.ndarray, any_hit=False) -> np.ndarray:
         r = np.ascontiguousarray(rays, RAY_DTYPE)

@@ -119,6 +119,7 @@ struct PassBuffers {
     uint32_t* sortHist;       // bins counters (zeroed by k_sort_scan after use)
     uint32_t* sortOffs;       // bins running offsets
     SortCtrl* sortCtrl;       // kMaxIterations entries
+    uint32_t* rayCounts;      // HRC_OPT_PIXEL_RAY_COUNTS: rays per pixel (shared by all lanes, hence atomics), else nullptr
 };
 
 struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle, refillIdleAny; int sortBits; };

@@ -56,6 +56,7 @@ struct HrcContext_t {
     // sample index, no state change in between) the pass is already rendered or under way and is simply committed; anything else discards
     // the predictions. A caller that renders and reads back one pass at a time (the reference viewer's loop) then gets its readback
     // overlapped with the next passes without queueing anything itself.
+    uint32_t* dRayCounts = nullptr;        // HRC_OPT_PIXEL_RAY_COUNTS
     int specDepth = 0; uint64_t stateVersion = 0;
     HrcFrameParams deferredParams[kDeferredLanes] = {}; uint64_t deferredVersion[kDeferredLanes] = {};
     std::vector<GraphEntry> graphs;        // captured passes of the main lane
@@ -195,7 +196,7 @@ int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
         return allocQueues(c, L.pb, n);
     };
     if (int r = allocate()) { freeQueues(L.pb); freeDev(L.accum); return r; }      // a retry starts from scratch instead of finding a lane without queues
-    L.pb.accum = L.accum;
+    L.pb.accum = L.accum; L.pb.rayCounts = c->dRayCounts;
     return HRC_OK;
 }
 
@@ -372,6 +373,16 @@ HRC_API int hrcSetOption(HrcContext c, int32_t option, int32_t value) {
     if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
     if (option == HRC_OPT_TRAVERSAL_COUNTERS) c->counters = value != 0;
     else if (option == HRC_OPT_KERNEL_TIMING) c->kernelTiming = value != 0;
+    else if (option == HRC_OPT_PIXEL_RAY_COUNTS) {
+        if (!c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "ray counts need a framebuffer size first");
+        cudaSetDevice(c->device); joinLanes(c); waitPendingDeferred(c);
+        CU(c, cudaStreamSynchronize(c->stream));
+        freeDev(c->dRayCounts);
+        if (value) { CU(c, cudaMalloc(&c->dRayCounts, (size_t)c->w * c->h * sizeof(uint32_t))); CU(c, cudaMemset(c->dRayCounts, 0, (size_t)c->w * c->h * sizeof(uint32_t))); }
+        c->pb.rayCounts = c->dRayCounts;
+        for (auto& L : c->extra) L.pb.rayCounts = c->dRayCounts;
+        for (auto& L : c->deferred) L.pb.rayCounts = c->dRayCounts;
+    }
     else if (option == HRC_OPT_SPECULATIVE_PASSES) {
         if (value < 0 || value > HRC_MAX_DEFERRED_PASSES) return fail(c, HRC_ERR_INVALID_VALUE, "0..3 speculative passes");
         if (c->deferredCount > 0) { int r = hrcDiscardDeferred(c); if (r) return r; }
@@ -396,6 +407,9 @@ HRC_API int hrcResize(HrcContext c, int32_t w, int32_t h) {
         freeQueues(c->pb); freeExtraLanes(c); freeDev(c->accum); freeDev(c->staging); freeDev(c->dSeqOffsetX); freeDev(c->dSequenceId);
         if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
         c->pinnedBytes = 0; c->pb.accum = nullptr; c->w = c->h = 0;
+        freeDev(c->dRayCounts); c->pb.rayCounts = nullptr;
+        for (auto& L : c->extra) L.pb.rayCounts = nullptr;
+        for (auto& L : c->deferred) L.pb.rayCounts = nullptr;
         c->pixelTables = false; c->offsetCount = 0;
         freeDev(c->dBlockCoords); freeDev(c->dBlockRand); c->blocksX = c->blocksY = 0;   // block tables depend on the frame size
         destroyGraphs(c);
@@ -422,6 +436,7 @@ HRC_API int hrcClear(HrcContext c) {
     if (!c || !c->accum) return fail(c, HRC_ERR_INVALID_OPERATION, "no framebuffer");
     cudaSetDevice(c->device); joinLanes(c);
     CU(c, cudaMemsetAsync(c->accum, 0, (size_t)c->w * c->h * sizeof(float4), c->stream));
+    if (c->dRayCounts) CU(c, cudaMemsetAsync(c->dRayCounts, 0, (size_t)c->w * c->h * sizeof(uint32_t), c->stream));
     c->accumOutsideBandsZero = !c->devicePixelsExported; c->rbBandCount = 0;
     return HRC_OK;
 }
@@ -1114,6 +1129,15 @@ HRC_API int hrcTraceRays(HrcContext c, int32_t n, const HrcRay* rays, int32_t an
     e = cudaStreamSynchronize(c->stream);
     cudaFree(dr); cudaFree(dh);
     if (e != cudaSuccess) return failCuda(c, e, "hrcTraceRays");
+    return HRC_OK;
+}
+
+HRC_API int hrcReadRayCounts(HrcContext c, uint32_t* hostOut) {
+    if (!c || !hostOut) return fail(c, HRC_ERR_INVALID_VALUE, "null pointer");
+    if (!c->dRayCounts) return fail(c, HRC_ERR_INVALID_OPERATION, "HRC_OPT_PIXEL_RAY_COUNTS is off");
+    cudaSetDevice(c->device); joinLanes(c);
+    CU(c, cudaMemcpyAsync(hostOut, c->dRayCounts, (size_t)c->w * c->h * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
     return HRC_OK;
 }
 

@@ -37,7 +37,14 @@ __device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a
 __device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x * s, a.y * s, a.z * s); }
+#ifndef HR_EXACT_DIV
+#define HR_EXACT_DIV 0
+#endif
+#if HR_EXACT_DIV
+__device__ __forceinline__ float3 operator/(float3 a, float s) { return f3(__fdiv_rn(a.x, s), __fdiv_rn(a.y, s), __fdiv_rn(a.z, s)); }   // component-wise IEEE division, as GLSL / glm define vec3 / float
+#else
 __device__ __forceinline__ float3 operator/(float3 a, float s) { const float r = 1.0f / s; return f3(a.x * r, a.y * r, a.z * r); }   // one IEEE reciprocal, <= 1 ulp from a true division
+#endif
 __device__ __forceinline__ float dot(float3 a, float3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 __device__ __forceinline__ float3 cross(float3 a, float3 b) { return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 __device__ __forceinline__ float3 normalize(float3 a) { return a * (1.0f / sqrtf(dot(a, a))); }
@@ -697,6 +704,7 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                         const float t = tr.bestT;
                         extraT += t; ++maskedPasses;                                     // :84
                         atomicAdd(&ctrl->maskedContinuations, 1u);
+                        if (pb.rayCounts) atomicAdd(pb.rayCounts + (__float_as_uint(pb.shadow.w[rayIdx].w) & 0x00ffffffu), 1u);
                         tr.begin(offsetOrigin(sv, tr.d), tr.d, 0.0f, tr.tmaxRay - t);    // :80
                         continue;
                     }
@@ -1229,6 +1237,7 @@ __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene
                 if (e.hasExt && ((int)in.depth + 1 > hardCap || lastIter)) e.hasExt = false;
             }
         }
+        if (pb.rayCounts && k < count) atomicAdd(pb.rayCounts + in.pixel, 1u + (e.hasOcc ? 1u : 0u));   // parity hook: this ray and the occlusion ray it emits
         if (CLS == 0) continue;
         // ---- compaction: one atomic per warp per queue ------------------------------------
         const uint32_t occMask = __ballot_sync(0xffffffffu, e.hasOcc);

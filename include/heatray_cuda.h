@@ -66,6 +66,9 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out);
 enum {
     HRC_OPT_TRAVERSAL_COUNTERS = 0,  /* count nodes visited / triangles tested (slightly slower kernels) */
     HRC_OPT_KERNEL_TIMING = 1,       /* CUDA events between kernels: HrcPassStats.ms* are filled by hrcRenderPass */
+    HRC_OPT_PIXEL_RAY_COUNTS = 3,    /* parity hook: count the rays (primary + extension + occlusion segments) every pixel's paths submit to traversal,
+                                      * readable with hrcReadRayCounts; hrcClear zeroes the counts. A pixel whose value differs from another
+                                      * implementation's together with its ray count took a different discrete decision somewhere on its path. */
     HRC_OPT_SPECULATIVE_PASSES = 2   /* n = 0..3 (default 0): hrcRenderPass(i) also starts passes i+1..i+n of the same progressive render (same frame
                                       * parameters, consecutive sample indices below maxSampleIndex) into side buffers nothing else sees. When the next
                                       * hrcRenderPass asks for exactly the predicted pass and no state changed in between, it is committed instead of
@@ -292,6 +295,8 @@ typedef struct HrcHit { float t, u, v; int32_t primId; /* -1 = miss; bit 30 set 
 #define HRC_HIT_BACKFACE 0x40000000
 /* Closest hit (anyHit = 0) or occlusion test (anyHit = 1: primId = 0 if occluded else -1) for n host rays. */
 HRC_API int hrcTraceRays(HrcContext ctx, int32_t n, const HrcRay* rays, int32_t anyHit, HrcHit* hits);
+/* Rays per pixel since the last hrcClear (needs HRC_OPT_PIXEL_RAY_COUNTS): w*h counts, row 0 = bottom row like the accumulation buffer. */
+HRC_API int hrcReadRayCounts(HrcContext ctx, uint32_t* hostOut);
 /* Scene facts after commit. */
 typedef struct HrcSceneInfo {
     uint64_t triangleCount, nodeCount;

@@ -84,9 +84,10 @@ def _psnr(a, b, peak):
 @pytest.mark.parametrize("name", list(SMALL))
 def test_image_parity_equal_spp(name, oracle_backend, gpu_backend):
     """Same scene, camera, QMC tables and pass count: accumulated images must agree.
-    Tolerance: transcendental functions differ by ulps between glibc and CUDA, which perturbs bounce directions by ~1e-7
-    and can flip a discrete decision on a few paths per million; so: alpha exact, >= 99% of pixels within 1e-3 relative
-    (+1e-4 absolute), and PSNR of the resolved image >= 40 dB against the clamp value."""
+    Tolerance: transcendental functions differ by ulps between glibc and CUDA (everything else rounds identically: the kernels are built
+    without FMA contraction), which perturbs bounce directions by ~1e-7 and can flip a discrete decision on a few paths per million; so:
+    alpha exact, >= 99.9 % of pixels within 1e-3 relative (+1e-4 absolute) — the achieved fraction is printed —, and PSNR of the
+    resolved image >= 55 dB against the clamp value."""
     spec = SMALL[name]()
     ro, rg = _pair(oracle_backend, gpu_backend, spec)
     so = sg = None
@@ -96,9 +97,12 @@ def test_image_parity_equal_spp(name, oracle_backend, gpu_backend):
     assert np.array_equal(po[..., 3], pg[..., 3]) and (po[..., 3] == spec.passes).all()
     assert np.isfinite(pg).all()
     close = np.isclose(pg[..., :3], po[..., :3], rtol=1e-3, atol=1e-4).all(-1)
-    assert close.mean() >= 0.99, f"only {close.mean():.4f} of pixels match"
+    tight = np.isclose(pg[..., :3], po[..., :3], rtol=1e-5, atol=1e-6).all(-1)
     io, ig = renderer.resolve(po), renderer.resolve(pg)
-    assert _psnr(io, ig, spec.max_channel_value) >= 40.0
+    print(f"{name}: {close.mean():.5f} of pixels within 1e-3, {tight.mean():.5f} within 1e-5, PSNR {_psnr(io, ig, spec.max_channel_value):.1f} dB")
+    assert close.mean() >= 0.999, f"only {close.mean():.4f} of pixels match"
+    assert tight.mean() >= 0.98
+    assert _psnr(io, ig, spec.max_channel_value) >= 55.0
     # ray accounting: same paths => (nearly) the same number of segments; bound 2*D+2 per pixel per pass
     assert sg.raysPrimary == so.raysPrimary == spec.width * spec.height
     assert abs(int(sg.rays) - int(so.rays)) <= 0.002 * so.rays
@@ -116,8 +120,9 @@ def test_builtin_scenes_image_parity(name, oracle_backend, gpu_backend):
     po, pg = ro.pixels(), rg.pixels()
     assert np.array_equal(po[..., 3], pg[..., 3]) and (po[..., 3] == spec.passes).all()
     close = np.isclose(pg[..., :3], po[..., :3], rtol=1e-3, atol=1e-4).all(-1)
-    assert close.mean() >= 0.99, f"only {close.mean():.4f} of pixels match"
-    assert _psnr(renderer.resolve(po), renderer.resolve(pg), spec.max_channel_value) >= 40.0
+    print(f"{name}: {close.mean():.5f} of pixels within 1e-3, PSNR {_psnr(renderer.resolve(po), renderer.resolve(pg), spec.max_channel_value):.1f} dB")
+    assert close.mean() >= 0.999, f"only {close.mean():.4f} of pixels match"
+    assert _psnr(renderer.resolve(po), renderer.resolve(pg), spec.max_channel_value) >= 55.0
     assert abs(int(sg.rays) - int(so.rays)) <= 0.002 * so.rays and pg[..., :3].std() > 0.01
 
 
@@ -498,3 +503,31 @@ def test_empty_scene_and_misses(gpu_backend, oracle_backend):
         px = r.pixels()
         assert st.raysPrimary == 32 * 16 and st.raysExtension == 0 and st.raysOcclusion == 0
         assert np.allclose(px[..., :3], np.array([0.5, 1.0, 1.5], np.float32), rtol=1e-6)
+
+
+@pytest.mark.parametrize("mode", ["showNANs", "showInf"])
+def test_accumulator_nan_inf_visualizer(mode, oracle_backend, gpu_backend):
+    """accumulator.rlsl:16-21: with the accumulator visualiser on, a contribution holding a NaN (or an Inf) is shown as 100, any other as
+    min(c, 1) * 0.1. An emitter whose (float) emissive texture holds Inf produces both: its primary hits carry Inf (weight 1 * inf), and paths that reach it over
+    the red or green wall carry NaN as well (their weight has zero channels: 0 * inf). GLSL min(): a NaN in the first operand stays."""
+    spec = scenes.cornell_box(width=96, height=96, passes=3, max_depth=4)
+    spec.materials[3].textures["emissiveTexture"] = np.full((1, 1, 4), np.inf, np.float32)     # emissiveColor itself is saturated by Material::modify; a float texture is not
+    spec.materials[1].params["baseColor"] = (0.65, 0.0, 0.0)
+    spec.materials[2].params["baseColor"] = (0.0, 0.45, 0.0)
+    ro, rg = _pair(oracle_backend, gpu_backend, spec)
+    for r in (ro, rg):
+        g = r.globals
+        g.enableAccumulatorVisualizer = 1
+        setattr(g, mode, 1)
+        r.b.set_globals(g)
+        r.b.clear()
+    for _ in range(spec.passes):
+        ro.render_pass(); rg.render_pass()
+    po, pg = ro.pixels(), rg.pixels()
+    assert np.array_equal(po[..., 3], pg[..., 3])
+    flagged_o, flagged_g = (po[..., 0] >= 100.0), (pg[..., 0] >= 100.0)
+    assert flagged_o.sum() > 50 and (flagged_o == flagged_g).mean() >= 0.999
+    same = np.isclose(pg[..., :3], po[..., :3], rtol=1e-3, atol=1e-4, equal_nan=True).all(-1)
+    assert same.mean() >= 0.999
+    if mode == "showInf":
+        assert np.isnan(po).any() == np.isnan(pg).any()               # NaN contributions pass through min(c, 1) * 0.1 as NaN on both sides
