@@ -33,7 +33,7 @@ def _sources():
 
 
 def _headers():
-    return sorted(CSRC.glob("*.h")) + sorted((ROOT / "include").glob("*.h"))
+    return sorted(CSRC.glob("*.h")) + sorted((ROOT / "include").glob("*.h")) + [Path(__file__)]      # the flags live in this file
 
 
 def _stale(target: Path, deps) -> bool:
