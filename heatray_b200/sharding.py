@@ -25,6 +25,9 @@ def reduce_accumulation(tensor, dst: int = 0):
     return tensor
 
 
+_ROWS = {}      # row-index tensors per (height, band height, world, device)
+
+
 def gather_bands(acc, band_height: int, rank: int, world: int, dst: int = 0):
     """Screen-band exchange step: every rank sends ONLY the rows it rendered (frame / world bytes) and rank `dst` puts them in
     place; the other ranks' buffers are left as they are. `acc` is the (H, W, 4) fp32 accumulation buffer of this rank (pixels
@@ -35,7 +38,10 @@ def gather_bands(acc, band_height: int, rank: int, world: int, dst: int = 0):
     if not (dist.is_initialized() and world > 1):
         return acc
     height = acc.shape[0]
-    rows = [torch.from_numpy(np.flatnonzero(band_rows(height, band_height, r, world))).to(acc.device) for r in range(world)]
+    key = (height, band_height, world, str(acc.device))
+    if key not in _ROWS:
+        _ROWS[key] = [torch.from_numpy(np.flatnonzero(band_rows(height, band_height, r, world))).to(acc.device) for r in range(world)]
+    rows = _ROWS[key]
     most = max(len(x) for x in rows)
     mine = torch.zeros((most,) + tuple(acc.shape[1:]), dtype=acc.dtype, device=acc.device)      # equal-sized pieces for the collective
     mine[:len(rows[rank])] = acc[rows[rank]]
