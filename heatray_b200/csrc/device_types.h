@@ -101,6 +101,7 @@ struct DScene {
     const float* blockCoords; // interactive mode: blockW*blockH RGB texels of shuffled (row, col, 0)
     const float2* blockRand;  // interactive mode: per block (random(blockIndex), random(blockIndex.yx))
     float sortMin[3], sortScale[3];   // coherence sort grid: cell = (origin - sortMin) * sortScale, clamped to [0, 2^bits)
+    uint32_t nodeCount, pad0;         // wide BVH nodes
 };
 
 // Launch wrappers implemented in kernels.cu

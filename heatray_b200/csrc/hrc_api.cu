@@ -203,6 +203,7 @@ int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
 DScene sceneOf(HrcContext c) {
     DScene s{}; s.nodes = c->dNodes; s.tris = c->dTris; s.shade = c->dShade; s.attr = c->dAttr; s.materials = c->dMaterials; s.textures = c->dTextures;
     s.seq = c->dSeq; s.aperture = c->dAperture; s.seqOffsetX = c->dSeqOffsetX; s.sequenceId = c->dSequenceId; s.blockCoords = c->dBlockCoords; s.blockRand = c->dBlockRand;
+    s.nodeCount = (uint32_t)c->info.nodeCount;
     for (int k = 0; k < 3; ++k) {
         const float extent = c->sceneMax[k] - c->sceneMin[k];
         s.sortMin[k] = c->sceneMin[k]; s.sortScale[k] = extent > 0.0f ? (float)(1 << c->tuneSortBits) / extent : 0.0f;

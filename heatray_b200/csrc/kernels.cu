@@ -359,6 +359,12 @@ struct TraceStack {
 #endif
 };
 
+#ifndef HR_TOP_SMEM
+#define HR_TOP_SMEM 0            // nodes of the top BVH levels kept in shared memory by k_trace (1 + 8 = 9, 1 + 8 + 64 = 73); measured neutral, off (profiles/r02_notes.md)
+#endif
+#ifndef HR_TMA_REFILL
+#define HR_TMA_REFILL 0          // k_trace refills a warp's idle lanes with ONE bulk copy (cp.async.bulk, TMA 1-D) of the contiguous ray records instead of per-lane loads; measured, off
+#endif
 // Per-lane traversal state. A lane keeps it across the warp-synchronous phases of k_trace (node step, triangle rounds,
 // refill), so a warp tops itself up with fresh rays while slow rays are still in flight.
 struct Traversal {
@@ -392,7 +398,7 @@ struct Traversal {
     // Pops the nearest pending child of `group`, tests its 8 children, leaves the hit internal children in `group` and
     // files the hit leaf triangles as a pending triangle group.
     template <bool STATS, bool ANY>
-    __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, TraceStack& stack, TraceCounters& tc) {
+    __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, TraceStack& stack, TraceCounters& tc, const float4* topNodes = nullptr) {
         const uint32_t hits = group.y;
         const uint32_t bit = 31u - __clz(hits);                  // highest set bit = nearest remaining child
         group.y &= ~(1u << bit);
@@ -403,8 +409,17 @@ struct Traversal {
         const uint32_t rel = __popc(hits & ~(0xffffffffu << slot));   // internal children stored before this slot
         const uint32_t nodeIdx = group.x + rel;
 
-        const float4* np = nodes + (size_t)nodeIdx * 5;
-        const float4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+        float4 n0, n1, n2, n3, n4;
+#if HR_TOP_SMEM > 0
+        if (topNodes && nodeIdx < HR_TOP_SMEM) {          // experiment (north_star: "hot top-level nodes staged in shared memory"): the first levels of the breadth-first node array
+            const float4* sp = topNodes + nodeIdx * 5;
+            n0 = sp[0]; n1 = sp[1]; n2 = sp[2]; n3 = sp[3]; n4 = sp[4];
+        } else
+#endif
+        {
+            const float4* np = nodes + (size_t)nodeIdx * 5;
+            n0 = __ldg(np + 0); n1 = __ldg(np + 1); n2 = __ldg(np + 2); n3 = __ldg(np + 3); n4 = __ldg(np + 4);
+        }
         if (STATS) tc.nodes++;
 
         const uint32_t eimask = __float_as_uint(n0.w);
@@ -630,6 +645,24 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
     TraceCounters tc{0u, 0u, 0u};
     Traversal tr;
     HR_DECLARE_TRACE_STACK(stack);
+#if HR_TOP_SMEM > 0
+    __shared__ float4 topNodes[HR_TOP_SMEM * 5];
+    for (int k = threadIdx.x; k < HR_TOP_SMEM * 5; k += blockDim.x) topNodes[k] = (k / 5 < (int)sc.nodeCount) ? __ldg(nodes + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+#else
+    const float4* topNodes = nullptr;
+#endif
+#if HR_TMA_REFILL
+    __shared__ __align__(128) float4 refillBuf[4][64];        // per warp: 32 ray records of 32 B
+    __shared__ __align__(8) unsigned long long refillBar[4];
+    const uint32_t warpInBlock = threadIdx.x >> 5;
+    uint32_t refillPhase = 0;
+    if (lane == 0) {
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&refillBar[warpInBlock]);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar));
+    }
+    __syncwarp();
+#endif
     bool active = false, exhausted = false;
     uint32_t rayIdx = 0, doneIdx = 0;
     int doneClass = -1;                      // closest-hit only: class of a finished ray not yet appended to its list
@@ -658,11 +691,35 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                 uint32_t base = 0;
                 if ((int)lane == leader) base = atomicAdd(head, n);
                 base = __shfl_sync(kFull, base, leader);
+#if HR_TMA_REFILL
+                if (!ANY && !order) {       // one bulk copy of the warp's contiguous records [base, base + n) into shared memory, completion on the warp's mbarrier
+                    const uint32_t take = base < count ? min(n, count - base) : 0u;
+                    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&refillBar[warpInBlock]);
+                    if (take) {
+                        if ((int)lane == leader) {
+                            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&refillBuf[warpInBlock][0]);
+                            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(take * 32u) : "memory");
+                            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                         :: "r"(dst), "l"(qod + 2 * (size_t)base), "r"(take * 32u), "r"(bar) : "memory");
+                        }
+                        uint32_t done = 0;
+                        while (!done) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar), "r"(refillPhase) : "memory");
+                        refillPhase ^= 1u;
+                    }
+                }
+#endif
                 if (!active) {
-                    uint32_t i = base + __popc(idle & below);
+                    const uint32_t slotInBatch = __popc(idle & below);
+                    uint32_t i = base + slotInBatch;
                     if (i < count) {
                         if (!ANY && order) i = __ldcs(order + i);
+#if HR_TMA_REFILL
+                        const bool bulk = !ANY && !order;
+                        const float4 ro = bulk ? refillBuf[warpInBlock][2 * slotInBatch] : __ldcs(ANY ? pb.shadow.o + i : qod + 2 * (size_t)i);
+                        const float4 rd = bulk ? refillBuf[warpInBlock][2 * slotInBatch + 1] : __ldcs(ANY ? pb.shadow.d + i : qod + 2 * (size_t)i + 1);
+#else
                         const float4 ro = __ldcs(ANY ? pb.shadow.o + i : qod + 2 * (size_t)i), rd = __ldcs(ANY ? pb.shadow.d + i : qod + 2 * (size_t)i + 1);   // streamed: keep the BVH in L2
+#endif
 #if HR_RAY_PREFETCH_AHEAD > 0
                         // the queue is consumed in index order by all warps together: pull the ray HR_RAY_PREFETCH_AHEAD places further on into L2
                         if (i + HR_RAY_PREFETCH_AHEAD < count) {
@@ -682,7 +739,7 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
         }
 
         while (active) {
-            if (tr.hasNodeWork()) tr.nodeStep<STATS, ANY>(nodes, stack, tc);
+            if (tr.hasNodeWork()) tr.nodeStep<STATS, ANY>(nodes, stack, tc, topNodes);
             bool occluded = false;
             while (tr.tri.y) if (tr.triStep<ANY, STATS, MASKED>(tris, tc)) { occluded = true; break; }
             tr.popIfEmpty(stack);
