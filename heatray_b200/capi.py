@@ -246,7 +246,23 @@ def load_library() -> C.CDLL:
     return _lib
 
 
-def _declare_host(lib):
+_host = None
+
+
+def load_host_library() -> C.CDLL:
+    """The host layer alone (libheatray_host.so: QMC tables, packing, mesh providers, image / scene / session readers — no device code).
+    What the oracle-side renderer and bench.py's CPU reference arm use, so that those processes never map the CUDA backend."""
+    global _host
+    if _host is None:
+        path = PKG / "libheatray_host.so"
+        if not path.exists():
+            raise RuntimeError(f"{path} is missing: run `python -m heatray_b200.build`.")
+        _host = C.CDLL(str(path))
+        _declare_host(_host, backend=False)
+    return _host
+
+
+def _declare_host(lib, backend=True):
     lib.hrhSequenceOffsetCount.restype = C.c_size_t
     lib.hrhSequenceOffsetCount.argtypes = [i32, i32]
     lib.hrhGenerateSequenceOffsets.argtypes = [i32, i32, C.c_void_p, C.c_size_t]
@@ -272,15 +288,16 @@ def _declare_host(lib):
     lib.hrhFovTan.argtypes = [f32]
     lib.hrhApertureRadius.restype = f32
     lib.hrhApertureRadius.argtypes = [f32, f32]
-    lib.hrhDefaultRenderOptions.argtypes = [C.POINTER(RenderOptions)]
-    lib.hrhPassGeneratorCreate.argtypes = [i32, i32, i32, C.POINTER(C.c_void_p)]
-    lib.hrhPassGeneratorDestroy.argtypes = [C.c_void_p]
-    lib.hrhPassGeneratorResize.argtypes = [C.c_void_p, i32, i32]
-    lib.hrhPassGeneratorRenderPass.argtypes = [C.c_void_p, C.POINTER(RenderOptions), PASS_COMPLETE_CALLBACK, C.c_void_p]
-    lib.hrhPassGeneratorRunTask.argtypes = [C.c_void_p, CONTEXT_TASK, C.c_void_p]
-    lib.hrhPassGeneratorWaitIdle.argtypes = [C.c_void_p]
-    lib.hrhPassGeneratorLastError.restype = C.c_char_p
-    lib.hrhPassGeneratorLastError.argtypes = [C.c_void_p]
+    if backend:            # hr::PassGenerator drives the backend: it lives in libheatray_cuda.so
+        lib.hrhDefaultRenderOptions.argtypes = [C.POINTER(RenderOptions)]
+        lib.hrhPassGeneratorCreate.argtypes = [i32, i32, i32, C.POINTER(C.c_void_p)]
+        lib.hrhPassGeneratorDestroy.argtypes = [C.c_void_p]
+        lib.hrhPassGeneratorResize.argtypes = [C.c_void_p, i32, i32]
+        lib.hrhPassGeneratorRenderPass.argtypes = [C.c_void_p, C.POINTER(RenderOptions), PASS_COMPLETE_CALLBACK, C.c_void_p]
+        lib.hrhPassGeneratorRunTask.argtypes = [C.c_void_p, CONTEXT_TASK, C.c_void_p]
+        lib.hrhPassGeneratorWaitIdle.argtypes = [C.c_void_p]
+        lib.hrhPassGeneratorLastError.restype = C.c_char_p
+        lib.hrhPassGeneratorLastError.argtypes = [C.c_void_p]
     lib.hrhLoadImage.argtypes = [C.c_char_p, i32, C.POINTER(HrhImage)]
     lib.hrhLoadImageFromMemory.argtypes = [C.c_void_p, C.c_size_t, i32, C.POINTER(HrhImage)]
     lib.hrhFreeImage.argtypes = [C.POINTER(HrhImage)]
@@ -569,7 +586,7 @@ def _image_to_numpy(lib, im: HrhImage) -> np.ndarray:
 
 def load_image(path_or_bytes, flip=False) -> np.ndarray:
     """hrhLoadImage / hrhLoadImageFromMemory -> (h, w, channels) uint8 or float32 array."""
-    lib = load_library()
+    lib = load_host_library()
     im = HrhImage()
     if isinstance(path_or_bytes, (bytes, bytearray)):
         buf = (C.c_uint8 * len(path_or_bytes)).from_buffer_copy(path_or_bytes)

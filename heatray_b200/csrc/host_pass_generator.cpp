@@ -120,18 +120,18 @@ private:
         int rc = hrcResize(m_ctx, w, h); if (rc) { check(rc); return rc; }
         m_width = w; m_height = h;
         // generateSequenceOffsets (PassGenerator.cpp:150-159) + the per-pixel sequence ids (quirk B-Q2)
-        const size_t n = sequenceOffsetCount(w, h);
-        std::vector<float> off(n); generateSequenceOffsets(w, h, off.data(), n);
-        std::vector<uint8_t> ids((size_t)w * h); generateSequenceIds(w, h, kNumRandomSequences, ids.data());
+        const size_t n = hrhSequenceOffsetCount(w, h);
+        std::vector<float> off(n); hrhGenerateSequenceOffsets(w, h, off.data(), n);
+        std::vector<uint8_t> ids((size_t)w * h); hrhGenerateSequenceIds(w, h, kNumRandomSequences, ids.data());
         rc = hrcSetPixelTables(m_ctx, off.data(), n, ids.data()); check(rc);
         if (rc) return rc;
         // interactive block-coordinate texture + per-block hashes (PassGenerator.cpp:266-294, perspective.rlsl:42-57)
         const int bs = 3;                                                 // RenderOptions::kInteractiveBlockSize, PassGenerator.h:59
         std::vector<float> coords((size_t)bs * bs * 3);
-        generateInteractiveBlockCoords(bs, bs, m_blockShuffleSeed, coords.data());
+        hrhGenerateInteractiveBlockCoords(bs, bs, m_blockShuffleSeed, coords.data());
         const int bx = (w + bs - 1) / bs, by = (h + bs - 1) / bs;
         std::vector<float> brand((size_t)bx * by * 2);
-        generateInteractiveBlockRand(bx, by, brand.data());
+        hrhGenerateInteractiveBlockRand(bx, by, brand.data());
         rc = hrcSetInteractiveBlocks(m_ctx, bs, bs, coords.data(), bx, by, brand.data()); check(rc);
         return rc;
     }
@@ -197,7 +197,7 @@ private:
         if (o.sampleMode != n.sampleMode || o.maxRenderPasses != n.maxRenderPasses || o.bokehShape != n.bokehShape) {
             const uint32_t count = n.maxRenderPasses;
             std::vector<float> xy(2 * (size_t)kNumRandomSequences * count), ap(xy.size());
-            generateRandomSequences(n.sampleMode, n.bokehShape, kNumRandomSequences, count, xy.data(), ap.data());
+            hrhGenerateRandomSequences(n.sampleMode, n.bokehShape, kNumRandomSequences, count, xy.data(), ap.data());
             check(hrcSetSequences(m_ctx, kNumRandomSequences, (int)count, xy.data(), ap.data()));
         }
         m_globals.maxRayDepth = (int)n.maxRayDepth;

@@ -105,7 +105,7 @@ def rotate(axis, angle):
 
 # ---- mesh providers -------------------------------------------------------------------------------
 def plane_mesh(width, length, with_uv=False):
-    lib = capi.load_library()
+    lib = capi.load_host_library()
     pos, nrm, uv, idx = np.zeros((4, 3), np.float32), np.zeros((4, 3), np.float32), np.zeros((4, 2), np.float32), np.zeros(4, np.uint32)
     lib.hrhPlaneMesh(width, length, capi._ptr(pos), capi._ptr(nrm), capi._ptr(uv), capi._ptr(idx))
     return (pos, nrm, idx, uv) if with_uv else (pos, nrm, idx)
@@ -129,7 +129,7 @@ def sphere_mesh_uv(u_slices, v_slices, radius):
 def sphere_mesh(u_slices, v_slices, radius):
     key = (u_slices, v_slices, radius)
     if key not in _sphere_cache:
-        lib = capi.load_library()
+        lib = capi.load_host_library()
         nv, ni = C.c_uint32(), C.c_uint32()
         lib.hrhSphereMesh(u_slices, v_slices, radius, None, None, None, None, C.byref(nv), C.byref(ni))
         pos, nrm = np.zeros((nv.value, 3), np.float32), np.zeros((nv.value, 3), np.float32)
@@ -421,7 +421,7 @@ def import_scene(path, convert_to_meters=False, width=512, height=512, passes=16
     """OBJ / glTF asset -> SceneSpec through the C++ importer (host_import.cpp) and texture loader (host_image.cpp).
     Camera framing follows HeatrayRenderer.cpp:302-308: target = AABB centre, distance = 3 x AABB diagonal, focus on the target."""
     import ctypes as C
-    lib = capi.load_library()
+    lib = capi.load_host_library()
     h = C.c_void_p()
     rc = lib.hrhImportScene(str(path).encode(), int(convert_to_meters), C.byref(h))
     if rc != capi.HRC_OK:
@@ -440,7 +440,7 @@ def preset_scene(name, width=512, height=512, passes=16, max_depth=5, env=None, 
     """One of the reference's built-in scenes (HeatrayRenderer::changeScene, HeatrayRenderer.cpp:123-286) through hrhBuildPresetScene.
     The reference does not re-frame the camera for them: the default OrbitCamera applies (distance 19, OrbitCamera.h:22-25), focus on it."""
     import ctypes as C
-    lib = capi.load_library()
+    lib = capi.load_host_library()
     h = C.c_void_p()
     rc = lib.hrhBuildPresetScene(str(name).encode(), C.byref(h))
     if rc != capi.HRC_OK:

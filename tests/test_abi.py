@@ -67,8 +67,9 @@ def test_product_fails_loudly_without_gpu(lib):
 
 
 def test_product_does_not_link_the_oracle():
-    out = subprocess.run(["nm", "-D", str(capi.LIB_PATH)], capture_output=True, text=True).stdout
-    assert " orc" not in out and "liboracle" not in subprocess.run(["ldd", str(capi.LIB_PATH)], capture_output=True, text=True).stdout
+    for lib_path in (capi.LIB_PATH, capi.PKG / "libheatray_host.so", capi.PKG / "libheatray_openrl.so"):
+        out = subprocess.run(["nm", "-D", str(lib_path)], capture_output=True, text=True).stdout
+        assert " orc" not in out and "liboracle" not in subprocess.run(["ldd", str(lib_path)], capture_output=True, text=True).stdout
     for f in (ROOT / "heatray_b200").rglob("*.py"):
         text = f.read_text()
         assert not re.search(r"^\s*(from|import)\s+oracle", text, re.M) and "liboracle" not in text, f
@@ -76,3 +77,17 @@ def test_product_does_not_link_the_oracle():
         if f.is_dir():
             continue
         assert "oracle/" not in f.read_text().replace("the CPU oracle", ""), f
+
+
+def test_host_library_has_no_device_code_and_openrl_shim_exports_the_entry_points():
+    """libheatray_host.so (what the CPU reference arm loads) carries no CUDA: no cudart symbols, no fatbin section; it reaches the backend only
+    through weak references. libheatray_openrl.so exports every entry point include/heatray_openrl.h declares."""
+    host = capi.PKG / "libheatray_host.so"
+    syms = subprocess.run(["nm", "-D", str(host)], capture_output=True, text=True).stdout
+    assert "cuda" not in syms.lower() and ".nv_fatbin" not in subprocess.run(["readelf", "-S", str(host)], capture_output=True, text=True).stdout
+    assert all(line.split()[0] == "w" for line in syms.splitlines() if " hrc" in line and line.split()[-1].startswith("hrc"))
+    assert "libheatray_host.so" in subprocess.run(["ldd", str(capi.LIB_PATH)], capture_output=True, text=True).stdout
+    header = (ROOT / "include" / "heatray_openrl.h").read_text()
+    wanted = set(re.findall(r"\b((?:rl[A-Z]|OpenRL|hrl)\w+)\s*\(", header)) - {"rlGetError"} | {"rlGetError"}
+    exported = {line.split()[-1] for line in subprocess.run(["nm", "-D", "--defined-only", str(capi.PKG / "libheatray_openrl.so")], capture_output=True, text=True).stdout.splitlines() if " T " in line}
+    assert len(wanted) >= 62 and wanted <= exported, sorted(wanted - exported)
