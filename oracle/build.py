@@ -19,7 +19,7 @@ def build_oracle(force: bool = False) -> None:
         raise RuntimeError("oracle build failed")
     ref = odir / "ref_probe" / "build_ref.sh"
     if Path("/root/reference/Source").is_dir() and ref.exists():
-        have = all((odir / "_ref" / n).exists() for n in ("libref_qmc.so", "libref_lut.so", "libref_rlsl.so", "libref_display.so", "libref_stb.so", "libref_session.so", "libref_shaders.so"))
+        have = all((odir / "_ref" / n).exists() for n in ("libref_qmc.so", "libref_lut.so", "libref_rlsl.so", "libref_display.so", "libref_stb.so", "libref_session.so", "libref_shaders.so", "libref_scene.so"))
         if force or not have:
             res = subprocess.run(["sh", str(ref)], capture_output=True, text=True)
             if res.returncode != 0:

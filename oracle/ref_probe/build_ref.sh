@@ -31,4 +31,26 @@ g++ -std=c++20 -O1 -fPIC -shared -include cstdint -I$REF/Source -I$REF/3rdParty 
 # #include lines like ShaderCodeLoader.cpp and rewrites the RLSL-only declarations (listed in its header) into /tmp; rlsl_shim.h supplies the built-ins.
 python3 rlsl_to_cpp.py /tmp/hr_ref_shaders
 g++ -std=gnu++20 -D_MSC_EXTENSIONS -O2 -ffp-contract=off -fPIC -shared -fsingle-precision-constant -I/tmp/hr_ref_shaders -I. -I$REF/3rdParty -I$REF/3rdParty/glm -w ref_shaders.cpp -o "$OUT/libref_shaders.so"
+# The reference's own host code for the path, unmodified, against the product's OpenRL entry points (libheatray_openrl.so): PassGenerator, Scene, Mesh,
+# Lighting, the materials, the lights, the shader loader and the header-only RLWrapper classes. assimp/config.h is the one generated header the Assimp
+# headers need (cmake's configure_file of config.h.in with nothing defined); TextureLoader.cpp (FreeImage + stb) and Assimp itself are not built: ref_scene.cpp
+# holds the stand-ins.
+SHIM="$HERE/../../heatray_b200"
+if [ -f "$SHIM/libheatray_openrl.so" ]; then
+  mkdir -p /tmp/hr_ref_scene/inc/assimp /tmp/hr_ref_scene/obj
+  sed 's/#cmakedefine.*//' "$REF/3rdParty/assimp/include/assimp/config.h.in" > /tmp/hr_ref_scene/inc/assimp/config.h
+  SFL="$FL -O1 -I$REF/3rdParty/assimp/include -I/tmp/hr_ref_scene/inc -DGLM_ENABLE_EXPERIMENTAL"
+  OBJS=""
+  for f in HeatrayRenderer/PassGenerator HeatrayRenderer/Scene/Scene HeatrayRenderer/Scene/Mesh HeatrayRenderer/Scene/Lighting HeatrayRenderer/Materials/PhysicallyBasedMaterial \
+           HeatrayRenderer/Materials/GlassMaterial HeatrayRenderer/Materials/MultiScatterUtil HeatrayRenderer/Lights/DirectionalLight HeatrayRenderer/Lights/PointLight \
+           HeatrayRenderer/Lights/SpotLight HeatrayRenderer/Lights/EnvironmentLight Utility/ShaderCodeLoader Utility/FileIO Utility/Log; do
+    o=/tmp/hr_ref_scene/obj/$(basename $f).o
+    g++ $SFL -c "$REF/Source/$f.cpp" -o $o &
+    OBJS="$OBJS $o"
+  done
+  g++ $SFL -c ref_scene.cpp -o /tmp/hr_ref_scene/obj/ref_scene.o &
+  gcc -fPIC -DREF_SCENE_STUBS -c ref_c_stubs.c -o /tmp/hr_ref_scene/obj/ref_c_stubs.o
+  wait
+  g++ -shared -o "$OUT/libref_scene.so" $OBJS /tmp/hr_ref_scene/obj/ref_scene.o /tmp/hr_ref_scene/obj/ref_c_stubs.o -L"$SHIM" -lheatray_openrl -Wl,-rpath,'$ORIGIN/../../heatray_b200' -pthread -Wl,-z,defs
+fi
 echo "oracle/_ref built"
