@@ -268,23 +268,33 @@ class Rig:
 
     def exchange(self, buf=None):
         """The one collective of the path, timed with CUDA events on torch's current stream (the pass streams were synchronised before).
-        Sample mode: fp32 sum of the accumulation buffers (HR_BENCH_COLLECTIVE = all_reduce (default, in-switch reduction where NCCL has NVLS) | reduce).
-        Band mode: gather of each rank's own rows onto rank 0 (disjoint pixels, frame / world bytes per rank)."""
+        One fp32 sum of the accumulation buffers onto rank 0 (see exchange_async for the alternatives that were measured)."""
         if self.world <= 1:
             return 0.0
         import torch.distributed as dist
         from heatray_b200 import sharding
         buf = self.acc if buf is None else buf
         self.ev0.record()
-        if self.bands:
-            sharding.gather_bands(buf, BAND_ROWS, self.rank, self.world, dst=0)
-        elif os.environ.get("HR_BENCH_COLLECTIVE", "all_reduce") == "reduce":
-            dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
-        else:
-            dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+        self.exchange_async(buf)
         self.ev1.record()
         self.ev1.synchronize()
         return self.ev0.elapsed_time(self.ev1)
+
+    def collective(self):
+        return os.environ.get("HR_BENCH_COLLECTIVE", "reduce")
+
+    def exchange_async(self, buf):
+        """Enqueues the collective on torch's current stream (no host wait). HR_BENCH_COLLECTIVE: reduce (default: fp32 sum onto rank 0; for bands the
+        other ranks' rows are zeros, so the sum is exact), all_reduce, gather (band mode: each rank sends only its own rows)."""
+        import torch.distributed as dist
+        from heatray_b200 import sharding
+        kind = self.collective()
+        if self.bands and kind == "gather":
+            sharding.gather_bands(buf, BAND_ROWS, self.rank, self.world, dst=0)
+        elif kind == "all_reduce":
+            dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+        else:
+            dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
 
     def close(self):
         self.b.close()
@@ -433,11 +443,30 @@ def main():
     # The caller is the reference viewer's loop (HeatrayRenderer.cpp:366-408): hrcRenderPass, then map the pixel pack buffer, one pass at a
     # time. N > 1: every step ends with the exchange step on a copy of the accumulation buffers and rank 0 alone copies the combined frame
     # to its host (the other ranks have nothing to show).
-    def caller_loop(n):
+    side = torch.cuda.Stream() if world > 1 else None
+    snap = torch.cuda.Event() if world > 1 else None
+
+    def caller_loop(n, overlapped=False):
         total = 0.0
+        pending = None
         for i in range(n):
             r.render_pass(want_stats=False, sample_index=sidx(i))
-            if world > 1:
+            if world > 1 and overlapped:
+                # the exchange of pass i (snapshot of the local sums -> collective -> rank 0's host copy) runs on a side stream while pass i+1 renders:
+                # the combined frame reaches the host one pass late, every step still delivers one
+                if pending is not None:
+                    pending.synchronize()
+                    if rank == 0:
+                        total += float(rig.host[0, 0, 3])
+                with torch.cuda.stream(side):
+                    rig.red.copy_(rig.acc)
+                    snap.record()
+                    rig.exchange_async(rig.red)
+                    if rank == 0:
+                        rig.host.copy_(rig.red, non_blocking=True)
+                    pending = torch.cuda.Event(); pending.record()
+                snap.synchronize()                # the next pass may write the accumulation buffer once the snapshot is taken
+            elif world > 1:
                 rig.red.copy_(rig.acc)
                 rig.exchange(rig.red)
                 if rank == 0:
@@ -448,16 +477,20 @@ def main():
                 px = b.map_pixels()               # D2H of the RGBA32F accumulation buffer into pinned memory, every pass
                 total += float(px[0, 0, 3])
                 b.unmap_pixels()
+        if pending is not None:
+            pending.synchronize()
+            if rank == 0:
+                total += float(rig.host[0, 0, 3])
         return total
 
-    def timed_caller_loop(spec_depth):
+    def timed_caller_loop(spec_depth, overlapped=False):
         b.set_option(capi.OPT_SPECULATIVE_PASSES, spec_depth)
         b.clear()
-        caller_loop(max(8, W))                    # untimed: side buffers and their pass graphs exist before the clock starts
+        caller_loop(max(8, W), overlapped)        # untimed: side buffers and their pass graphs exist before the clock starts
         b.clear()
         barrier()
         t = time.perf_counter()
-        chk = caller_loop(K)
+        chk = caller_loop(K, overlapped)
         barrier()
         ms = (time.perf_counter() - t) * 1e3
         b.set_option(capi.OPT_SPECULATIVE_PASSES, 0)
@@ -466,9 +499,13 @@ def main():
     e2e_plain_ms, chk_plain = timed_caller_loop(0)
     e2e_spec_ms, chk_spec = timed_caller_loop(3)
     assert chk_plain == chk_spec, "speculated passes leaked into a frame the caller read"
-    # One GPU: the headline is the caller loop with the backend's speculative look-ahead. Several GPUs: every step ends in a collective that all
-    # ranks must reach together, and passes speculated ahead on every rank delay it, so the headline is the plain loop (both are reported).
-    e2e_ms = e2e_spec_ms if world == 1 else e2e_plain_ms
+    # One GPU: the headline is the caller loop with the backend's speculative look-ahead. Several GPUs: every step ends in a collective that all ranks
+    # must reach together (passes speculated ahead on every rank delay it badly), so the headline overlaps the exchange of pass i with pass i+1 instead.
+    e2e_overlap_ms = None
+    if world > 1:
+        e2e_overlap_ms, chk_ov = timed_caller_loop(0, overlapped=True)
+        assert chk_ov == chk_plain
+    e2e_ms = e2e_spec_ms if world == 1 else e2e_overlap_ms
 
     # The same K steps with the caller queueing ahead explicitly (hr::PassGenerator's look-ahead when renderPass jobs are queued behind the
     # running one): passes i+1 .. i+3 render into deferred buffers while pass i is read back.
@@ -516,6 +553,7 @@ def main():
         t = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms, e2e_spec_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms, e2e_spec_ms = t.tolist()
+        e2e_overlap_ms = e2e_ms
         rt = torch.tensor([float(rays_total)], device="cuda", dtype=torch.float64)
         dist.all_reduce(rt, op=dist.ReduceOp.SUM)
         rays_all = rt.item()
@@ -575,8 +613,9 @@ def main():
                "api": ("per step: hrcRenderPass, then hrcReadPixels / hrcReleasePixels (pinned host buffer), one pass at a time - the reference viewer's loop (HeatrayRenderer.cpp:366-408) - "
                        "with HRC_OPT_SPECULATIVE_PASSES = 3: the backend keeps the next three passes of the progressive render running while the caller reads this one back; "
                        "every step delivers its own full frame (exactly i + 1 samples) to the host") if world == 1 else
-                      ("per step and rank: hrcRenderPass, device copy of the accumulation buffer, the exchange step on the copy, "
-                       "rank 0 copies the combined frame to its pinned host buffer; the other ranks read nothing back"),
+                      ("per step and rank: hrcRenderPass, then on a side stream a device snapshot of the accumulation buffer, the exchange step on the snapshot and "
+                       "rank 0's copy of the combined frame to its pinned host buffer, overlapped with the next pass (the frame arrives one pass late; the other "
+                       "ranks read nothing back); e2e.serial is the same without the overlap"),
                "speculative_passes": 3 if world == 1 else 0,
                "serial": {"value": rays_all / (e2e_plain_ms / 1e3) / 1e6, "ms_per_step": e2e_plain_ms / K,
                           "api": "the same caller loop with HRC_OPT_SPECULATIVE_PASSES = 0: one pass in flight, readback not overlapped"},
@@ -596,7 +635,7 @@ def main():
                 "gpu_launches": launches + 3}       # + the lane joins (k_add_pixels) at the end of the timed region
         if world > 1:
             line["reduce_ms"] = reduce_ms
-            line["exchange"] = "gather of own rows" if bands else os.environ.get("HR_BENCH_COLLECTIVE", "all_reduce")
+            line["exchange"] = os.environ.get("HR_BENCH_COLLECTIVE", "reduce")
             line["reduce_check"] = reduce_check
             if strong:
                 line["strong"] = strong
@@ -609,7 +648,7 @@ def main():
         dist.destroy_process_group()
 
 
-def strong_terrain(lib, rank, world, local_rank, barrier, steps=16):
+def strong_terrain(lib, rank, world, local_rank, barrier, steps=32):
     """configs[3] (terrain, 10 M triangles, 4K) by interleaved screen bands on all ranks: strong scaling. Also times the same passes on rank 0
     alone over the full frame (the other ranks wait), so that the line carries its own single-GPU figure."""
     import torch
@@ -645,7 +684,7 @@ def strong_terrain(lib, rank, world, local_rank, barrier, steps=16):
     if rank == 0:
         value = rt.item() / (t[0].item() / 1e3) / 1e6
         n1_value = n1_rays / (n1_ms / 1e3) / 1e6
-        out = {"config": f"configs[3] terrain ({spec.triangle_count} triangles, {spec.width}x{spec.height}), interleaved {BAND_ROWS}-row screen bands, gather of own rows",
+        out = {"config": f"configs[3] terrain ({spec.triangle_count} triangles, {spec.width}x{spec.height}), interleaved {BAND_ROWS}-row screen bands, exchange = {rig.collective()}",
                "value": value, "unit": UNIT, "ms_per_step": t[0].item() / steps, "steps": steps, "exchange_ms": t[1].item(),
                "n1_value": n1_value, "n1_ms_per_step": n1_ms / steps, "speedup": value / n1_value, "efficiency": value / n1_value / world,
                "reduce_check": check}
