@@ -159,7 +159,7 @@ BAND_ROWS = int(os.environ.get("HR_BENCH_BAND_ROWS", "16"))
 
 def config_dict(spec, name, n_gpus, extra=None, shard="sample"):
     par = "single GPU" if n_gpus <= 1 else (f"sample-index sharding x{n_gpus}, one NCCL fp32 sum of the accumulation buffers" if shard == "sample"
-                                            else f"screen-band sharding x{n_gpus} (interleaved {BAND_ROWS}-row bands), one NCCL gather of each rank's own rows")
+                                            else f"screen-band sharding x{n_gpus} (interleaved {BAND_ROWS}-row bands), one NCCL sum onto rank 0 (the other ranks' rows are zeros)")
     d = {"workload": WORKLOAD_NAMES[name], "scene": spec.name, "triangles": spec.triangle_count, "resolution": f"{spec.width}x{spec.height}",
          "max_ray_depth": spec.max_depth, "spp_per_step": 1, "qmc": "owen-scrambled sobol (16 sequences)",
          "parallelism": par,
@@ -387,7 +387,9 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # the collective's kernel goes on a high-priority stream: with passes in flight on every lane a normal-priority NCCL kernel waits behind them for SMs
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=os.environ.get("HR_BENCH_NCCL_PRIORITY", "1") != "0")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), pg_options=opts)
 
     def barrier():
         if world > 1:
@@ -443,7 +445,7 @@ def main():
     # The caller is the reference viewer's loop (HeatrayRenderer.cpp:366-408): hrcRenderPass, then map the pixel pack buffer, one pass at a
     # time. N > 1: every step ends with the exchange step on a copy of the accumulation buffers and rank 0 alone copies the combined frame
     # to its host (the other ranks have nothing to show).
-    side = torch.cuda.Stream() if world > 1 else None
+    side = torch.cuda.Stream(priority=-1) if world > 1 else None
     snap = torch.cuda.Event() if world > 1 else None
 
     def caller_loop(n, overlapped=False):
@@ -484,6 +486,7 @@ def main():
         return total
 
     def timed_caller_loop(spec_depth, overlapped=False):
+        b.set_option(capi.OPT_SPECULATIVE_STRIDE, 1 if bands else world)      # a sample-sharded rank renders every world-th sample index
         b.set_option(capi.OPT_SPECULATIVE_PASSES, spec_depth)
         b.clear()
         caller_loop(max(8, W), overlapped)        # untimed: side buffers and their pass graphs exist before the clock starts
@@ -501,11 +504,12 @@ def main():
     assert chk_plain == chk_spec, "speculated passes leaked into a frame the caller read"
     # One GPU: the headline is the caller loop with the backend's speculative look-ahead. Several GPUs: every step ends in a collective that all ranks
     # must reach together (passes speculated ahead on every rank delay it badly), so the headline overlaps the exchange of pass i with pass i+1 instead.
-    e2e_overlap_ms = None
+    e2e_overlap_ms = e2e_spec_overlap_ms = 0.0
     if world > 1:
         e2e_overlap_ms, chk_ov = timed_caller_loop(0, overlapped=True)
-        assert chk_ov == chk_plain
-    e2e_ms = e2e_spec_ms if world == 1 else e2e_overlap_ms
+        e2e_spec_overlap_ms, chk_sov = timed_caller_loop(3, overlapped=True)
+        assert chk_ov == chk_plain and chk_sov == chk_plain
+    e2e_ms = e2e_spec_ms if world == 1 else e2e_spec_overlap_ms
 
     # The same K steps with the caller queueing ahead explicitly (hr::PassGenerator's look-ahead when renderPass jobs are queued behind the
     # running one): passes i+1 .. i+3 render into deferred buffers while pass i is read back.
@@ -550,10 +554,9 @@ def main():
 
     # ---- gather over ranks (max time, summed rays) -------------------------------------------------
     if world > 1:
-        t = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms, e2e_spec_ms], device="cuda", dtype=torch.float64)
+        t = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms, e2e_spec_ms, e2e_overlap_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms, e2e_spec_ms = t.tolist()
-        e2e_overlap_ms = e2e_ms
+        dev_ms, wall_ms, e2e_ms, e2e_plain_ms, reduce_ms, e2e_spec_ms, e2e_overlap_ms = t.tolist()
         rt = torch.tensor([float(rays_total)], device="cuda", dtype=torch.float64)
         dist.all_reduce(rt, op=dist.ReduceOp.SUM)
         rays_all = rt.item()
@@ -613,14 +616,18 @@ def main():
                "api": ("per step: hrcRenderPass, then hrcReadPixels / hrcReleasePixels (pinned host buffer), one pass at a time - the reference viewer's loop (HeatrayRenderer.cpp:366-408) - "
                        "with HRC_OPT_SPECULATIVE_PASSES = 3: the backend keeps the next three passes of the progressive render running while the caller reads this one back; "
                        "every step delivers its own full frame (exactly i + 1 samples) to the host") if world == 1 else
-                      ("per step and rank: hrcRenderPass, then on a side stream a device snapshot of the accumulation buffer, the exchange step on the snapshot and "
-                       "rank 0's copy of the combined frame to its pinned host buffer, overlapped with the next pass (the frame arrives one pass late; the other "
-                       "ranks read nothing back); e2e.serial is the same without the overlap"),
-               "speculative_passes": 3 if world == 1 else 0,
+                      ("per step and rank: hrcRenderPass with HRC_OPT_SPECULATIVE_PASSES = 3, then on a high-priority side stream a device snapshot of the accumulation "
+                       "buffer, the exchange step on the snapshot and rank 0's copy of the combined frame to its pinned host buffer, overlapped with the next pass "
+                       "(the combined frame reaches the host one pass late; the other ranks read nothing back); e2e.serial is the same loop with neither"),
+               "speculative_passes": 3,
                "serial": {"value": rays_all / (e2e_plain_ms / 1e3) / 1e6, "ms_per_step": e2e_plain_ms / K,
                           "api": "the same caller loop with HRC_OPT_SPECULATIVE_PASSES = 0: one pass in flight, readback not overlapped"},
                "speculative3": {"value": rays_all / (e2e_spec_ms / 1e3) / 1e6, "ms_per_step": e2e_spec_ms / K,
                                 "api": "the same caller loop with HRC_OPT_SPECULATIVE_PASSES = 3"}}
+        if world > 1:
+            e2e["overlapped_exchange"] = {"value": rays_all / (e2e_overlap_ms / 1e3) / 1e6, "ms_per_step": e2e_overlap_ms / K,
+                                          "api": "the exchange overlapped with the next pass, HRC_OPT_SPECULATIVE_PASSES = 0"}
+            e2e["speculative3"]["api"] += ", exchange not overlapped"
         if e2e_look_ms:
             e2e["lookahead3"] = {"value": rays_all / (e2e_look_ms / 1e3) / 1e6, "ms_per_step": e2e_look_ms / K,
                                  "api": "caller queues ahead itself: hrcEnqueuePassDeferred keeps 3 passes ahead, hrcReadPixels, hrcCommitDeferred (hr::PassGenerator with renderPass jobs queued)"}

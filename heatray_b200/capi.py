@@ -23,7 +23,7 @@ TEX_R32F, TEX_RGB32F, TEX_RGBA32F, TEX_RGBA8 = 0, 1, 2, 3
 WRAP_CLAMP, WRAP_REPEAT = 0, 1
 DRAW_TRIANGLES, DRAW_TRIANGLE_STRIP = 0, 1
 HIT_BACKFACE = 0x40000000
-OPT_TRAVERSAL_COUNTERS, OPT_KERNEL_TIMING, OPT_SPECULATIVE_PASSES, OPT_PIXEL_RAY_COUNTS = 0, 1, 2, 3
+OPT_TRAVERSAL_COUNTERS, OPT_KERNEL_TIMING, OPT_SPECULATIVE_PASSES, OPT_PIXEL_RAY_COUNTS, OPT_SPECULATIVE_STRIDE = 0, 1, 2, 3, 4
 SAMPLE_RANDOM, SAMPLE_HALTON, SAMPLE_HAMMERSLEY, SAMPLE_BLUE_NOISE, SAMPLE_SOBOL = range(5)
 BOKEH_CIRCULAR, BOKEH_PENTAGON, BOKEH_HEXAGON, BOKEH_OCTAGON = range(4)
 

@@ -57,7 +57,7 @@ struct HrcContext_t {
     // the predictions. A caller that renders and reads back one pass at a time (the reference viewer's loop) then gets its readback
     // overlapped with the next passes without queueing anything itself.
     uint32_t* dRayCounts = nullptr;        // HRC_OPT_PIXEL_RAY_COUNTS
-    int specDepth = 0; uint64_t stateVersion = 0;
+    int specDepth = 0, specStride = 1; uint64_t stateVersion = 0;
     HrcFrameParams deferredParams[kDeferredLanes] = {}; uint64_t deferredVersion[kDeferredLanes] = {};
     std::vector<GraphEntry> graphs;        // captured passes of the main lane
     bool useGraphs = true; uint64_t graphClock = 0;
@@ -388,6 +388,11 @@ HRC_API int hrcSetOption(HrcContext c, int32_t option, int32_t value) {
         if (value < 0 || value > HRC_MAX_DEFERRED_PASSES) return fail(c, HRC_ERR_INVALID_VALUE, "0..3 speculative passes");
         if (c->deferredCount > 0) { int r = hrcDiscardDeferred(c); if (r) return r; }
         c->specDepth = value;
+    }
+    else if (option == HRC_OPT_SPECULATIVE_STRIDE) {
+        if (value < 1 || value > 4096) return fail(c, HRC_ERR_INVALID_VALUE, "speculation stride 1..4096");
+        if (c->deferredCount > 0) { int r = hrcDiscardDeferred(c); if (r) return r; }
+        c->specStride = value;
     }
     else return fail(c, HRC_ERR_INVALID_VALUE, "unknown option");
     return HRC_OK;
@@ -987,7 +992,7 @@ static int renderOrCommitPredicted(HrcContext c, const HrcFrameParams* fp, int* 
     if (fp->interactiveMode) return HRC_OK;                                         // block passes change their parameters every pass: not predicted
     HrcFrameParams nx = *fp;
     for (int ahead = c->deferredCount + 1; ahead <= c->specDepth; ++ahead) {
-        nx.sampleIndex = fp->sampleIndex + ahead;
+        nx.sampleIndex = fp->sampleIndex + ahead * c->specStride;
         if ((float)nx.sampleIndex >= fp->maxSampleIndex) break;                      // the progressive render ends at maxRenderPasses (PassGenerator.cpp:368)
         const int d = c->deferredNext;
         if (c->deferred[d].active) joinLanes(c);                                    // its previous pass was committed but not folded in yet

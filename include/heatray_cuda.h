@@ -69,8 +69,10 @@ enum {
     HRC_OPT_PIXEL_RAY_COUNTS = 3,    /* parity hook: count the rays (primary + extension + occlusion segments) every pixel's paths submit to traversal,
                                       * readable with hrcReadRayCounts; hrcClear zeroes the counts. A pixel whose value differs from another
                                       * implementation's together with its ray count took a different discrete decision somewhere on its path. */
+    HRC_OPT_SPECULATIVE_STRIDE = 4,  /* s = 1..4096 (default 1): the sample-index step HRC_OPT_SPECULATIVE_PASSES predicts with (pass i is followed by i + s).
+                                      * A rank of a sample-index-sharded render (rank q of N renders q, q + N, q + 2N, ...) sets s = N. */
     HRC_OPT_SPECULATIVE_PASSES = 2   /* n = 0..3 (default 0): hrcRenderPass(i) also starts passes i+1..i+n of the same progressive render (same frame
-                                      * parameters, consecutive sample indices below maxSampleIndex) into side buffers nothing else sees. When the next
+                                      * parameters, sample indices i + s, i + 2s, ... below maxSampleIndex; s = HRC_OPT_SPECULATIVE_STRIDE) into side buffers nothing else sees. When the next
                                       * hrcRenderPass asks for exactly the predicted pass and no state changed in between, it is committed instead of
                                       * rendered; any other request discards the predictions. For callers that render and read back one pass at a
                                       * time (the reference viewer's loop, HeatrayRenderer.cpp:366-408): the readback then overlaps the next passes.

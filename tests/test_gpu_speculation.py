@@ -43,6 +43,31 @@ def test_speculated_progressive_render_equals_plain(gpu_backend, depth):
     _same(r.pixels(), plain[0])                                    # nothing of the discarded predictions leaks in
 
 
+def test_speculation_stride_follows_a_sharded_rank(gpu_backend):
+    """HRC_OPT_SPECULATIVE_STRIDE: rank 1 of 4 renders sample indices 1, 5, 9, 13; the predictions must be those, and be committed."""
+    b = gpu_backend
+    r = renderer.Renderer(b)
+    r.load_scene(_spec())
+    idx = [1, 5, 9, 13]
+    plain = []
+    for i in idx:
+        r.render_pass(sample_index=i)
+        plain.append(r.pixels().copy())
+    with pytest.raises(capi.HrcError):
+        b.set_option(capi.OPT_SPECULATIVE_STRIDE, 0)
+    b.set_option(capi.OPT_SPECULATIVE_STRIDE, 4)
+    b.set_option(capi.OPT_SPECULATIVE_PASSES, 2)
+    b.clear(); b.reset_stats()
+    for k, i in enumerate(idx):
+        r.render_pass(sample_index=i)
+        got = r.pixels()
+        assert (got[..., 3] == k + 1).all()
+        _same(got, plain[k])
+    b.set_option(capi.OPT_SPECULATIVE_PASSES, 0)                   # discards what is pending (index 17 is past the 16-entry table: never predicted)
+    b.set_option(capi.OPT_SPECULATIVE_STRIDE, 1)
+    b.clear()
+
+
 def test_mispredictions_are_discarded(gpu_backend):
     b = gpu_backend
     r = renderer.Renderer(b)

@@ -13,7 +13,7 @@ for name in ("bench", "bench_all_reduce", "bench_terrain_rows8", "bench_terrain_
         d = json.loads(open(f"gpurun_out/${T}_{name}_n$N.json").read().strip().splitlines()[-1])
     except Exception as e:
         print(name, "no line", e); continue
-    print(name, "value %.0f ms %.3f reduce_ms %.3f (%s) e2e %.0f serial %.0f spec3 %.0f" % (d["value"], d["ms_per_step"], d.get("reduce_ms", 0), d.get("exchange"), d["e2e"]["value"], d["e2e"]["serial"]["value"], d["e2e"]["speculative3"]["value"]))
+    print(name, "value %.0f ms %.3f reduce_ms %.3f (%s) e2e %.0f serial %.0f spec3 %.0f" % (d["value"], d["ms_per_step"], d.get("reduce_ms", 0), d.get("exchange"), d["e2e"]["value"], d["e2e"]["serial"]["value"], d["e2e"]["speculative3"]["value"]), "overlap-only %.0f" % d["e2e"].get("overlapped_exchange", {}).get("value", 0))
     print("   reduce_check", d.get("reduce_check"))
     if d.get("strong"): print("   strong", {k: v for k, v in d["strong"].items() if k != "config"})
 PY
