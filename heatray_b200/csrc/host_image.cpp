@@ -4,7 +4,10 @@
 // (stbi_load / stbi_loadf, vertical flip on) and HeatrayRenderer::saveScreenshot (HeatrayRenderer.cpp:1619-1662) writes
 // through FreeImage. Neither library is used here: this file carries its own PNG (zlib inflate, all colour types and bit
 // depths, Adam7, tRNS), JPEG (baseline + progressive Huffman, 8-bit) and Radiance RGBE decoders, and PNG / RGBE / PFM
-// writers. tests/test_images.py pins the decoders bit for bit against stb_image as vendored by the reference.
+// writers. tests/test_images.py pins the decoders bit for bit against stb_image as vendored by the reference. To be bit-identical
+// the JPEG decoder has to follow stb_image's arithmetic, not just the standard: the inverse DCT below is the 12-bit fixed-point
+// factorisation of 3rdParty/stb/stb_image.h:2270-2327 (stbi__idct_block: same constants, same rounding offsets, same pass order),
+// and the chroma upsampling / YCbCr conversion use stb_image's fixed-point weights (stbi__resample_row_v_2 / h_2 / hv_2 and stbi__YCbCr_to_RGB_row, stb_image.h:3239-3310, 3434-3460).
 #include "host_api.h"
 
 #include <algorithm>
@@ -643,7 +646,7 @@ struct JDecoder {
     }
 };
 
-// 1-D pass of the 12-bit fixed-point inverse DCT; outputs the even part x0..x3 and the odd part t0..t3.
+// 1-D pass of the 12-bit fixed-point inverse DCT (the STBI__IDCT_1D step, stb_image.h:2270-2307); outputs the even part x0..x3 and the odd part t0..t3.
 struct Idct1D { int x0, x1, x2, x3, t0, t1, t2, t3; };
 inline int f2f(double x) { return (int)(x * 4096 + 0.5); }
 inline Idct1D idct1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7) {

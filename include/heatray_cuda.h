@@ -85,7 +85,9 @@ HRC_API int hrcDestroyContext(HrcContext ctx);
 HRC_API const char* hrcGetLastError(HrcContext ctx);
 
 /* ---- framebuffer + readback (↔ Framebuffer/Texture RGBA32F + PixelPackBuffer) ------- */
-/* ↔ runInitJob FBO part + runResizeJob (PassGenerator.cpp:172-197, 301-323); clears. */
+/* ↔ runInitJob FBO part + runResizeJob (PassGenerator.cpp:172-197, 301-323); clears.
+ * Limit: width * height <= 2^24 pixels (16.7 M; 3840x2160 is 8.3 M): a ray record carries its pixel index in 24 bits next to its depth and
+ * flags. Larger frames return HRC_ERR_UNSUPPORTED; render them as tiles or by screen bands on several contexts (HrcFrameParams.bandHeight / bandIndex / bandCount). */
 HRC_API int hrcResize(HrcContext ctx, int32_t width, int32_t height);
 /* ↔ rlClear(RL_COLOR_BUFFER_BIT) (PassGenerator.cpp:439) */
 HRC_API int hrcClear(HrcContext ctx);
