@@ -438,6 +438,8 @@ def main():
         st = r.render_pass(want_stats=True, sample_index=sidx(i))
         ms_closest += st.msClosest; ms_any += st.msAny; ms_shade += st.msShade; ms_raygen += st.msRaygen; ms_primary += st.msClosestPrimary; inst_ms += st.gpuMs
         launches += int(st.closestLaunches + st.anyLaunches + st.shadeLaunches) + 2     # + raygen, finish
+        if int(os.environ.get("HRC_TUNE_TAIL_RAYS", "0")) > 0:                       # the timed passes also launch k_tail_decide + k_path per iteration boundary
+            launches += 2 * (int(st.closestLaunches) - 1)
     b.set_option(capi.OPT_KERNEL_TIMING, 0)
     clocks = sampler.finish(window=(t0, t1))
 

@@ -72,6 +72,11 @@ struct ShadowQueue {
 
 // Per-iteration control words, zeroed at the start of every pass.
 struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; uint32_t classCount[3]; uint32_t maskedContinuations; };   // class 0: miss, 1: PBR, 2: glass
+// One more entry behind the per-iteration ones describes the pass's tail (k_tail_decide / k_path): extCount = rays the path kernel
+// takes over (0: the wavefront runs to its end), extHead = the iteration whose extension queue they sit in.
+constexpr int kCtrlEntries = kMaxIterations + 1;
+static_assert(kCtrlEntries <= 128, "k_clear_ctrl zeroes the control words with one 128-thread block");
+constexpr uint32_t kQueueDrained = 0x80000000u;          // extHead of an iteration the path kernel took: k_trace finds nothing to pull
 
 // Coherence sort of the extension rays between wavefront iterations (HRC_TUNE_SORT_BITS > 0): k_shade files every emitted ray under
 // key = octant << 3b | morton(cell of its origin in a 2^b-per-axis grid over the scene box), k_sort_scan turns the histogram into bin
@@ -110,7 +115,7 @@ struct PassBuffers {
     ShadowQueue shadow;
     float4* hits;             // t, u, v, primId | material class << 28 | HRC_HIT_BACKFACE  (-1: miss)
     uint32_t* classIdx[3];    // per-class lists of ray indices of the current iteration, filled by k_trace<closest>
-    IterCtrl* ctrl;           // kMaxIterations entries
+    IterCtrl* ctrl;           // kCtrlEntries entries
     DeviceStats* stats;
     float4* accum;
     uint32_t capacity;        // rays per queue
@@ -123,7 +128,7 @@ struct PassBuffers {
     uint32_t* rayCounts;      // HRC_OPT_PIXEL_RAY_COUNTS: rays per pixel (shared by all lanes, hence atomics), else nullptr
 };
 
-struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle, refillIdleAny; int sortBits; };
+struct LaunchConfig { int smCount; int traceBlocksPerSM; int traceThreads; bool collectStats; bool masked; bool shadeMiss, shadePbr, shadeGlass; int refillIdle, refillIdleAny; int sortBits; int tailRays; };
 
 constexpr int kFrameSlots = 1 + (kMaxLanes - 1) + kDeferredLanes;     // one constant-memory DFrame per lane: main, extra lanes, deferred lanes
 void uploadFrame(const DFrame* pinnedFrame, int slot, cudaStream_t s);  // stream-ordered copy into the lane's slot; the source must stay valid until it ran
@@ -133,6 +138,10 @@ void launchTraceClosest(const DScene& sc, int slot, const PassBuffers& pb, int i
 void launchShade(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
 void launchTraceAny(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
 void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);   // orders the extension rays of iteration `iter` (emitted by shade(iter - 1))
+// Tail of a pass (lc.tailRays > 0): once an iteration's extension queue holds no more than lc.tailRays rays, ONE launch of k_path follows every
+// remaining path to its end (trace, shade, occlusion ray, next bounce, in registers) and the wavefront kernels behind it find their queues empty.
+void launchTailDecide(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);          // after shade(iter - 1) (or raygen), same stream
+void launchPathTail(const DScene& sc, int slot, const PassBuffers& pb, int iter, int iterations, const LaunchConfig& lc, cudaStream_t s);   // after any(iter - 1)
 void launchFinishPass(const PassBuffers& pb, int iterations, bool rearm, cudaStream_t s);   // rearm: also zero the control words for the next pass
 void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig& lc, cudaStream_t s);
 void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s);

@@ -74,6 +74,7 @@ struct HrcContext_t {
     int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
     bool devicePixelsExported = false;     // hrcGetDevicePixels handed the buffer out: the caller may write any row at any time (in-place NCCL reduce), so reads copy whole frames until hrcResize
     long long pinnedZeroKey = -1;          // which rows of the pinned frame may be non-zero: -1 any, 0 none (fresh), else the band set's key
+    int tuneTailRays = 0;                  // HRC_TUNE_TAIL_RAYS: an iteration with at most this many extension rays hands the rest of the pass to k_path. Measured: no gain at any threshold (profiles/r02_notes.md), so 0 = off
     int tuneSortBits = 0;                  // HRC_TUNE_SORT_BITS: cells per axis (2^bits) of the coherence sort grid, 0 = off
     float sceneMin[3] = {0, 0, 0}, sceneMax[3] = {1, 1, 1};
     int tunePipelinedBlocksPerSM = 4;      // traversal CTAs per SM for pipelined passes: kernels of several lanes are resident together, so each takes fewer slots
@@ -187,8 +188,8 @@ int ensureLane(HrcContext c, HrcContext_t::Lane& L) {
         for (int i = 0; i < 2 * kMaxIterations; ++i) { cudaEvent_t ev; CU(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); L.evSync.push_back(ev); }
         CU(c, cudaEventCreateWithFlags(&L.evDone, cudaEventDisableTiming));
         if (!c->evMerged) CU(c, cudaEventCreateWithFlags(&c->evMerged, cudaEventDisableTiming));
-        CU(c, cudaMalloc(&L.pb.ctrl, sizeof(IterCtrl) * kMaxIterations)); CU(c, cudaMalloc(&L.pb.stats, sizeof(DeviceStats)));
-        CU(c, cudaMemset(L.pb.stats, 0, sizeof(DeviceStats))); CU(c, cudaMemset(L.pb.ctrl, 0, sizeof(IterCtrl) * kMaxIterations));
+        CU(c, cudaMalloc(&L.pb.ctrl, sizeof(IterCtrl) * kCtrlEntries)); CU(c, cudaMalloc(&L.pb.stats, sizeof(DeviceStats)));
+        CU(c, cudaMemset(L.pb.stats, 0, sizeof(DeviceStats))); CU(c, cudaMemset(L.pb.ctrl, 0, sizeof(IterCtrl) * kCtrlEntries));
     }
     auto allocate = [&]() -> int {
         CU(c, cudaMalloc(&L.accum, n * sizeof(float4)));
@@ -214,6 +215,7 @@ LaunchConfig configOf(HrcContext c) {
     LaunchConfig lc{}; lc.smCount = c->smCount; lc.traceBlocksPerSM = 8; lc.traceThreads = 128; lc.collectStats = c->counters;
     lc.refillIdle = c->tuneRefillIdle; lc.refillIdleAny = c->tuneRefillIdleAny; lc.traceBlocksPerSM = c->tuneBlocksPerSM;
     lc.masked = c->anyMasked; lc.sortBits = c->tuneSortBits;
+    lc.tailRays = c->counters ? 0 : c->tuneTailRays;          // with traversal counters on every ray goes through the instrumented wavefront kernels
     lc.shadeMiss = c->lights.envEnabled != 0; lc.shadePbr = c->anyPbr; lc.shadeGlass = c->anyGlass;
     return lc;
 }
@@ -315,14 +317,15 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     if (const char* e2 = std::getenv("HRC_TUNE_GRAPHS")) c->useGraphs = std::atoi(e2) != 0;      // 0: launch every kernel of a pass individually (experiments)
     if (cudaMallocHost(&c->frameRing, sizeof(DFrame) * kFrameRing) != cudaSuccess) { int r = fail(nullptr, HRC_ERR_OUT_OF_MEMORY, "pinned frame ring"); delete c; return r; }
     for (auto& ev : c->frameEv) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (const char* e2 = std::getenv("HRC_TUNE_TAIL_RAYS")) c->tuneTailRays = std::max(0, std::min(1 << 22, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_SORT_BITS")) c->tuneSortBits = std::max(0, std::min(kSortMaxBits, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_BLOCKS_PER_SM_PIPE")) c->tunePipelinedBlocksPerSM = std::max(1, std::min(16, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_PASS_LANES")) c->passLanes = std::max(1, std::min(kMaxLanes, std::atoi(e2)));   // 1: no overlap between passes
     cudaEventCreate(&c->evStart); cudaEventCreate(&c->evStop); cudaEventCreate(&c->evTimer0); cudaEventCreate(&c->evTimer1);
-    cudaMalloc(&c->pb.ctrl, sizeof(IterCtrl) * kMaxIterations);
+    cudaMalloc(&c->pb.ctrl, sizeof(IterCtrl) * kCtrlEntries);
     cudaMalloc(&c->pb.stats, sizeof(DeviceStats));
     cudaMemsetAsync(c->pb.stats, 0, sizeof(DeviceStats), c->stream);
-    cudaMemsetAsync(c->pb.ctrl, 0, sizeof(IterCtrl) * kMaxIterations, c->stream);
+    cudaMemsetAsync(c->pb.ctrl, 0, sizeof(IterCtrl) * kCtrlEntries, c->stream);
     if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) { int r = failCuda(nullptr, e, "context setup"); delete c; return r; }
     std::memset(&c->globals, 0, sizeof(c->globals));
     c->globals.maxRayDepth = 5; c->globals.maxChannelValue = 3.14159265358979f;   // GlobalData defaults, PassGenerator.h:270-272
@@ -799,12 +802,19 @@ HRC_API int hrcSetGlobals(HrcContext c, const HrcGlobals* g) {
 static void issuePass(const DScene& sc, int slot, uint32_t total, const PassBuffers& pb, const LaunchConfig& lc, int iterations, bool overlap,
                       cudaStream_t s, cudaStream_t s2, const std::vector<cudaEvent_t>& evSync) {
     launchRaygen(sc, slot, total, pb, s);
+    const bool tail = lc.tailRays > 0;
+    if (tail && total <= (uint32_t)lc.tailRays) {         // a frame this small is all tail: the primary rays go straight to the path kernel
+        launchTailDecide(pb, 0, lc, s);
+        launchPathTail(sc, slot, pb, 0, iterations, lc, s);
+    }
     if (!overlap || iterations < 2) {
         for (int it = 0; it < iterations; ++it) {
             launchTraceClosest(sc, slot, pb, it, lc, s);
             launchShade(sc, slot, pb, it, lc, s);
+            if (tail && it + 1 < iterations) launchTailDecide(pb, it + 1, lc, s);
             if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
             launchTraceAny(sc, slot, pb, it, lc, s);
+            if (tail && it + 1 < iterations) launchPathTail(sc, slot, pb, it + 1, iterations, lc, s);
         }
     } else {
         // Occlusion rays of iteration i and extension rays of iteration i+1 are independent (both were emitted by shade(i)):
@@ -814,10 +824,14 @@ static void issuePass(const DScene& sc, int slot, uint32_t total, const PassBuff
             launchTraceClosest(sc, slot, pb, it, lc, s);
             if (it > 0) cudaStreamWaitEvent(s, evSync[2 * (it - 1) + 1], 0);
             launchShade(sc, slot, pb, it, lc, s);
+            if (tail && it + 1 < iterations) launchTailDecide(pb, it + 1, lc, s);
             cudaEventRecord(evSync[2 * it], s);
             if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
             cudaStreamWaitEvent(s2, evSync[2 * it], 0);
             launchTraceAny(sc, slot, pb, it, lc, s2);
+            // the path kernel accumulates into the pixels any(it) writes: behind it on the second stream, and shade(it + 1) (a no-op once the
+            // tail is taken) waits for both
+            if (tail && it + 1 < iterations) launchPathTail(sc, slot, pb, it + 1, iterations, lc, s2);
             cudaEventRecord(evSync[2 * it + 1], s2);
         }
         cudaStreamWaitEvent(s, evSync[2 * (iterations - 1) + 1], 0);

@@ -520,15 +520,16 @@ struct Traversal {
 };
 
 // Plain per-thread traversal (the hrcTraceRays parity hook): same steps, no warp scheduling.
-template <bool ANY>
-__device__ __forceinline__ void traverseSimple(const float4* __restrict__ nodes, const float4* __restrict__ tris, Traversal& tr) {
+// Returns true when an any-hit ray stopped at an occluder.
+template <bool ANY, bool MASKED = false>
+__device__ __forceinline__ bool traverseSimple(const float4* __restrict__ nodes, const float4* __restrict__ tris, Traversal& tr) {
     HR_DECLARE_TRACE_STACK(stack);
     TraceCounters tc{0u, 0u, 0u};
     for (;;) {
         if (tr.hasNodeWork()) tr.nodeStep<false, ANY>(nodes, stack, tc);
-        while (tr.tri.y) if (tr.triStep<ANY, false, false>(tris, tc)) return;
+        while (tr.tri.y) if (tr.triStep<ANY, false, MASKED>(tris, tc)) return true;
         tr.popIfEmpty(stack);
-        if (tr.finished()) return;
+        if (tr.finished()) return false;
     }
 }
 
@@ -537,7 +538,7 @@ __device__ __forceinline__ void traverseSimple(const float4* __restrict__ nodes,
 // ---------------------------------------------------------------------------------------
 __global__ void k_clear_ctrl(IterCtrl* ctrl) {
     int i = threadIdx.x;
-    if (i < kMaxIterations) ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};
+    if (i < kCtrlEntries) ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};
 }
 
 // perspective.rlsl:39-93 — one thread per pixel of this context's screen bands.
@@ -617,6 +618,29 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const int slot,
 // warp-synchronous point: finished rays are appended to the per-material-class index lists (one atomic per warp per
 // class: the compaction that lets each shade kernel run one material) and the idle lanes pull fresh rays from the queue
 // (one atomic per warp) while the other lanes keep their traversal state.
+// An occlusion ray found no occluder on its way, but an alpha-masked (non-occluder) surface, tr.bestPrim: physicallyBased.rlsl:70-90
+// (policy A-5). Returns true when the surface lets the ray through (tr then holds the continuation ray behind it, extraT the
+// distance travelled so far, :80-84); false when the ray is shadowed (:88-90).
+__device__ __forceinline__ bool maskedSurfaceStep(const DScene& sc, Traversal& tr, float& extraT, int& maskedPasses) {
+    const int prim = tr.bestPrim & 0x0fffffff;
+    const float4* sp = sc.shade + (size_t)prim * 4;
+    const int mat = __float_as_int(__ldg(sp).w);
+    const uint32_t tf = sc.materials[mat].typeFlags;
+    float alpha = 1.0f;
+    if ((tf & 0xfu) == HRC_MATERIAL_PBR && ((tf >> 4) & HRC_MAT_HAS_BASE_COLOR_TEXTURE) && sc.attr) {
+        Surface sv; loadVaryings(sc, prim, tr.bestU, tr.bestV, false, false, sv);
+        alpha = sampleMaterialTexture(sc, sc.materials[mat].baseColorTex, sv.uv).w;
+    }
+    if ((tf & 0xfu) == HRC_MATERIAL_PBR && ((tf >> 4) & HRC_MAT_ALPHA_MASK) && alpha < 1.0f && maskedPasses < kMaxMaskedSurfaces) {
+        Surface sv; sv.P = tr.o + tr.d * tr.bestT; sv.Ng = xyz(__ldg(sp + 3));
+        const float t = tr.bestT;
+        extraT += t; ++maskedPasses;                                     // :84
+        tr.begin(offsetOrigin(sv, tr.d), tr.d, 0.0f, tr.tmaxRay - t);    // :80
+        return true;
+    }
+    return false;
+}
+
 // Tried and measured slower on B200 (profiles/r01_v3_notes.md): parking leaf triangles in a per-lane ring and testing
 // them in warp-wide rounds (triangle-test lane utilisation doubled, node-step utilisation and scheduling overhead ate the
 // gain), and "one node step or one triangle per trip".
@@ -746,23 +770,9 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
             if (occluded) { active = false; break; }                       // any-hit: nothing to shade
             if (tr.finished()) {
                 if (ANY && MASKED && (tr.bestPrim & 0x0fffffff) != 0x0fffffff) {
-                    // No occluder on the way, but an alpha-masked (non-occluder) surface: physicallyBased.rlsl:70-90 (policy A-5).
-                    const int prim = tr.bestPrim & 0x0fffffff;
-                    const float4* sp = sc.shade + (size_t)prim * 4;
-                    const int mat = __float_as_int(__ldg(sp).w);
-                    const uint32_t tf = sc.materials[mat].typeFlags;
-                    float alpha = 1.0f;
-                    if ((tf & 0xfu) == HRC_MATERIAL_PBR && ((tf >> 4) & HRC_MAT_HAS_BASE_COLOR_TEXTURE) && sc.attr) {
-                        Surface sv; loadVaryings(sc, prim, tr.bestU, tr.bestV, false, false, sv);
-                        alpha = sampleMaterialTexture(sc, sc.materials[mat].baseColorTex, sv.uv).w;
-                    }
-                    if ((tf & 0xfu) == HRC_MATERIAL_PBR && ((tf >> 4) & HRC_MAT_ALPHA_MASK) && alpha < 1.0f && maskedPasses < kMaxMaskedSurfaces) {
-                        Surface sv; sv.P = tr.o + tr.d * tr.bestT; sv.Ng = xyz(__ldg(sp + 3));
-                        const float t = tr.bestT;
-                        extraT += t; ++maskedPasses;                                     // :84
+                    if (maskedSurfaceStep(sc, tr, extraT, maskedPasses)) {               // passes through: the ray goes on behind the surface
                         atomicAdd(&ctrl->maskedContinuations, 1u);
                         if (pb.rayCounts) atomicAdd(pb.rayCounts + (__float_as_uint(pb.shadow.w[rayIdx].w) & 0x00ffffffu), 1u);
-                        tr.begin(offsetOrigin(sv, tr.d), tr.d, 0.0f, tr.tmaxRay - t);    // :80
                         continue;
                     }
                     active = false;                                                      // :88-90 shadowed
@@ -778,6 +788,8 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                                                       : make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));
                     doneIdx = rayIdx;
                     doneClass = tr.found ? 1 + ((tr.bestPrim >> 28) & 3) : 0;
+                    if (pb.rayCounts && !tr.found && !fr.lights.envEnabled)     // parity hook: without an environment light no k_shade<0> runs to count the missed ray
+                        atomicAdd(pb.rayCounts + __float_as_uint(((iter & 1) ? pb.ext[1].wm : pb.ext[0].wm)[2 * (size_t)rayIdx].w), 1u);
                 }
                 break;
             }
@@ -1215,6 +1227,31 @@ __device__ __forceinline__ uint32_t raySortKey(const DScene& sc, float3 o, float
     return (oct << (3 * bits)) | spreadBits3(ix) | (spreadBits3(iy) << 1) | (spreadBits3(iz) << 2);
 }
 
+// The material shader of one hit: `hr` is the hit record k_trace<closest> writes (t, u, v, primitive | class << 28 | HRC_HIT_BACKFACE).
+// CLS 1: physicallyBased.rlsl, 2: glass.rlsl. One body for the wavefront's k_shade<CLS> and the path kernel k_path.
+template <int CLS>
+__device__ __forceinline__ void shadeHit(const DScene& sc, const DFrame& fr, float4* accum, const InRay& in, float4 hr, Emit& e) {
+    const int primBits = __float_as_int(hr.w);
+    const int prim = primBits & 0x0fffffff;
+    const bool back = (primBits & HRC_HIT_BACKFACE) != 0;
+    const float4* sp = sc.shade + (size_t)prim * 4;
+    const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2), s3 = __ldg(sp + 3);
+    Surface s;
+    s.P = in.o + in.d * hr.x;
+    s.Ng = xyz(s3);
+    s.T = hr.x;
+    const bool frontFacing = __float_as_int(s1.w) ? back : !back;   // policy A-10
+    const float bw = (1.0f - hr.y) - hr.z;
+    const float3 n = (xyz(s0) * bw + xyz(s1) * hr.y) + xyz(s2) * hr.z;
+    const DMaterial m = sc.materials[__float_as_int(s0.w)];
+    s.uv = make_float2(0.f, 0.f); s.tangent = f3(0.f); s.bitangent = f3(0.f); s.color = f3(0.f);
+    const uint32_t mflags = m.typeFlags >> 4;
+    if (sc.attr && (mflags & (kMatAnyTexture | HRC_MAT_VERTEX_COLORS)))
+        loadVaryings(sc, prim, hr.y, hr.z, (mflags & kMatTangentSpace) != 0, (mflags & HRC_MAT_VERTEX_COLORS) != 0, s);
+    if (CLS == 1) shadePBR(sc, fr, accum, in, m, s, n, frontFacing, e);
+    else          shadeGlass(sc, fr, accum, in, m, s, n, frontFacing, e);
+}
+
 template <int CLS>
 __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene sc, const int slot, PassBuffers pb, int iter, int sortBits) {
     const DFrame& fr = g_frames[slot];
@@ -1272,25 +1309,7 @@ __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene
                 const float4 ro = __ldcs(rq.od + 2 * i);
                 const float4 hr = __ldcs(pb.hits + i);
                 in.o = xyz(ro); in.tmax = ro.w;
-                const int primBits = __float_as_int(hr.w);
-                const int prim = primBits & 0x0fffffff;
-                const bool back = (primBits & HRC_HIT_BACKFACE) != 0;
-                const float4* sp = sc.shade + (size_t)prim * 4;
-                const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2), s3 = __ldg(sp + 3);
-                Surface s;
-                s.P = in.o + in.d * hr.x;
-                s.Ng = xyz(s3);
-                s.T = hr.x;
-                const bool frontFacing = __float_as_int(s1.w) ? back : !back;   // policy A-10
-                const float bw = (1.0f - hr.y) - hr.z;
-                const float3 n = (xyz(s0) * bw + xyz(s1) * hr.y) + xyz(s2) * hr.z;
-                const DMaterial m = sc.materials[__float_as_int(s0.w)];
-                s.uv = make_float2(0.f, 0.f); s.tangent = f3(0.f); s.bitangent = f3(0.f); s.color = f3(0.f);
-                const uint32_t mflags = m.typeFlags >> 4;
-                if (sc.attr && (mflags & (kMatAnyTexture | HRC_MAT_VERTEX_COLORS)))
-                    loadVaryings(sc, prim, hr.y, hr.z, (mflags & kMatTangentSpace) != 0, (mflags & HRC_MAT_VERTEX_COLORS) != 0, s);
-                if (CLS == 1) shadePBR(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
-                else          shadeGlass(sc, fr, pb.accum, in, m, s, n, frontFacing, e);
+                shadeHit<CLS>(sc, fr, pb.accum, in, hr, e);
                 if (e.hasExt && ((int)in.depth + 1 > hardCap || lastIter)) e.hasExt = false;
             }
         }
@@ -1326,6 +1345,88 @@ __global__ void __launch_bounds__(128, HR_SHADE_MIN_BLOCKS) k_shade(const DScene
                 atomicAdd(pb.sortHist + key, 1u);
             }
         }
+    }
+}
+
+// ---- tail of a pass: the remaining paths in one launch ---------------------------------
+// Late wavefront iterations hold a few thousand rays each and cost a fixed ~60-90 us of kernel boundaries (trace, three shade classes,
+// occlusion trace). k_tail_decide runs after shade(iter - 1): when the extension queue of iteration `iter` has come down to `threshold`
+// rays it hands them to k_path and marks the queue drained, so the wavefront kernels still to be launched (the launch sequence is fixed
+// when the pass graph is captured) pull nothing and return at once.
+__global__ void k_tail_decide(PassBuffers pb, int iter, uint32_t threshold) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    IterCtrl* tail = pb.ctrl + kMaxIterations;
+    if (tail->extCount) return;                                   // the tail of this pass has been handed over already
+    const uint32_t n = pb.ctrl[iter].extCount;
+    if (n == 0u || n > threshold) return;
+    tail->extCount = n; tail->extHead = (uint32_t)iter;
+    pb.ctrl[iter].extHead = kQueueDrained;                        // extCount stays: k_finish_pass counts these rays as before
+}
+
+// One thread per remaining path: what k_trace<closest>, k_shade<0..2> and k_trace<any> of iterations iter, iter + 1, ... would do for it, in
+// the same order (shade(i) accumulates, then the light shader of its occlusion ray, then shade(i + 1)), with the same device functions:
+// the pixel sums are bit-identical to the wavefront's. Rays stay in registers; only the counters and the pixels are written.
+template <bool MASKED>
+__global__ void __launch_bounds__(128, 3) k_path(const DScene sc, const int slot, const PassBuffers pb, int iter, int iterations) {
+    const IterCtrl* tail = pb.ctrl + kMaxIterations;
+    const uint32_t count = tail->extCount;
+    if (count == 0u || tail->extHead != (uint32_t)iter) return;
+    const DFrame& fr = g_frames[slot];
+    const RayQueue rq = (iter & 1) ? pb.ext[1] : pb.ext[0];
+    const float4* __restrict__ nodes = sc.nodes;
+    const float4* __restrict__ tris = sc.tris;
+    const int hardCap = fr.g.maxRayDepth + 16;                                // policy A-14
+    uint32_t extRays = 0, occRays = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const float4 ro = __ldcs(rq.od + 2 * (size_t)i), rd = __ldcs(rq.od + 2 * (size_t)i + 1), rw = __ldcs(rq.wm + 2 * (size_t)i), rm = __ldcs(rq.wm + 2 * (size_t)i + 1);
+        const uint32_t mx = __float_as_uint(rm.x);
+        InRay in;
+        in.o = xyz(ro); in.tmax = ro.w; in.d = xyz(rd); in.weight = xyz(rw); in.pixel = __float_as_uint(rw.w);
+        in.depth = mx & 0xffu; in.sequenceID = mx >> 16; in.sequenceIndexOffset = __float_as_int(rm.y);
+        uint32_t missKind = (mx >> 8) & 0xfu;
+        for (int it = iter;; ++it) {
+            Traversal tr;
+            tr.begin(in.o, in.d, 0.0f, in.tmax);
+            traverseSimple<false>(nodes, tris, tr);
+            Emit e; e.hasOcc = false; e.hasExt = false;
+            if (!tr.found) {
+                shadeMiss(sc, fr, pb.accum, in.pixel, missKind, 0u, in.d, in.weight, 0.0f, 0.0f);   // extension rays only miss into the environment
+            } else {
+                const float4 hr = make_float4(tr.bestT, tr.bestU, tr.bestV, __int_as_float(tr.bestPrim));
+                if (((tr.bestPrim >> 28) & 3) == 0) shadeHit<1>(sc, fr, pb.accum, in, hr, e);
+                else                                shadeHit<2>(sc, fr, pb.accum, in, hr, e);
+                if (e.hasExt && ((int)in.depth + 1 > hardCap || it + 1 >= kMaxIterations)) e.hasExt = false;
+            }
+            if (pb.rayCounts) atomicAdd(pb.rayCounts + in.pixel, 1u + (e.hasOcc ? 1u : 0u));
+            if (e.hasOcc) {                                        // k_trace<any>(it): the light shader runs when nothing occludes
+                ++occRays;
+                float extraT = 0.0f; int maskedPasses = 0;
+                tr.begin(e.occO, e.occD, 0.0f, e.occTmax);
+                bool lit;
+                for (;;) {
+                    if (traverseSimple<true, MASKED>(nodes, tris, tr)) { lit = false; break; }
+                    if (MASKED && (tr.bestPrim & 0x0fffffff) != 0x0fffffff) {
+                        if (maskedSurfaceStep(sc, tr, extraT, maskedPasses)) {
+                            ++occRays;
+                            if (pb.rayCounts) atomicAdd(pb.rayCounts + in.pixel, 1u);
+                            continue;
+                        }
+                        lit = false; break;
+                    }
+                    lit = true; break;
+                }
+                if (lit) shadeMiss(sc, fr, pb.accum, in.pixel, e.occMissKind, e.occMissIndex, tr.d, e.occW, tr.tmaxRay, extraT);
+            }
+            if (!e.hasExt || it + 1 >= iterations) break;          // rays emitted by the last iteration of the pass are not traced
+            ++extRays;
+            if (e.extMissKind != 0xffu) missKind = e.extMissKind;
+            in.o = e.extO; in.d = e.extD; in.weight = e.extW; in.tmax = __int_as_float(0x7f800000); in.depth += 1u;
+        }
+    }
+    for (int sft = 16; sft > 0; sft >>= 1) { extRays += __shfl_xor_sync(0xffffffffu, extRays, sft); occRays += __shfl_xor_sync(0xffffffffu, occRays, sft); }
+    if ((threadIdx.x & 31u) == 0u) {
+        if (extRays) atomicAdd(&pb.stats->raysExtension, (unsigned long long)extRays);
+        if (occRays) atomicAdd(&pb.stats->raysOcclusion, (unsigned long long)occRays);
     }
 }
 
@@ -1376,7 +1477,7 @@ __global__ void k_finish_pass(PassBuffers pb, int iterations, int rearm) {
     pb.stats->raysPrimary += pb.ctrl[0].extCount;
     pb.stats->raysExtension += ext;
     pb.stats->raysOcclusion += occ;
-    if (rearm) for (int i = 0; i < kMaxIterations; ++i) pb.ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};   // the next pass on these buffers starts without a clear kernel
+    if (rearm) for (int i = 0; i < kCtrlEntries; ++i) pb.ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};   // the next pass on these buffers starts without a clear kernel
 }
 
 // hrcTraceRays: the fixed-ray-set parity hook. Same node / triangle steps as the pass kernels.
@@ -1405,7 +1506,7 @@ __global__ void k_add_pixels(float4* accum, const float4* src, size_t n) {
 // ---------------------------------------------------------------------------------------
 // Launch wrappers
 // ---------------------------------------------------------------------------------------
-void launchClearCtrl(const PassBuffers& pb, cudaStream_t s) { k_clear_ctrl<<<1, kMaxIterations, 0, s>>>(pb.ctrl); }
+void launchClearCtrl(const PassBuffers& pb, cudaStream_t s) { k_clear_ctrl<<<1, 128, 0, s>>>(pb.ctrl); }
 
 void uploadFrame(const DFrame* pinnedFrame, int slot, cudaStream_t s) {
     cudaMemcpyToSymbolAsync(g_frames, pinnedFrame, sizeof(DFrame), (size_t)slot * sizeof(DFrame), cudaMemcpyHostToDevice, s);
@@ -1446,6 +1547,16 @@ void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cud
     const uint32_t bins = 8u << (3 * lc.sortBits);
     k_sort_scan<<<1, 1024, 0, s>>>(pb, iter, bins < 1024u ? 1024u : bins);
     k_sort_scatter<<<lc.smCount * 4, 256, 0, s>>>(pb, iter);
+}
+
+void launchTailDecide(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+    if (lc.tailRays > 0) k_tail_decide<<<1, 32, 0, s>>>(pb, iter, (uint32_t)lc.tailRays);
+}
+void launchPathTail(const DScene& sc, int slot, const PassBuffers& pb, int iter, int iterations, const LaunchConfig& lc, cudaStream_t s) {
+    if (lc.tailRays <= 0) return;
+    const int grid = (lc.tailRays + 127) / 128;                    // one thread per ray of the largest tail that is taken
+    if (lc.masked) k_path<true><<<grid, 128, 0, s>>>(sc, slot, pb, iter, iterations);
+    else           k_path<false><<<grid, 128, 0, s>>>(sc, slot, pb, iter, iterations);
 }
 
 void launchFinishPass(const PassBuffers& pb, int iterations, bool rearm, cudaStream_t s) { k_finish_pass<<<1, 32, 0, s>>>(pb, iterations, rearm ? 1 : 0); }
