@@ -638,7 +638,7 @@ def main():
                 "config": config_dict(spec, args.config, world, shard=shard, extra={"bvh_nodes": int(info.nodeCount), "bvh_build_s": float(info.buildSeconds),
                                                                  "scene_bytes": int(info.nodeBytes + info.triangleBytes + info.shadingBytes),
                                                                  "pass_pipelining": "value: the K passes are enqueued back to back (hrcEnqueuePass, the reference's offline mode) and rotate over %s sets of "
-                                                                                    "queues / accumulation buffers, so the latency-bound tail of a pass overlaps the head of the next; each lane replays its pass as one captured CUDA graph" % os.environ.get("HRC_TUNE_PASS_LANES", "4")}),
+                                                                                    "queues / accumulation buffers, so the latency-bound tail of a pass overlaps the head of the next; each lane replays its pass as one captured CUDA graph" % os.environ.get("HRC_TUNE_PASS_LANES", "8")}),
                 "rays_per_step_per_gpu": rays_total / K, "wall_ms_per_step": wall_ms / K, "timed_region_ms": dev_ms,
                 "clocks": clocks, "roofline": roof, "e2e": e2e,
                 "gpu_launches": launches + 3}       # + the lane joins (k_add_pixels) at the end of the timed region

@@ -8,7 +8,7 @@
 namespace hr {
 
 constexpr int kMaxIterations = 64;        // wavefront iterations per pass: maxRayDepth + 1 (+16 pass-through cap, policy A-14)
-constexpr int kMaxLanes = 4;              // hrcEnqueuePass rotates consecutive passes over up to this many sets of queues / accumulation buffers
+constexpr int kMaxLanes = 8;              // hrcEnqueuePass rotates consecutive passes over up to this many sets of queues / accumulation buffers
 constexpr int kDeferredLanes = 4;         // side lanes of hrcEnqueuePassDeferred: up to kDeferredLanes - 1 passes pending at a time
 constexpr int kTraceStack = 32;           // per-thread traversal stack entries (uint2)
 

@@ -62,7 +62,7 @@ struct HrcContext_t {
     std::vector<GraphEntry> graphs;        // captured passes of the main lane
     bool useGraphs = true; uint64_t graphClock = 0;
     DFrame* frameRing = nullptr; cudaEvent_t frameEv[kFrameRing] = {}; bool frameUsed[kFrameRing] = {}; int frameNext = 0;
-    int passLanes = 4, nextLane = 0;
+    int passLanes = 8, nextLane = 0;
     // Deferred passes (hrcEnqueuePassDeferred): rendered into side lanes that joins ignore until hrcCommitDeferred, so a caller can
     // already render passes i+1 .. i+3 while pass i is being read back (hr::PassGenerator does that when its next job is queued).
     // A ring: the deferredCount lanes before deferredNext are pending, oldest first; one lane more than may be pending, so the lane

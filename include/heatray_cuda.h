@@ -273,7 +273,7 @@ typedef struct HrcPassStats {
 HRC_API int hrcRenderPass(HrcContext ctx, const HrcFrameParams* frame, HrcPassStats* stats);
 /* Asynchronous variant: enqueue only (no host sync, no stats read-back). hrcSynchronize() waits.
  * hrcGetStats() returns the totals accumulated since the last hrcResetStats().
- * Consecutive enqueued passes are pipelined: they rotate over up to 4 internal sets of queues and accumulation buffers so that the
+ * Consecutive enqueued passes are pipelined: they rotate over up to 8 internal sets of queues and accumulation buffers so that the
  * latency-bound last bounces of one pass overlap the start of the next (passes are independent given sampleIndex and the result is
  * a sum, accumulator.rlsl:27). Every other entry point folds those buffers into the one the caller sees first, so this is not
  * observable except through fp32 addition order; the result is deterministic for a given sequence of calls. */
