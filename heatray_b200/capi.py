@@ -228,7 +228,7 @@ BACKEND_SYMBOLS = [
     "CreateContext", "DestroyContext", "SetOption", "GetLastError", "Resize", "Clear", "ReadPixels", "ReleasePixels", "AddPixels", "GetDevicePixels", "Resolve",
     "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "SetMeshTransform", "ClearScene", "CommitScene",
     "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetInteractiveBlocks", "SetGlobals",
-    "RenderPass", "EnqueuePass", "EnqueuePassDeferred", "CommitDeferred", "DiscardDeferred", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo", "ReadRayCounts",
+    "RenderPass", "EnqueuePass", "EnqueuePassDeferred", "CommitDeferred", "DiscardDeferred", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo", "ReadRayCounts", "TraceRaysNoAlloc",
 ]
 
 _lib = None
@@ -573,6 +573,16 @@ class Backend:
         hits = np.zeros(r.shape[0], HIT_DTYPE)
         self._call("TraceRays", i32(r.shape[0]), _ptr(r), i32(int(any_hit)), _ptr(hits))
         return hits
+
+    def trace_rays_no_alloc(self, rays: np.ndarray, any_hit=False) -> np.ndarray:
+        """hrcTraceRaysNoAlloc: the same, staged in the library's static device array (at most NO_ALLOC_MAX_RAYS rays, no cudaMalloc)."""
+        r = np.ascontiguousarray(rays, RAY_DTYPE)
+        hits = np.zeros(r.shape[0], HIT_DTYPE)
+        self._call("TraceRaysNoAlloc", i32(r.shape[0]), _ptr(r), i32(int(any_hit)), _ptr(hits))
+        return hits
+
+
+NO_ALLOC_MAX_RAYS = 262144
 
 
 # ---- images (host_image.cpp) --------------------------------------------------------------------

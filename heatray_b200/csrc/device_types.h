@@ -145,6 +145,9 @@ void launchPathTail(const DScene& sc, int slot, const PassBuffers& pb, int iter,
 void launchFinishPass(const PassBuffers& pb, int iterations, bool rearm, cudaStream_t s);   // rearm: also zero the control words for the next pass
 void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, bool anyHit, const LaunchConfig& lc, cudaStream_t s);
 void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s);
+// hrcTraceRaysNoAlloc: staging buffers for up to kNoAllocMaxRays rays / hits inside a static __device__ array (kernels.cu); `device` must be current.
+constexpr int kNoAllocMaxRays = HRC_NO_ALLOC_MAX_RAYS;
+cudaError_t traceScratchBuffers(int device, HrcRay** rays, HrcHit** hits);
 void launchResolve(const float4* accum, const HrcPostProcess& post, int format, int w, int h, void* out, cudaStream_t s);   // resolve.cu
 
 } // namespace hr

@@ -1,5 +1,6 @@
 // hrc_api.cu — implementation of the backend C-ABI (include/heatray_cuda.h) over CUDA device memory.
 // Reference-side counterparts are cited in the header next to each entry point.
+#include <mutex>
 #include "device_types.h"
 #include "bvh_builder.h"
 
@@ -1149,6 +1150,28 @@ HRC_API int hrcTraceRays(HrcContext c, int32_t n, const HrcRay* rays, int32_t an
     e = cudaStreamSynchronize(c->stream);
     cudaFree(dr); cudaFree(dh);
     if (e != cudaSuccess) return failCuda(c, e, "hrcTraceRays");
+    return HRC_OK;
+}
+
+// hrcTraceRays without allocations (include/heatray_cuda.h): rays and hits are staged in the library's static device array.
+static std::mutex g_noAllocCallMutex;      // one call at a time per process: the array is shared by every context on a device
+HRC_API int hrcTraceRaysNoAlloc(HrcContext c, int32_t n, const HrcRay* rays, int32_t anyHit, HrcHit* hits) {
+    if (!c) return fail(nullptr, HRC_ERR_INVALID_VALUE, "null context");
+    if (!c->committed) return fail(c, HRC_ERR_INVALID_OPERATION, "trace without a committed scene");
+    if (n < 0 || (n && (!rays || !hits))) return fail(c, HRC_ERR_INVALID_VALUE, "bad ray buffers");
+    if (n > HRC_NO_ALLOC_MAX_RAYS) return fail(c, HRC_ERR_INVALID_VALUE, "hrcTraceRaysNoAlloc takes at most HRC_NO_ALLOC_MAX_RAYS (262144) rays per call: split the set or use hrcTraceRays");
+    if (n == 0) return HRC_OK;
+    cudaSetDevice(c->device);
+    std::lock_guard<std::mutex> lock(g_noAllocCallMutex);
+    HrcRay* dr = nullptr; HrcHit* dh = nullptr;
+    cudaError_t e = traceScratchBuffers(c->device, &dr, &dh);
+    if (e != cudaSuccess) return failCuda(c, e, "cudaGetSymbolAddress of the static trace scratch");
+    CU(c, cudaMemcpyAsync(dr, rays, (size_t)n * sizeof(HrcRay), cudaMemcpyHostToDevice, c->stream));
+    launchTraceRays(sceneOf(c), dr, dh, n, anyHit != 0, configOf(c), c->stream);
+    CU(c, cudaMemcpyAsync(hits, dh, (size_t)n * sizeof(HrcHit), cudaMemcpyDeviceToHost, c->stream));
+    e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) return failCuda(c, e, "hrcTraceRaysNoAlloc");
     return HRC_OK;
 }
 

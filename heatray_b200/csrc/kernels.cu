@@ -9,6 +9,7 @@
 //                   brdfs.rlsl, lightSampling.rlsl, utility.rlsl, sequence.rlsl, accumulator.rlsl)
 //
 // No tensor cores: this is pointer chasing + fp32 ALU, bound by the memory system.
+#include <mutex>
 #include "device_types.h"
 
 #include <cuda_fp16.h>
@@ -1565,6 +1566,33 @@ void launchTraceRays(const DScene& sc, const HrcRay* rays, HrcHit* hits, int n, 
     if (n <= 0) return;
     if (anyHit) k_trace_rays<true><<<(n + 127) / 128, 128, 0, s>>>(sc, rays, hits, n);
     else        k_trace_rays<false><<<(n + 127) / 128, 128, 0, s>>>(sc, rays, hits, n);
+}
+
+// ---- hrcTraceRaysNoAlloc: the fixed-ray-set hook with its staging buffers in a static device array --------------------------------
+// hrcTraceRays stages the host rays / hits in device buffers it allocates per call; callers that must not allocate (see the header)
+// get the same kernel over this array instead. One array per GPU that loads the library, held until the process exits:
+// kNoAllocMaxRays * (32 B ray + 16 B hit) = 12 MiB. Every call on a device shares it.
+namespace {
+static __device__ __align__(256) unsigned char g_traceScratch[(size_t)kNoAllocMaxRays * (sizeof(HrcRay) + sizeof(HrcHit))];
+constexpr int kScratchDevices = 64;
+std::mutex g_scratchMutex;
+unsigned char* g_scratchAddr[kScratchDevices] = {};      // device address of g_traceScratch on each device, resolved on first use
+}
+
+// In host code `g_traceScratch` is only the host-side handle of the symbol, never a device address: the address the kernel needs comes
+// from cudaGetSymbolAddress, per device, with that device current (the caller has made `device` current).
+cudaError_t traceScratchBuffers(int device, HrcRay** rays, HrcHit** hits) {
+    if (device < 0 || device >= kScratchDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_scratchMutex);
+    if (!g_scratchAddr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_traceScratch);
+        if (e != cudaSuccess) return e;
+        g_scratchAddr[device] = static_cast<unsigned char*>(p);
+    }
+    *rays = reinterpret_cast<HrcRay*>(g_scratchAddr[device]);
+    *hits = reinterpret_cast<HrcHit*>(g_scratchAddr[device] + (size_t)kNoAllocMaxRays * sizeof(HrcRay));
+    return cudaSuccess;
 }
 
 void launchAddPixels(float4* accum, const float4* src, size_t n, cudaStream_t s) {

@@ -299,6 +299,15 @@ typedef struct HrcHit { float t, u, v; int32_t primId; /* -1 = miss; bit 30 set 
 #define HRC_HIT_BACKFACE 0x40000000
 /* Closest hit (anyHit = 0) or occlusion test (anyHit = 1: primId = 0 if occluded else -1) for n host rays. */
 HRC_API int hrcTraceRays(HrcContext ctx, int32_t n, const HrcRay* rays, int32_t anyHit, HrcHit* hits);
+/* hrcTraceRays for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * allocation). No counterpart in the reference. Same inputs, same outputs and the same
+ * kernel as hrcTraceRays, but the device-side staging of rays and hits lives in a static device array inside the library (12 MiB on
+ * every GPU that loads it, held until the process exits) instead of per-call allocations: the call allocates and frees nothing.
+ * Limit: n <= HRC_NO_ALLOC_MAX_RAYS, more is HRC_ERR_INVALID_VALUE. All calls on one GPU share the array, which keeps the last call's
+ * contents (nothing in it has to start at zero: every hit a call returns was written by that call). Host threads are serialised
+ * inside the call, and it returns after its work has finished; anything that makes two of these calls overlap on the GPU races. */
+#define HRC_NO_ALLOC_MAX_RAYS 262144
+HRC_API int hrcTraceRaysNoAlloc(HrcContext ctx, int32_t n, const HrcRay* rays, int32_t anyHit, HrcHit* hits);
 /* Rays per pixel since the last hrcClear (needs HRC_OPT_PIXEL_RAY_COUNTS): w*h counts, row 0 = bottom row like the accumulation buffer. */
 HRC_API int hrcReadRayCounts(HrcContext ctx, uint32_t* hostOut);
 /* Scene facts after commit. */
