@@ -261,6 +261,10 @@ class Rig:
             self.acc = torch.as_tensor(_Arr(), device=f"cuda:{local_rank}")
             self.red = torch.empty_like(self.acc)                 # the exchange step of the e2e region works on a copy: the local sum keeps growing
             self.host = torch.empty(self.acc.shape, dtype=self.acc.dtype, pin_memory=True) if rank == 0 else None
+        self.peer = None
+        if world > 1 and self.collective() == "peer":
+            from heatray_b200 import sharding
+            self.peer = sharding.PeerExchange(lib, local_rank, rank, world, spec.height, spec.width)
         self.ev0, self.ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def sidx(self, step):
@@ -283,12 +287,25 @@ class Rig:
     def collective(self):
         return os.environ.get("HR_BENCH_COLLECTIVE", "reduce")
 
+    def combined(self, buf=None):
+        """Rank 0: where the exchanged frame is (the peer exchange has its own result buffer, the NCCL collectives work in place)."""
+        return self.peer.result() if self.peer else (self.acc if buf is None else buf)
+
     def exchange_async(self, buf):
-        """Enqueues the collective on torch's current stream (no host wait). HR_BENCH_COLLECTIVE: reduce (default: fp32 sum onto rank 0; for bands the
-        other ranks' rows are zeros, so the sum is exact), all_reduce, gather (band mode: each rank sends only its own rows)."""
+        """Enqueues the exchange on torch's current stream (no host wait). HR_BENCH_COLLECTIVE: reduce (default: NCCL fp32 sum onto rank 0, in-switch
+        reduction on NVSwitch; for bands the other ranks' rows are zeros, so the sum is exact), all_reduce, gather (band mode: each rank sends only its own
+        rows), or peer: ONE own kernel per rank over NVLink peer memory (hrcExchangeSum / hrcExchangeBands, csrc/peer_exchange.cu). Measured back to back at
+        8 ranks (profiles/r02_notes.md): 33 MB reduce 72 us, peer sum 130 us, peer bands 71 us; 133 MB reduce 221, peer bands 195 us."""
         import torch.distributed as dist
         from heatray_b200 import sharding
         kind = self.collective()
+        if self.peer:
+            stream = self.torch.cuda.current_stream().cuda_stream
+            if self.bands:
+                self.peer.bands(buf.data_ptr(), BAND_ROWS, stream)
+            else:
+                self.peer.sum(buf.data_ptr(), stream)
+            return
         if self.bands and kind == "gather":
             sharding.gather_bands(buf, BAND_ROWS, self.rank, self.world, dst=0)
         elif kind == "all_reduce":
@@ -297,6 +314,9 @@ class Rig:
             dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)
 
     def close(self):
+        if self.peer:
+            self.peer.status()
+            self.peer.close()
         self.b.close()
 
 
@@ -334,7 +354,7 @@ def exchange_check(rig, barrier, passes_per_rank=4):
     rig.exchange()
     out = None
     if rig.rank == 0:
-        multi = rig.acc.clone()
+        multi = rig.combined().clone()
         b.clear()
         if rig.bands:
             r.set_band(0, 0, 1)
@@ -467,14 +487,17 @@ def main():
                     snap.record()
                     rig.exchange_async(rig.red)
                     if rank == 0:
-                        rig.host.copy_(rig.red, non_blocking=True)
+                        rig.host.copy_(rig.combined(rig.red), non_blocking=True)
                     pending = torch.cuda.Event(); pending.record()
                 snap.synchronize()                # the next pass may write the accumulation buffer once the snapshot is taken
             elif world > 1:
-                rig.red.copy_(rig.acc)
-                rig.exchange(rig.red)
+                if rig.peer:
+                    rig.exchange(rig.acc)
+                else:
+                    rig.red.copy_(rig.acc)
+                    rig.exchange(rig.red)
                 if rank == 0:
-                    rig.host.copy_(rig.red, non_blocking=True)
+                    rig.host.copy_(rig.combined(rig.red), non_blocking=True)
                     torch.cuda.synchronize()
                     total += float(rig.host[0, 0, 3])
             else:
@@ -548,6 +571,7 @@ def main():
 
     # ---- multi-GPU: correctness of the exchange on the hardware, and the strong-scaling case BASELINE.json names (configs[3] by bands) ----
     reduce_check = exchange_check(rig, barrier) if world > 1 else None
+    exchange_name = (rig.collective() + (" (one kernel per rank over NVLink peer memory: hrcExchangeSum / hrcExchangeBands)" if rig.peer else " (NCCL)")) if world > 1 else None
     strong = None
     if world > 1 and not args.no_strong and args.config != "terrain" and not args.small:
         rig.close()
@@ -644,7 +668,7 @@ def main():
                 "gpu_launches": launches + 3}       # + the lane joins (k_add_pixels) at the end of the timed region
         if world > 1:
             line["reduce_ms"] = reduce_ms
-            line["exchange"] = os.environ.get("HR_BENCH_COLLECTIVE", "reduce")
+            line["exchange"] = exchange_name
             line["reduce_check"] = reduce_check
             if strong:
                 line["strong"] = strong

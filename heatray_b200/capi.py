@@ -229,6 +229,7 @@ BACKEND_SYMBOLS = [
     "CreateTexture2D", "DestroyTexture", "CreateMaterial", "UpdateMaterial", "CreateMesh", "DestroyMesh", "SetMeshTransform", "ClearScene", "CommitScene",
     "SetEnvironment", "SetDirectionalLights", "SetPointLights", "SetSpotLights", "SetSequences", "SetPixelTables", "SetInteractiveBlocks", "SetGlobals",
     "RenderPass", "EnqueuePass", "EnqueuePassDeferred", "CommitDeferred", "DiscardDeferred", "Synchronize", "ResetStats", "TimerStart", "TimerStop", "GetStats", "TraceRays", "GetSceneInfo", "ReadRayCounts", "TraceRaysNoAlloc",
+    "ExchangeCreate", "ExchangeConnect", "ExchangeSum", "ExchangeBands", "ExchangeResult", "ExchangeStatus", "ExchangeDestroy", "ExchangeGetLastError",
 ]
 
 _lib = None
@@ -583,6 +584,7 @@ class Backend:
 
 
 NO_ALLOC_MAX_RAYS = 262144
+EXCHANGE_HANDLE_BYTES, EXCHANGE_MAX_RANKS = 192, 8
 
 
 # ---- images (host_image.cpp) --------------------------------------------------------------------

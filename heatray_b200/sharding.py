@@ -52,3 +52,69 @@ def gather_bands(acc, band_height: int, rank: int, world: int, dst: int = 0):
             if r != dst:
                 acc[rows[r]] = pieces[r][:len(rows[r])]
     return acc
+
+
+class PeerExchange:
+    """The exchange step as ONE kernel per rank over NVLink peer memory (csrc/peer_exchange.cu, hrcExchange* in include/heatray_cuda.h)
+    instead of an NCCL collective. torch.distributed is used once, to hand the CUDA-IPC handles round (plumbing); every later call
+    only enqueues a device copy and a kernel on the given CUDA stream.
+
+        ex = PeerExchange(lib, device, rank, world, height, width)        # collective: every rank constructs it
+        ex.sum(acc_ptr, stream)  /  ex.bands(acc_ptr, band_height, stream)  # collective: same number of calls on every rank
+        frame = ex.result()                                               # rank 0: (H, W, 4) fp32 torch view of the combined frame
+    """
+
+    def __init__(self, lib, device: int, rank: int, world: int, height: int, width: int):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        from . import capi
+        self.lib, self.rank, self.world, self.height, self.width, self.device = lib, rank, world, height, width, device
+        self._C = C
+        for name, args in (("hrcExchangeCreate", [C.c_int32, C.c_int32, C.c_int32, C.c_uint64, C.POINTER(C.c_void_p), C.c_void_p]),
+                           ("hrcExchangeConnect", [C.c_void_p, C.c_void_p]), ("hrcExchangeSum", [C.c_void_p, C.c_void_p, C.c_void_p]),
+                           ("hrcExchangeBands", [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]), ("hrcExchangeResult", [C.c_void_p, C.POINTER(C.c_void_p)]),
+                           ("hrcExchangeStatus", [C.c_void_p]), ("hrcExchangeDestroy", [C.c_void_p])):
+            getattr(lib, name).argtypes = args
+            getattr(lib, name).restype = C.c_int
+        lib.hrcExchangeGetLastError.argtypes = [C.c_void_p]
+        lib.hrcExchangeGetLastError.restype = C.c_char_p
+        self.ex = C.c_void_p()
+        handle = (C.c_uint8 * capi.EXCHANGE_HANDLE_BYTES)()
+        self._check(lib.hrcExchangeCreate(device, rank, world, height * width, C.byref(self.ex), handle), created=False)
+        if world > 1:
+            gathered = [None] * world
+            dist.all_gather_object(gathered, bytes(handle))
+            blob = b"".join(gathered)
+            self._check(lib.hrcExchangeConnect(self.ex, C.c_char_p(blob)))
+            dist.barrier()                                    # every rank has mapped every peer before the first exchange
+        self._result = None
+        if rank == 0:
+            p = C.c_void_p()
+            self._check(lib.hrcExchangeResult(self.ex, C.byref(p)))
+
+            class _Arr:
+                __cuda_array_interface__ = {"shape": (height, width, 4), "typestr": "<f4", "data": (p.value, False), "version": 2}
+            self._result = torch.as_tensor(_Arr(), device=f"cuda:{device}")
+
+    def _check(self, rc, created=True):
+        if rc != 0:
+            from . import capi
+            raise capi.HrcError(rc, (self.lib.hrcExchangeGetLastError(self.ex if created else None) or b"").decode())
+
+    def sum(self, src_ptr: int, stream: int = 0):
+        self._check(self.lib.hrcExchangeSum(self.ex, self._C.c_void_p(src_ptr), self._C.c_void_p(stream)))
+
+    def bands(self, src_ptr: int, band_height: int, stream: int = 0):
+        self._check(self.lib.hrcExchangeBands(self.ex, self._C.c_void_p(src_ptr), self.width, band_height, self._C.c_void_p(stream)))
+
+    def result(self):
+        return self._result
+
+    def status(self):
+        self._check(self.lib.hrcExchangeStatus(self.ex))
+
+    def close(self):
+        if self.ex:
+            self.lib.hrcExchangeDestroy(self.ex)
+            self.ex = None

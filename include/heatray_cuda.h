@@ -102,6 +102,31 @@ HRC_API int hrcAddPixels(HrcContext ctx, const float* rgba);
 /* Device pointer of the accumulation buffer (w*h float4), for NCCL reduce without staging. */
 HRC_API int hrcGetDevicePixels(HrcContext ctx, void** devPtr);
 
+/* ---- multi-GPU frame exchange over NVLink peer memory (no reference equivalent) ----
+ * One process per GPU renders its share (sample indices or screen bands); the frames are combined on rank 0 by ONE kernel launch per rank
+ * that reads the peers' snapshots / writes rank 0's result directly through peer mappings (csrc/peer_exchange.cu): no NCCL call, no host
+ * synchronisation. Set-up: every rank calls hrcExchangeCreate and hands its HRC_EXCHANGE_HANDLE_BYTES of CUDA-IPC handles to all others
+ * through whatever process group the caller has (torch.distributed all_gather in heatray_b200/sharding.py), then hrcExchangeConnect with
+ * all of them in rank order. Every rank must then call hrcExchangeSum / hrcExchangeBands the same number of times, like any collective;
+ * the calls only enqueue work on `cudaStream` (a cudaStream_t, NULL = the default stream). On rank 0 the combined frame is complete in the
+ * buffer hrcExchangeResult returns once that stream has run the call. */
+typedef struct HrcExchange_t* HrcExchange;
+#define HRC_EXCHANGE_MAX_RANKS 8
+#define HRC_EXCHANGE_HANDLE_BYTES 192
+HRC_API int hrcExchangeCreate(int32_t device, int32_t rank, int32_t world, uint64_t float4Count, HrcExchange* out, uint8_t* handleOut);
+HRC_API int hrcExchangeConnect(HrcExchange ex, const uint8_t* allHandles /* world * HRC_EXCHANGE_HANDLE_BYTES */);
+/* Sample-index sharding: result = sum over the ranks, in rank order, of `srcDevice` (float4Count float4 on this rank's GPU, e.g. hrcGetDevicePixels).
+ * The call copies `srcDevice` into its own exported snapshot buffer first, in stream order: the caller may go on writing it afterwards. */
+HRC_API int hrcExchangeSum(HrcExchange ex, const float* srcDevice, void* cudaStream);
+/* Screen-band sharding: row y of the result comes from rank (y / bandHeight) % world (bit-identical to a single-GPU frame). Each rank's kernel reads its
+ * rows straight from `srcDevice` (no snapshot: nobody else reads it), which must stay unchanged until `cudaStream` has run the call. */
+HRC_API int hrcExchangeBands(HrcExchange ex, const float* srcDevice, int32_t width, int32_t bandHeight, void* cudaStream);
+HRC_API int hrcExchangeResult(HrcExchange ex, const float** devicePtr);   /* rank 0 only */
+/* Waits for the device and reports a peer that never arrived / finished (the kernel's spins are bounded, ~3 s). */
+HRC_API int hrcExchangeStatus(HrcExchange ex);
+HRC_API int hrcExchangeDestroy(HrcExchange ex);
+HRC_API const char* hrcExchangeGetLastError(HrcExchange ex);
+
 /* ---- resolve + colour pipeline (↔ displayGL.frag:28-151 drawn by HeatrayRenderer.h:228-262, and the
  * screenshot paths of HeatrayRenderer::saveScreenshot, HeatrayRenderer.cpp:1619-1662). The reference runs this as a
  * GL fragment shader over the window; here it is one CUDA kernel over the accumulation buffer (no graphics API). */
