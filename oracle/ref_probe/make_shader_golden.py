@@ -35,5 +35,21 @@ def main():
     print(path, path.stat().st_size, "bytes,", len(digests), "groups")
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and "--vertex" not in sys.argv:
     main()
+
+
+def vertex_golden():
+    """tests/golden/vertex_ref.npz: vertex.rlsl compiled as C++ (oracle/_ref/libref_shaders.so::ref_vertex) on vertex_cases(SEED + 2, 400) per #define set."""
+    lib = loader.ref_lib("shaders")
+    cases = sp.vertex_cases(SEED + 2, 400)
+    out = {"digest": np.array(sp.input_digest(cases))}
+    for f in sp.VERTEX_VARIANTS:
+        out[f"vertex_{f}"] = sp.ref_vertex(lib, f, cases)
+    path = ROOT / "tests" / "golden" / "vertex_ref.npz"
+    np.savez_compressed(path, **out)
+    print(path, path.stat().st_size, "bytes")
+
+
+if __name__ == "__main__" and "--vertex" in sys.argv:
+    vertex_golden()

@@ -79,6 +79,8 @@ void collect(OrcShadeResult& out) {
 
 typedef void (*MaterialRun)(const void* params, const OrcShadeCase& c, int sampleIndex);
 struct MaterialVariant { uint32_t flags; MaterialRun run; };
+typedef void (*VertexRun)(const OrcVertexCase& c, OrcVertexResult& o);
+struct VertexVariant { uint32_t flags; VertexRun run; };
 
 namespace frame_shader {
 #define PROGRAM_KIND 0
@@ -172,4 +174,10 @@ REF_API void ref_miss(int n, const OrcProbeRay* rays, OrcShadeResult* results) {
 // Frame shader for pixels xy[2i], xy[2i+1] of a w x h frame.
 REF_API void ref_raygen(const HrcFrameParams* fp, int w, int h, int n, const int32_t* xy, OrcShadeResult* results) {
     for (int i = 0; i < n; ++i) { frame_shader::run(*fp, w, h, xy[2 * i], xy[2 * i + 1]); collect(results[i]); }
+}
+// vertex.rlsl for vertices of one #define set (bit 1 HAS_TEXTURES, 2 USE_TANGENT_SPACE, 4 VERTEX_COLORS); -1 when that set was not compiled.
+REF_API int ref_vertex(uint32_t flags, int n, const OrcVertexCase* cases, OrcVertexResult* results) {
+    for (const VertexVariant& v : kVertexVariants)
+        if (v.flags == flags) { for (int i = 0; i < n; ++i) v.run(cases[i], results[i]); return 0; }
+    return -1;
 }

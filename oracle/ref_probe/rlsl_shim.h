@@ -77,6 +77,7 @@ static vec3 rl_IntersectionPoint;
 static float rl_IntersectionT;
 static bool rl_FrontFacing;
 static vec4 rl_FrameCoord, rl_FrameSize;
+static vec4 rl_Position;                             // vertex shaders
 static bool rl_isFrameShader = false;
 static std::vector<RLRay> rl_emitted;
 static std::vector<RLAccum> rl_accumulated;

@@ -11,6 +11,7 @@ never into the repository. Shader arithmetic is not touched; every rewrite is li
   T name[1];  (inside a block)    ->  const T* name;          (OpenRL blocks end in an unsized array; the host binds a buffer)
   uniform T name;                 ->  static T name;
   varying T name;                 ->  static T name;
+  attribute T name;               ->  static T name;          (vertex.rlsl)
   rayattribute T name;            ->  (dropped: the four attributes are members of the shim's Ray, rayAttributes.rlsl:8-11)
   out T name   (parameters)       ->  T& name
   void main() / void setup()      ->  static void rlsl_main() / static void rlsl_setup()
@@ -74,6 +75,7 @@ def rewrite(text: str, used: set[int]) -> str:
     text = re.sub(r"uniformblock\s+(\w+)\s*\{(.*?)\};", block, text, flags=re.S)
     text = re.sub(r"^uniform\s+", "static ", text, flags=re.M)
     text = re.sub(r"^varying\s+", "static ", text, flags=re.M)
+    text = re.sub(r"^attribute\s+", "static ", text, flags=re.M)
     text = re.sub(r"^rayattribute\s+[^;]*;", "", text, flags=re.M)
     text = re.sub(r"\bout\s+(vec[234]|float|int|primitive)\s+(\w+)", r"\1& \2", text)
     text = re.sub(r"^void\s+main\s*\(\s*\)", "static void rlsl_main()", text, flags=re.M)
@@ -118,6 +120,19 @@ def variants_text() -> str:
             out += [f"#undef {d}" for d in defs]
             out.append("}")
             table[kind].append((f, ns))
+    # vertex.rlsl under the #define sets Material::build hands the vertex shader (bit 1 HAS_TEXTURES, 2 USE_TANGENT_SPACE, 4 VERTEX_COLORS)
+    vtab = []
+    for f in (0, 1, 3, 4, 5, 7):
+        defs = [name for bit, name in ((1, "HAS_TEXTURES"), (2, "USE_TANGENT_SPACE"), (4, "VERTEX_COLORS")) if f & bit]
+        ns = f"vertex_{f}"
+        out.append(f"namespace {ns} {{")
+        out += [f"#define {d}" for d in defs]
+        out.append('#include "vertex.inc"')
+        out.append('#include "ref_vertex_program.inc"')
+        out += [f"#undef {d}" for d in defs]
+        out.append("}")
+        vtab.append((f, ns))
+    out.append("static const VertexVariant kVertexVariants[] = {" + ", ".join(f"{{{f}u, {ns}::run}}" for f, ns in vtab) + "};")
     for kind, name in ((1, "kPbrVariants"), (2, "kGlassVariants")):
         out.append(f"static const MaterialVariant {name}[] = {{" + ", ".join(f"{{0x{f:x}u, {ns}::run}}" for f, ns in table[kind]) + "};")
     return "\n".join(out) + "\n"
@@ -127,7 +142,7 @@ def main() -> None:
     out = Path(sys.argv[1] if len(sys.argv) > 1 else "/tmp/hr_ref_shaders")
     out.mkdir(parents=True, exist_ok=True)
     used: set[int] = set()
-    for prog in ("perspective", "physicallyBased", "glass", "environmentLight", "directionalLight", "pointLight", "spotLight"):
+    for prog in ("perspective", "physicallyBased", "glass", "environmentLight", "directionalLight", "pointLight", "spotLight", "vertex"):
         (out / f"{prog}.inc").write_text(rewrite(load_program(prog + ".rlsl"), used))
     (out / "variants.inc").write_text(variants_text())
     stale = [PATCHES[i][0] for i in range(len(PATCHES)) if i not in used]

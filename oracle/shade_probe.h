@@ -36,4 +36,14 @@ typedef struct OrcShadeResult {
     float accumSum[4];                              /* sum of everything passed to accumulate(): rgb (+ a for the vec4 form) */
 } OrcShadeResult;
 
+/* vertex.rlsl:25-43: one vertex through the vertex program of a material (#define set as bits: 1 HAS_TEXTURES, 2 USE_TANGENT_SPACE, 4 VERTEX_COLORS). */
+typedef struct OrcVertexCase {
+    float worldFromEntity[16];                      /* column-major, like glm */
+    float position[3], normal[3], texCoord[2], tangent[3], bitangent[3], color[3];
+} OrcVertexCase;
+typedef struct OrcVertexResult {
+    float position[4];                              /* rl_Position */
+    float normal[3], texCoord[2], tangent[3], bitangent[3], color[3];      /* the varyings; zero where the #define set has none */
+} OrcVertexResult;
+
 #endif

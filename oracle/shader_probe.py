@@ -353,3 +353,47 @@ def input_digest(*arrays) -> str:
     for a in arrays:
         h.update(np.ascontiguousarray(a).tobytes())
     return h.hexdigest()
+
+
+# ---- vertex.rlsl (the geometry flattening of commitScene) ---------------------------------------------------------------------------
+VERTEX_CASE = np.dtype([("worldFromEntity", "<f4", (16,)), ("position", "<f4", (3,)), ("normal", "<f4", (3,)), ("texCoord", "<f4", (2,)),
+                        ("tangent", "<f4", (3,)), ("bitangent", "<f4", (3,)), ("color", "<f4", (3,))])
+VERTEX_RESULT = np.dtype([("position", "<f4", (4,)), ("normal", "<f4", (3,)), ("texCoord", "<f4", (2,)), ("tangent", "<f4", (3,)),
+                          ("bitangent", "<f4", (3,)), ("color", "<f4", (3,))])
+VERTEX_VARIANTS = [0, 1, 3, 4, 5, 7]          # bit 1 HAS_TEXTURES, 2 USE_TANGENT_SPACE, 4 VERTEX_COLORS (oracle/ref_probe/rlsl_to_cpp.py)
+
+
+def vertex_cases(seed: int, n: int) -> np.ndarray:
+    """Random vertices under random worldFromEntity matrices: rotations, non-uniform and negative scales, shears, large translations
+    (column-major, affine: last row 0 0 0 1 as every transform the reference builds)."""
+    rng = np.random.default_rng(seed)
+    c = np.zeros(n, VERTEX_CASE)
+    A = rng.normal(size=(n, 3, 3)) * rng.choice([0.01, 1.0, 100.0], size=(n, 1, 1))
+    q, _ = np.linalg.qr(rng.normal(size=(n, 3, 3)))
+    pure = rng.random(n) < 0.3
+    A[pure] = q[pure]                                             # some pure rotations / reflections
+    M = np.zeros((n, 4, 4))
+    M[:, :3, :3] = A
+    M[:, :3, 3] = rng.normal(size=(n, 3)) * rng.choice([0.0, 1.0, 1000.0], size=(n, 1))
+    M[:, 3, 3] = 1.0
+    c["worldFromEntity"] = M.transpose(0, 2, 1).reshape(n, 16).astype(np.float32)      # column-major
+    c["position"] = (rng.normal(size=(n, 3)) * rng.choice([1e-3, 1.0, 1e3], size=(n, 1))).astype(np.float32)
+    for k in ("normal", "tangent", "bitangent"):
+        v = rng.normal(size=(n, 3)); c[k] = (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+    c["texCoord"] = rng.uniform(-2, 3, (n, 2)).astype(np.float32)
+    c["color"] = rng.random((n, 3)).astype(np.float32)
+    return c
+
+
+def ref_vertex(lib, flags: int, cases: np.ndarray) -> np.ndarray:
+    out = np.zeros(len(cases), VERTEX_RESULT)
+    lib.ref_vertex.argtypes = [C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+    assert lib.ref_vertex(flags, len(cases), _p(cases), _p(out)) == 0, f"vertex.rlsl was not compiled for #define set {flags}"
+    return out
+
+
+def oracle_vertex(lib, flags: int, cases: np.ndarray) -> np.ndarray:
+    out = np.zeros(len(cases), VERTEX_RESULT)
+    lib.orcProbeVertex.argtypes = [C.c_uint32, C.c_int32, C.c_void_p, C.c_void_p]
+    assert lib.orcProbeVertex(flags, len(cases), _p(cases), _p(out)) == 0
+    return out

@@ -1,6 +1,6 @@
 """BASELINE.json configs #2, #3 and #4 at their FULL sizes (262 K / 496 K triangles at 1920x1080; 10 M triangles at 3840x2160; 8 bounces) on the GPU, checked through
 the oracle (image parity at the full frame size: two whole passes of #2 and #3 at 1920x1080, #4's full 10 M-triangle scene on a 960x540
-frame) and through size-independent properties:
+frame (two passes) and at its full 3840x2160 (one pass)) and through size-independent properties:
   * closest-hit IDs and t,u,v bit-exact against the oracle's BVH on random rays plus the secondary / occlusion rays of an oracle
     pass over a low-resolution frame of the SAME full scene;
   * progressive contract: alpha == pass count on every pixel, sums finite and bounded by passes * rays-per-pixel * maxChannelValue;
@@ -124,7 +124,7 @@ def _parity_report(pc, pg, rc, rg):
     return worst, frac, float((rc != rg).mean())
 
 
-@pytest.mark.parametrize("name,size,passes", [("config2_sphere_grid", (1920, 1080), 2), ("config3_material_grid", (1920, 1080), 2), ("config4_terrain", (960, 540), 2)])
+@pytest.mark.parametrize("name,size,passes", [("config2_sphere_grid", (1920, 1080), 2), ("config3_material_grid", (1920, 1080), 2), ("config4_terrain", (960, 540), 2), ("config4_terrain", (3840, 2160), 1)])
 def test_full_size_image_parity_vs_oracle(name, size, passes, lib, oracle_mod):
     """Whole passes of the full scenes on the CPU oracle (shading pinned bit for bit to the reference's shader text, tests/test_shader_pinning.py)
     and on the GPU. The sample counts are equal on every pixel; the colours differ only where the two libms' sin / cos / exp / atan2 differ in the

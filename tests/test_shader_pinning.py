@@ -182,3 +182,35 @@ def test_deviation_d1_second_extension_ray_without_environment(oracle_mod, lib, 
     sel = extra == 1
     trimmed["rays"][sel, 0] = ref["rays"][sel, 1]; trimmed["rays"][sel, 1] = 0; trimmed["rayCount"][sel] -= 1
     _assert_same(trimmed, orc, "all other outputs")
+
+
+# ---- vertex.rlsl: the geometry flattening ----------------------------------------------------------------------------------------------
+VERTEX_GOLD = Path(__file__).parent / "golden" / "vertex_ref.npz"
+SEED_VERTEX = 20261105 + 2
+
+
+def _same_vertices(ref, got, what):
+    for f in ref.dtype.names:
+        assert np.array_equal(ref[f].view(np.uint32), got[f].view(np.uint32)), f"{what}: {f} differs"
+
+
+def test_vertex_shader_matches_reference_golden(oracle_mod):
+    """vertex.rlsl:25-43 (rl_Position = worldFromEntity * vec4(p, 1); normal / tangent / bitangent = mat3(worldFromEntity) * v, quirk B-Q7: not the
+    inverse transpose) against the oracle's xformPoint / xformNormal, which commitScene applies to every vertex. Bar: bit for bit."""
+    gold = np.load(VERTEX_GOLD)
+    cases = sp.vertex_cases(SEED_VERTEX, 400)
+    assert sp.input_digest(cases) == str(gold["digest"]), "vertex_cases drifted: rerun oracle/ref_probe/make_shader_golden.py --vertex"
+    o = oracle_mod.load()
+    for f in sp.VERTEX_VARIANTS:
+        _same_vertices(gold[f"vertex_{f}"], sp.oracle_vertex(o, f, cases), f"#define set {f}")
+
+
+def test_vertex_shader_live(oracle_mod, ref_side):
+    cases = sp.vertex_cases(9, 200000)
+    o = oracle_mod.load()
+    for f in sp.VERTEX_VARIANTS:
+        ref = sp.ref_vertex(ref_side.lib, f, cases)
+        _same_vertices(ref, sp.oracle_vertex(o, f, cases), f"#define set {f}")
+        assert (ref["position"][:, 3] == 1.0).all()
+        if not f & 2:
+            assert not ref["tangent"].any() and not ref["bitangent"].any()
