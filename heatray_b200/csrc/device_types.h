@@ -54,6 +54,7 @@ struct DFrame {
     int32_t numSequences, sequenceLength;
     uint32_t offsetCount;
     int32_t interactiveMode, blockW, blockH, blockSampleX, blockSampleY, blocksX;   // perspective.rlsl:20-22,42-57
+    int32_t rayTileW, rayTileH;        // k_raygen: a warp's 32 primary rays cover a rayTileW x rayTileH pixel tile (0: 32 consecutive pixels of a row)
     DLights lights;
 };
 

@@ -75,6 +75,7 @@ struct HrcContext_t {
     int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
     bool devicePixelsExported = false;     // hrcGetDevicePixels handed the buffer out: the caller may write any row at any time (in-place NCCL reduce), so reads copy whole frames until hrcResize
     long long pinnedZeroKey = -1;          // which rows of the pinned frame may be non-zero: -1 any, 0 none (fresh), else the band set's key
+    int tuneRayTileW = 4;                  // HRC_TUNE_RAY_TILE_W: width of the pixel tile of a warp's 32 primary rays (8 -> 8 x 4, 4 -> 4 x 8, 0 -> a 32 x 1 strip)
     int tuneTailRays = 0;                  // HRC_TUNE_TAIL_RAYS: an iteration with at most this many extension rays hands the rest of the pass to k_path. Measured: no gain at any threshold (profiles/r02_notes.md), so 0 = off
     int tuneSortBits = 0;                  // HRC_TUNE_SORT_BITS: cells per axis (2^bits) of the coherence sort grid, 0 = off
     float sceneMin[3] = {0, 0, 0}, sceneMax[3] = {1, 1, 1};
@@ -318,6 +319,7 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     if (const char* e2 = std::getenv("HRC_TUNE_GRAPHS")) c->useGraphs = std::atoi(e2) != 0;      // 0: launch every kernel of a pass individually (experiments)
     if (cudaMallocHost(&c->frameRing, sizeof(DFrame) * kFrameRing) != cudaSuccess) { int r = fail(nullptr, HRC_ERR_OUT_OF_MEMORY, "pinned frame ring"); delete c; return r; }
     for (auto& ev : c->frameEv) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (const char* e2 = std::getenv("HRC_TUNE_RAY_TILE_W")) { const int v = std::atoi(e2); c->tuneRayTileW = (v == 2 || v == 4 || v == 8 || v == 16) ? v : 0; }
     if (const char* e2 = std::getenv("HRC_TUNE_TAIL_RAYS")) c->tuneTailRays = std::max(0, std::min(1 << 22, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_SORT_BITS")) c->tuneSortBits = std::max(0, std::min(kSortMaxBits, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_BLOCKS_PER_SM_PIPE")) c->tunePipelinedBlocksPerSM = std::max(1, std::min(16, std::atoi(e2)));
@@ -878,6 +880,9 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     fr.interactiveMode = fp->interactiveMode ? 1 : 0; fr.blockW = c->blockW; fr.blockH = c->blockH;
     fr.blockSampleX = fp->currentBlockPixelSample[0]; fr.blockSampleY = fp->currentBlockPixelSample[1]; fr.blocksX = c->blocksX;
     fr.lights = c->lights;
+    // tiles need whole tiles: frame width a multiple of the tile width, the context's rows a multiple of the tile height; interactive passes compact their rays anyway
+    const int tileW = c->tuneRayTileW, tileH = tileW > 0 ? 32 / tileW : 0;
+    if (tileW > 0 && !fr.interactiveMode && fr.w % tileW == 0 && fr.localRows % tileH == 0) { fr.rayTileW = tileW; fr.rayTileH = tileH; }
     if (fr.lights.envEnabled && fr.lights.envTex >= 0 && !c->textures[fr.lights.envTex].alive) return fail(c, HRC_ERR_INVALID_OPERATION, "environment texture was destroyed");
 
     const int iterations = fr.g.maxRayDepth + 1 + (c->anySingleSided ? 16 : 0);

@@ -552,7 +552,16 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene sc, const int slot,
     bool sampled = t < total;
     uint32_t pixel = 0; float fx = 0.f, fy = 0.f;
     if (sampled) {
-        const int lr = t / W, x = t - lr * W;
+        int lr = t / W, x = t - lr * W;
+        if (fr.rayTileW > 0) {
+            // ray t of the pass = pixel (t % 32) of tile (t / 32): the 32 rays a traversal warp pulls together start through one compact pixel tile
+            // instead of a 32 x 1 strip (narrower frustum: the warp's lanes walk the same nodes for longer). Which queue slot a pixel's ray sits in
+            // has no influence on the pixel's value (one path per pixel per pass).
+            const uint32_t tile = t >> 5, in = t & 31u, tilesX = (uint32_t)W / (uint32_t)fr.rayTileW;
+            const uint32_t ty = tile / tilesX, tx = tile - ty * tilesX;
+            x = (int)(tx * fr.rayTileW + in % (uint32_t)fr.rayTileW);
+            lr = (int)(ty * fr.rayTileH + in / (uint32_t)fr.rayTileW);
+        }
         int y = lr;
         if (fr.bandCount > 1) { const int lb = lr / fr.bandHeight; y = (lb * fr.bandCount + fr.bandIndex) * fr.bandHeight + (lr - lb * fr.bandHeight); }
         pixel = (uint32_t)y * W + x;
