@@ -72,7 +72,7 @@ struct ShadowQueue {
 };
 
 // Per-iteration control words, zeroed at the start of every pass.
-struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; uint32_t classCount[3]; uint32_t maskedContinuations; };   // class 0: miss, 1: PBR, 2: glass
+struct IterCtrl { uint32_t extCount, shadowCount, extHead, shadowHead; uint32_t classCount[3]; uint32_t maskedContinuations; uint32_t litCount; uint32_t pad[3]; };   // class 0: miss, 1: PBR, 2: glass; litCount: occlusion rays that reached their light
 // One more entry behind the per-iteration ones describes the pass's tail (k_tail_decide / k_path): extCount = rays the path kernel
 // takes over (0: the wavefront runs to its end), extHead = the iteration whose extension queue they sit in.
 constexpr int kCtrlEntries = kMaxIterations + 1;
@@ -116,6 +116,7 @@ struct PassBuffers {
     ShadowQueue shadow;
     float4* hits;             // t, u, v, primId | material class << 28 | HRC_HIT_BACKFACE  (-1: miss)
     uint32_t* classIdx[3];    // per-class lists of ray indices of the current iteration, filled by k_trace<closest>
+    uint32_t* litIdx;         // occlusion rays of the current iteration that reached their light, filled by k_trace<any> for k_shade_lights (nullptr: the light shaders run inside k_trace<any>)
     IterCtrl* ctrl;           // kCtrlEntries entries
     DeviceStats* stats;
     float4* accum;
@@ -138,6 +139,7 @@ void launchRaygen(const DScene& sc, int slot, uint32_t total, const PassBuffers&
 void launchTraceClosest(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
 void launchShade(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
 void launchTraceAny(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);
+void launchShadeLights(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);   // after launchTraceAny, same stream (no-op without pb.litIdx)
 void launchSortRays(const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s);   // orders the extension rays of iteration `iter` (emitted by shade(iter - 1))
 // Tail of a pass (lc.tailRays > 0): once an iteration's extension queue holds no more than lc.tailRays rays, ONE launch of k_path follows every
 // remaining path to its end (trace, shade, occlusion ray, next bounce, in registers) and the wavefront kernels behind it find their queues empty.

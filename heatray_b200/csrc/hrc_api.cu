@@ -75,6 +75,7 @@ struct HrcContext_t {
     int rbBandHeight = 0, rbBandIndex = 0, rbBandCount = 0; bool accumOutsideBandsZero = true;
     bool devicePixelsExported = false;     // hrcGetDevicePixels handed the buffer out: the caller may write any row at any time (in-place NCCL reduce), so reads copy whole frames until hrcResize
     long long pinnedZeroKey = -1;          // which rows of the pinned frame may be non-zero: -1 any, 0 none (fresh), else the band set's key
+    bool tuneDeferLights = true;           // HRC_TUNE_DEFER_LIGHTS: occlusion rays that reach their light are listed by k_trace<any> and shaded by k_shade_lights (0: inline in k_trace<any>)
     int tuneRayTileW = 4;                  // HRC_TUNE_RAY_TILE_W: width of the pixel tile of a warp's 32 primary rays (8 -> 8 x 4, 4 -> 4 x 8, 0 -> a 32 x 1 strip)
     int tuneTailRays = 0;                  // HRC_TUNE_TAIL_RAYS: an iteration with at most this many extension rays hands the rest of the pass to k_path. Measured: no gain at any threshold (profiles/r02_notes.md), so 0 = off
     int tuneSortBits = 0;                  // HRC_TUNE_SORT_BITS: cells per axis (2^bits) of the coherence sort grid, 0 = off
@@ -129,6 +130,7 @@ void destroyGraphs(HrcContext c) {
 void freeQueues(PassBuffers& pb) {
     for (int k = 0; k < 2; ++k) { freeDev(pb.ext[k].od); freeDev(pb.ext[k].wm); }
     for (int k = 0; k < 3; ++k) freeDev(pb.classIdx[k]);
+    freeDev(pb.litIdx);
     freeDev(pb.shadow.o); freeDev(pb.shadow.d); freeDev(pb.shadow.w); freeDev(pb.hits);
     freeDev(pb.sortKeys); freeDev(pb.sortOrder); freeDev(pb.sortHist); freeDev(pb.sortOffs); freeDev(pb.sortCtrl);
     pb.capacity = 0;
@@ -138,6 +140,7 @@ int allocQueues(HrcContext c, PassBuffers& pb, size_t n) {
         CU(c, cudaMalloc(&pb.ext[k].od, 2 * n * sizeof(float4))); CU(c, cudaMalloc(&pb.ext[k].wm, 2 * n * sizeof(float4)));
     }
     for (int k = 0; k < 3; ++k) CU(c, cudaMalloc(&pb.classIdx[k], n * sizeof(uint32_t)));
+    if (c->tuneDeferLights) CU(c, cudaMalloc(&pb.litIdx, n * sizeof(uint32_t)));
     CU(c, cudaMalloc(&pb.shadow.o, n * sizeof(float4))); CU(c, cudaMalloc(&pb.shadow.d, n * sizeof(float4)));
     CU(c, cudaMalloc(&pb.shadow.w, n * sizeof(float4))); CU(c, cudaMalloc(&pb.hits, n * sizeof(float4)));
     if (c->tuneSortBits > 0) {                       // coherence sort of the extension rays (device_types.h)
@@ -319,6 +322,7 @@ HRC_API int hrcCreateContext(const HrcContextDesc* desc, HrcContext* out) {
     if (const char* e2 = std::getenv("HRC_TUNE_GRAPHS")) c->useGraphs = std::atoi(e2) != 0;      // 0: launch every kernel of a pass individually (experiments)
     if (cudaMallocHost(&c->frameRing, sizeof(DFrame) * kFrameRing) != cudaSuccess) { int r = fail(nullptr, HRC_ERR_OUT_OF_MEMORY, "pinned frame ring"); delete c; return r; }
     for (auto& ev : c->frameEv) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (const char* e2 = std::getenv("HRC_TUNE_DEFER_LIGHTS")) c->tuneDeferLights = std::atoi(e2) != 0;
     if (const char* e2 = std::getenv("HRC_TUNE_RAY_TILE_W")) { const int v = std::atoi(e2); c->tuneRayTileW = (v == 2 || v == 4 || v == 8 || v == 16) ? v : 0; }
     if (const char* e2 = std::getenv("HRC_TUNE_TAIL_RAYS")) c->tuneTailRays = std::max(0, std::min(1 << 22, std::atoi(e2)));
     if (const char* e2 = std::getenv("HRC_TUNE_SORT_BITS")) c->tuneSortBits = std::max(0, std::min(kSortMaxBits, std::atoi(e2)));
@@ -817,6 +821,7 @@ static void issuePass(const DScene& sc, int slot, uint32_t total, const PassBuff
             if (tail && it + 1 < iterations) launchTailDecide(pb, it + 1, lc, s);
             if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
             launchTraceAny(sc, slot, pb, it, lc, s);
+            launchShadeLights(sc, slot, pb, it, lc, s);
             if (tail && it + 1 < iterations) launchPathTail(sc, slot, pb, it + 1, iterations, lc, s);
         }
     } else {
@@ -832,6 +837,7 @@ static void issuePass(const DScene& sc, int slot, uint32_t total, const PassBuff
             if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s);
             cudaStreamWaitEvent(s2, evSync[2 * it], 0);
             launchTraceAny(sc, slot, pb, it, lc, s2);
+            launchShadeLights(sc, slot, pb, it, lc, s2);
             // the path kernel accumulates into the pixels any(it) writes: behind it on the second stream, and shade(it + 1) (a no-op once the
             // tail is taken) waits for both
             if (tail && it + 1 < iterations) launchPathTail(sc, slot, pb, it + 1, iterations, lc, s2);
@@ -891,7 +897,10 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     if (pipelined) lc.traceBlocksPerSM = c->tunePipelinedBlocksPerSM;
     HrcContext_t::Lane* L = lane > 0 ? &c->extra[lane - 1] : lane < 0 ? &c->deferred[-lane - 1] : nullptr;      // lane < 0: deferred lane -lane-1
     const int slot = lane > 0 ? lane : lane < 0 ? kMaxLanes + (-lane - 1) : 0;
-    const PassBuffers& pb = L ? L->pb : c->pb;
+    PassBuffers pb = L ? L->pb : c->pb;
+    // Deferred light shading pays where the light shader is long (the environment lookup: atan2, texture fetch) and loses a little on scenes with punctual
+    // lights only, whose light shaders are a few multiplies (config #1: -4 %, profiles/r02_notes.md): there they stay inside k_trace<any>.
+    if (!fr.lights.envEnabled) pb.litIdx = nullptr;
     const std::vector<cudaEvent_t>& evSync = L ? L->evSync : c->evSync;
     cudaStream_t s = L ? L->s : c->stream, s2 = L ? L->s2 : c->stream2;
     const uint32_t total = (uint32_t)fr.w * (uint32_t)fr.localRows;
@@ -903,7 +912,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
     uploadFrame(&c->frameRing[k], slot, s);
     CU(c, cudaEventRecord(c->frameEv[k], s));
 
-    if (launches) { launches[0] = iterations; launches[1] = iterations * ((int)lc.shadeMiss + (int)lc.shadePbr + (int)lc.shadeGlass); launches[2] = iterations; }
+    if (launches) { launches[0] = iterations; launches[1] = iterations * ((int)lc.shadeMiss + (int)lc.shadePbr + (int)lc.shadeGlass + (pb.litIdx ? 1 : 0)); launches[2] = iterations; }
     if (timeKernels) {
         // instrumented pass: CUDA events between the kernels, nothing overlapped
         const size_t evNeeded = (size_t)(3 * iterations + 2);
@@ -916,7 +925,7 @@ static int enqueuePass(HrcContext c, const HrcFrameParams* fp, bool timeKernels,
         for (int it = 0; it < iterations; ++it) {
             launchTraceClosest(sc, slot, pb, it, lc, s); mark();
             launchShade(sc, slot, pb, it, lc, s);    if (it + 1 < iterations) launchSortRays(pb, it + 1, lc, s); mark();
-            launchTraceAny(sc, slot, pb, it, lc, s); mark();
+            launchTraceAny(sc, slot, pb, it, lc, s); launchShadeLights(sc, slot, pb, it, lc, s); mark();
         }
         launchFinishPass(pb, iterations, false, s);
         cudaError_t e = cudaGetLastError();

@@ -539,7 +539,7 @@ __device__ __forceinline__ bool traverseSimple(const float4* __restrict__ nodes,
 // ---------------------------------------------------------------------------------------
 __global__ void k_clear_ctrl(IterCtrl* ctrl) {
     int i = threadIdx.x;
-    if (i < kCtrlEntries) ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};
+    if (i < kCtrlEntries) ctrl[i] = IterCtrl{};
 }
 
 // perspective.rlsl:39-93 — one thread per pixel of this context's screen bands.
@@ -719,6 +719,17 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                 }
                 doneClass = -1;
             }
+            if (ANY && pb.litIdx) {                                       // retire: rays that reached their light go to k_shade_lights (the light shaders at 32 lanes instead of ~5)
+                const uint32_t m = __ballot_sync(kFull, doneClass == 0);
+                if (m) {
+                    const int leader = __ffs(m) - 1;
+                    uint32_t base = 0;
+                    if ((int)lane == leader) base = atomicAdd(&ctrl->litCount, (uint32_t)__popc(m));
+                    base = __shfl_sync(kFull, base, leader);
+                    if (doneClass == 0) pb.litIdx[base + __popc(m & below)] = doneIdx;
+                }
+                doneClass = -1;
+            }
             if (!exhausted) {                                             // refill
                 const uint32_t n = __popc(idle);
                 const int leader = __ffs(idle) - 1;
@@ -789,7 +800,12 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
                     break;
                 }
                 active = false;
-                if (ANY) {             // the ray reached its light: run the light shader (policy A-5/A-6)
+                if (ANY && pb.litIdx) {          // the ray reached its light: file it for k_shade_lights
+                    if (MASKED && maskedPasses > 0) {                       // what the light shader needs of the continuation ray goes back into the (now dead) queue record
+                        pb.shadow.o[rayIdx].w = tr.tmaxRay; pb.shadow.d[rayIdx].w = extraT;
+                    }
+                    doneIdx = rayIdx; doneClass = 0;
+                } else if (ANY) {      // the ray reached its light: run the light shader here (policy A-5/A-6)
                     const float4 w = __ldcs(pb.shadow.w + rayIdx);
                     const uint32_t bits = __float_as_uint(w.w);
                     shadeMiss<HR_ACCUM_RED != 0>(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, tr.d, xyz(w), tr.tmaxRay, MASKED ? extraT : pb.shadow.d[rayIdx].w);
@@ -1479,6 +1495,20 @@ __global__ void __launch_bounds__(256) k_sort_scatter(PassBuffers pb, int iter) 
     }
 }
 
+// The light ("miss") shaders of the occlusion rays of iteration `iter` that reached their light (policy A-5 / A-6), one ray per thread over the list
+// k_trace<any> filed them in. Same shadeMiss, same inputs as the inline call it replaces, one occlusion ray per pixel and iteration: pixel sums are bit-identical.
+__global__ void __launch_bounds__(128) k_shade_lights(const DScene sc, const int slot, const PassBuffers pb, int iter) {
+    const DFrame& fr = g_frames[slot];
+    const uint32_t count = pb.ctrl[iter].litCount;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        const uint32_t i = pb.litIdx[k];
+        const float4 w = __ldcs(pb.shadow.w + i), d = __ldcs(pb.shadow.d + i);
+        const float tmax = __ldcs(pb.shadow.o + i).w;
+        const uint32_t bits = __float_as_uint(w.w);
+        shadeMiss(sc, fr, pb.accum, bits & 0x00ffffffu, (bits >> 24) & 7u, bits >> 27, xyz(d), xyz(w), tmax, d.w);
+    }
+}
+
 __global__ void k_finish_pass(PassBuffers pb, int iterations, int rearm) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     unsigned long long ext = 0, occ = 0;
@@ -1487,7 +1517,7 @@ __global__ void k_finish_pass(PassBuffers pb, int iterations, int rearm) {
     pb.stats->raysPrimary += pb.ctrl[0].extCount;
     pb.stats->raysExtension += ext;
     pb.stats->raysOcclusion += occ;
-    if (rearm) for (int i = 0; i < kCtrlEntries; ++i) pb.ctrl[i] = IterCtrl{0u, 0u, 0u, 0u, {0u, 0u, 0u}, 0u};   // the next pass on these buffers starts without a clear kernel
+    if (rearm) for (int i = 0; i < kCtrlEntries; ++i) pb.ctrl[i] = IterCtrl{};   // the next pass on these buffers starts without a clear kernel
 }
 
 // hrcTraceRays: the fixed-ray-set parity hook. Same node / triangle steps as the pass kernels.
@@ -1542,6 +1572,10 @@ void launchTraceAny(const DScene& sc, int slot, const PassBuffers& pb, int iter,
         if (lc.collectStats) k_trace<true, true, false><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdleAny);
         else                 k_trace<true, false, false><<<grid, 128, 0, s>>>(sc, slot, pb, iter, lc.refillIdleAny);
     }
+}
+
+void launchShadeLights(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
+    if (pb.litIdx) k_shade_lights<<<lc.smCount * 8, 128, 0, s>>>(sc, slot, pb, iter);
 }
 
 void launchShade(const DScene& sc, int slot, const PassBuffers& pb, int iter, const LaunchConfig& lc, cudaStream_t s) {
