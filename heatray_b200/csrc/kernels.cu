@@ -363,6 +363,9 @@ struct TraceStack {
 #ifndef HR_TOP_SMEM
 #define HR_TOP_SMEM 0            // nodes of the top BVH levels kept in shared memory by k_trace (1 + 8 = 9, 1 + 8 + 64 = 73); measured neutral, off (profiles/r02_notes.md)
 #endif
+#ifndef HR_TRI_PREFETCH
+#define HR_TRI_PREFETCH 0        // 128-byte lines of a node's leaf triangles prefetched at the start of its node step (experiment, see profiles/r02_notes.md)
+#endif
 #ifndef HR_TMA_REFILL
 #define HR_TMA_REFILL 0          // k_trace refills a warp's idle lanes with ONE bulk copy (cp.async.bulk, TMA 1-D) of the contiguous ray records instead of per-lane loads; measured, off
 #endif
@@ -399,7 +402,7 @@ struct Traversal {
     // Pops the nearest pending child of `group`, tests its 8 children, leaves the hit internal children in `group` and
     // files the hit leaf triangles as a pending triangle group.
     template <bool STATS, bool ANY>
-    __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, TraceStack& stack, TraceCounters& tc, const float4* topNodes = nullptr) {
+    __device__ __forceinline__ void nodeStep(const float4* __restrict__ nodes, TraceStack& stack, TraceCounters& tc, const float4* topNodes = nullptr, const float4* trisForPrefetch = nullptr) {
         const uint32_t hits = group.y;
         const uint32_t bit = 31u - __clz(hits);                  // highest set bit = nearest remaining child
         group.y &= ~(1u << bit);
@@ -422,6 +425,15 @@ struct Traversal {
             n0 = __ldg(np + 0); n1 = __ldg(np + 1); n2 = __ldg(np + 2); n3 = __ldg(np + 3); n4 = __ldg(np + 4);
         }
         if (STATS) tc.nodes++;
+#if HR_TRI_PREFETCH > 0
+        // experiment: the node's leaf triangles sit contiguously at its triBase; pull their first lines towards L1 while the slab tests run
+        // (the dependent triangle fetch is 41 % of the closest-hit kernel's stall samples)
+        if (trisForPrefetch) {
+            const char* tp = reinterpret_cast<const char*>(trisForPrefetch + (size_t)__float_as_uint(n1.y) * 3);
+#pragma unroll
+            for (int k = 0; k < HR_TRI_PREFETCH; ++k) asm volatile("prefetch.global.L1 [%0];" :: "l"(tp + k * 128));
+        }
+#endif
 
         const uint32_t eimask = __float_as_uint(n0.w);
         // Child plane distance (origin + q*cell - o) / d as ONE FMA on the widened magic number (1024 + q):
@@ -784,7 +796,7 @@ __global__ void __launch_bounds__(128, HR_TRACE_MIN_BLOCKS) k_trace(const DScene
         }
 
         while (active) {
-            if (tr.hasNodeWork()) tr.nodeStep<STATS, ANY>(nodes, stack, tc, topNodes);
+            if (tr.hasNodeWork()) tr.nodeStep<STATS, ANY>(nodes, stack, tc, topNodes, tris);
             bool occluded = false;
             while (tr.tri.y) if (tr.triStep<ANY, STATS, MASKED>(tris, tc)) { occluded = true; break; }
             tr.popIfEmpty(stack);
