@@ -1,4 +1,4 @@
-"""One rank of tests/test_gpu_peer_exchange.py: RANK / WORLD_SIZE / MASTER_* from the environment, gloo for the handle exchange,
+"""One rank of tests/test_zy_gpu_peer_exchange.py: RANK / WORLD_SIZE / MASTER_* from the environment, gloo for the handle exchange,
 ranks spread over the visible GPUs (all on cuda:0 when there is only one: CUDA IPC works between processes on one device too)."""
 import os
 import sys

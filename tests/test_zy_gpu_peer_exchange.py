@@ -1,7 +1,8 @@
 """hrcExchangeSum / hrcExchangeBands (csrc/peer_exchange.cu): the multi-GPU frame exchange as one kernel per rank over peer memory.
 Ranks are separate processes (CUDA IPC needs them to be); they use different GPUs when the box has several, else they share cuda:0.
 Bar: the sum equals the rank-ordered fp32 sum bit for bit; the band exchange reproduces the single-GPU frame bit for bit; five
-exchanges in a row on the same buffers."""
+exchanges in a row on the same buffers. The file sorts next to last on purpose: this is the only test that needs several
+processes to share the GPU."""
 import os
 import socket
 import subprocess
