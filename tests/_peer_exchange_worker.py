@@ -23,7 +23,13 @@ def main():
     torch.cuda.set_device(dev)
     device = f"cuda:{dev}"
     lib = capi.load_library()
-    ex = sharding.PeerExchange(lib, dev, rank, world, h, w)
+    try:
+        ex = sharding.PeerExchange(lib, dev, rank, world, h, w)
+    except capi.HrcError as e:
+        if "cudaIpc" in str(e):                                    # a box that does not allow CUDA IPC between these processes: nothing to test
+            print(f"rank {rank}: SKIP {e}", flush=True)
+            os._exit(77)
+        raise
     stream = torch.cuda.current_stream().cuda_stream
     ok = True
     for call in range(3):                                          # sums: three calls in a row, new data each time

@@ -37,6 +37,8 @@ def test_peer_exchange_matches_rank_ordered_sum_and_single_gpu_bands(lib, world)
         for p in procs:
             if p.poll() is None:
                 p.kill()
+    if any(p.returncode == 77 for p in procs):
+        pytest.skip("CUDA IPC between processes is not available on this box:\n" + outs[0][-500:])
     for rank, (p, out) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, f"rank {rank} failed:\n{out[-3000:]}"
         assert f"rank {rank}: OK" in out
