@@ -26,6 +26,7 @@ namespace {
 struct Backend {
     void* handle = nullptr; std::string prefix = "hrc";
     int (*CreateContext)(const HrcContextDesc*, HrcContext*) = nullptr;
+    int (*SetOption)(HrcContext, int32_t, int32_t) = nullptr;          // optional: backends without options (the CPU oracle has few) still bind
     int (*DestroyContext)(HrcContext) = nullptr;
     const char* (*GetLastError)(HrcContext) = nullptr;
     int (*Resize)(HrcContext, int32_t, int32_t) = nullptr;
@@ -78,6 +79,7 @@ bool resolveBackend(void* h, const std::string& p) {
               sym(h, p + "SetSpotLights", b.SetSpotLights) & sym(h, p + "SetSequences", b.SetSequences) & sym(h, p + "SetPixelTables", b.SetPixelTables) &
               sym(h, p + "SetInteractiveBlocks", b.SetInteractiveBlocks) & sym(h, p + "SetGlobals", b.SetGlobals) & sym(h, p + "RenderPass", b.RenderPass);
     if (!ok) return false;
+    sym(h, p + "SetOption", b.SetOption);
     b.ok = true; g_backend = b;
     return true;
 }
@@ -127,6 +129,7 @@ struct MatRec { HrcMaterial handle = -1; uint64_t version = 0; };
 
 struct Ctx {
     HrcContext hrc = nullptr; RLenum error = RL_NO_ERROR;
+    HrcGlobals lastGlobals{}; bool haveGlobals = false;      // the Globals block as last forwarded (sampleIndex zeroed)
     std::set<Buf*> bufs; std::set<Tex*> texs; std::set<Fbo*> fbos; std::set<Shader*> shaders; std::set<Program*> programs;
     std::map<int, std::unique_ptr<Prim>> prims; int nextPrim = 1;
     std::map<RLenum, Buf*> boundBuf; Tex* boundTex2D = nullptr; Fbo* boundFbo = nullptr; int boundPrim = 0; bool frontCW = false;
@@ -451,6 +454,14 @@ HRL_API OpenRLContext OpenRLCreateContext(const OpenRLContextAttribute*, OpenRLN
         std::fprintf(stderr, "[heatray_openrl] %s\n", g_errorText.c_str());
         return nullptr;
     }
+    // The reference viewer renders one pass per rlRenderFrame and maps the pixel pack buffer after each (HeatrayRenderer.cpp:366-408). With
+    // HEATRAY_OPENRL_SPECULATIVE_PASSES = 1..3 the backend keeps that many passes of the same progressive render running ahead (HRC_OPT_SPECULATIVE_PASSES,
+    // include/heatray_cuda.h): the unmodified caller's readback then overlaps the next passes. Off by default: the picture then differs from the
+    // one-pass-at-a-time sum by fp32 addition order.
+    if (const char* e = std::getenv("HEATRAY_OPENRL_SPECULATIVE_PASSES")) {
+        const int n = std::atoi(e);
+        if (n > 0 && g_backend.SetOption) { g_calls["hrcSetOption"]++; g_backend.SetOption(c->hrc, HRC_OPT_SPECULATIVE_PASSES, n > HRC_MAX_DEFERRED_PASSES ? HRC_MAX_DEFERRED_PASSES : n); }
+    }
     return c.release();
 }
 HRL_API int OpenRLSetCurrentContext(OpenRLContext ctx) { g_ctx = static_cast<Ctx*>(ctx); return 1; }
@@ -661,7 +672,13 @@ HRL_API void rlRenderFrame(void) {
     Buf* gb = blockOf(c, c->framePrim.get(), "Globals");
     if (!gb || gb->data.size() < sizeof(HrcGlobals)) { setError(RL_INVALID_OPERATION, "frame program without its Globals block"); return; }
     HrcGlobals g; std::memcpy(&g, gb->data.data(), sizeof(g));
-    if (!BK(SetGlobals, &g)) return;
     fp.sampleIndex = g.sampleIndex;
+    // PassGenerator rewrites the whole block every pass to bump Globals.sampleIndex (PassGenerator.cpp:349-360); the backend takes the sample index from
+    // the frame parameters, so the block is forwarded only when something else in it changed (a forwarded block is a state change: it ends look-ahead)
+    g.sampleIndex = 0;
+    if (!c->haveGlobals || std::memcmp(&g, &c->lastGlobals, sizeof(g)) != 0) {
+        if (!BK(SetGlobals, &g)) return;
+        c->lastGlobals = g; c->haveGlobals = true;
+    }
     BK(RenderPass, &fp, nullptr);
 }

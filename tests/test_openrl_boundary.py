@@ -206,3 +206,34 @@ def test_reference_host_code_over_the_openrl_entry_points_cpu(oracle_mod, lib, t
 def test_reference_host_code_over_the_openrl_entry_points_gpu(lib, tmp_path):
     """The same through the CUDA backend: what the reference's viewer would show on a B200."""
     _run_boundary(lib, "hrc", lambda: capi.Backend(lib, "hrc", device=0), tmp_path)
+
+
+@pytest.mark.gpu
+def test_reference_viewer_loop_with_backend_lookahead_gpu(lib, tmp_path, monkeypatch):
+    """HEATRAY_OPENRL_SPECULATIVE_PASSES: the unmodified reference loop (one rlRenderFrame per pass, PassGenerator.cpp:325-401) with the backend running
+    ahead. The Globals block PassGenerator rewrites every pass only to bump sampleIndex must not count as a state change (it would end the look-ahead
+    every pass), and the frames must equal the plain loop's: same sample counts, sums up to fp32 addition order."""
+    w, h, passes = 96, 64, 8
+    env = dict(enabled=True, solid=(0.6, 0.7, 0.9), map=None, ev=0.5, theta=0.3)
+    cam = dict(distance=7.0, phi=0.4, theta=0.35, target=(0.0, 0.0, 0.0), focal_length=35.0, fstop=2.8, focus_distance=7.0)
+    spec = scenes.preset_scene("Multi-Material", width=w, height=h, passes=passes, max_depth=5, env=env, camera=cam)
+    frames = {}
+    for depth in (0, 3):
+        if depth:
+            monkeypatch.setenv("HEATRAY_OPENRL_SPECULATIVE_PASSES", str(depth))
+        else:
+            monkeypatch.delenv("HEATRAY_OPENRL_SPECULATIVE_PASSES", raising=False)
+        host = RefHost(lib, "hrc", tmp_path, w, h)
+        try:
+            assert host.lib.refscene_load_preset(host.p, b"Multi-Material") == 1
+            first = host.render(_options(spec, passes), 3)
+            globals_before, options = host.calls("hrcSetGlobals"), host.calls("hrcSetOption")
+            frames[depth] = (first, host.render(_options(spec, passes), 5, reset=False))
+            assert host.calls("hrcSetGlobals") == globals_before, "the per-pass rewrite of Globals.sampleIndex was forwarded as a state change"
+            assert options == (1 if depth else 0)                  # hrcSetOption(HRC_OPT_SPECULATIVE_PASSES) once, at context creation
+        finally:
+            host.close()
+    for k in (0, 1):
+        plain, ahead = frames[0][k], frames[3][k]
+        assert np.array_equal(plain[..., 3], ahead[..., 3]) and (ahead[..., 3] == (3, 8)[k]).all()
+        assert np.allclose(plain[..., :3], ahead[..., :3], rtol=2e-5, atol=1e-6)
