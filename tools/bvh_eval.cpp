@@ -35,7 +35,8 @@ static bool triTest(const BuildTriangle& t, const Ray& r, float& tt) {
 
 struct Counts { double nodes = 0, tris = 0, rays = 0; };
 
-static void trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, const Ray& r, bool any, Counts& c) {
+// Returns the nearest hit distance (closest) or 0 / -1 for occluded / not occluded (any); r.tmax when nothing is hit.
+static float trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, const Ray& r, bool any, Counts& c) {
     float idir[3]; uint32_t octInv = 0;
     for (int a = 0; a < 3; ++a) {
         float d = r.d[a]; if (std::fabs(d) < 1e-20f) d = std::copysign(1e-20f, d);
@@ -90,12 +91,12 @@ static void trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, co
             float t;
             Ray rr = r; rr.tmax = r.tmax;
             if (triTest(tris[bvh.triOrder[triBase + ti]], rr, t)) {
-                if (any) return;
+                if (any) return 0.0f;
                 if (t < bestT) bestT = t;
             }
         }
         if (!(g.hits & 0xff000000u)) {
-            if (stack.empty()) return;
+            if (stack.empty()) return any ? -1.0f : bestT;
             g = stack.back(); stack.pop_back();
         }
     }
@@ -116,6 +117,20 @@ int main(int argc, char** argv) {
     WideBVH bvh;
     buildWideBVH(tris.data(), tris.size(), 0, bvh);
     Counts c[3];
+    if (argc > 2 && std::strcmp(argv[2], "--check") == 0) {
+        // every ray against every triangle: the walk over the compressed wide BVH must find exactly the brute-force answer (same triangle test)
+        size_t bad = 0;
+        for (const Ray& r : rays) {
+            const bool any = r.kind == 2;
+            const float got = trace(bvh, tris, r, any, c[r.kind]);
+            float best = r.tmax; bool hit = false;
+            for (const BuildTriangle& t : tris) { float tt; if (triTest(t, r, tt)) { hit = true; if (tt < best) best = tt; } }
+            const float want = any ? (hit ? 0.0f : -1.0f) : best;
+            if (got != want) { if (bad < 5) std::printf("MISMATCH kind %d: bvh %.9g brute force %.9g\n", r.kind, got, want); ++bad; }
+        }
+        std::printf("check: %zu rays, %zu mismatches, %zu nodes, depth %u\n", rays.size(), bad, bvh.nodes.size(), bvh.maxDepth);
+        return bad ? 1 : 0;
+    }
     for (const Ray& r : rays) trace(bvh, tris, r, r.kind == 2, c[r.kind]);
     const char* names[3] = {"primary", "extension", "occlusion"};
     double cost = 0, total = 0;
