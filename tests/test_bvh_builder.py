@@ -62,3 +62,56 @@ def test_wide_bvh_walk_equals_brute_force(bvh_eval, tmp_path, kind):
     res = subprocess.run([str(bvh_eval), str(path), "--check"], capture_output=True, text=True)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "0 mismatches" in res.stdout
+
+
+@pytest.mark.gpu
+def test_gpu_traversal_counters_match_the_cpu_walk(bvh_eval, tmp_path, lib, oracle_mod):
+    """the roofline's algorithmic bytes are 80 B x node steps + 48 B x triangle tests, counted by the kernels themselves
+    (HRC_OPT_TRAVERSAL_COUNTERS). The same counts from an independent place: the rays of the same pass captured from the oracle, walked over the
+    same BVH8 on the CPU. They agree to a fraction of a percent (not exactly: the two slab tests round differently in the last place, and a path
+    whose last-place difference flips a decision contributes different rays)."""
+    from heatray_b200 import capi, renderer, scenes
+    from oracle import loader
+    spec = scenes.sphere_grid(width=240, height=135, passes=4, grid=4, u_slices=32, v_slices=16, env_size=(128, 64), max_depth=6)
+    tris = []
+    for m in spec.meshes:
+        M = np.asarray(m.transform, np.float32).reshape(4, 4)
+        w = np.asarray(m.positions, np.float32).reshape(-1, 3) @ M[:3, :3].T + M[:3, 3]
+        idx = np.asarray(m.indices).reshape(-1)
+        if m.draw_mode == capi.DRAW_TRIANGLES:
+            tri = idx.reshape(-1, 3)
+        else:
+            tri = np.stack([idx[:-2], idx[1:-1], idx[2:]], 1)
+            tri = tri[(tri[:, 0] != tri[:, 1]) & (tri[:, 1] != tri[:, 2]) & (tri[:, 0] != tri[:, 2])]
+        tris.append(w[tri].reshape(-1, 9))
+    tris = np.concatenate(tris).astype(np.float32)
+    ob = loader.backend()
+    try:
+        ro = renderer.Renderer(ob)
+        ro.load_scene(spec)
+        loader.capture_rays(ob, 4_000_000)
+        ro.render_pass(sample_index=0)
+        rays, kinds = loader.captured_rays(ob)
+    finally:
+        ob.close()
+    rec = np.zeros(len(rays), RAY)
+    rec["o"], rec["tmin"], rec["d"], rec["tmax"], rec["kind"] = rays["origin"], rays["tmin"], rays["direction"], rays["tmax"], kinds
+    path = tmp_path / "pass.bin"
+    with open(path, "wb") as f:
+        f.write(np.uint64(len(tris)).tobytes()); f.write(tris.tobytes()); f.write(np.uint64(len(rec)).tobytes()); f.write(rec.tobytes())
+    out = subprocess.run([str(bvh_eval), str(path)], capture_output=True, text=True, check=True).stdout
+    tot = out.strip().splitlines()[-1].split()
+    cpu = {tot[i]: float(tot[i + 1]) for i in range(1, len(tot), 2)}
+    gb = capi.Backend(lib, "hrc", device=0, collect_stats=True)
+    try:
+        rg = renderer.Renderer(gb)
+        rg.load_scene(spec)
+        gb.reset_stats()
+        st = rg.render_pass(sample_index=0)
+    finally:
+        gb.close()
+    gpu = {"closest_nodes": st.nodesVisited, "closest_tris": st.trianglesTested, "any_nodes": st.nodesVisitedAny, "any_tris": st.trianglesTestedAny}
+    assert int(st.raysPrimary + st.raysExtension + st.raysOcclusion) == pytest.approx(len(rays), rel=2e-3)
+    print({k: (int(gpu[k]), int(cpu[k])) for k in gpu})
+    for k in gpu:
+        assert gpu[k] == pytest.approx(cpu[k], rel=1e-3), (k, gpu[k], cpu[k])          # measured on a B200: 730070 vs 730072 node steps, triangle tests and the occlusion counts equal

@@ -144,5 +144,6 @@ int main(int argc, char** argv) {
         total += c[k].rays;
     }
     std::printf("  lane-adjusted cost per ray %.2f\n", cost / total);
+    std::printf("totals closest_nodes %.0f closest_tris %.0f any_nodes %.0f any_tris %.0f\n", c[0].nodes + c[1].nodes, c[0].tris + c[1].tris, c[2].nodes, c[2].tris);
     return 0;
 }
