@@ -409,7 +409,11 @@ struct Traversal {
         if (group.y & 0xff000000u) {
             if (sp < kTraceStack) stack.put(sp++, group); else if (STATS) tc.overflow++;
         }
-        const uint32_t slot = (bit - 24u) ^ (octInv & 7u);
+        // Visiting order of a node's children: front to back for closest-hit rays. Occlusion rays only need ANY occluder and find one sooner BACK to front
+        // (they start on a surface and head for a light: what lies near the origin rarely blocks; measured on the CPU walk of the same tree,
+        // tools/bvh_eval.cpp: -5 % node steps, -4 % triangle tests per occlusion ray), so they use the mirrored octant. Plane selection below keeps octInv.
+        const uint32_t ordInv = ANY ? (octInv ^ 7u) : octInv;
+        const uint32_t slot = (bit - 24u) ^ (ordInv & 7u);
         const uint32_t rel = __popc(hits & ~(0xffffffffu << slot));   // internal children stored before this slot
         const uint32_t nodeIdx = group.x + rel;
 
@@ -454,7 +458,7 @@ struct Traversal {
 #else
         const float tfar = ANY ? tmaxRay : bestT;   // occlusion rays cull against maxT only: bestT then tracks the nearest alpha-masked hit, which must not hide occluders
 #endif
-        const uint32_t octInv4 = octInv * 0x01010101u;
+        const uint32_t octInv4 = ordInv * 0x01010101u;
 
         uint32_t hitMask = 0;
 #pragma unroll

@@ -43,6 +43,7 @@ static float trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, c
         idir[a] = 1.0f / d;
         if (!(d < 0.0f)) octInv |= (4u >> a);                 // x -> bit 2, y -> bit 1, z -> bit 0: slot bit set = positive side
     }
+    if (any) octInv ^= 7u;                                  // occlusion rays visit children back to front (kernels.cu: Traversal::nodeStep); the slab test below does not use octInv
     float bestT = r.tmax;
     struct Group { uint32_t base, hits, imask; };
     std::vector<Group> stack;
