@@ -45,9 +45,9 @@ static float trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, c
     }
     if (any) octInv ^= 7u;                                  // occlusion rays visit children back to front (kernels.cu: Traversal::nodeStep); the slab test below does not use octInv
     float bestT = r.tmax;
-    struct Group { uint32_t base, hits, imask; };
+    struct Group { uint32_t base, hits, imask; float tn[8]; };      // tn: entry distance of each pending internal child, by bit position (BVH_EVAL_GROUP_CULL only)
     std::vector<Group> stack;
-    Group g{0u, 0x80000000u, 0u};                            // root = "child 7 of a virtual parent whose childBase is 0"
+    Group g{0u, 0x80000000u, 0u, {0, 0, 0, 0, 0, 0, 0, 0}};                            // root = "child 7 of a virtual parent whose childBase is 0"
     bool rootPending = true;
     c.rays += 1;
     for (;;) {
@@ -64,7 +64,7 @@ static float trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, c
             if (g.hits & 0xff000000u) stack.push_back(g);
             const WideNode& n = bvh.nodes[nodeIdx];
             c.nodes += 1;
-            uint32_t hitMask = 0;
+            uint32_t hitMask = 0; float newTn[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             const float tfar = any ? r.tmax : bestT;
             float cell[3]; for (int a = 0; a < 3; ++a) cell[a] = n.exp[a] ? std::ldexp(1.0f, (int)n.exp[a] - 127) : 0.0f;
             for (int s = 0; s < 8; ++s) {
@@ -79,10 +79,10 @@ static float trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, c
                 }
                 if (!(tn <= tf * 1.000001f)) continue;
                 const bool inner = (m & 0x20) && ((m & 0x1f) >= 24);
-                if (inner) hitMask |= 1u << (24u + ((uint32_t)s ^ (octInv & 7u)));
+                if (inner) { hitMask |= 1u << (24u + ((uint32_t)s ^ (octInv & 7u))); newTn[(uint32_t)s ^ (octInv & 7u)] = tn; }
                 else hitMask |= (uint32_t)(m >> 5) << (m & 0x1f);
             }
-            g.base = n.childBase; g.imask = n.imask; g.hits = hitMask & 0xff000000u;
+            g.base = n.childBase; g.imask = n.imask; g.hits = hitMask & 0xff000000u; for (int q = 0; q < 8; ++q) g.tn[q] = newTn[q];
             triBase = n.triBase; triBits = hitMask & 0x00ffffffu;
         }
         while (triBits) {
@@ -99,6 +99,14 @@ static float trace(const WideBVH& bvh, const std::vector<BuildTriangle>& tris, c
         if (!(g.hits & 0xff000000u)) {
             if (stack.empty()) return any ? -1.0f : bestT;
             g = stack.back(); stack.pop_back();
+            // What-if (not in the kernel): a group coming off the stack is dropped when the nearest of its remaining children already lies beyond the
+            // best hit. The key models 16 spare bits of the stack word: the entry distance truncated to its upper 16 bits (rounds down: conservative).
+            static const bool groupCull = std::getenv("BVH_EVAL_GROUP_CULL") != nullptr;
+            if (groupCull && !any) {
+                float mn = 3.4e38f; for (int q = 0; q < 8; ++q) if (g.hits & (1u << (24 + q))) mn = std::fmin(mn, g.tn[q]);
+                uint32_t bits; std::memcpy(&bits, &mn, 4); bits &= 0xffff0000u; std::memcpy(&mn, &bits, 4);
+                if (mn > bestT) { g.hits = 0; continue; }
+            }
         }
     }
 }
